@@ -1,0 +1,268 @@
+/*
+ * sysml_b200.h -- flat C ABI of libsystemml_b200.so, the sm_100a native library behind SystemML's
+ * GPU instruction classes.
+ *
+ * What this boundary replaces.  In the reference, the GPU instruction classes
+ * (the *GPUInstruction.java classes under runtime/instructions/gpu) call static methods of LibMatrixCUDA /
+ * LibMatrixCuMatMult, which hand raw device pointers (jcuda.Pointer, owned by GPUObject /
+ * GPUMemoryManager) to JCuda: cuBLAS, cuSPARSE and the PTX kernels of src/main/cpp/kernels/SystemML.cu.
+ * Every function below takes the place of one such JCuda call site; the citation on each
+ * declaration is the reference interface it stands in for.  Paths are relative to
+ *   J/  = src/main/java/org/apache/sysml/
+ * The JNI stub a maintainer adds on the Java side is shown in INTEGRATION.md; it follows the
+ * reference's own native-plugin convention (J/utils/NativeHelper.java:323-327, src/main/cpp/systemml.h).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; all extents are int64_t (the reference GPU path is int32,
+ *    LibMatrixCUDA.java:685,1735-1740, and cannot hold 10M x 1000);
+ *  - dense matrices are row-major double (DenseBlockDRB layout; GPUObject.java:52-99);
+ *  - CSR is 0-based {double val[nnz], int32 rowptr[rows+1], int32 colind[nnz]} exactly as
+ *    CSRPointer.java:76-100 holds it (so nnz < 2^31);
+ *  - pointers named d_* / without prefix are DEVICE pointers on the context's device; h_* are host;
+ *  - every function returns 0 (SYSML_OK) or a negative SYSML_E_* code, never aborts and never throws;
+ *    sysml_b200_last_error() returns the message (the Java side turns it into DMLRuntimeException,
+ *    as JCudaKernels.checkResult does, JCudaKernels.java:115-119);
+ *  - calls are asynchronous on the context's stream unless stated; sysml_b200_sync() is the
+ *    "sysml.gpu.sync.postProcess" synchronisation (GPUInstruction.java:202-208);
+ *  - a context is NOT thread-safe: one per (host thread, device), like GPUContext
+ *    (GPUContext.java:181-184).
+ *  - there is no CPU fallback anywhere in this library.
+ */
+#ifndef SYSML_B200_H
+#define SYSML_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define SYSML_OK 0
+#define SYSML_E_INVALID (-1)     /* null pointer, bad enum, negative size            */
+#define SYSML_E_DIM (-2)         /* dimension mismatch                               */
+#define SYSML_E_OOM (-3)         /* cudaMalloc failed (GPUMemoryManager.java:138-148) */
+#define SYSML_E_CUDA (-4)        /* any other CUDA runtime error                     */
+#define SYSML_E_UNSUPPORTED (-5) /* valid request this build does not implement      */
+#define SYSML_E_LIMIT (-6)       /* size beyond a documented fixed limit             */
+
+typedef struct sysml_b200_ctx sysml_b200_ctx;
+
+/* ChainType of lops/MapMultChain.java:31-32 / MMChainCPInstruction.java:69-83 */
+#define SYSML_CHAIN_XtXv 0  /* t(X) %*% (X %*% v)        */
+#define SYSML_CHAIN_XtwXv 1 /* t(X) %*% (w * (X %*% v))  */
+#define SYSML_CHAIN_XtXvy 2 /* t(X) %*% ((X %*% v) - y)  */
+
+/* aggregate opcodes (AggregateUnaryGPUInstruction opcodes uak+ uark+ uack+ uasqk+ uamax uarimax ...) */
+#define SYSML_AGG_SUM 0
+#define SYSML_AGG_SUMSQ 1
+#define SYSML_AGG_MAX 2
+#define SYSML_AGG_MIN 3
+#define SYSML_AGG_MAXINDEX 4 /* rowIndexMax: 1-based, LAST maximal column wins (LibMatrixAgg.java:3081-3089) */
+#define SYSML_AGG_MININDEX 5
+#define SYSML_AGG_MEAN 6
+#define SYSML_AGG_PROD 7
+#define SYSML_AGG_VAR 8
+/* direction.  Beware the reference's inverted naming (LibMatrixCUDA.java:696):
+ * ROW = one result per row (rowSums, index fn ReduceCol), COL = one result per column (colSums, ReduceRow) */
+#define SYSML_DIR_ALL 0
+#define SYSML_DIR_ROW 1
+#define SYSML_DIR_COL 2
+
+/* cellwise binary opcodes: numbering of LibMatrixCUDA.getBinaryOp (LibMatrixCUDA.java:1551-1575) and
+ * binaryOp in src/main/cpp/kernels/SystemML.cu:452-512 */
+#define SYSML_OP_PLUS 0
+#define SYSML_OP_MINUS 1
+#define SYSML_OP_MULTIPLY 2
+#define SYSML_OP_DIVIDE 3
+#define SYSML_OP_POWER 4
+#define SYSML_OP_LESS 5
+#define SYSML_OP_LESSEQUAL 6
+#define SYSML_OP_GREATER 7
+#define SYSML_OP_GREATEREQUAL 8
+#define SYSML_OP_EQUAL 9
+#define SYSML_OP_NOTEQUAL 10
+#define SYSML_OP_MIN 11
+#define SYSML_OP_MAX 12
+#define SYSML_OP_AND 13
+#define SYSML_OP_OR 14
+#define SYSML_OP_MINUS1MULTIPLY 15
+#define SYSML_OP_MINUSNZ 16
+#define SYSML_OP_MODULUS 17
+#define SYSML_OP_INTDIV 18
+/* broadcast code of the second operand: matrix_matrix_cellwise_op's vecStatus (SystemML.cu:698-735) */
+#define SYSML_BCAST_NONE 0 /* B is rows x cols          */
+#define SYSML_BCAST_COL 1  /* B is rows x 1 (col vector) */
+#define SYSML_BCAST_ROW 2  /* B is 1 x cols (row vector) */
+
+/* unary opcodes (kernels matrix_exp ... matrix_sigmoid, SystemML.cu:1541-1960;
+ * LibMatrixCUDA.java:1969-2290) */
+#define SYSML_UN_EXP 0
+#define SYSML_UN_SQRT 1
+#define SYSML_UN_ROUND 2
+#define SYSML_UN_ABS 3
+#define SYSML_UN_LOG 4
+#define SYSML_UN_FLOOR 5
+#define SYSML_UN_CEIL 6
+#define SYSML_UN_SIGN 7
+#define SYSML_UN_SIGMOID 8
+#define SYSML_UN_SIN 9
+#define SYSML_UN_COS 10
+#define SYSML_UN_TAN 11
+#define SYSML_UN_TANH 12
+
+/* ------------------------------------------------------------------------------------------------
+ * Context and device memory.
+ * Replaces: GPUContextPool.initializeGPU / getDeviceCount (GPUContextPool.java:84-160),
+ *           GPUContext.<init>/initializeThread/destroy (GPUContext.java:93-109,133-184),
+ *           GPUMemoryManager.malloc/free/cudaMemGetInfo (GPUMemoryManager.java:157-322,521-526),
+ *           GPUObject.copyFromHostToDevice / copyFromDeviceToHost (GPUObject.java:755-946).
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_device_count(int* count);
+const char* sysml_b200_version(void);
+/* Creates a context on `device` with its own non-blocking stream. */
+int sysml_b200_ctx_create(int device, sysml_b200_ctx** out);
+/* Same, but all work is queued on a stream the caller owns (cudaStream_t passed as void*). */
+int sysml_b200_ctx_create_on_stream(int device, void* cuda_stream, sysml_b200_ctx** out);
+int sysml_b200_ctx_destroy(sysml_b200_ctx* ctx);
+int sysml_b200_sync(sysml_b200_ctx* ctx);
+const char* sysml_b200_last_error(sysml_b200_ctx* ctx); /* ctx may be NULL: last error of this thread */
+void* sysml_b200_ctx_stream(sysml_b200_ctx* ctx);       /* the cudaStream_t in use */
+int sysml_b200_ctx_device(sysml_b200_ctx* ctx);
+int sysml_b200_ctx_sm_count(sysml_b200_ctx* ctx);
+int sysml_b200_mem_info(sysml_b200_ctx* ctx, int64_t* free_bytes, int64_t* total_bytes);
+/* Number of kernels this context has launched since creation (GPUStatistics.cudaKernelCount analogue). */
+int64_t sysml_b200_launch_count(sysml_b200_ctx* ctx);
+
+/* Unlike GPUMemoryManager.malloc (java:265) memory is NOT zero-filled; ops write every output cell. */
+int sysml_b200_malloc(sysml_b200_ctx* ctx, int64_t bytes, void** d_ptr);
+int sysml_b200_free(sysml_b200_ctx* ctx, void* d_ptr);
+int sysml_b200_memset0(sysml_b200_ctx* ctx, void* d_ptr, int64_t bytes);
+int sysml_b200_h2d(sysml_b200_ctx* ctx, void* d_dst, const void* h_src, int64_t bytes); /* synchronous */
+int sysml_b200_d2h(sysml_b200_ctx* ctx, void* h_dst, const void* d_src, int64_t bytes); /* synchronous */
+int sysml_b200_d2d(sysml_b200_ctx* ctx, void* d_dst, const void* d_src, int64_t bytes);
+/* Pinned host staging (cudaMallocHost / cudaFreeHost). */
+int sysml_b200_host_alloc(sysml_b200_ctx* ctx, int64_t bytes, void** h_ptr);
+int sysml_b200_host_free(sysml_b200_ctx* ctx, void* h_ptr);
+
+/* CUDA-event timers on the context's stream, so the Java-side fine-grained timers
+ * (GPUInstruction.java:54-146) can be fed device times instead of System.nanoTime(). */
+int sysml_b200_timer_start(sysml_b200_ctx* ctx);
+int sysml_b200_timer_stop_ms(sysml_b200_ctx* ctx, double* ms); /* records, synchronises, returns elapsed */
+
+/* ------------------------------------------------------------------------------------------------
+ * mmchain (the hot op of LinearRegCG / GLM).
+ * Replaces: LibMatrixMult.matrixMultChain (LibMatrixMult.java:243-329) as reached from
+ * MMChainCPInstruction.processInstruction (cp/MMChainCPInstruction.java:69-83).  The reference has
+ * NO GPU twin (AggBinaryOp.isGPUEnabled is false for MAPMM_CHAIN, J/hops/AggBinaryOp.java:159-162);
+ * this is the entry a new MMChainGPUInstruction binds.
+ *   X: n x m row-major, v: m, w: n (NULL for XtXv), out: m.  X is read from HBM exactly once.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_mmchain_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w,
+                             double* out, int64_t n, int64_t m, int chain_type);
+/* CSR twin: LibMatrixMult.matrixMultChainSparse (LibMatrixMult.java:1655-1684). */
+int sysml_b200_mmchain_csr(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                           const double* val, const double* v, const double* w, double* out, int64_t n,
+                           int64_t m, int chain_type);
+/* Host-vector form: X resident on the device (as GPUObject caches it), v / w / out are HOST buffers;
+ * copies v (and w when h_w != NULL and d_w == NULL) in, runs the kernel, copies out back and
+ * synchronises.  This is the call shape of the reference's native plugin entry points, which take
+ * Java heap arrays (NativeHelper.java:323-327; systemml.cpp:78-124). */
+int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const double* X, const double* h_v,
+                                     const double* h_w, const double* d_w, double* h_out, int64_t n,
+                                     int64_t m, int chain_type);
+
+/* ------------------------------------------------------------------------------------------------
+ * tsmm.  Replaces LibMatrixCUDA.matmultTSMM (LibMatrixCUDA.java:477-524: cublasDsyrk + copy_u2l_dense)
+ * called by MMTSJGPUInstruction.processInstruction (gpu/MMTSJGPUInstruction.java:78-89); CPU twin
+ * LibMatrixMult.matrixMultTransposeSelf (LibMatrixMult.java:331-399).
+ *   left != 0: out = t(X) %*% X (cols x cols); left == 0: out = X %*% t(X) (rows x rows).
+ *   h_nnz_out (HOST pointer, may be NULL): exact non-zero count of out, as copyUpperToLowerTriangle
+ *   returns it (LibMatrixMult.java:3633-3672); when non-NULL the call synchronises before returning.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_tsmm_dense(sysml_b200_ctx* ctx, const double* X, double* out, int64_t rows, int64_t cols,
+                          int left, int64_t* h_nnz_out);
+int sysml_b200_tsmm_csr_left(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                             const double* val, double* out, int64_t rows, int64_t cols,
+                             int64_t* h_nnz_out);
+
+/* ------------------------------------------------------------------------------------------------
+ * General matrix multiply C = op(A) %*% op(B).
+ * Replaces LibMatrixCuMatMult.matmult (LibMatrixCuMatMult.java:139-229) called by
+ * AggregateBinaryGPUInstruction.processInstruction (gpu/AggregateBinaryGPUInstruction.java:73-89):
+ *   dense x dense : cublasDdot / cublasDgemv / cublasDgemm (LibMatrixCuMatMult.java:362-408)
+ *   CSR   x dense : cusparseDcsrmv / cusparseDcsrmm2 + dgeam (java:266-341)
+ * a_rows x a_cols and b_rows x b_cols are the STORED shapes; trans flags as in the instruction
+ * string "GPU.ba+*.A.B.out.leftT.rightT".  C is row-major (m x n) and fully written.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_matmult_dense(sysml_b200_ctx* ctx, const double* A, const double* B, double* C,
+                             int64_t a_rows, int64_t a_cols, int64_t b_rows, int64_t b_cols, int trans_a,
+                             int trans_b);
+int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                                 const double* val, const double* B, double* C, int64_t a_rows,
+                                 int64_t a_cols, int64_t b_rows, int64_t b_cols, int trans_a);
+
+/* ------------------------------------------------------------------------------------------------
+ * Aggregate-unary.  Replaces LibMatrixCUDA.unaryAggregate (LibMatrixCUDA.java:573-894) called by
+ * AggregateUnaryGPUInstruction.processInstruction (gpu/AggregateUnaryGPUInstruction.java:67-101);
+ * CPU twin LibMatrixAgg.aggregateUnaryMatrix (LibMatrixAgg.java:194-282).
+ *   out: 1 (ALL), rows (ROW) or cols (COL) doubles on the device.  MAXINDEX/MININDEX are ROW only and
+ *   write the 1-based index as a double (the n x 2 "index,value" block of d_uarimxx collapses to its
+ *   first column, which is what the CP instruction keeps: MatrixBlock.java:4080-4125).
+ *   Sums are compensated (two-sum) so they track the reference's Kahan result, not the plain tree sum
+ *   of the old GPU path (LibMatrixCUDA.java:584-585).
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols, int op,
+                               int dir, double* out);
+int sysml_b200_agg_unary_csr(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                             const double* val, int64_t rows, int64_t cols, int op, int dir, double* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * Cellwise.  Replace LibMatrixCUDA.matrixMatrixArithmetic / matrixMatrixRelational (java:1245-1270,
+ * 1209-1230; kernel matrix_matrix_cellwise_op SystemML.cu:698), matrixScalarArithmetic (java:1126-1195;
+ * kernel matrix_scalar_op SystemML.cu:750), axpy (java:2295-2350; cublasDaxpy / daxpy_matrix_vector
+ * SystemML.cu:627), the unary kernels (SystemML.cu:1541-1960) and fill (SystemML.cu:783).
+ * CPU twin: LibMatrixBincell.bincellOp (LibMatrixBincell.java:87-339) + the value functions in runtime/functionobjects.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_binary_mm(sysml_b200_ctx* ctx, const double* A, const double* B, double* C, int64_t rows,
+                         int64_t cols, int bcast, int op);
+int sysml_b200_binary_ms(sysml_b200_ctx* ctx, const double* A, double scalar, double* C, int64_t len,
+                         int op, int scalar_left);
+int sysml_b200_axpy(sysml_b200_ctx* ctx, const double* A, const double* B, double alpha, double* C,
+                    int64_t rows, int64_t cols, int bcast);
+int sysml_b200_unary(sysml_b200_ctx* ctx, const double* A, double* C, int64_t len, int op);
+int sysml_b200_fill(sysml_b200_ctx* ctx, double* A, int64_t len, double value);
+/* C = t(A); replaces LibMatrixCUDA.transpose (java:1723-1729, cublasDgeam). */
+int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols);
+
+/* ------------------------------------------------------------------------------------------------
+ * Sparsity bookkeeping.  Replace cusparseDnnz / cusparseDdense2csr / cusparseDcsr2dense
+ * (GPUObject.java:199,223,508; CSRPointer.java:463-481).  Counts use (x != 0): -0.0 is zero, NaN is not.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_count_nnz(sysml_b200_ctx* ctx, const double* X, int64_t len, int64_t* h_nnz);
+/* two-phase like the reference: first call with colind == NULL fills rowptr and *h_nnz. */
+int sysml_b200_dense_to_csr(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols,
+                            int32_t* rowptr, int32_t* colind, double* val, int64_t* h_nnz);
+int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                            const double* val, int64_t rows, int64_t cols, double* X);
+
+/* ------------------------------------------------------------------------------------------------
+ * Synthetic data (scripts/datagen/genRandData4LinearRegression.dml uses Rand(min,max,pdf=uniform,seed)).
+ * Counter-based: cell i of the GLOBAL array gets hash(seed, offset + i), so any row shard equals the
+ * same rows of the full matrix.  No reference GPU counterpart (RandGPU does not exist); the CPU twin is
+ * LibMatrixDatagen.  Used by bench.py and the tests.
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_rand_uniform(sysml_b200_ctx* ctx, double* out, int64_t len, uint64_t seed, int64_t offset,
+                            double lo, double hi);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SYSML_B200_H */

@@ -1,0 +1,221 @@
+"""ctypes loader for the CPU oracle (oracle/sysml_oracle.cpp).
+
+TEST INFRASTRUCTURE: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs import this module.  It is the checker, never the product.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libsysml_oracle.so")
+
+i64 = C.c_int64
+dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+lp = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+
+XtXv, XtwXv, XtXvy = 0, 1, 2
+# aggregate opcodes / directions (same numbering as include/sysml_b200.h)
+SUM, SUMSQ, MAX, MIN, MAXINDEX, MININDEX, MEAN, PROD = range(8)
+ALL, ROW, COL = 0, 1, 2
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "sysml_oracle.cpp")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "all"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        L.orc_num_threads.restype = C.c_int
+        L.orc_java_test_matrix.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, i64, dp]
+        L.orc_java_next_doubles.argtypes = [i64, C.c_int, dp]
+        L.orc_balanced_blocks.argtypes = [C.c_int, C.c_int, C.c_int, ip]
+        L.orc_balanced_blocks.restype = C.c_int
+        L.orc_mmchain_dense.argtypes = [dp, dp, C.c_void_p, dp, i64, i64, C.c_int, C.c_int]
+        L.orc_mmchain_csr.argtypes = [lp, ip, dp, dp, C.c_void_p, dp, i64, i64, C.c_int, C.c_int]
+        L.orc_tsmm_dense.argtypes = [dp, dp, i64, i64, C.c_int, C.c_int]
+        L.orc_tsmm_dense.restype = i64
+        L.orc_tsmm_csr_left.argtypes = [lp, ip, dp, dp, i64, i64, C.c_int]
+        L.orc_tsmm_csr_left.restype = i64
+        L.orc_matmult_dense.argtypes = [dp, dp, dp, i64, i64, i64, C.c_int]
+        L.orc_matmult_dense.restype = i64
+        L.orc_matmult_csr_dense.argtypes = [lp, ip, dp, dp, dp, i64, i64, i64, C.c_int]
+        L.orc_matmult_csr_dense.restype = i64
+        L.orc_agg_unary_dense.argtypes = [dp, i64, i64, C.c_int, C.c_int, dp, C.c_void_p, C.c_int]
+        L.orc_agg_unary_csr.argtypes = [lp, ip, dp, i64, i64, C.c_int, C.c_int, dp, C.c_void_p, C.c_int]
+        L.orc_binary_scalar.argtypes = [C.c_double, C.c_double, C.c_int]
+        L.orc_binary_scalar.restype = C.c_double
+        L.orc_binary_mm.argtypes = [dp, dp, dp, i64, i64, C.c_int, C.c_int]
+        L.orc_binary_ms.argtypes = [dp, C.c_double, dp, i64, C.c_int, C.c_int]
+        L.orc_axpy.argtypes = [dp, dp, C.c_double, dp, i64, i64, C.c_int]
+        L.orc_count_nnz.argtypes = [dp, i64]
+        L.orc_count_nnz.restype = i64
+        L.orc_dense_to_csr.argtypes = [dp, i64, i64, lp, C.c_void_p, C.c_void_p]
+        L.orc_dense_to_csr.restype = i64
+        L.orc_rand_uniform.argtypes = [dp, i64, C.c_uint64, i64, C.c_double, C.c_double]
+        _lib = L
+    return _lib
+
+
+def num_threads():
+    return lib().orc_num_threads()
+
+
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def java_test_matrix(rows, cols, lo, hi, sparsity, seed):
+    """TestUtils.generateTestMatrix (src/test/java/org/apache/sysml/test/utils/TestUtils.java:1285-1297)."""
+    out = np.zeros((rows, cols), dtype=np.float64)
+    lib().orc_java_test_matrix(rows, cols, lo, hi, sparsity, seed, out)
+    return out
+
+
+def java_next_doubles(seed, n):
+    out = np.zeros(n, dtype=np.float64)
+    lib().orc_java_next_doubles(seed, n, out)
+    return out
+
+
+def balanced_blocks(length, k, const_k):
+    out = np.zeros(max(8 * k + k, 1), dtype=np.int32)
+    n = lib().orc_balanced_blocks(length, k, int(const_k), out)
+    return out[:n].tolist()
+
+
+def rand_uniform(length, seed, offset=0, lo=-1.0, hi=1.0):
+    out = np.empty(length, dtype=np.float64)
+    lib().orc_rand_uniform(out, length, seed, offset, lo, hi)
+    return out
+
+
+def mmchain_dense(X, v, w, ct, k=1):
+    n, m = X.shape
+    out = np.zeros(m, dtype=np.float64)
+    v = np.ascontiguousarray(v.reshape(-1))
+    w = None if w is None else np.ascontiguousarray(w.reshape(-1))
+    lib().orc_mmchain_dense(X, v, _vp(w), out, n, m, ct, k)
+    return out
+
+
+def mmchain_csr(rp, ci, va, shape, v, w, ct, k=1):
+    n, m = shape
+    out = np.zeros(m, dtype=np.float64)
+    v = np.ascontiguousarray(v.reshape(-1))
+    w = None if w is None else np.ascontiguousarray(w.reshape(-1))
+    lib().orc_mmchain_csr(rp, ci, va, v, _vp(w), out, n, m, ct, k)
+    return out
+
+
+def tsmm_dense(X, left=True, k=1):
+    rows, cols = X.shape
+    dim = cols if left else rows
+    out = np.zeros((dim, dim), dtype=np.float64)
+    nnz = lib().orc_tsmm_dense(X, out, rows, cols, int(left), k)
+    return out, nnz
+
+
+def tsmm_csr_left(rp, ci, va, shape, k=1):
+    rows, cols = shape
+    out = np.zeros((cols, cols), dtype=np.float64)
+    nnz = lib().orc_tsmm_csr_left(rp, ci, va, out, rows, cols, k)
+    return out, nnz
+
+
+def matmult_dense(A, B, k=1):
+    m, cd = A.shape
+    cd2, n = B.shape
+    assert cd == cd2
+    Cm = np.zeros((m, n), dtype=np.float64)
+    nnz = lib().orc_matmult_dense(A, B, Cm, m, cd, n, k)
+    return Cm, nnz
+
+
+def matmult_csr_dense(rp, ci, va, shape, B, k=1):
+    m, cd = shape
+    cd2, n = B.shape
+    assert cd == cd2
+    Cm = np.zeros((m, n), dtype=np.float64)
+    nnz = lib().orc_matmult_csr_dense(rp, ci, va, B, Cm, m, cd, n, k)
+    return Cm, nnz
+
+
+def _outlen(rows, cols, d):
+    return 1 if d == ALL else (rows if d == ROW else cols)
+
+
+def agg_unary_dense(X, op, d, k=1, with_corr=False):
+    rows, cols = X.shape
+    out = np.zeros(_outlen(rows, cols, d), dtype=np.float64)
+    corr = np.zeros_like(out)
+    lib().orc_agg_unary_dense(X, rows, cols, op, d, out, _vp(corr), k)
+    return (out, corr) if with_corr else out
+
+
+def agg_unary_csr(rp, ci, va, shape, op, d, k=1, with_corr=False):
+    rows, cols = shape
+    out = np.zeros(_outlen(rows, cols, d), dtype=np.float64)
+    corr = np.zeros_like(out)
+    lib().orc_agg_unary_csr(rp, ci, va, rows, cols, op, d, out, _vp(corr), k)
+    return (out, corr) if with_corr else out
+
+
+def binary_scalar(x, y, op):
+    return lib().orc_binary_scalar(x, y, op)
+
+
+def binary_mm(A, B, op):
+    rows, cols = A.shape
+    if B.shape == A.shape:
+        bc = 0
+    elif B.shape == (rows, 1):
+        bc = 1
+    elif B.shape == (1, cols):
+        bc = 2
+    else:
+        raise ValueError("shape mismatch")
+    out = np.empty_like(A)
+    lib().orc_binary_mm(A, np.ascontiguousarray(B), out, rows, cols, bc, op)
+    return out
+
+
+def binary_ms(A, s, op, scalar_left=False):
+    out = np.empty_like(A)
+    lib().orc_binary_ms(A, float(s), out, A.size, op, int(scalar_left))
+    return out
+
+
+def axpy(A, B, alpha):
+    rows, cols = A.shape
+    bc = 0 if B.shape == A.shape else (1 if B.shape == (rows, 1) else 2)
+    out = np.empty_like(A)
+    lib().orc_axpy(A, np.ascontiguousarray(B), float(alpha), out, rows, cols, bc)
+    return out
+
+
+def count_nnz(A):
+    return lib().orc_count_nnz(np.ascontiguousarray(A).reshape(-1), A.size)
+
+
+def dense_to_csr(A):
+    rows, cols = A.shape
+    rp = np.zeros(rows + 1, dtype=np.int64)
+    nnz = lib().orc_dense_to_csr(A, rows, cols, rp, None, None)
+    ci = np.zeros(max(nnz, 1), dtype=np.int32)
+    va = np.zeros(max(nnz, 1), dtype=np.float64)
+    lib().orc_dense_to_csr(A, rows, cols, rp, _vp(ci), _vp(va))
+    return rp, ci[:nnz].copy() if nnz else ci[:0].copy(), va[:nnz].copy() if nnz else va[:0].copy()

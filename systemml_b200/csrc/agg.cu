@@ -1,0 +1,367 @@
+// agg.cu -- aggregate-unary reductions over a dense row-major matrix: sum, sum of squares, max, min,
+// product, mean in the three directions (ALL / per-ROW / per-COLUMN) and rowIndexMax / rowIndexMin.
+//
+// Reference semantics: LibMatrixAgg.aggregateUnaryMatrix (LibMatrixAgg.java:194-282) with the dense
+// kernels d_uakp/d_uarkp/d_uackp (:1624-1669), d_ua*sqkp (:1685-1750), d_uamxx/d_uarmxx/d_uacmxx
+// (:1843-1889), d_uarimxx/d_uarimin (:1902-1927, indexmax/indexmin :3081-3099), d_uam* (:2100-2135),
+// d_ua*mean (:1940-2010).  GPU twin being replaced: LibMatrixCUDA.unaryAggregate
+// (LibMatrixCUDA.java:573-894; kernels reduce / reduce_row / reduce_col, SystemML.cu:916-1540).
+//
+// The reference sums with Kahan compensation in strict element order.  A parallel reduction cannot
+// keep that order, so every partial here is carried as an error-free (hi, lo) pair (two-sum) and the
+// pairs are merged in a fixed order: the result is deterministic and tracks the Kahan sum to ~1 ulp.
+// +-Inf inputs give +-Inf like KahanPlus' fast path (functionobjects/KahanPlus.java:92-95); a mix of
+// +Inf and -Inf gives NaN here whereas the reference returns the LAST infinity seen.
+//
+// All kernels are HBM-bound: algorithmic bytes = 8*rows*cols + output.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace {
+
+enum { K_SUM = 0, K_SUMSQ = 1, K_MAX = 2, K_MIN = 3, K_PROD = 7 };
+
+__device__ __forceinline__ double jmax(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) & __double_as_longlong(b));
+  return (a >= b) ? a : b;
+}
+__device__ __forceinline__ double jmin(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) | __double_as_longlong(b));
+  return (a <= b) ? a : b;
+}
+
+// Accumulator abstraction: OP-specific state, element update, merge and finalisation.
+template <int OP>
+struct Acc {
+  double hi, lo;
+  __device__ __forceinline__ void init() {
+    hi = (OP == K_MAX) ? -CUDART_INF : (OP == K_MIN) ? CUDART_INF : (OP == K_PROD) ? 1.0 : 0.0;
+    lo = 0.0;
+  }
+  __device__ __forceinline__ void push(double x) {
+    if (OP == K_SUM || OP == K_SUMSQ) {
+      const double v = (OP == K_SUMSQ) ? __dmul_rn(x, x) : x;
+      double s, e;
+      two_sum(hi, v, s, e);
+      hi = s;
+      lo = __dadd_rn(lo, e);
+    } else if (OP == K_MAX) {
+      hi = jmax(hi, x);
+    } else if (OP == K_MIN) {
+      hi = jmin(hi, x);
+    } else {
+      hi = __dmul_rn(hi, x);
+    }
+  }
+  __device__ __forceinline__ void merge(double ohi, double olo) {
+    if (OP == K_SUM || OP == K_SUMSQ) {
+      double s, e;
+      two_sum(hi, ohi, s, e);
+      hi = s;
+      lo = __dadd_rn(__dadd_rn(lo, olo), e);
+    } else if (OP == K_MAX) {
+      hi = jmax(hi, ohi);
+    } else if (OP == K_MIN) {
+      hi = jmin(hi, ohi);
+    } else {
+      hi = __dmul_rn(hi, ohi);
+    }
+  }
+  __device__ __forceinline__ double result() const {
+    if (OP == K_SUM || OP == K_SUMSQ) {
+      // an infinite hi leaves NaN in lo (inf - inf inside two_sum): the sum is the infinity itself
+      return (isinf(hi) || lo != lo) ? hi : __dadd_rn(hi, lo);
+    }
+    return hi;
+  }
+};
+
+template <int OP>
+__device__ __forceinline__ void warp_merge(Acc<OP>& a) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ohi = __shfl_xor_sync(0xffffffffu, a.hi, o);
+    const double olo = __shfl_xor_sync(0xffffffffu, a.lo, o);
+    a.merge(ohi, olo);
+  }
+}
+// merge within aligned lane groups of width W (power of two <= 32)
+template <int OP>
+__device__ __forceinline__ void group_merge(Acc<OP>& a, int W) {
+  for (int o = W >> 1; o > 0; o >>= 1) {
+    const double ohi = __shfl_xor_sync(0xffffffffu, a.hi, o);
+    const double olo = __shfl_xor_sync(0xffffffffu, a.lo, o);
+    a.merge(ohi, olo);
+  }
+}
+
+// ---------------- ALL: grid-stride + last-block finish ----------------
+template <int OP>
+__global__ void __launch_bounds__(512) agg_all_kernel(const double* __restrict__ X, i64 len, int vec2, double* __restrict__ partial,
+                                                      unsigned int* counter, double* __restrict__ out, double scale) {
+  Acc<OP> a[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) a[q].init();
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  const i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec2) {
+    const double2* X2 = reinterpret_cast<const double2*>(X);
+    const i64 n2 = len >> 1;
+    i64 i = tid;
+    for (; i + stride < n2; i += 2 * stride) {
+      const double2 u = ldg_stream2(X2 + i), w = ldg_stream2(X2 + i + stride);
+      a[0].push(u.x);
+      a[1].push(u.y);
+      a[2].push(w.x);
+      a[3].push(w.y);
+    }
+    if (i < n2) {
+      const double2 u = ldg_stream2(X2 + i);
+      a[0].push(u.x);
+      a[1].push(u.y);
+    }
+    if (tid == 0 && (len & 1)) a[2].push(X[len - 1]);
+  } else {
+    for (i64 i = tid; i < len; i += stride) a[0].push(ldg_stream(X + i));
+  }
+  a[0].merge(a[1].hi, a[1].lo);
+  a[2].merge(a[3].hi, a[3].lo);
+  a[0].merge(a[2].hi, a[2].lo);
+  warp_merge(a[0]);
+  __shared__ double sh[2][32];
+  __shared__ unsigned int s_ticket;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  if (lane == 0) {
+    sh[0][warp] = a[0].hi;
+    sh[1][warp] = a[0].lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    Acc<OP> b;
+    b.init();
+    if (lane < nwarps) {
+      b.hi = sh[0][lane];
+      b.lo = sh[1][lane];
+    }
+    warp_merge(b);
+    if (lane == 0) {
+      partial[2 * blockIdx.x] = b.hi;
+      partial[2 * blockIdx.x + 1] = b.lo;
+      __threadfence();
+      s_ticket = atomicAdd(counter, 1u);
+    }
+  }
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence();
+  if (warp == 0) {
+    Acc<OP> b;
+    b.init();
+    for (int i = lane; i < (int)gridDim.x; i += 32) b.merge(__ldcg(partial + 2 * i), __ldcg(partial + 2 * i + 1));
+    warp_merge(b);
+    if (lane == 0) {
+      double r = b.result();
+      if (scale != 1.0) r = __ddiv_rn(r, scale);
+      out[0] = r;
+      *counter = 0u;
+    }
+  }
+}
+
+// ---------------- ROW: W lanes per row (W = 1..32, power of two) ----------------
+template <int OP>
+__global__ void agg_row_kernel(const double* __restrict__ X, i64 rows, i64 cols, int W, double* __restrict__ out, double scale) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (W - 1);
+  const int rows_per_warp = 32 / W;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 base = warp * rows_per_warp; base < rows; base += nwarps * rows_per_warp) {
+    const i64 r = base + lane / W;
+    Acc<OP> a;
+    a.init();
+    if (r < rows) {
+      const double* row = X + r * cols;
+      for (i64 j = sub; j < cols; j += W) a.push(ldg_stream(row + j));
+    }
+    group_merge(a, W);
+    if (r < rows && sub == 0) {
+      double v = a.result();
+      if (scale != 1.0) v = __ddiv_rn(v, scale);
+      out[r] = v;
+    }
+  }
+}
+
+// rowIndexMax / rowIndexMin: >= / <= so the LAST extremum wins; NaN never wins; all-NaN row -> 0
+template <int ISMAX>
+__global__ void agg_rowindex_kernel(const double* __restrict__ X, i64 rows, i64 cols, int W, double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (W - 1);
+  const int rows_per_warp = 32 / W;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 base = warp * rows_per_warp; base < rows; base += nwarps * rows_per_warp) {
+    const i64 r = base + lane / W;
+    double best = ISMAX ? -CUDART_INF : CUDART_INF;
+    i64 idx = -1;
+    if (r < rows) {
+      const double* row = X + r * cols;
+      for (i64 j = sub; j < cols; j += W) {
+        const double x = ldg_stream(row + j);
+        const bool take = ISMAX ? (x >= best) : (x <= best);
+        idx = take ? j : idx;
+        best = take ? x : best;
+      }
+    }
+    for (int o = W >> 1; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const i64 oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      // a candidate exists only if idx >= 0; ties go to the larger column index
+      const bool other_better = (oi >= 0) && ((idx < 0) || (ISMAX ? (ob > best) : (ob < best)) || (ob == best && oi > idx));
+      best = other_better ? ob : best;
+      idx = other_better ? oi : idx;
+    }
+    if (r < rows && sub == 0) out[r] = (double)(idx + 1);
+  }
+}
+
+// ---------------- COL: block = CPB columns x RPB row-lanes; grid = col tiles x row splits ----------------
+template <int OP>
+__global__ void __launch_bounds__(256) agg_col_kernel(const double* __restrict__ X, i64 rows, i64 cols, int CPB, int RPB,
+                                                      double* __restrict__ partial) {
+  extern __shared__ double sh[];  // [2][RPB][CPB]
+  const int t = threadIdx.x;
+  const int cl = t % CPB, rl = t / CPB;
+  const i64 c = (i64)blockIdx.x * CPB + cl;
+  const bool active = (rl < RPB) && (c < cols);
+  Acc<OP> a0, a1;
+  a0.init();
+  a1.init();
+  if (active) {
+    const i64 rstep = (i64)RPB * gridDim.y;
+    i64 r = (i64)blockIdx.y * RPB + rl;
+    for (; r + rstep < rows; r += 2 * rstep) {
+      const double u = ldg_stream(X + r * cols + c);
+      const double w = ldg_stream(X + (r + rstep) * cols + c);
+      a0.push(u);
+      a1.push(w);
+    }
+    if (r < rows) a0.push(ldg_stream(X + r * cols + c));
+    a0.merge(a1.hi, a1.lo);
+  }
+  if (rl < RPB) {
+    sh[rl * CPB + cl] = a0.hi;
+    sh[(RPB + rl) * CPB + cl] = a0.lo;
+  }
+  __syncthreads();
+  if (rl == 0 && c < cols) {
+    for (int q = 1; q < RPB; q++) a0.merge(sh[q * CPB + cl], sh[(RPB + q) * CPB + cl]);
+    partial[((size_t)blockIdx.y * 2) * cols + c] = a0.hi;
+    partial[((size_t)blockIdx.y * 2 + 1) * cols + c] = a0.lo;
+  }
+}
+template <int OP>
+__global__ void agg_col_finish_kernel(const double* __restrict__ partial, int splits, i64 cols, double* __restrict__ out, double scale) {
+  const i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  Acc<OP> a;
+  a.init();
+  for (int s = 0; s < splits; s++) a.merge(partial[((size_t)s * 2) * cols + c], partial[((size_t)s * 2 + 1) * cols + c]);
+  double v = a.result();
+  if (scale != 1.0) v = __ddiv_rn(v, scale);
+  out[c] = v;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int OP>
+int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, double* out, double scale) {
+  const i64 len = rows * cols;
+  if (dir == SYSML_DIR_ALL) {
+    i64 blocks = (len + 512 * 8 - 1) / (512 * 8);
+    const i64 cap = (i64)ctx->sm_count * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)blocks * 2 * sizeof(double), &ws);
+    if (rc) return rc;
+    agg_all_kernel<OP><<<(unsigned)blocks, 512, 0, ctx->stream>>>(X, len, aligned16(X) ? 1 : 0, (double*)ws, ctx->counters + 1, out, scale);
+    SYSML_LAUNCH_CHECK(ctx, "agg_all_kernel");
+    return SYSML_OK;
+  }
+  if (dir == SYSML_DIR_ROW) {
+    int W = 32;
+    while (W > 1 && (W >> 1) >= cols) W >>= 1;
+    const i64 rows_per_block = (256 / 32) * (32 / W);
+    i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
+    const i64 cap = (i64)ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    agg_row_kernel<OP><<<(unsigned)blocks, 256, 0, ctx->stream>>>(X, rows, cols, W, out, scale);
+    SYSML_LAUNCH_CHECK(ctx, "agg_row_kernel");
+    return SYSML_OK;
+  }
+  // COL
+  const int CPB = (int)(cols < 256 ? cols : 256);
+  const int RPB = 256 / CPB;
+  const i64 ctiles = (cols + CPB - 1) / CPB;
+  i64 splits = ((i64)ctx->sm_count * 8 + ctiles - 1) / ctiles;
+  const i64 max_splits = (rows + (i64)RPB * 8 - 1) / ((i64)RPB * 8);
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  if (splits > 65535) splits = 65535;
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, (size_t)splits * 2 * cols * sizeof(double), &ws);
+  if (rc) return rc;
+  dim3 grid((unsigned)ctiles, (unsigned)splits);
+  agg_col_kernel<OP><<<grid, 256, 2 * RPB * CPB * sizeof(double), ctx->stream>>>(X, rows, cols, CPB, RPB, (double*)ws);
+  SYSML_LAUNCH_CHECK(ctx, "agg_col_kernel");
+  agg_col_finish_kernel<OP><<<(unsigned)((cols + 127) / 128), 128, 0, ctx->stream>>>((double*)ws, (int)splits, cols, out, scale);
+  SYSML_LAUNCH_CHECK(ctx, "agg_col_finish_kernel");
+  return SYSML_OK;
+}
+
+}  // namespace
+
+extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols, int op, int dir,
+                                          double* out) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "agg_unary: negative dimension");
+  if (dir < 0 || dir > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary: bad direction %d", dir);
+  if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary: out is null");
+  if (rows * cols == 0) return sysml_set_error(ctx, SYSML_E_DIM, "agg_unary: empty input (%lld x %lld)", (long long)rows, (long long)cols);
+  if (!X) return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary: X is null");
+  const double cnt = (dir == SYSML_DIR_ALL) ? (double)rows * (double)cols : (dir == SYSML_DIR_ROW ? (double)cols : (double)rows);
+  switch (op) {
+    case SYSML_AGG_SUM: return run_agg<K_SUM>(ctx, X, rows, cols, dir, out, 1.0);
+    case SYSML_AGG_SUMSQ: return run_agg<K_SUMSQ>(ctx, X, rows, cols, dir, out, 1.0);
+    case SYSML_AGG_MAX: return run_agg<K_MAX>(ctx, X, rows, cols, dir, out, 1.0);
+    case SYSML_AGG_MIN: return run_agg<K_MIN>(ctx, X, rows, cols, dir, out, 1.0);
+    case SYSML_AGG_PROD: return run_agg<K_PROD>(ctx, X, rows, cols, dir, out, 1.0);
+    case SYSML_AGG_MEAN: return run_agg<K_SUM>(ctx, X, rows, cols, dir, out, cnt);
+    case SYSML_AGG_MAXINDEX:
+    case SYSML_AGG_MININDEX: {
+      if (dir != SYSML_DIR_ROW)
+        return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row (LibMatrixAgg.java:1318-1329)");
+      int W = 32;
+      while (W > 1 && (W >> 1) >= cols) W >>= 1;
+      const i64 rows_per_block = (256 / 32) * (32 / W);
+      i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
+      const i64 cap = (i64)ctx->sm_count * 16;
+      if (blocks > cap) blocks = cap;
+      if (op == SYSML_AGG_MAXINDEX)
+        agg_rowindex_kernel<1><<<(unsigned)blocks, 256, 0, ctx->stream>>>(X, rows, cols, W, out);
+      else
+        agg_rowindex_kernel<0><<<(unsigned)blocks, 256, 0, ctx->stream>>>(X, rows, cols, W, out);
+      SYSML_LAUNCH_CHECK(ctx, "agg_rowindex_kernel");
+      return SYSML_OK;
+    }
+    case SYSML_AGG_VAR: return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "variance is not implemented yet");
+  }
+  return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary: unknown opcode %d", op);
+}

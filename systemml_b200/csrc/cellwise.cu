@@ -1,0 +1,351 @@
+// cellwise.cu -- cellwise binary (matrix-matrix with row/column-vector broadcast, matrix-scalar),
+// axpy, unary, fill and transpose.  All HBM-bound: one pass, 128-bit accesses where alignment allows,
+// grid sized as a multiple of the SM count.
+//
+// Reference semantics: LibMatrixBincell.bincellOp (LibMatrixBincell.java:87-339) with the value
+// functions in runtime/functionobjects; GPU twins matrix_matrix_cellwise_op / matrix_scalar_op /
+// daxpy_matrix_vector / fill (src/main/cpp/kernels/SystemML.cu:698,750,627,783) and the unary kernels
+// (:1541-1960).  Opcode numbering = LibMatrixCUDA.getBinaryOp (LibMatrixCUDA.java:1551-1575).
+//
+// Algorithmic bytes: 8*(size(A) + size(B) + rows*cols) for binary, 16*len for scalar/unary.
+#include "common.cuh"
+
+namespace {
+
+// Java Math.max/min: NaN propagates, -0.0 < +0.0 (functionobjects/Builtin.java:356-361)
+__device__ __forceinline__ double jmax(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) & __double_as_longlong(b));
+  return (a >= b) ? a : b;
+}
+__device__ __forceinline__ double jmin(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) | __double_as_longlong(b));
+  return (a <= b) ? a : b;
+}
+// IntegerDivide.executeIntDiv (functionobjects/IntegerDivide.java:62-73): floor(x/y + 2^-53) via long cast
+__device__ __forceinline__ double intdiv(double x, double y) {
+  const double r = __ddiv_rn(x, y);
+  if (isnan(r) || isinf(r)) return r;
+  return (double)(long long)floor(__dadd_rn(r, 0x1.0p-53));
+}
+
+template <int OP>
+__device__ __forceinline__ double binop(double x, double y) {
+  switch (OP) {
+    case SYSML_OP_PLUS: return __dadd_rn(x, y);
+    case SYSML_OP_MINUS: return __dsub_rn(x, y);
+    case SYSML_OP_MULTIPLY: return __dmul_rn(x, y);
+    case SYSML_OP_DIVIDE: return __ddiv_rn(x, y);
+    case SYSML_OP_POWER: return pow(x, y);
+    case SYSML_OP_LESS: return (x < y) ? 1.0 : 0.0;
+    case SYSML_OP_LESSEQUAL: return (x <= y) ? 1.0 : 0.0;
+    case SYSML_OP_GREATER: return (x > y) ? 1.0 : 0.0;
+    case SYSML_OP_GREATEREQUAL: return (x >= y) ? 1.0 : 0.0;
+    case SYSML_OP_EQUAL: return (x == y) ? 1.0 : 0.0;
+    case SYSML_OP_NOTEQUAL: return (x != y) ? 1.0 : 0.0;
+    case SYSML_OP_MIN: return jmin(x, y);
+    case SYSML_OP_MAX: return jmax(x, y);
+    case SYSML_OP_AND: return ((x != 0.0) && (y != 0.0)) ? 1.0 : 0.0;  // functionobjects/And.java:46-48
+    case SYSML_OP_OR: return ((x != 0.0) || (y != 0.0)) ? 1.0 : 0.0;   // functionobjects/Or.java:46-48
+    case SYSML_OP_MINUS1MULTIPLY: return __dsub_rn(1.0, __dmul_rn(x, y));  // no FMA: Java rounds twice
+    case SYSML_OP_MINUSNZ: return (x != 0.0) ? __dsub_rn(x, y) : 0.0;
+    case SYSML_OP_MODULUS:  // functionobjects/Modulus.java:49-53
+      if (y == 0.0) return __longlong_as_double(0x7ff8000000000000LL);
+      return __dsub_rn(x, __dmul_rn(intdiv(x, y), y));
+    case SYSML_OP_INTDIV: return intdiv(x, y);
+  }
+  return 0.0;
+}
+
+template <int OP>
+__device__ __forceinline__ double unop(double x) {
+  switch (OP) {
+    case SYSML_UN_EXP: return exp(x);
+    case SYSML_UN_SQRT: return sqrt(x);
+    case SYSML_UN_ROUND: return floor(__dadd_rn(x, 0.5));  // Java Math.round semantics: floor(x + 0.5)
+    case SYSML_UN_ABS: return fabs(x);
+    case SYSML_UN_LOG: return log(x);
+    case SYSML_UN_FLOOR: return floor(x);
+    case SYSML_UN_CEIL: return ceil(x);
+    case SYSML_UN_SIGN: return (x > 0.0) ? 1.0 : ((x < 0.0) ? -1.0 : ((x != x) ? x : 0.0));
+    case SYSML_UN_SIGMOID: return 1.0 / (1.0 + exp(-x));
+    case SYSML_UN_SIN: return sin(x);
+    case SYSML_UN_COS: return cos(x);
+    case SYSML_UN_TAN: return tan(x);
+    case SYSML_UN_TANH: return tanh(x);
+  }
+  return 0.0;
+}
+
+// ---------------- flat kernels (no broadcast) ----------------
+template <int OP>
+__global__ void binary_flat_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C, i64 len, int vec2) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  const i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec2) {
+    const i64 n2 = len >> 1;
+    const double2* A2 = reinterpret_cast<const double2*>(A);
+    const double2* B2 = reinterpret_cast<const double2*>(B);
+    double2* C2 = reinterpret_cast<double2*>(C);
+    for (i64 i = tid; i < n2; i += stride) {
+      const double2 a = ldg_stream2(A2 + i), b = ldg_stream2(B2 + i);
+      C2[i] = make_double2(binop<OP>(a.x, b.x), binop<OP>(a.y, b.y));
+    }
+    if (tid == 0 && (len & 1)) C[len - 1] = binop<OP>(A[len - 1], B[len - 1]);
+  } else {
+    for (i64 i = tid; i < len; i += stride) C[i] = binop<OP>(ldg_stream(A + i), ldg_stream(B + i));
+  }
+}
+
+// broadcast kernels: one division per thread at start, then incremental (row, col) stepping
+template <int OP, int BC>
+__global__ void binary_bcast_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C, i64 rows, i64 cols) {
+  const i64 len = rows * cols;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= len) return;
+  i64 r = i / cols, c = i - r * cols;
+  const i64 dr = stride / cols, dc = stride - dr * cols;
+  for (; i < len; i += stride) {
+    const double b = (BC == SYSML_BCAST_COL) ? __ldg(B + r) : __ldg(B + c);
+    C[i] = binop<OP>(ldg_stream(A + i), b);
+    r += dr;
+    c += dc;
+    if (c >= cols) {
+      c -= cols;
+      r++;
+    }
+  }
+}
+
+template <int OP, int LEFT>
+__global__ void scalar_kernel(const double* __restrict__ A, double s, double* __restrict__ C, i64 len, int vec2) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  const i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec2) {
+    const i64 n2 = len >> 1;
+    const double2* A2 = reinterpret_cast<const double2*>(A);
+    double2* C2 = reinterpret_cast<double2*>(C);
+    for (i64 i = tid; i < n2; i += stride) {
+      const double2 a = ldg_stream2(A2 + i);
+      C2[i] = LEFT ? make_double2(binop<OP>(s, a.x), binop<OP>(s, a.y)) : make_double2(binop<OP>(a.x, s), binop<OP>(a.y, s));
+    }
+    if (tid == 0 && (len & 1)) C[len - 1] = LEFT ? binop<OP>(s, A[len - 1]) : binop<OP>(A[len - 1], s);
+  } else {
+    for (i64 i = tid; i < len; i += stride) {
+      const double a = ldg_stream(A + i);
+      C[i] = LEFT ? binop<OP>(s, a) : binop<OP>(a, s);
+    }
+  }
+}
+
+template <int OP>
+__global__ void unary_kernel(const double* __restrict__ A, double* __restrict__ C, i64 len, int vec2) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  const i64 tid = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec2) {
+    const i64 n2 = len >> 1;
+    const double2* A2 = reinterpret_cast<const double2*>(A);
+    double2* C2 = reinterpret_cast<double2*>(C);
+    for (i64 i = tid; i < n2; i += stride) {
+      const double2 a = ldg_stream2(A2 + i);
+      C2[i] = make_double2(unop<OP>(a.x), unop<OP>(a.y));
+    }
+    if (tid == 0 && (len & 1)) C[len - 1] = unop<OP>(A[len - 1]);
+  } else {
+    for (i64 i = tid; i < len; i += stride) C[i] = unop<OP>(ldg_stream(A + i));
+  }
+}
+
+// C = A + alpha*B (two roundings, like Java's in1 + cnt*in2)
+template <int BC>
+__global__ void axpy_kernel(const double* __restrict__ A, const double* __restrict__ B, double alpha, double* __restrict__ C, i64 rows, i64 cols) {
+  const i64 len = rows * cols;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= len) return;
+  i64 r = 0, c = 0, dr = 0, dc = 0;
+  if (BC != SYSML_BCAST_NONE) {
+    r = i / cols;
+    c = i - r * cols;
+    dr = stride / cols;
+    dc = stride - dr * cols;
+  }
+  for (; i < len; i += stride) {
+    const double b = (BC == SYSML_BCAST_NONE) ? ldg_stream(B + i) : ((BC == SYSML_BCAST_COL) ? __ldg(B + r) : __ldg(B + c));
+    C[i] = __dadd_rn(ldg_stream(A + i), __dmul_rn(alpha, b));
+    if (BC != SYSML_BCAST_NONE) {
+      r += dr;
+      c += dc;
+      if (c >= cols) {
+        c -= cols;
+        r++;
+      }
+    }
+  }
+}
+
+__global__ void fill_kernel(double* __restrict__ A, i64 len, double v) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += stride) A[i] = v;
+}
+
+// 32x32 tiled transpose through padded shared memory
+__global__ void transpose_kernel(const double* __restrict__ A, double* __restrict__ C, i64 rows, i64 cols) {
+  __shared__ double tile[32][33];
+  const i64 tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+  for (i64 t = blockIdx.x; t < tiles_c * tiles_r; t += gridDim.x) {
+    const i64 tr = t / tiles_c, tc = t - tr * tiles_c;
+    const i64 r0 = tr * 32, c0 = tc * 32;
+    for (int y = threadIdx.y; y < 32; y += blockDim.y) {
+      const i64 r = r0 + y, c = c0 + threadIdx.x;
+      if (r < rows && c < cols) tile[y][threadIdx.x] = A[r * cols + c];
+    }
+    __syncthreads();
+    for (int y = threadIdx.y; y < 32; y += blockDim.y) {
+      const i64 c = c0 + y, r = r0 + threadIdx.x;  // output row = c, output col = r
+      if (r < rows && c < cols) C[c * rows + r] = tile[threadIdx.x][y];
+    }
+    __syncthreads();
+  }
+}
+
+inline unsigned grid_for(sysml_b200_ctx* ctx, i64 work_items, int threads, int per_sm) {
+  i64 blocks = (work_items + threads - 1) / threads;
+  const i64 cap = (i64)ctx->sm_count * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int OP>
+int launch_binary(sysml_b200_ctx* ctx, const double* A, const double* B, double* C, i64 rows, i64 cols, int bcast) {
+  const i64 len = rows * cols;
+  if (bcast == SYSML_BCAST_NONE) {
+    const int vec2 = aligned16(A) && aligned16(B) && aligned16(C);
+    binary_flat_kernel<OP><<<grid_for(ctx, vec2 ? len / 2 + 1 : len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, len, vec2);
+  } else if (bcast == SYSML_BCAST_COL) {
+    binary_bcast_kernel<OP, SYSML_BCAST_COL><<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, rows, cols);
+  } else {
+    binary_bcast_kernel<OP, SYSML_BCAST_ROW><<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, rows, cols);
+  }
+  SYSML_LAUNCH_CHECK(ctx, "binary cellwise kernel");
+  return SYSML_OK;
+}
+
+template <int OP>
+int launch_scalar(sysml_b200_ctx* ctx, const double* A, double s, double* C, i64 len, int left) {
+  const int vec2 = aligned16(A) && aligned16(C);
+  const unsigned g = grid_for(ctx, vec2 ? len / 2 + 1 : len, 256, 16);
+  if (left)
+    scalar_kernel<OP, 1><<<g, 256, 0, ctx->stream>>>(A, s, C, len, vec2);
+  else
+    scalar_kernel<OP, 0><<<g, 256, 0, ctx->stream>>>(A, s, C, len, vec2);
+  SYSML_LAUNCH_CHECK(ctx, "scalar cellwise kernel");
+  return SYSML_OK;
+}
+
+template <int OP>
+int launch_unary(sysml_b200_ctx* ctx, const double* A, double* C, i64 len) {
+  const int vec2 = aligned16(A) && aligned16(C);
+  unary_kernel<OP><<<grid_for(ctx, vec2 ? len / 2 + 1 : len, 256, 16), 256, 0, ctx->stream>>>(A, C, len, vec2);
+  SYSML_LAUNCH_CHECK(ctx, "unary cellwise kernel");
+  return SYSML_OK;
+}
+
+}  // namespace
+
+#define SYSML_FOR_ALL_BINOPS(X) \
+  X(0) X(1) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18)
+#define SYSML_FOR_ALL_UNOPS(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12)
+
+extern "C" int sysml_b200_binary_mm(sysml_b200_ctx* ctx, const double* A, const double* B, double* C, int64_t rows,
+                                    int64_t cols, int bcast, int op) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "binary_mm: negative dimension");
+  if (bcast < 0 || bcast > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: bad broadcast code %d", bcast);
+  if (rows * cols == 0) return SYSML_OK;
+  if (!A || !B || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: null pointer");
+  switch (op) {
+#define X(o) \
+  case o: return launch_binary<o>(ctx, A, B, C, rows, cols, bcast);
+    SYSML_FOR_ALL_BINOPS(X)
+#undef X
+  }
+  return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: unknown opcode %d", op);
+}
+
+extern "C" int sysml_b200_binary_ms(sysml_b200_ctx* ctx, const double* A, double scalar, double* C, int64_t len, int op,
+                                    int scalar_left) {
+  SYSML_ENTER(ctx);
+  if (len < 0) return sysml_set_error(ctx, SYSML_E_DIM, "binary_ms: negative length");
+  if (len == 0) return SYSML_OK;
+  if (!A || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_ms: null pointer");
+  switch (op) {
+#define X(o) \
+  case o: return launch_scalar<o>(ctx, A, scalar, C, len, scalar_left);
+    SYSML_FOR_ALL_BINOPS(X)
+#undef X
+  }
+  return sysml_set_error(ctx, SYSML_E_INVALID, "binary_ms: unknown opcode %d", op);
+}
+
+extern "C" int sysml_b200_unary(sysml_b200_ctx* ctx, const double* A, double* C, int64_t len, int op) {
+  SYSML_ENTER(ctx);
+  if (len < 0) return sysml_set_error(ctx, SYSML_E_DIM, "unary: negative length");
+  if (len == 0) return SYSML_OK;
+  if (!A || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "unary: null pointer");
+  switch (op) {
+#define X(o) \
+  case o: return launch_unary<o>(ctx, A, C, len);
+    SYSML_FOR_ALL_UNOPS(X)
+#undef X
+  }
+  return sysml_set_error(ctx, SYSML_E_INVALID, "unary: unknown opcode %d", op);
+}
+
+extern "C" int sysml_b200_axpy(sysml_b200_ctx* ctx, const double* A, const double* B, double alpha, double* C,
+                               int64_t rows, int64_t cols, int bcast) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "axpy: negative dimension");
+  if (rows * cols == 0) return SYSML_OK;
+  if (!A || !B || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "axpy: null pointer");
+  const unsigned g = grid_for(ctx, rows * cols, 256, 16);
+  if (bcast == SYSML_BCAST_NONE)
+    axpy_kernel<SYSML_BCAST_NONE><<<g, 256, 0, ctx->stream>>>(A, B, alpha, C, rows, cols);
+  else if (bcast == SYSML_BCAST_COL)
+    axpy_kernel<SYSML_BCAST_COL><<<g, 256, 0, ctx->stream>>>(A, B, alpha, C, rows, cols);
+  else if (bcast == SYSML_BCAST_ROW)
+    axpy_kernel<SYSML_BCAST_ROW><<<g, 256, 0, ctx->stream>>>(A, B, alpha, C, rows, cols);
+  else
+    return sysml_set_error(ctx, SYSML_E_INVALID, "axpy: bad broadcast code %d", bcast);
+  SYSML_LAUNCH_CHECK(ctx, "axpy_kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_fill(sysml_b200_ctx* ctx, double* A, int64_t len, double value) {
+  SYSML_ENTER(ctx);
+  if (len < 0 || (len > 0 && !A)) return sysml_set_error(ctx, SYSML_E_INVALID, "fill: bad arguments");
+  if (len == 0) return SYSML_OK;
+  fill_kernel<<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, len, value);
+  SYSML_LAUNCH_CHECK(ctx, "fill_kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "transpose: negative dimension");
+  if (rows * cols == 0) return SYSML_OK;
+  if (!A || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "transpose: null pointer");
+  const i64 tiles = ((rows + 31) / 32) * ((cols + 31) / 32);
+  i64 blocks = tiles;
+  const i64 cap = (i64)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  transpose_kernel<<<(unsigned)blocks, dim3(32, 8), 0, ctx->stream>>>(A, C, rows, cols);
+  SYSML_LAUNCH_CHECK(ctx, "transpose_kernel");
+  return SYSML_OK;
+}

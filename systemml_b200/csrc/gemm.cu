@@ -1,0 +1,367 @@
+// gemm.cu -- FP64 tensor-core (DMMA) contractions: tsmm t(X)%*%X / X%*%t(X) and general dense matmult.
+//
+// Reference semantics: LibMatrixMult.matrixMultTransposeSelfDense (LibMatrixMult.java:1686-1837) +
+// copyUpperToLowerTriangle (:3633-3672, incl. the exact nnz count) for tsmm; matrixMultDenseDense
+// (:880-1103) for matmult.  GPU twins being replaced: cublasDsyrk + copy_u2l_dense
+// (LibMatrixCUDA.java:477-524; SystemML.cu:413) and cublasDgemm/Dgemv/Ddot (LibMatrixCuMatMult.java:362-408).
+//
+// Design (B200).  tcgen05 / TMEM have no f64 kind; FP64 tensor work on sm_100a is the warp-level
+// mma.sync m8n8k4 path (SASS DMMA.8x8x4).  FP64 is so slow relative to shared-memory and L2 bandwidth
+// (ridge ~6 flop/B) that the kernel is DMMA-issue bound; the job of everything else is to stay out of
+// the way: 4-stage cp.async (LDGSTS) pipeline, padded shared-memory tiles with leading dimensions
+// = 4 (mod 16) doubles so that every fragment load is bank-conflict free for all four operand layouts,
+// one __syncthreads per 16-deep k block, 128 DMMA per warp between barriers.
+//   - tsmm computes only tiles with tj >= ti (the upper triangle); the finishing kernel sums the split-K
+//     partials in a fixed order, writes both triangles (replaces copy_u2l_dense) and counts non-zeros.
+//   - the contraction dimension (rows of X for tsmm: 10^7) is split across CTAs so that the grid is a
+//     multiple of the SM count; partials are reduced deterministically, not with atomics.
+// Algorithmic flops: tsmm n*m*(m+1); matmult 2*M*N*K.
+#include "common.cuh"
+
+int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m);
+int sysml_dense_vm(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, i64 n, i64 m);
+
+namespace {
+
+constexpr int BK = 16;
+constexpr int STAGES = 4;
+
+struct GemmArgs {
+  const double* A;
+  const double* B;
+  double* out;  // C (splits == 1 && !sym) or partial base
+  i64 M, N, K;
+  i64 lda, ldb;
+  i64 k_per_split;
+  int tiles_m, tiles_n;
+  int sym;      // only tiles tj >= ti
+  int vecA, vecB;
+};
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src, int src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// Copies a logical [R][Ccols] tile whose rows are contiguous in global memory (row r at src + r*ld)
+// into shared memory with leading dimension LD; rows >= rvalid and columns >= cvalid are zero-filled.
+template <int R, int CCOLS, int LD, int NT>
+__device__ __forceinline__ void load_tile(double* s, const double* src, i64 ld, i64 rvalid, i64 cvalid, int vec, int tid) {
+  if (vec) {
+    constexpr int CH = CCOLS / 2;
+    for (int c = tid; c < R * CH; c += NT) {
+      const int r = c / CH, cc = (c - r * CH) * 2;
+      i64 nb = (r < rvalid) ? (cvalid - cc) * 8 : 0;
+      nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+      cp_async16(s + r * LD + cc, nb > 0 ? (const void*)(src + (i64)r * ld + cc) : (const void*)src, (int)nb);
+    }
+  } else {
+    for (int c = tid; c < R * CCOLS; c += NT) {
+      const int r = c / CCOLS, cc = c - r * CCOLS;
+      const bool ok = (r < rvalid) && (cc < cvalid);
+      cp_async8(s + r * LD + cc, ok ? (const void*)(src + (i64)r * ld + cc) : (const void*)src, ok ? 8 : 0);
+    }
+  }
+}
+
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+struct GemmCfg {
+  static constexpr int NT = WARPS_M * WARPS_N * 32;
+  static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
+  static constexpr int MT = WM / 8, NTL = WN / 8;
+  static constexpr int LDA = TA ? (BM + 4) : (BK + 4);
+  static constexpr int LDB = TB ? (BK + 4) : (BN + 4);
+  static constexpr int A_ELEMS = TA ? BK * LDA : BM * LDA;
+  static constexpr int B_ELEMS = TB ? BN * LDB : BK * LDB;
+  static constexpr size_t SMEM = (size_t)STAGES * (A_ELEMS + B_ELEMS) * sizeof(double);
+};
+
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) dgemm_kernel(const GemmArgs g) {
+  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  constexpr int NT = Cfg::NT, MT = Cfg::MT, NTL = Cfg::NTL, LDA = Cfg::LDA, LDB = Cfg::LDB;
+  extern __shared__ __align__(16) double smem[];
+  double* As = smem;
+  double* Bs = smem + STAGES * Cfg::A_ELEMS;
+
+  // ---- which tile / which slice of K ----
+  int ti, tj;
+  if (g.sym) {
+    int t = blockIdx.x;
+    ti = 0;
+    while (t >= g.tiles_n - ti) {
+      t -= g.tiles_n - ti;
+      ti++;
+    }
+    tj = ti + t;
+  } else {
+    ti = blockIdx.x / g.tiles_n;
+    tj = blockIdx.x - ti * g.tiles_n;
+  }
+  const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+  const i64 kbeg = (i64)blockIdx.y * g.k_per_split;
+  const i64 kend = (kbeg + g.k_per_split < g.K) ? kbeg + g.k_per_split : g.K;
+  const int nkb = (int)((kend - kbeg + BK - 1) / BK);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wm0 = (warp / WARPS_N) * Cfg::WM, wn0 = (warp % WARPS_N) * Cfg::WN;
+  const int gid = lane >> 2, tig = lane & 3;
+
+  auto issue = [&](int kb) {
+    const int s = kb % STAGES;
+    const i64 k0 = kbeg + (i64)kb * BK;
+    const i64 kvalid = kend - k0;  // may exceed BK
+    double* as = As + s * Cfg::A_ELEMS;
+    double* bs = Bs + s * Cfg::B_ELEMS;
+    if (TA)
+      load_tile<BK, BM, LDA, NT>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, g.vecA, tid);
+    else
+      load_tile<BM, BK, LDA, NT>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, g.vecA, tid);
+    if (TB)
+      load_tile<BN, BK, LDB, NT>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, g.vecB, tid);
+    else
+      load_tile<BK, BN, LDB, NT>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, g.vecB, tid);
+  };
+
+  double acc[MT][NTL][2];
+#pragma unroll
+  for (int a = 0; a < MT; a++)
+#pragma unroll
+    for (int b = 0; b < NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; s++) {
+    if (s < nkb) issue(s);
+    cp_async_commit();
+  }
+  for (int kb = 0; kb < nkb; kb++) {
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();
+    if (kb + STAGES - 1 < nkb) issue(kb + STAGES - 1);
+    cp_async_commit();
+    const double* as = As + (kb % STAGES) * Cfg::A_ELEMS;
+    const double* bs = Bs + (kb % STAGES) * Cfg::B_ELEMS;
+#pragma unroll
+    for (int k4 = 0; k4 < BK; k4 += 4) {
+      double af[MT], bf[NTL];
+#pragma unroll
+      for (int a = 0; a < MT; a++) {
+        const int i = wm0 + a * 8 + gid, k = k4 + tig;  // A[i][k]
+        af[a] = TA ? as[k * LDA + i] : as[i * LDA + k];
+      }
+#pragma unroll
+      for (int b = 0; b < NTL; b++) {
+        const int j = wn0 + b * 8 + gid, k = k4 + tig;  // B[k][j]
+        bf[b] = TB ? bs[j * LDB + k] : bs[k * LDB + j];
+      }
+#pragma unroll
+      for (int a = 0; a < MT; a++)
+#pragma unroll
+        for (int b = 0; b < NTL; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+  }
+  cp_async_wait<0>();
+
+  // ---- epilogue: C fragment (row = gid, cols = 2*tig, 2*tig+1) ----
+  double* outp = g.out + (size_t)blockIdx.y * (size_t)g.M * (size_t)g.N;
+#pragma unroll
+  for (int a = 0; a < MT; a++) {
+    const i64 i = i0 + wm0 + a * 8 + gid;
+    if (i >= g.M) continue;
+#pragma unroll
+    for (int b = 0; b < NTL; b++) {
+      const i64 j = j0 + wn0 + b * 8 + 2 * tig;
+      if (j < g.N) outp[i * g.N + j] = acc[a][b][0];
+      if (j + 1 < g.N) outp[i * g.N + j + 1] = acc[a][b][1];
+    }
+  }
+}
+
+// C[idx] = sum over splits (fixed order, compensated)
+__global__ void reduce_partials_kernel(const double* __restrict__ partial, int splits, i64 len, double* __restrict__ C) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += stride) {
+    CompSum a;
+    for (int s = 0; s < splits; s++) a.add(ldg_stream(partial + (size_t)s * len + i));
+    C[i] = a.value();
+  }
+}
+
+// tsmm epilogue: sum partials over the upper triangle, write both triangles, count non-zeros
+// (diagonal counts 1, off-diagonal 2: LibMatrixMult.java:3651-3668).
+__global__ void tsmm_finish_kernel(const double* __restrict__ partial, int splits, i64 n, double* __restrict__ C,
+                                   unsigned long long* __restrict__ nnz) {
+  const i64 len = n * n;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  unsigned long long cnt = 0;
+  i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < len) {
+    i64 i = idx / n, j = idx - i * n;
+    const i64 di = stride / n, dj = stride - di * n;
+    for (; idx < len; idx += stride) {
+      if (j >= i) {
+        CompSum a;
+        for (int s = 0; s < splits; s++) a.add(ldg_stream(partial + (size_t)s * len + idx));
+        const double v = a.value();
+        C[idx] = v;
+        if (j > i) C[j * n + i] = v;
+        if (v != 0.0) cnt += (j == i) ? 1ull : 2ull;
+      }
+      i += di;
+      j += dj;
+      if (j >= n) {
+        j -= n;
+        i++;
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(nnz, cnt);
+}
+
+inline bool even_aligned(const double* p, i64 ld) { return ((reinterpret_cast<uintptr_t>(p) & 15) == 0) && ((ld & 1) == 0); }
+
+struct Plan {
+  int tiles_m, tiles_n, ntiles, splits;
+  i64 k_per_split;
+};
+inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, bool sym) {
+  Plan p;
+  p.tiles_m = (int)((M + BM - 1) / BM);
+  p.tiles_n = (int)((N + BN - 1) / BN);
+  p.ntiles = sym ? p.tiles_n * (p.tiles_n + 1) / 2 : p.tiles_m * p.tiles_n;
+  const i64 kblocks = (K + BK - 1) / BK;
+  // aim at ~6 waves of CTAs (1 CTA per SM) but keep >= 32 k-blocks (512 contraction steps) per CTA
+  i64 want = ((i64)ctx->sm_count * 6 + p.ntiles - 1) / p.ntiles;
+  i64 maxs = kblocks / 32;
+  if (maxs < 1) maxs = 1;
+  if (want > maxs) want = maxs;
+  if (want < 1) want = 1;
+  if (want > 1) {
+    // round the CTA count to a multiple of the SM count when that costs little
+    const i64 total = want * p.ntiles;
+    const i64 rounded = (total / ctx->sm_count) * ctx->sm_count;
+    if (rounded >= p.ntiles && rounded / p.ntiles >= 1) want = rounded / p.ntiles > 0 ? rounded / p.ntiles : want;
+  }
+  if (want > 65535) want = 65535;
+  i64 kbs = (kblocks + want - 1) / want;
+  p.k_per_split = kbs * BK;
+  p.splits = (int)((K + p.k_per_split - 1) / p.k_per_split);
+  if (p.splits < 1) p.splits = 1;
+  return p;
+}
+
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
+             int64_t* h_nnz) {
+  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  auto kern = dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+  const Plan p = make_plan(ctx, M, N, K, BM, BN, sym);
+  const bool direct = (p.splits == 1) && !sym;
+  GemmArgs g{};
+  g.A = A; g.B = B; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb;
+  g.k_per_split = p.k_per_split; g.tiles_m = p.tiles_m; g.tiles_n = p.tiles_n; g.sym = sym ? 1 : 0;
+  g.vecA = even_aligned(A, lda) ? 1 : 0;
+  g.vecB = even_aligned(B, ldb) ? 1 : 0;
+  double* partial = nullptr;
+  unsigned long long* d_nnz = nullptr;
+  if (!direct) {
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, 256 + (size_t)p.splits * M * N * sizeof(double), &ws);
+    if (rc) return rc;
+    d_nnz = (unsigned long long*)ws;
+    partial = (double*)((char*)ws + 256);
+    g.out = partial;
+  } else {
+    g.out = C;
+  }
+  dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
+  SYSML_LAUNCH_CHECK(ctx, "dgemm_kernel");
+  if (direct) return SYSML_OK;
+  const i64 len = M * N;
+  i64 blocks = (len + 255) / 256;
+  const i64 cap = (i64)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (sym) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(d_nnz, 0, sizeof(unsigned long long), ctx->stream));
+    tsmm_finish_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(partial, p.splits, N, C, d_nnz);
+    SYSML_LAUNCH_CHECK(ctx, "tsmm_finish_kernel");
+    if (h_nnz) {
+      unsigned long long h = 0;
+      SYSML_CUDA(ctx, cudaMemcpyAsync(&h, d_nnz, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+      SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      *h_nnz = (int64_t)h;
+    }
+  } else {
+    reduce_partials_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(partial, p.splits, len, C);
+    SYSML_LAUNCH_CHECK(ctx, "reduce_partials_kernel");
+  }
+  return SYSML_OK;
+}
+
+// picks the tile shape from N: square 128x128 for wide outputs, 256 x (8..64) for skinny ones
+template <bool TA, bool TB>
+int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
+                  int64_t* h_nnz) {
+  if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
+  if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 32) return run_gemm<TA, TB, 256, 32, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 48) return run_gemm<TA, TB, 256, 48, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  return run_gemm<TA, TB, 256, 64, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+}
+
+}  // namespace
+
+extern "C" int sysml_b200_tsmm_dense(sysml_b200_ctx* ctx, const double* X, double* out, int64_t rows, int64_t cols, int left,
+                                     int64_t* h_nnz_out) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "tsmm: negative dimension");
+  if (h_nnz_out) *h_nnz_out = 0;
+  const i64 dim = left ? cols : rows;
+  const i64 K = left ? rows : cols;
+  if (dim == 0) return SYSML_OK;
+  if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm: out is null");
+  if (K == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)(dim * dim) * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (!X) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm: X is null");
+  if (left) return dispatch_gemm<true, false>(ctx, X, cols, X, cols, out, dim, dim, K, true, h_nnz_out);
+  return dispatch_gemm<false, true>(ctx, X, cols, X, cols, out, dim, dim, K, true, h_nnz_out);
+}
+
+extern "C" int sysml_b200_matmult_dense(sysml_b200_ctx* ctx, const double* A, const double* B, double* C, int64_t a_rows,
+                                        int64_t a_cols, int64_t b_rows, int64_t b_cols, int trans_a, int trans_b) {
+  SYSML_ENTER(ctx);
+  if (a_rows < 0 || a_cols < 0 || b_rows < 0 || b_cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "matmult: negative dimension");
+  const i64 M = trans_a ? a_cols : a_rows, K = trans_a ? a_rows : a_cols;
+  const i64 K2 = trans_b ? b_cols : b_rows, N = trans_b ? b_rows : b_cols;
+  if (K != K2) return sysml_set_error(ctx, SYSML_E_DIM, "matmult: inner dimensions %lld vs %lld", (long long)K, (long long)K2);
+  if (M * N == 0) return SYSML_OK;
+  if (!C) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult: C is null");
+  if (K == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(M * N) * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (!A || !B) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult: null operand");
+  // vector shapes -> the HBM-bound row-streaming kernels of mmchain.cu (cublasDgemv / Ddot twins)
+  if (N == 1) return trans_a ? sysml_dense_vm(ctx, A, B, C, K, M) : sysml_dense_mv(ctx, A, B, C, M, K);
+  if (M == 1) return trans_b ? sysml_dense_mv(ctx, B, A, C, N, K) : sysml_dense_vm(ctx, B, A, C, K, N);
+  if (!trans_a && !trans_b) return dispatch_gemm<false, false>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
+  if (trans_a && !trans_b) return dispatch_gemm<true, false>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
+  if (!trans_a && trans_b) return dispatch_gemm<false, true>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
+  return dispatch_gemm<true, true>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
+}

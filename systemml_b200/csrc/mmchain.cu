@@ -1,0 +1,474 @@
+// mmchain.cu -- single-pass row-streaming kernels over a dense row-major X (n x m, FP64):
+//
+//   CHAIN : out = t(X) %*% (w * (X %*% v))   (and the XtXv / XtXvy variants)   -- mmchain
+//   MV    : out = X %*% v                                                       -- dense matrix-vector
+//   VM    : out = t(X) %*% y  (= t(t(y) %*% X))                                 -- dense vector-matrix
+//
+// Reference semantics: LibMatrixMult.matrixMultChainDense (LibMatrixMult.java:1594-1653),
+// matrixMultDenseDenseMVShortRHS/TallRHS (:950-970), matrixMultDenseDenseVM (:972-993).
+//
+// Design (B200): all three are HBM-bound, X must cross HBM exactly once.  A persistent grid of
+// (SMs x CTAs/SM) CTAs walks row tiles.  Full rows are contiguous, so a tile of R rows is ONE
+// contiguous span of R*m*8 bytes: a producer warp moves it global->shared with a 1-D bulk copy
+// (cp.async.bulk, the TMA engine; SASS UBLKCP) completing on an mbarrier, through a STAGES-deep
+// ring so that several tiles per SM are in flight.  Consumer threads pull their columns of the
+// tile into registers ONCE, use them for the X*v partial dot products (warp-shuffle reduction),
+// release the stage, and reuse the same registers for the t(X)*tmp update, accumulating their
+// columns of the result in registers across all tiles of the CTA.  Per-CTA column partials go to
+// a scratch buffer; the last CTA to finish (atomic ticket) adds them up with compensated
+// (two-sum) arithmetic in a fixed order, so the result is deterministic run to run.
+//
+// Algorithmic bytes per launch: 8*n*m (X once) + 8*m (v) + 8*m (out) [+ 8*n (w)];  flops 4*n*m.
+#include "common.cuh"
+
+namespace {
+
+enum { MODE_CHAIN = 0, MODE_MV = 1, MODE_VM = 2 };
+
+struct StreamArgs {
+  const double* X;
+  const double* v;   // m-vector (CHAIN, MV)
+  const double* w;   // n-vector: weights / y (CHAIN ct 1,2; VM: the left vector)
+  double* out;       // CHAIN, VM: m ; MV: n
+  double* partial;   // [gridDim.x * G][m] scratch (CHAIN, VM)
+  unsigned int* counter;
+  i64 n;
+  int m;
+  int ct;
+  i64 total_tiles;
+  int use_tma;
+};
+
+// NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
+// RG rows per thread-group per tile, STAGES-deep ring.  G = NTC/TC groups, R = G*RG rows per tile.
+template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES>
+__global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a) {
+  constexpr int G = NTC / TC;
+  constexpr int R = G * RG;
+  constexpr int NWG = TC / 32;  // warps per group
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+  uint64_t* empty = full + STAGES;
+  double* red = reinterpret_cast<double*>(smem_raw + 128);          // [2][G][NWG][RG]
+  double* tiles = reinterpret_cast<double*>(smem_raw + 128 + 2 * G * NWG * RG * 8 + 0);
+  // tiles must be 16B aligned: 128 + multiple of 16 (2*G*NWG*RG*8 is a multiple of 16)
+  const int tid = threadIdx.x;
+  const int m = a.m;
+  const i64 n = a.n;
+  const size_t stage_elems = (size_t)R * m;
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], NTC);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (tid >= NTC) {
+    // ===================== producer warp =====================
+    const int lane = tid - NTC;
+    const uint64_t pol = l2_policy_evict_first();
+    int it = 0;
+    for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+      const int s = it % STAGES;
+      const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+      mbar_wait(&empty[s], ph ^ 1u);
+      const i64 r0 = tile * R;
+      const i64 rows = (n - r0 < R) ? (n - r0) : R;
+      double* dst = tiles + (size_t)s * stage_elems;
+      const double* src = a.X + r0 * (i64)m;
+      if (a.use_tma && rows == R) {
+        if (lane == 0) {
+          const uint32_t bytes = (uint32_t)(stage_elems * sizeof(double));
+          mbar_expect_tx(&full[s], bytes);
+          bulk_g2s(dst, src, bytes, &full[s], pol);
+        }
+      } else {
+        // ragged last tile / unaligned base: warp copy with zero padding of rows >= n
+        const i64 valid = rows * (i64)m;
+        for (i64 i = lane; i < (i64)stage_elems; i += 32) dst[i] = (i < valid) ? ldg_stream(src + i) : 0.0;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
+      }
+    }
+    return;
+  }
+
+  // ===================== consumer threads =====================
+  const int g = tid / TC;
+  const int tt = tid % TC;
+  const int lane = tid & 31;
+  const int wg = tt >> 5;
+
+  double vreg[CPT];
+  double c[CPT];
+#pragma unroll
+  for (int k = 0; k < CPT; k++) {
+    const int j = tt + TC * k;
+    vreg[k] = (MODE != MODE_VM && j < m) ? a.v[j] : 0.0;
+    c[k] = 0.0;
+  }
+
+  int it = 0;
+  for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+    const int s = it % STAGES;
+    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+    const i64 r0 = tile * R + (i64)g * RG;
+
+    double wv[RG];
+    if (MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv)) {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) wv[rr] = (r0 + rr < n) ? __ldg(a.w + r0 + rr) : 0.0;
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) wv[rr] = 0.0;
+    }
+
+    mbar_wait(&full[s], ph);
+    const double* T = tiles + (size_t)s * stage_elems + (size_t)g * RG * m;
+
+    double x[RG][CPT];
+#pragma unroll
+    for (int rr = 0; rr < RG; rr++) {
+#pragma unroll
+      for (int k = 0; k < CPT; k++) {
+        const int j = tt + TC * k;
+        x[rr][k] = (j < m) ? T[rr * m + j] : 0.0;
+      }
+    }
+
+    double t[RG];
+    if (MODE != MODE_VM) {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) {
+        double p = 0.0;
+#pragma unroll
+        for (int k = 0; k < CPT; k++) p = fma(x[rr][k], vreg[k], p);
+        t[rr] = p;
+      }
+    }
+    // every x value has been consumed (or, for VM, is ordered by the release below): free the stage
+    mbar_arrive(&empty[s]);
+
+    if (MODE != MODE_VM) {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) t[rr] = warp_sum(t[rr]);
+      if (NWG > 1) {
+        double* rbuf = red + ((size_t)(it & 1) * G + g) * NWG * RG;
+        if (lane == 0) {
+#pragma unroll
+          for (int rr = 0; rr < RG; rr++) rbuf[wg * RG + rr] = t[rr];
+        }
+        named_bar_sync(1 + g, TC);
+#pragma unroll
+        for (int rr = 0; rr < RG; rr++) {
+          double sacc = 0.0;
+#pragma unroll
+          for (int q = 0; q < NWG; q++) sacc += rbuf[q * RG + rr];
+          t[rr] = sacc;
+        }
+      }
+    }
+
+    if (MODE == MODE_MV) {
+      if (tt == 0) {
+#pragma unroll
+        for (int rr = 0; rr < RG; rr++)
+          if (r0 + rr < n) a.out[r0 + rr] = t[rr];
+      }
+      continue;
+    }
+    if (MODE == MODE_CHAIN) {
+      if (a.ct == SYSML_CHAIN_XtwXv) {
+#pragma unroll
+        for (int rr = 0; rr < RG; rr++) t[rr] *= wv[rr];
+      } else if (a.ct == SYSML_CHAIN_XtXvy) {
+#pragma unroll
+        for (int rr = 0; rr < RG; rr++) t[rr] -= wv[rr];
+      }
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) t[rr] = wv[rr];
+    }
+#pragma unroll
+    for (int k = 0; k < CPT; k++) {
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) c[k] = fma(t[rr], x[rr][k], c[k]);
+    }
+  }
+
+  if (MODE == MODE_MV) return;
+
+  // ---- per-CTA column partials -> scratch; last CTA reduces them in a fixed order ----
+  {
+    double* prow = a.partial + ((size_t)blockIdx.x * G + g) * m;
+#pragma unroll
+    for (int k = 0; k < CPT; k++) {
+      const int j = tt + TC * k;
+      if (j < m) prow[j] = c[k];
+    }
+  }
+  __threadfence();
+  named_bar_sync(15, NTC);
+  __shared__ unsigned int s_ticket;
+  if (tid == 0) s_ticket = atomicAdd(a.counter, 1u);
+  named_bar_sync(15, NTC);
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence();
+  const int nparts = gridDim.x * G;
+  for (int j = tid; j < m; j += NTC) {
+    CompSum acc0, acc1;
+    int b = 0;
+    for (; b + 1 < nparts; b += 2) {
+      acc0.add(__ldcg(a.partial + (size_t)b * m + j));
+      acc1.add(__ldcg(a.partial + (size_t)(b + 1) * m + j));
+    }
+    if (b < nparts) acc0.add(__ldcg(a.partial + (size_t)b * m + j));
+    acc0.add(acc1);
+    a.out[j] = acc0.value();
+  }
+  if (tid == 0) *a.counter = 0u;
+}
+
+template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES>
+int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
+  constexpr int G = NTC / TC;
+  constexpr int R = G * RG;
+  constexpr int NWG = TC / 32;
+  auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES>;
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8;
+  if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowstream: smem %zu too large", smem);
+  SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  a.total_tiles = (a.n + R - 1) / R;
+  const size_t stage_bytes = (size_t)R * a.m * 8;
+  a.use_tma = ((reinterpret_cast<uintptr_t>(a.X) & 15) == 0) && (stage_bytes % 16 == 0) && (stage_bytes < (1u << 20));
+  i64 grid = (i64)ctx->sm_count * ctas_per_sm;
+  if (grid > a.total_tiles) grid = a.total_tiles;
+  if (grid < 1) grid = 1;
+  if (MODE != MODE_MV) {
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)grid * G * a.m * sizeof(double), &ws);
+    if (rc) return rc;
+    a.partial = (double*)ws;
+    a.counter = ctx->counters + 0;
+  }
+  kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
+  SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel");
+  return SYSML_OK;
+}
+
+// Shape -> configuration.  Tile bytes are kept near 32 KB (64 KB for wide rows) so that, with a
+// 3-deep ring and 2 CTAs per SM (1 for wide rows), 128-190 KB per SM are in flight.
+template <int MODE>
+int launch_rowstream(sysml_b200_ctx* ctx, const StreamArgs& a) {
+  const int m = a.m;
+  if (m <= 64) return launch_cfg<MODE, 128, 32, 2, 8, 4>(ctx, a, 2);
+  if (m <= 128) return launch_cfg<MODE, 128, 32, 4, 8, 3>(ctx, a, 2);
+  if (m <= 256) return launch_cfg<MODE, 128, 32, 8, 4, 3>(ctx, a, 2);
+  if (m <= 512) return launch_cfg<MODE, 128, 64, 8, 4, 3>(ctx, a, 2);
+  if (m <= 1024) return launch_cfg<MODE, 128, 128, 8, 4, 3>(ctx, a, 2);
+  if (m <= 2048) return launch_cfg<MODE, 256, 256, 8, 4, 3>(ctx, a, 1);
+  if (m <= 4096) return launch_cfg<MODE, 256, 256, 16, 2, 3>(ctx, a, 1);
+  return SYSML_E_UNSUPPORTED;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Wide-row fallbacks (m > 4096): X is read twice for mmchain (MV then VM).
+// ------------------------------------------------------------------------------------------------
+// one warp per row, grid-stride over rows
+__global__ void mv_wide_kernel(const double* __restrict__ X, const double* __restrict__ v, double* __restrict__ out,
+                               i64 n, i64 m) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 i = warp; i < n; i += nwarps) {
+    const double* row = X + i * m;
+    double p0 = 0.0, p1 = 0.0;
+    i64 j = lane;
+    for (; j + 32 < m; j += 64) {
+      p0 = fma(ldg_stream(row + j), __ldg(v + j), p0);
+      p1 = fma(ldg_stream(row + j + 32), __ldg(v + j + 32), p1);
+    }
+    if (j < m) p0 = fma(ldg_stream(row + j), __ldg(v + j), p0);
+    double p = warp_sum(p0 + p1);
+    if (lane == 0) out[i] = p;
+  }
+}
+
+// out[j] = sum_i y[i] * X[i,j].  grid.x tiles columns (blockDim.x each), grid.y splits rows;
+// row-split partials are summed (compensated, fixed order) by vm_wide_reduce_kernel.
+__global__ void vm_wide_kernel(const double* __restrict__ X, const double* __restrict__ y,
+                               double* __restrict__ partial, i64 n, i64 m) {
+  const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  const i64 rows_per = (n + gridDim.y - 1) / gridDim.y;
+  const i64 rl = (i64)blockIdx.y * rows_per;
+  const i64 ru = (rl + rows_per < n) ? rl + rows_per : n;
+  double c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;
+  i64 i = rl;
+  for (; i + 3 < ru; i += 4) {
+    c0 = fma(__ldg(y + i), ldg_stream(X + i * m + j), c0);
+    c1 = fma(__ldg(y + i + 1), ldg_stream(X + (i + 1) * m + j), c1);
+    c2 = fma(__ldg(y + i + 2), ldg_stream(X + (i + 2) * m + j), c2);
+    c3 = fma(__ldg(y + i + 3), ldg_stream(X + (i + 3) * m + j), c3);
+  }
+  for (; i < ru; i++) c0 = fma(__ldg(y + i), ldg_stream(X + i * m + j), c0);
+  partial[(size_t)blockIdx.y * m + j] = (c0 + c1) + (c2 + c3);
+}
+
+__global__ void vm_wide_reduce_kernel(const double* __restrict__ partial, double* __restrict__ out, int parts, i64 m) {
+  const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  CompSum acc;
+  for (int b = 0; b < parts; b++) acc.add(partial[(size_t)b * m + j]);
+  out[j] = acc.value();
+}
+
+__global__ void apply_weights_kernel(double* __restrict__ t, const double* __restrict__ w, i64 n, int ct) {
+  const i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (ct == SYSML_CHAIN_XtwXv)
+    t[i] *= w[i];
+  else if (ct == SYSML_CHAIN_XtXvy)
+    t[i] -= w[i];
+}
+
+int mv_wide(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m) {
+  const int threads = 256;
+  i64 blocks = (n + 7) / 8;
+  const i64 maxb = (i64)ctx->sm_count * 8;
+  if (blocks > maxb) blocks = maxb;
+  if (blocks < 1) blocks = 1;
+  mv_wide_kernel<<<(unsigned)blocks, threads, 0, ctx->stream>>>(X, v, out, n, m);
+  SYSML_LAUNCH_CHECK(ctx, "mv_wide_kernel");
+  return SYSML_OK;
+}
+
+int vm_wide(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, i64 n, i64 m, size_t ws_offset_bytes) {
+  const int threads = 128;
+  const i64 ctiles = (m + threads - 1) / threads;
+  i64 splits = ((i64)ctx->sm_count * 8 + ctiles - 1) / ctiles;
+  if (splits > (n + 63) / 64) splits = (n + 63) / 64;
+  if (splits < 1) splits = 1;
+  if (splits > 65535) splits = 65535;
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, ws_offset_bytes + (size_t)splits * m * sizeof(double), &ws);
+  if (rc) return rc;
+  double* partial = (double*)((char*)ws + ws_offset_bytes);
+  dim3 grid((unsigned)ctiles, (unsigned)splits);
+  vm_wide_kernel<<<grid, threads, 0, ctx->stream>>>(X, y, partial, n, m);
+  SYSML_LAUNCH_CHECK(ctx, "vm_wide_kernel");
+  vm_wide_reduce_kernel<<<(unsigned)ctiles, threads, 0, ctx->stream>>>(partial, out, (int)splits, m);
+  SYSML_LAUNCH_CHECK(ctx, "vm_wide_reduce_kernel");
+  return SYSML_OK;
+}
+
+}  // namespace
+
+// internal entry points used by matmult.cu as well
+int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m) {
+  if (m <= 4096) {
+    StreamArgs a{};
+    a.X = X; a.v = v; a.w = nullptr; a.out = out; a.n = n; a.m = (int)m; a.ct = 0;
+    return launch_rowstream<MODE_MV>(ctx, a);
+  }
+  return mv_wide(ctx, X, v, out, n, m);
+}
+
+int sysml_dense_vm(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, i64 n, i64 m) {
+  if (m <= 4096) {
+    StreamArgs a{};
+    a.X = X; a.v = nullptr; a.w = y; a.out = out; a.n = n; a.m = (int)m; a.ct = 0;
+    return launch_rowstream<MODE_VM>(ctx, a);
+  }
+  return vm_wide(ctx, X, y, out, n, m, 0);
+}
+
+static int validate_chain(sysml_b200_ctx* ctx, const void* X, const void* v, const void* w, const void* out, i64 n, i64 m, int ct) {
+  if (ct < 0 || ct > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain: unknown chain type %d", ct);
+  if (n < 0 || m < 0) return sysml_set_error(ctx, SYSML_E_DIM, "mmchain: negative dimension (%lld x %lld)", n, m);
+  if (m > 0 && !out) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain: out is null");
+  if (n > 0 && m > 0 && (!X || !v)) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain: X or v is null");
+  if (ct != SYSML_CHAIN_XtXv && n > 0 && !w) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain: chain type %d needs w", ct);
+  if (m > 0x7fffffffLL) return sysml_set_error(ctx, SYSML_E_LIMIT, "mmchain: more than 2^31-1 columns");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_mmchain_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w,
+                                        double* out, int64_t n, int64_t m, int chain_type) {
+  SYSML_ENTER(ctx);
+  int rc = validate_chain(ctx, X, v, w, out, n, m, chain_type);
+  if (rc) return rc;
+  if (m == 0) return SYSML_OK;
+  if (n == 0) {  // empty X: result is the zero vector (LibMatrixMult.java:245-248)
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (m <= 4096) {
+    StreamArgs a{};
+    a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type;
+    return launch_rowstream<MODE_CHAIN>(ctx, a);
+  }
+  // wide rows: t = X v ; t = w*t | t-w ; out = t(X) t   (X read twice)
+  void* ws = nullptr;
+  const size_t tbytes = (((size_t)n * sizeof(double)) + 255) & ~(size_t)255;
+  // reserve the partial area up front so the second workspace call cannot move the block
+  {
+    const i64 ctiles = (m + 127) / 128;
+    i64 splits = ((i64)ctx->sm_count * 8 + ctiles - 1) / ctiles;
+    if (splits > (n + 63) / 64) splits = (n + 63) / 64;
+    if (splits < 1) splits = 1;
+    rc = sysml_workspace(ctx, tbytes + (size_t)splits * m * sizeof(double), &ws);
+    if (rc) return rc;
+  }
+  double* t = (double*)ws;
+  rc = mv_wide(ctx, X, v, t, n, m);
+  if (rc) return rc;
+  if (chain_type != SYSML_CHAIN_XtXv) {
+    apply_weights_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(t, w, n, chain_type);
+    SYSML_LAUNCH_CHECK(ctx, "apply_weights_kernel");
+  }
+  return vm_wide(ctx, X, t, out, n, m, tbytes);
+}
+
+extern "C" int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const double* X, const double* h_v,
+                                                const double* h_w, const double* d_w, double* h_out, int64_t n,
+                                                int64_t m, int chain_type) {
+  SYSML_ENTER(ctx);
+  if (!h_v || !h_out) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_hostvec: h_v or h_out is null");
+  if (n < 0 || m < 0) return sysml_set_error(ctx, SYSML_E_DIM, "mmchain_hostvec: negative dimension");
+  const bool need_w = chain_type != SYSML_CHAIN_XtXv;
+  if (need_w && !h_w && !d_w) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_hostvec: chain type %d needs w", chain_type);
+  const bool copy_w = need_w && !d_w;
+  // small device staging vectors owned by the context (v, out, and w when it comes from the host)
+  const size_t mpad = (size_t)((m + 31) / 32) * 32;
+  const size_t need = (2 * mpad + (copy_w ? (size_t)n : 0)) * sizeof(double);
+  if (ctx->vec_stage_bytes < need) {
+    SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->vec_stage) SYSML_CUDA(ctx, cudaFree(ctx->vec_stage));
+    ctx->vec_stage = nullptr;
+    ctx->vec_stage_bytes = 0;
+    SYSML_CUDA(ctx, cudaMalloc(&ctx->vec_stage, need));
+    ctx->vec_stage_bytes = need;
+  }
+  double* s_dev = (double*)ctx->vec_stage;
+  double* d_v = s_dev;
+  double* d_out = s_dev + mpad;
+  double* d_wbuf = d_out + mpad;
+  void* pin = nullptr;
+  int rc = sysml_pinned(ctx, (size_t)(2 * m) * sizeof(double), &pin);
+  if (rc) return rc;
+  double* p_v = (double*)pin;
+  double* p_out = p_v + m;
+  memcpy(p_v, h_v, (size_t)m * sizeof(double));
+  SYSML_CUDA(ctx, cudaMemcpyAsync(d_v, p_v, (size_t)m * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  if (copy_w) SYSML_CUDA(ctx, cudaMemcpyAsync(d_wbuf, h_w, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  rc = sysml_b200_mmchain_dense(ctx, X, d_v, need_w ? (copy_w ? d_wbuf : d_w) : nullptr, d_out, n, m, chain_type);
+  if (rc) return rc;
+  SYSML_CUDA(ctx, cudaMemcpyAsync(p_out, d_out, (size_t)m * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(h_out, p_out, (size_t)m * sizeof(double));
+  return SYSML_OK;
+}

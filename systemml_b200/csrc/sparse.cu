@@ -1,0 +1,694 @@
+// sparse.cu -- CSR kernels: SpMV, SpMM (CSR x dense), t(CSR) x dense, sparse mmchain, sparse tsmm,
+// sparse aggregates, dense<->CSR conversion and nnz counting.
+//
+// CSR layout = CSRPointer.java:76-100: double val[nnz], int32 rowptr[rows+1], int32 colind[nnz], 0-based.
+//
+// Reference semantics: LibMatrixMult.matrixMultSparseDense (LibMatrixMult.java:1170-1395),
+// matrixMultChainSparse (:1655-1684), matrixMultTransposeSelfSparse (:1839-1960);
+// LibMatrixAgg s_ua* (LibMatrixAgg.java:2137-2195, 2426-2614); GPU twins cusparseDcsrmv / Dcsrmm2
+// (LibMatrixCuMatMult.java:313-341), cusparseDnnz / Ddense2csr / Dcsr2dense (GPUObject.java:199-245,508).
+//
+// SpMV: L lanes cooperate on one row, L chosen from mean nnz/row (2..32) -- "vector-per-row" for long
+// rows, "sub-warp per row" for short ones; consecutive rows sit in consecutive lane groups so val/colind
+// reads of a warp are contiguous.  HBM-bound: 12*nnz + 4*(rows+1) + 8*cols + 8*rows bytes.
+// Scatter-type outputs (t(X)%*%y, sparse mmchain, sparse tsmm, column sums) use fp64 RED atomics into
+// an L2-resident output; their summation order is not fixed (run-to-run differences ~1 ulp).
+#include <math.h>
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ double jmax(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) & __double_as_longlong(b));
+  return (a >= b) ? a : b;
+}
+__device__ __forceinline__ double jmin(double a, double b) {
+  if (a != a) return a;
+  if (b != b) return b;
+  if (a == 0.0 && b == 0.0) return __longlong_as_double(__double_as_longlong(a) | __double_as_longlong(b));
+  return (a <= b) ? a : b;
+}
+template <int L>
+__device__ __forceinline__ double group_sum(double v) {
+#pragma unroll
+  for (int o = L >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+inline int pick_lanes(i64 nnz, i64 rows) {
+  const double mean = rows > 0 ? (double)nnz / (double)rows : 0.0;
+  int L = 2;
+  while (L < 32 && L < mean) L <<= 1;
+  return L;
+}
+inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
+  const i64 rows_per_block = (threads / 32) * (32 / L);
+  i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
+  const i64 cap = (i64)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+// MODE 0: out[r] = A[r,:] . v                      (SpMV)
+// MODE 1: c[col] += (w-adjusted A[r,:].v) * A[r,col] (sparse mmchain), ct as in SYSML_CHAIN_*
+// MODE 2: c[col] += y[r] * A[r,col]                 (t(A) %*% y)
+template <int L, int MODE>
+__global__ void __launch_bounds__(256) csr_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                      const double* __restrict__ va, const double* __restrict__ v,
+                                                      const double* __restrict__ w, double* __restrict__ out, i64 rows, int ct) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (L - 1);
+  constexpr int RPW = 32 / L;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 base = warp * RPW; base < rows; base += nwarps * RPW) {
+    const i64 r = base + lane / L;
+    int lo = 0, hi = 0;
+    if (r < rows) {
+      lo = __ldg(rp + r);
+      hi = __ldg(rp + r + 1);
+    }
+    double p = 0.0;
+    if (MODE != 2) {
+      for (int k = lo + sub; k < hi; k += L) p = fma(ldg_stream(va + k), __ldg(v + __ldg(ci + k)), p);
+      p = group_sum<L>(p);
+    }
+    if (MODE == 0) {
+      if (r < rows && sub == 0) out[r] = p;
+      continue;
+    }
+    if (r >= rows || hi == lo) continue;
+    double t;
+    if (MODE == 1) {
+      const double wr = (ct != SYSML_CHAIN_XtXv) ? __ldg(w + r) : 0.0;
+      if (ct == SYSML_CHAIN_XtwXv && wr == 0.0) continue;  // LibMatrixMult.java:1667
+      t = (ct == SYSML_CHAIN_XtwXv) ? p * wr : ((ct == SYSML_CHAIN_XtXvy) ? p - wr : p);
+    } else {
+      t = __ldg(w + r);
+    }
+    if (t == 0.0) continue;  // LibMatrixMult.java:1680 / VM skips zero entries of the left vector (:978)
+    for (int k = lo + sub; k < hi; k += L) atomicAdd(out + __ldg(ci + k), t * va[k]);
+  }
+}
+
+// C[r, 0:n) = sum_k A[r,k] * B[k, 0:n): one warp per row, lanes over output columns (n <= 64: two per lane)
+template <int NPL>
+__global__ void __launch_bounds__(256) csr_spmm_skinny_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                              const double* __restrict__ va, const double* __restrict__ B,
+                                                              double* __restrict__ C, i64 rows, int n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = __ldg(rp + r), hi = __ldg(rp + r + 1);
+    double acc[NPL];
+#pragma unroll
+    for (int q = 0; q < NPL; q++) acc[q] = 0.0;
+    for (int k0 = lo; k0 < hi; k0 += 32) {
+      // lanes fetch 32 non-zeros at once, then broadcast them one by one
+      const int kk = k0 + lane;
+      const double a_l = (kk < hi) ? ldg_stream(va + kk) : 0.0;
+      const int c_l = (kk < hi) ? __ldg(ci + kk) : 0;
+      const int cnt = (hi - k0 < 32) ? (hi - k0) : 32;
+      for (int q = 0; q < cnt; q++) {
+        const double a = __shfl_sync(0xffffffffu, a_l, q);
+        const i64 brow = (i64)__shfl_sync(0xffffffffu, c_l, q) * n;
+#pragma unroll
+        for (int u = 0; u < NPL; u++) {
+          const int j = lane + 32 * u;
+          if (j < n) acc[u] = fma(a, __ldg(B + brow + j), acc[u]);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < NPL; u++) {
+      const int j = lane + 32 * u;
+      if (j < n) C[r * n + j] = acc[u];
+    }
+  }
+}
+
+// general n: grid.y tiles the output columns by 128 (4 per lane)
+__global__ void __launch_bounds__(256) csr_spmm_wide_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                            const double* __restrict__ va, const double* __restrict__ B,
+                                                            double* __restrict__ C, i64 rows, i64 n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  const i64 j0 = (i64)blockIdx.y * 128;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = __ldg(rp + r), hi = __ldg(rp + r + 1);
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int k = lo; k < hi; k++) {
+      const double a = __ldg(va + k);
+      const i64 brow = (i64)__ldg(ci + k) * n;
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const i64 j = j0 + lane + 32 * u;
+        if (j < n) acc[u] = fma(a, __ldg(B + brow + j), acc[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const i64 j = j0 + lane + 32 * u;
+      if (j < n) C[r * n + j] = acc[u];
+    }
+  }
+}
+
+// C (a_cols x n) += t(A) %*% B : row r of A scatters a * B[r, :] into C[col, :]
+__global__ void __launch_bounds__(256) csr_tspmm_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                        const double* __restrict__ va, const double* __restrict__ B,
+                                                        double* __restrict__ C, i64 rows, i64 n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = __ldg(rp + r), hi = __ldg(rp + r + 1);
+    for (int k = lo; k < hi; k++) {
+      const double a = __ldg(va + k);
+      if (a == 0.0) continue;
+      double* crow = C + (i64)__ldg(ci + k) * n;
+      for (i64 j = lane; j < n; j += 32) atomicAdd(crow + j, a * __ldg(B + r * n + j));
+    }
+  }
+}
+
+// sparse tsmm LEFT: for each row, C[ci[i], ci[j]] += v[i]*v[j] for j >= i (upper triangle)
+__global__ void __launch_bounds__(256) csr_tsmm_left_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                            const double* __restrict__ va, double* __restrict__ C, i64 rows, i64 n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = __ldg(rp + r), hi = __ldg(rp + r + 1);
+    for (int i = lo; i < hi; i++) {
+      const double a = __ldg(va + i);
+      if (a == 0.0) continue;
+      double* crow = C + (i64)__ldg(ci + i) * n;
+      for (int j = i + lane; j < hi; j += 32) atomicAdd(crow + __ldg(ci + j), a * __ldg(va + j));
+    }
+  }
+}
+
+// mirror upper -> lower and count non-zeros (diagonal 1, off-diagonal 2): copyUpperToLowerTriangle
+__global__ void mirror_count_kernel(double* __restrict__ C, i64 n, unsigned long long* __restrict__ nnz) {
+  const i64 total = n * n;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  unsigned long long cnt = 0;
+  for (i64 idx = (i64)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+    const i64 i = idx / n, j = idx - i * n;
+    if (j < i) continue;
+    const double v = C[idx];
+    if (j > i) C[j * n + i] = v;
+    if (v != 0.0) cnt += (j == i) ? 1ull : 2ull;
+  }
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(nnz, cnt);
+}
+
+// ---------------- nnz / conversions ----------------
+__global__ void count_nnz_kernel(const double* __restrict__ X, i64 len, unsigned long long* __restrict__ out) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  unsigned long long cnt = 0;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += stride) cnt += (ldg_stream(X + i) != 0.0) ? 1ull : 0ull;
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(out, cnt);
+}
+
+// one warp per row: rowcnt[r] = #non-zeros
+__global__ void row_nnz_kernel(const double* __restrict__ X, i64 rows, i64 cols, int* __restrict__ rowcnt) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    int cnt = 0;
+    for (i64 j = lane; j < cols; j += 32) cnt += (ldg_stream(X + r * cols + j) != 0.0) ? 1 : 0;
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) rowcnt[r + 1] = cnt;
+  }
+}
+
+// single-block exclusive scan of rowcnt[1..rows] into rowptr (rowptr[0] = 0); 64-bit running total
+__global__ void __launch_bounds__(1024) scan_rowptr_kernel(int* __restrict__ rowptr, i64 rows, unsigned long long* __restrict__ total) {
+  __shared__ unsigned long long wsum[32];
+  __shared__ unsigned long long carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) {
+    carry = 0;
+    rowptr[0] = 0;
+  }
+  __syncthreads();
+  for (i64 base = 0; base < rows; base += 1024) {
+    const i64 i = base + threadIdx.x;
+    unsigned long long v = (i < rows) ? (unsigned long long)rowptr[i + 1] : 0ull;
+    unsigned long long x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      unsigned long long s = wsum[lane];
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += y;
+      }
+      wsum[lane] = s;
+    }
+    __syncthreads();
+    const unsigned long long incl = x + (warp ? wsum[warp - 1] : 0ull) + carry;
+    if (i < rows) rowptr[i + 1] = (int)incl;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+// one warp per row: ordered compaction with ballot
+__global__ void fill_csr_kernel(const double* __restrict__ X, i64 rows, i64 cols, const int* __restrict__ rowptr,
+                                int* __restrict__ ci, double* __restrict__ va) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    int pos = rowptr[r];
+    for (i64 j0 = 0; j0 < cols; j0 += 32) {
+      const i64 j = j0 + lane;
+      const double x = (j < cols) ? ldg_stream(X + r * cols + j) : 0.0;
+      const unsigned m = __ballot_sync(0xffffffffu, x != 0.0);
+      if (x != 0.0) {
+        const int off = __popc(m & ((1u << lane) - 1));
+        ci[pos + off] = (int)j;
+        va[pos + off] = x;
+      }
+      pos += __popc(m);
+    }
+  }
+}
+
+__global__ void csr_to_dense_kernel(const int* __restrict__ rp, const int* __restrict__ ci, const double* __restrict__ va,
+                                    i64 rows, i64 cols, double* __restrict__ X) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = rp[r], hi = rp[r + 1];
+    for (int k = lo + lane; k < hi; k += 32) X[r * cols + ci[k]] = va[k];
+  }
+}
+
+// ---------------- sparse aggregates ----------------
+// per-row: sum / sumsq (op 0/1), max / min (2/3) with the implicit-zero correction, rowIndexMax/Min (4/5)
+__global__ void __launch_bounds__(256) csr_agg_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+                                                          const double* __restrict__ va, i64 rows, i64 cols, int op,
+                                                          double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 r = warp; r < rows; r += nwarps) {
+    const int lo = rp[r], hi = rp[r + 1];
+    const int alen = hi - lo;
+    if (op <= 1) {
+      CompSum s;
+      for (int k = lo + lane; k < hi; k += 32) {
+        const double x = va[k];
+        s.add(op == 1 ? __dmul_rn(x, x) : x);
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        CompSum t;
+        t.hi = __shfl_xor_sync(0xffffffffu, s.hi, o);
+        t.lo = __shfl_xor_sync(0xffffffffu, s.lo, o);
+        s.add(t);
+      }
+      if (lane == 0) out[r] = (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
+    } else if (op <= 3) {
+      double t = (op == 2) ? -CUDART_INF : CUDART_INF;
+      for (int k = lo + lane; k < hi; k += 32) t = (op == 2) ? jmax(t, va[k]) : jmin(t, va[k]);
+      for (int o = 16; o > 0; o >>= 1) {
+        const double u = __shfl_xor_sync(0xffffffffu, t, o);
+        t = (op == 2) ? jmax(t, u) : jmin(t, u);
+      }
+      if (alen < cols) t = (op == 2) ? jmax(t, 0.0) : jmin(t, 0.0);
+      if (lane == 0) out[r] = t;
+    } else {
+      // LibMatrixAgg.s_uarimxx / s_uarimin (LibMatrixAgg.java:2536-2614)
+      const bool ismax = (op == 4);
+      double best = ismax ? -CUDART_INF : CUDART_INF;
+      int idx = -1;  // position within the row
+      for (int k = lo + lane; k < hi; k += 32) {
+        const double x = va[k];
+        const bool take = ismax ? (x >= best) : (x <= best);
+        idx = take ? (k - lo) : idx;
+        best = take ? x : best;
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        const bool other = (oi >= 0) && ((idx < 0) || (ismax ? (ob > best) : (ob < best)) || (ob == best && oi > idx));
+        best = other ? ob : best;
+        idx = other ? oi : idx;
+      }
+      double res;
+      if (alen == 0) {
+        res = (double)cols;  // empty row: last column, value 0 (:2559-2563)
+      } else {
+        res = (idx >= 0) ? (double)ci[lo + idx] + 1.0 : 0.0;
+        const double bv = (idx >= 0) ? best : CUDART_NAN;
+        const bool zero_wins = ismax ? (0.0 > bv) : (0.0 < bv);  // strictly: Builtin.execute(0,v)==1
+        if (alen < cols && zero_wins) {
+          // last column that holds an implicit zero: walk back while the tail is densely occupied
+          // (all lanes compute the same answer; rows are short or the walk is short)
+          i64 ix = cols - 1;
+          for (int j = hi - 1; j >= lo; j--, ix--)
+            if (ci[j] != ix) break;
+          res = (double)(ix + 1);
+        }
+      }
+      if (lane == 0) out[r] = res;
+    }
+  }
+}
+
+// ALL over the value array (sum, sumsq): reuse the dense kernel through the public entry; max/min here
+__global__ void csr_agg_all_minmax_kernel(const double* __restrict__ va, i64 nnz, int ismax, double* __restrict__ partial) {
+  double t = ismax ? -CUDART_INF : CUDART_INF;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) t = ismax ? jmax(t, va[i]) : jmin(t, va[i]);
+  for (int o = 16; o > 0; o >>= 1) {
+    const double u = __shfl_xor_sync(0xffffffffu, t, o);
+    t = ismax ? jmax(t, u) : jmin(t, u);
+  }
+  __shared__ double sh[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) sh[warp] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int q = 1; q < (int)(blockDim.x >> 5); q++) t = ismax ? jmax(t, sh[q]) : jmin(t, sh[q]);
+    partial[blockIdx.x] = t;
+  }
+}
+__global__ void csr_agg_all_minmax_finish(const double* __restrict__ partial, int nparts, int ismax, int has_zero, double* __restrict__ out) {
+  if (threadIdx.x || blockIdx.x) return;
+  double t = ismax ? -CUDART_INF : CUDART_INF;
+  for (int i = 0; i < nparts; i++) t = ismax ? jmax(t, partial[i]) : jmin(t, partial[i]);
+  if (has_zero) t = ismax ? jmax(t, 0.0) : jmin(t, 0.0);
+  out[0] = t;
+}
+
+// per-column sum/sumsq via atomics into a zeroed output; max/min with counts
+__global__ void csr_agg_col_sum_kernel(const int* __restrict__ ci, const double* __restrict__ va, i64 nnz, int sq, double* __restrict__ out) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+    const double x = va[k];
+    atomicAdd(out + ci[k], sq ? x * x : x);
+  }
+}
+__device__ __forceinline__ void atomic_minmax_double(double* addr, double v, int ismax) {
+  unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+  unsigned long long old = *a, assumed;
+  do {
+    assumed = old;
+    const double cur = __longlong_as_double((long long)assumed);
+    const double nv = ismax ? jmax(cur, v) : jmin(cur, v);
+    if (__double_as_longlong(nv) == (long long)assumed) break;
+    old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(nv));
+  } while (assumed != old);
+}
+__global__ void csr_agg_col_minmax_kernel(const int* __restrict__ ci, const double* __restrict__ va, i64 nnz, int ismax,
+                                          double* __restrict__ out, int* __restrict__ cnt) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+    atomic_minmax_double(out + ci[k], va[k], ismax);
+    atomicAdd(cnt + ci[k], 1);
+  }
+}
+__global__ void csr_agg_col_minmax_finish(double* __restrict__ out, const int* __restrict__ cnt, i64 cols, i64 rows, int ismax) {
+  const i64 j = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= cols) return;
+  if ((i64)cnt[j] < rows) out[j] = ismax ? jmax(out[j], 0.0) : jmin(out[j], 0.0);
+}
+
+inline unsigned flat_grid(sysml_b200_ctx* ctx, i64 items, int threads) {
+  i64 blocks = (items + threads - 1) / threads;
+  const i64 cap = (i64)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+inline unsigned warp_rows_grid(sysml_b200_ctx* ctx, i64 rows) {
+  i64 blocks = (rows + 7) / 8;
+  const i64 cap = (i64)ctx->sm_count * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (unsigned)blocks;
+}
+
+template <int MODE>
+int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const double* va, const double* v, const double* w,
+                   double* out, i64 rows, i64 nnz, int ct) {
+  const int L = pick_lanes(nnz, rows);
+  const unsigned g = rows_grid(ctx, rows, L, 256);
+  switch (L) {
+    case 2: csr_row_kernel<2, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+    case 4: csr_row_kernel<4, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+    case 8: csr_row_kernel<8, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+    case 16: csr_row_kernel<16, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+    default: csr_row_kernel<32, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+  }
+  SYSML_LAUNCH_CHECK(ctx, "csr_row_kernel");
+  return SYSML_OK;
+}
+
+int fetch_nnz(sysml_b200_ctx* ctx, const int32_t* rowptr, i64 rows, i64* nnz) {
+  int last = 0;
+  SYSML_CUDA(ctx, cudaMemcpyAsync(&last, rowptr + rows, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *nnz = last;
+  return SYSML_OK;
+}
+
+}  // namespace
+
+extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols, int op, int dir, double* out);
+
+extern "C" int sysml_b200_mmchain_csr(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                      const double* v, const double* w, double* out, int64_t n, int64_t m, int chain_type) {
+  SYSML_ENTER(ctx);
+  if (chain_type < 0 || chain_type > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_csr: unknown chain type %d", chain_type);
+  if (n < 0 || m < 0) return sysml_set_error(ctx, SYSML_E_DIM, "mmchain_csr: negative dimension");
+  if (m == 0) return SYSML_OK;
+  if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_csr: out is null");
+  SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
+  if (n == 0) return SYSML_OK;
+  if (!rowptr || !v) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_csr: null pointer");
+  if (chain_type != SYSML_CHAIN_XtXv && !w) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_csr: chain type %d needs w", chain_type);
+  i64 nnz = 0;
+  int rc = fetch_nnz(ctx, rowptr, n, &nnz);
+  if (rc) return rc;
+  if (nnz == 0) return SYSML_OK;
+  return launch_csr_row<1>(ctx, rowptr, colind, val, v, w, out, n, nnz, chain_type);
+}
+
+extern "C" int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                                            const double* val, const double* B, double* C, int64_t a_rows, int64_t a_cols,
+                                            int64_t b_rows, int64_t b_cols, int trans_a) {
+  SYSML_ENTER(ctx);
+  if (a_rows < 0 || a_cols < 0 || b_rows < 0 || b_cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_csr_dense: negative dimension");
+  const i64 inner = trans_a ? a_rows : a_cols;
+  const i64 m = trans_a ? a_cols : a_rows;
+  if (inner != b_rows) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_csr_dense: inner dimensions %lld vs %lld", (long long)inner, (long long)b_rows);
+  const i64 n = b_cols;
+  if (m * n == 0) return SYSML_OK;
+  if (!C) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_csr_dense: C is null");
+  if (inner == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(m * n) * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (!rowptr || !B) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_csr_dense: null pointer");
+  i64 nnz = 0;
+  int rc = fetch_nnz(ctx, rowptr, a_rows, &nnz);
+  if (rc) return rc;
+  if (trans_a) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(m * n) * sizeof(double), ctx->stream));
+    if (nnz == 0) return SYSML_OK;
+    if (n == 1) return launch_csr_row<2>(ctx, rowptr, colind, val, nullptr, B, C, a_rows, nnz, 0);
+    csr_tspmm_kernel<<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, n);
+    SYSML_LAUNCH_CHECK(ctx, "csr_tspmm_kernel");
+    return SYSML_OK;
+  }
+  if (n == 1) return launch_csr_row<0>(ctx, rowptr, colind, val, B, nullptr, C, a_rows, nnz, 0);
+  if (n <= 32) {
+    csr_spmm_skinny_kernel<1><<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, (int)n);
+  } else if (n <= 64) {
+    csr_spmm_skinny_kernel<2><<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, (int)n);
+  } else {
+    const i64 ctiles = (n + 127) / 128;
+    if (ctiles > 65535) return sysml_set_error(ctx, SYSML_E_LIMIT, "matmult_csr_dense: more than 8M output columns");
+    i64 gx = (a_rows + 7) / 8;
+    const i64 cap = ((i64)ctx->sm_count * 16 + ctiles - 1) / ctiles;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    csr_spmm_wide_kernel<<<dim3((unsigned)gx, (unsigned)ctiles), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, n);
+  }
+  SYSML_LAUNCH_CHECK(ctx, "csr_spmm kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_tsmm_csr_left(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                        double* out, int64_t rows, int64_t cols, int64_t* h_nnz_out) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "tsmm_csr: negative dimension");
+  if (h_nnz_out) *h_nnz_out = 0;
+  if (cols == 0) return SYSML_OK;
+  if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm_csr: out is null");
+  SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)(cols * cols) * sizeof(double), ctx->stream));
+  if (rows == 0) return SYSML_OK;
+  if (!rowptr) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm_csr: rowptr is null");
+  csr_tsmm_left_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(rowptr, colind, val, out, rows, cols);
+  SYSML_LAUNCH_CHECK(ctx, "csr_tsmm_left_kernel");
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, 256, &ws);
+  if (rc) return rc;
+  unsigned long long* d_nnz = (unsigned long long*)ws;
+  SYSML_CUDA(ctx, cudaMemsetAsync(d_nnz, 0, sizeof(unsigned long long), ctx->stream));
+  mirror_count_kernel<<<flat_grid(ctx, cols * cols, 256), 256, 0, ctx->stream>>>(out, cols, d_nnz);
+  SYSML_LAUNCH_CHECK(ctx, "mirror_count_kernel");
+  if (h_nnz_out) {
+    unsigned long long h = 0;
+    SYSML_CUDA(ctx, cudaMemcpyAsync(&h, d_nnz, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    *h_nnz_out = (int64_t)h;
+  }
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_count_nnz(sysml_b200_ctx* ctx, const double* X, int64_t len, int64_t* h_nnz) {
+  SYSML_ENTER(ctx);
+  if (len < 0 || !h_nnz || (len > 0 && !X)) return sysml_set_error(ctx, SYSML_E_INVALID, "count_nnz: bad arguments");
+  *h_nnz = 0;
+  if (len == 0) return SYSML_OK;
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, 256, &ws);
+  if (rc) return rc;
+  unsigned long long* d = (unsigned long long*)ws;
+  SYSML_CUDA(ctx, cudaMemsetAsync(d, 0, sizeof(unsigned long long), ctx->stream));
+  count_nnz_kernel<<<flat_grid(ctx, len, 256), 256, 0, ctx->stream>>>(X, len, d);
+  SYSML_LAUNCH_CHECK(ctx, "count_nnz_kernel");
+  unsigned long long h = 0;
+  SYSML_CUDA(ctx, cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *h_nnz = (int64_t)h;
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_dense_to_csr(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols, int32_t* rowptr,
+                                       int32_t* colind, double* val, int64_t* h_nnz) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0 || !rowptr || !h_nnz) return sysml_set_error(ctx, SYSML_E_INVALID, "dense_to_csr: bad arguments");
+  if (rows > 0 && cols > 0 && !X) return sysml_set_error(ctx, SYSML_E_INVALID, "dense_to_csr: X is null");
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, 256, &ws);
+  if (rc) return rc;
+  unsigned long long* d_total = (unsigned long long*)ws;
+  SYSML_CUDA(ctx, cudaMemsetAsync(rowptr, 0, (size_t)(rows + 1) * sizeof(int), ctx->stream));
+  if (rows > 0 && cols > 0) {
+    row_nnz_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(X, rows, cols, rowptr);
+    SYSML_LAUNCH_CHECK(ctx, "row_nnz_kernel");
+  }
+  scan_rowptr_kernel<<<1, 1024, 0, ctx->stream>>>(rowptr, rows, d_total);
+  SYSML_LAUNCH_CHECK(ctx, "scan_rowptr_kernel");
+  unsigned long long h = 0;
+  SYSML_CUDA(ctx, cudaMemcpyAsync(&h, d_total, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *h_nnz = (int64_t)h;
+  if (h >= (1ull << 31)) return sysml_set_error(ctx, SYSML_E_LIMIT, "dense_to_csr: nnz %llu does not fit int32 row pointers", h);
+  if (colind && val && h > 0) {
+    fill_csr_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(X, rows, cols, rowptr, colind, val);
+    SYSML_LAUNCH_CHECK(ctx, "fill_csr_kernel");
+  }
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                       int64_t rows, int64_t cols, double* X) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "csr_to_dense: negative dimension");
+  if (rows * cols == 0) return SYSML_OK;
+  if (!rowptr || !X) return sysml_set_error(ctx, SYSML_E_INVALID, "csr_to_dense: null pointer");
+  SYSML_CUDA(ctx, cudaMemsetAsync(X, 0, (size_t)(rows * cols) * sizeof(double), ctx->stream));
+  csr_to_dense_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, X);
+  SYSML_LAUNCH_CHECK(ctx, "csr_to_dense_kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_agg_unary_csr(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                        int64_t rows, int64_t cols, int op, int dir, double* out) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "agg_unary_csr: negative dimension");
+  if (dir < 0 || dir > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary_csr: bad direction %d", dir);
+  if (!out || !rowptr) return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary_csr: null pointer");
+  if (rows * cols == 0) return sysml_set_error(ctx, SYSML_E_DIM, "agg_unary_csr: empty input");
+  i64 nnz = 0;
+  int rc = fetch_nnz(ctx, rowptr, rows, &nnz);
+  if (rc) return rc;
+  const bool is_sum = (op == SYSML_AGG_SUM || op == SYSML_AGG_SUMSQ);
+  const bool is_mm = (op == SYSML_AGG_MAX || op == SYSML_AGG_MIN);
+  const bool is_idx = (op == SYSML_AGG_MAXINDEX || op == SYSML_AGG_MININDEX);
+  if (!is_sum && !is_mm && !is_idx) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "agg_unary_csr: opcode %d on CSR input", op);
+  if (is_idx && dir != SYSML_DIR_ROW) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row");
+  if (dir == SYSML_DIR_ROW) {
+    csr_agg_row_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out);
+    SYSML_LAUNCH_CHECK(ctx, "csr_agg_row_kernel");
+    return SYSML_OK;
+  }
+  if (dir == SYSML_DIR_ALL) {
+    if (is_sum) {
+      if (nnz == 0) {
+        SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, sizeof(double), ctx->stream));
+        return SYSML_OK;
+      }
+      return sysml_b200_agg_unary_dense(ctx, val, 1, nnz, op, SYSML_DIR_ALL, out);  // s_uakp: sum over values()
+    }
+    const int nparts = (int)flat_grid(ctx, nnz > 0 ? nnz : 1, 256);
+    void* ws = nullptr;
+    rc = sysml_workspace(ctx, (size_t)nparts * sizeof(double), &ws);
+    if (rc) return rc;
+    csr_agg_all_minmax_kernel<<<nparts, 256, 0, ctx->stream>>>(val, nnz, op == SYSML_AGG_MAX, (double*)ws);
+    SYSML_LAUNCH_CHECK(ctx, "csr_agg_all_minmax_kernel");
+    csr_agg_all_minmax_finish<<<1, 32, 0, ctx->stream>>>((double*)ws, nparts, op == SYSML_AGG_MAX, nnz < rows * cols, out);
+    SYSML_LAUNCH_CHECK(ctx, "csr_agg_all_minmax_finish");
+    return SYSML_OK;
+  }
+  // COL
+  if (is_sum) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)cols * sizeof(double), ctx->stream));
+    if (nnz == 0) return SYSML_OK;
+    csr_agg_col_sum_kernel<<<flat_grid(ctx, nnz, 256), 256, 0, ctx->stream>>>(colind, val, nnz, op == SYSML_AGG_SUMSQ, out);
+    SYSML_LAUNCH_CHECK(ctx, "csr_agg_col_sum_kernel");
+    return SYSML_OK;
+  }
+  void* ws = nullptr;
+  rc = sysml_workspace(ctx, (size_t)cols * sizeof(int), &ws);
+  if (rc) return rc;
+  SYSML_CUDA(ctx, cudaMemsetAsync(ws, 0, (size_t)cols * sizeof(int), ctx->stream));
+  {
+    // initialise the output with -+Inf
+    rc = sysml_b200_fill(ctx, out, cols, op == SYSML_AGG_MAX ? -HUGE_VAL : HUGE_VAL);
+    if (rc) return rc;
+  }
+  if (nnz > 0) {
+    csr_agg_col_minmax_kernel<<<flat_grid(ctx, nnz, 256), 256, 0, ctx->stream>>>(colind, val, nnz, op == SYSML_AGG_MAX, out, (int*)ws);
+    SYSML_LAUNCH_CHECK(ctx, "csr_agg_col_minmax_kernel");
+  }
+  csr_agg_col_minmax_finish<<<(unsigned)((cols + 255) / 256), 256, 0, ctx->stream>>>(out, (int*)ws, cols, rows, op == SYSML_AGG_MAX);
+  SYSML_LAUNCH_CHECK(ctx, "csr_agg_col_minmax_finish");
+  return SYSML_OK;
+}

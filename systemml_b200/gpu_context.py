@@ -1,0 +1,216 @@
+"""Host-side mirror of the reference's device-state types, over the C ABI.
+
+  GPUContext  <- J/runtime/instructions/gpu/context/GPUContext.java:93-184 (+ GPUMemoryManager.java:157-322)
+  GPUObject   <- .../context/GPUObject.java:52-99, 528-607, 755-946
+  CSRPointer  <- .../context/CSRPointer.java:76-100
+
+(J/ = src/main/java/org/apache/sysml/).  Names and argument meaning follow the reference so the
+parity tests read like its own GPU tests.  Everything numeric happens in the native library.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import native
+
+
+class GPUContext:
+    """One device + one stream.  Not thread-safe (GPUContext.java:181-184)."""
+
+    def __init__(self, device=0, stream=None):
+        self._lib = native.load()
+        h = C.c_void_p()
+        if stream is None:
+            rc = self._lib.sysml_b200_ctx_create(device, C.byref(h))
+        else:
+            rc = self._lib.sysml_b200_ctx_create_on_stream(device, C.c_void_p(stream), C.byref(h))
+        native.check(None, rc)
+        self.handle = h
+        self.device = device
+
+    # -- lifecycle -------------------------------------------------------------------------------
+    def destroy(self):
+        if self.handle:
+            self._lib.sysml_b200_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.destroy()
+
+    def call(self, name, *args):
+        rc = getattr(self._lib, name)(self.handle, *args)
+        native.check(self.handle, rc)
+
+    def sync(self):
+        self.call("sysml_b200_sync")
+
+    @property
+    def stream(self):
+        return self._lib.sysml_b200_ctx_stream(self.handle)
+
+    @property
+    def sm_count(self):
+        return self._lib.sysml_b200_ctx_sm_count(self.handle)
+
+    def launch_count(self):
+        return self._lib.sysml_b200_launch_count(self.handle)
+
+    def getAvailableMemory(self):
+        """GPUContext.getAvailableMemory (GPUContext.java:218-226)."""
+        f, t = C.c_int64(), C.c_int64()
+        self.call("sysml_b200_mem_info", C.byref(f), C.byref(t))
+        return f.value, t.value
+
+    # -- memory (GPUMemoryManager.malloc / free) ---------------------------------------------------
+    def allocate(self, nbytes):
+        p = C.c_void_p()
+        self.call("sysml_b200_malloc", int(nbytes), C.byref(p))
+        return p.value or 0
+
+    def cudaFreeHelper(self, ptr):
+        if ptr:
+            self.call("sysml_b200_free", C.c_void_p(ptr))
+
+    def h2d(self, dptr, host):
+        host = np.ascontiguousarray(host)
+        self.call("sysml_b200_h2d", C.c_void_p(dptr), host.ctypes.data_as(C.c_void_p), host.nbytes)
+
+    def d2h(self, dptr, shape, dtype=np.float64):
+        out = np.empty(shape, dtype=dtype)
+        if out.nbytes:
+            self.call("sysml_b200_d2h", out.ctypes.data_as(C.c_void_p), C.c_void_p(dptr), out.nbytes)
+        return out
+
+    # -- timers ------------------------------------------------------------------------------------
+    def timer_start(self):
+        self.call("sysml_b200_timer_start")
+
+    def timer_stop_ms(self):
+        ms = C.c_double()
+        self.call("sysml_b200_timer_stop_ms", C.byref(ms))
+        return ms.value
+
+    # -- convenience constructors ------------------------------------------------------------------
+    def dense(self, host):
+        return GPUObject.from_host_dense(self, host)
+
+    def csr(self, rowptr, colind, val, shape):
+        return GPUObject.from_host_csr(self, rowptr, colind, val, shape)
+
+    def empty(self, rows, cols):
+        return GPUObject.allocate_dense(self, rows, cols)
+
+    def rand(self, rows, cols, seed, lo=-1.0, hi=1.0, offset=0):
+        o = GPUObject.allocate_dense(self, rows, cols)
+        self.call("sysml_b200_rand_uniform", C.c_void_p(o.ptr), rows * cols, seed, offset, lo, hi)
+        return o
+
+
+class CSRPointer:
+    """val / rowPtr / colInd device arrays + nnz (CSRPointer.java:76-100); int32 indices, 0-based."""
+
+    def __init__(self, gctx, nnz, rows):
+        self.gctx = gctx
+        self.nnz = int(nnz)
+        self.rows = int(rows)
+        self.val = gctx.allocate(max(self.nnz, 1) * 8)
+        self.rowPtr = gctx.allocate((self.rows + 1) * 4)
+        self.colInd = gctx.allocate(max(self.nnz, 1) * 4)
+
+    def deallocate(self):
+        for p in (self.val, self.rowPtr, self.colInd):
+            self.gctx.cudaFreeHelper(p)
+        self.val = self.rowPtr = self.colInd = 0
+
+
+class GPUObject:
+    """Device state of one matrix: dense row-major double* or a CSRPointer (GPUObject.java:52-99)."""
+
+    def __init__(self, gctx, rows, cols):
+        self.gctx = gctx
+        self.rows = int(rows)
+        self.cols = int(cols)
+        self.ptr = 0          # jcudaDenseMatrixPtr
+        self.csr = None       # jcudaSparseMatrixPtr
+        self.dirty = False
+        self.owns = True
+
+    # -- constructors ----------------------------------------------------------------------------
+    @staticmethod
+    def allocate_dense(gctx, rows, cols):
+        o = GPUObject(gctx, rows, cols)
+        o.ptr = gctx.allocate(max(rows * cols, 1) * 8)
+        return o
+
+    @staticmethod
+    def from_host_dense(gctx, host):
+        """copyFromHostToDevice, dense branch (GPUObject.java:755-870)."""
+        host = np.ascontiguousarray(host, dtype=np.float64)
+        if host.ndim == 1:
+            host = host.reshape(-1, 1)
+        o = GPUObject.allocate_dense(gctx, host.shape[0], host.shape[1])
+        if host.size:
+            gctx.h2d(o.ptr, host)
+        return o
+
+    @staticmethod
+    def from_host_csr(gctx, rowptr, colind, val, shape):
+        """copyFromHostToDevice, CSR branch (GPUObject.java:785-838; CSRPointer.copyToDevice :153-213)."""
+        rows, cols = shape
+        nnz = int(rowptr[-1])
+        if nnz >= 2**31:
+            raise native.NativeError(native.E_LIMIT, "CSR with nnz >= 2^31 (int32 row pointers, CSRPointer.java:76-100)")
+        o = GPUObject(gctx, rows, cols)
+        o.csr = CSRPointer(gctx, nnz, rows)
+        gctx.h2d(o.csr.rowPtr, np.ascontiguousarray(rowptr, dtype=np.int32))
+        if nnz:
+            gctx.h2d(o.csr.colInd, np.ascontiguousarray(colind, dtype=np.int32))
+            gctx.h2d(o.csr.val, np.ascontiguousarray(val, dtype=np.float64))
+        return o
+
+    @staticmethod
+    def wrap(gctx, ptr, rows, cols):
+        """Borrow a device pointer owned by someone else (e.g. a torch tensor)."""
+        o = GPUObject(gctx, rows, cols)
+        o.ptr = int(ptr)
+        o.owns = False
+        return o
+
+    # -- state -----------------------------------------------------------------------------------
+    def isSparse(self):
+        return self.csr is not None
+
+    @property
+    def shape(self):
+        return (self.rows, self.cols)
+
+    def getNnz(self):
+        """GPUObject.getNnz (GPUObject.java:672-691): exact count on the device."""
+        if self.csr is not None:
+            return self.csr.nnz
+        n = C.c_int64()
+        self.gctx.call("sysml_b200_count_nnz", C.c_void_p(self.ptr), self.rows * self.cols, C.byref(n))
+        return n.value
+
+    def to_host(self):
+        """copyFromDeviceToHost (GPUObject.java:879-946).  Dense -> ndarray; CSR -> (rowptr, colind, val)."""
+        if self.csr is None:
+            return self.gctx.d2h(self.ptr, (self.rows, self.cols))
+        rp = self.gctx.d2h(self.csr.rowPtr, (self.rows + 1,), np.int32)
+        ci = self.gctx.d2h(self.csr.colInd, (self.csr.nnz,), np.int32)
+        va = self.gctx.d2h(self.csr.val, (self.csr.nnz,), np.float64)
+        return rp, ci, va
+
+    def clearData(self):
+        """GPUObject.clearData (GPUObject.java:948-970)."""
+        if self.owns and self.ptr:
+            self.gctx.cudaFreeHelper(self.ptr)
+        self.ptr = 0
+        if self.csr is not None:
+            self.csr.deallocate()
+            self.csr = None
+
+    free = clearData

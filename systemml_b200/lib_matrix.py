@@ -1,0 +1,220 @@
+"""LibMatrixB200 -- host-side mirror of LibMatrixCUDA / LibMatrixCuMatMult over the C ABI.
+
+Function names, argument order and error behaviour follow the reference's static methods
+(J/runtime/matrix/data/LibMatrixCUDA.java, LibMatrixCuMatMult.java) so that a GPU instruction
+class can call these in place of the JCuda-based ones:
+
+  matmult                 <- LibMatrixCuMatMult.matmult            (LibMatrixCuMatMult.java:139-229)
+  matmultTSMM             <- LibMatrixCUDA.matmultTSMM             (LibMatrixCUDA.java:477-524)
+  mmchain                 <- (new) CP twin MatrixBlock.chainMatrixMultOperations (MatrixBlock.java:3491-3518)
+  unaryAggregate          <- LibMatrixCUDA.unaryAggregate          (LibMatrixCUDA.java:573-894)
+  matrixMatrixArithmetic  <- LibMatrixCUDA.matrixMatrixArithmetic  (LibMatrixCUDA.java:1245-1270)
+  matrixScalarArithmetic  <- LibMatrixCUDA.matrixScalarArithmetic  (LibMatrixCUDA.java:1126-1195)
+  axpy                    <- LibMatrixCUDA.axpy                    (LibMatrixCUDA.java:2295-2350)
+  transpose               <- LibMatrixCUDA.transpose               (LibMatrixCUDA.java:1723-1729)
+
+Outputs are freshly allocated GPUObjects (getDenseMatrixOutputForGPUInstruction, LibMatrixCUDA.java:2474);
+scalar aggregates come back as Python floats (ec.setScalarOutput, LibMatrixCUDA.java:692-693).
+"""
+import ctypes as C
+
+from . import native
+from .gpu_context import GPUObject
+
+XtXv, XtwXv, XtXvy = 0, 1, 2
+CHAIN_TYPES = {"XtXv": XtXv, "XtwXv": XtwXv, "XtXvy": XtXvy}
+
+AGG_SUM, AGG_SUMSQ, AGG_MAX, AGG_MIN, AGG_MAXINDEX, AGG_MININDEX, AGG_MEAN, AGG_PROD, AGG_VAR = range(9)
+DIR_ALL, DIR_ROW, DIR_COL = 0, 1, 2
+
+# opcode -> (agg op, direction): GPUInstructionParser.java:111-133 plus the uarimax/uarimin this library adds
+AGG_OPCODES = {
+    "uak+": (AGG_SUM, DIR_ALL), "uark+": (AGG_SUM, DIR_ROW), "uack+": (AGG_SUM, DIR_COL),
+    "uasqk+": (AGG_SUMSQ, DIR_ALL), "uarsqk+": (AGG_SUMSQ, DIR_ROW), "uacsqk+": (AGG_SUMSQ, DIR_COL),
+    "uamax": (AGG_MAX, DIR_ALL), "uarmax": (AGG_MAX, DIR_ROW), "uacmax": (AGG_MAX, DIR_COL),
+    "uamin": (AGG_MIN, DIR_ALL), "uarmin": (AGG_MIN, DIR_ROW), "uacmin": (AGG_MIN, DIR_COL),
+    "uarimax": (AGG_MAXINDEX, DIR_ROW), "uarimin": (AGG_MININDEX, DIR_ROW),
+    "uamean": (AGG_MEAN, DIR_ALL), "uarmean": (AGG_MEAN, DIR_ROW), "uacmean": (AGG_MEAN, DIR_COL),
+    "ua*": (AGG_PROD, DIR_ALL), "uar*": (AGG_PROD, DIR_ROW), "uac*": (AGG_PROD, DIR_COL),
+    "uavar": (AGG_VAR, DIR_ALL), "uarvar": (AGG_VAR, DIR_ROW), "uacvar": (AGG_VAR, DIR_COL),
+}
+
+# LibMatrixCUDA.getBinaryOp numbering (LibMatrixCUDA.java:1551-1575)
+BINARY_OPS = {
+    "+": 0, "-": 1, "*": 2, "/": 3, "^": 4, "<": 5, "<=": 6, ">": 7, ">=": 8, "==": 9, "!=": 10,
+    "min": 11, "max": 12, "&&": 13, "||": 14, "1-*": 15, "-nz": 16, "%%": 17, "%/%": 18,
+}
+UNARY_OPS = {"exp": 0, "sqrt": 1, "round": 2, "abs": 3, "log": 4, "floor": 5, "ceil": 6, "sign": 7,
+             "sigmoid": 8, "sin": 9, "cos": 10, "tan": 11, "tanh": 12}
+BCAST_NONE, BCAST_COL, BCAST_ROW = 0, 1, 2
+
+
+def _p(x):
+    return C.c_void_p(x if x else None)
+
+
+def _dim_error(msg):
+    raise native.NativeError(native.E_DIM, msg)
+
+
+# ------------------------------------------------------------------------------------------------
+def mmchain(gCtx, instName, X, v, w, ctype):
+    """t(X)%*%(X%*%v) | t(X)%*%(w*(X%*%v)) | t(X)%*%((X%*%v)-w); output m x 1 dense."""
+    ct = CHAIN_TYPES[ctype] if isinstance(ctype, str) else int(ctype)
+    n, m = X.rows, X.cols
+    if v.rows * v.cols != m:
+        _dim_error("mmchain: v has %d cells, X has %d columns" % (v.rows * v.cols, m))
+    if ct != XtXv and (w is None or w.rows * w.cols != n):
+        _dim_error("mmchain: w must have %d cells" % n)
+    out = GPUObject.allocate_dense(gCtx, m, 1)
+    wp = w.ptr if (w is not None and ct != XtXv) else 0
+    if X.isSparse():
+        gCtx.call("sysml_b200_mmchain_csr", _p(X.csr.rowPtr), _p(X.csr.colInd), _p(X.csr.val), _p(v.ptr), _p(wp),
+                  _p(out.ptr), n, m, ct)
+    else:
+        gCtx.call("sysml_b200_mmchain_dense", _p(X.ptr), _p(v.ptr), _p(wp), _p(out.ptr), n, m, ct)
+    return out
+
+
+def mmchain_hostvec(gCtx, X, h_v, h_w, ctype, d_w=None):
+    """Host-vector entry: X resident on the device, v/w/out on the host (NativeHelper call shape)."""
+    import numpy as np
+    ct = CHAIN_TYPES[ctype] if isinstance(ctype, str) else int(ctype)
+    h_v = np.ascontiguousarray(h_v, dtype=np.float64).reshape(-1)
+    out = np.empty(X.cols, dtype=np.float64)
+    hw = None
+    if h_w is not None and d_w is None:
+        h_w = np.ascontiguousarray(h_w, dtype=np.float64).reshape(-1)
+        hw = h_w.ctypes.data_as(C.c_void_p)
+    gCtx.call("sysml_b200_mmchain_dense_hostvec", _p(X.ptr), h_v.ctypes.data_as(C.c_void_p), hw,
+              _p(d_w.ptr if d_w is not None else 0), out.ctypes.data_as(C.c_void_p), X.rows, X.cols, ct)
+    return out
+
+
+def matmultTSMM(gCtx, instName, left, isLeftTransposed=True, with_nnz=False):
+    """t(X)%*%X (isLeftTransposed) or X%*%t(X)."""
+    dim = left.cols if isLeftTransposed else left.rows
+    out = GPUObject.allocate_dense(gCtx, dim, dim)
+    nnz = C.c_int64(-1)
+    pn = C.byref(nnz) if with_nnz else None
+    if left.isSparse():
+        if not isLeftTransposed:
+            raise native.NativeError(native.E_UNSUPPORTED, "tsmm RIGHT on CSR input")
+        gCtx.call("sysml_b200_tsmm_csr_left", _p(left.csr.rowPtr), _p(left.csr.colInd), _p(left.csr.val),
+                  _p(out.ptr), left.rows, left.cols, pn)
+    else:
+        gCtx.call("sysml_b200_tsmm_dense", _p(left.ptr), _p(out.ptr), left.rows, left.cols,
+                  1 if isLeftTransposed else 0, pn)
+    return (out, nnz.value) if with_nnz else out
+
+
+def matmult(gCtx, instName, left, right, isLeftTransposed=False, isRightTransposed=False):
+    """C = op(A) %*% op(B) (dense x dense, CSR x dense)."""
+    m = left.cols if isLeftTransposed else left.rows
+    k1 = left.rows if isLeftTransposed else left.cols
+    k2 = right.cols if isRightTransposed else right.rows
+    n = right.rows if isRightTransposed else right.cols
+    if k1 != k2:
+        _dim_error("matmult: incompatible dimensions %d vs %d" % (k1, k2))
+    if right.isSparse():
+        raise native.NativeError(native.E_UNSUPPORTED, "matmult with sparse right-hand side")
+    out = GPUObject.allocate_dense(gCtx, m, n)
+    if left.isSparse():
+        if isRightTransposed:
+            raise native.NativeError(native.E_UNSUPPORTED, "CSR x t(dense)")
+        gCtx.call("sysml_b200_matmult_csr_dense", _p(left.csr.rowPtr), _p(left.csr.colInd), _p(left.csr.val),
+                  _p(right.ptr), _p(out.ptr), left.rows, left.cols, right.rows, right.cols,
+                  int(isLeftTransposed))
+    else:
+        gCtx.call("sysml_b200_matmult_dense", _p(left.ptr), _p(right.ptr), _p(out.ptr), left.rows, left.cols,
+                  right.rows, right.cols, int(isLeftTransposed), int(isRightTransposed))
+    return out
+
+
+def unaryAggregate(gCtx, instName, in1, opcode):
+    """opcode: 'uak+', 'uark+', 'uack+', 'uarimax', ... ; scalar for ALL, GPUObject otherwise."""
+    op, d = AGG_OPCODES[opcode] if isinstance(opcode, str) else opcode
+    rows, cols = in1.rows, in1.cols
+    orows, ocols = (1, 1) if d == DIR_ALL else ((rows, 1) if d == DIR_ROW else (1, cols))
+    out = GPUObject.allocate_dense(gCtx, orows, ocols)
+    if in1.isSparse():
+        gCtx.call("sysml_b200_agg_unary_csr", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val), rows, cols,
+                  op, d, _p(out.ptr))
+    else:
+        gCtx.call("sysml_b200_agg_unary_dense", _p(in1.ptr), rows, cols, op, d, _p(out.ptr))
+    if d == DIR_ALL:
+        val = float(out.to_host()[0, 0])
+        out.free()
+        return val
+    return out
+
+
+def _bcast(A, B):
+    if (B.rows, B.cols) == (A.rows, A.cols):
+        return BCAST_NONE
+    if B.cols == 1 and B.rows == A.rows:
+        return BCAST_COL
+    if B.rows == 1 and B.cols == A.cols:
+        return BCAST_ROW
+    _dim_error("cellwise: %dx%d vs %dx%d" % (A.rows, A.cols, B.rows, B.cols))
+
+
+def matrixMatrixArithmetic(gCtx, instName, in1, in2, op):
+    """C = A op B with column/row-vector broadcast of B (also the relational ops)."""
+    opc = BINARY_OPS[op] if isinstance(op, str) else int(op)
+    out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
+    gCtx.call("sysml_b200_binary_mm", _p(in1.ptr), _p(in2.ptr), _p(out.ptr), in1.rows, in1.cols, _bcast(in1, in2), opc)
+    return out
+
+
+matrixMatrixRelational = matrixMatrixArithmetic
+
+
+def matrixScalarArithmetic(gCtx, instName, in1, scalar, op, scalarLeft=False):
+    opc = BINARY_OPS[op] if isinstance(op, str) else int(op)
+    out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
+    gCtx.call("sysml_b200_binary_ms", _p(in1.ptr), float(scalar), _p(out.ptr), in1.rows * in1.cols, opc, int(scalarLeft))
+    return out
+
+
+def axpy(gCtx, instName, in1, in2, constant):
+    """out = in1 + constant*in2 ('+*'; pass -constant for '-*'), in2 may be a row/col vector."""
+    out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
+    gCtx.call("sysml_b200_axpy", _p(in1.ptr), _p(in2.ptr), float(constant), _p(out.ptr), in1.rows, in1.cols, _bcast(in1, in2))
+    return out
+
+
+def unaryOp(gCtx, instName, in1, op):
+    opc = UNARY_OPS[op] if isinstance(op, str) else int(op)
+    out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
+    gCtx.call("sysml_b200_unary", _p(in1.ptr), _p(out.ptr), in1.rows * in1.cols, opc)
+    return out
+
+
+def transpose(gCtx, instName, in1):
+    out = GPUObject.allocate_dense(gCtx, in1.cols, in1.rows)
+    gCtx.call("sysml_b200_transpose", _p(in1.ptr), _p(out.ptr), in1.rows, in1.cols)
+    return out
+
+
+def denseToSparse(gCtx, in1):
+    """GPUObject.denseToSparse (GPUObject.java:199-245): two-phase nnz count + fill."""
+    from .gpu_context import CSRPointer
+    rows, cols = in1.rows, in1.cols
+    tmp_rp = gCtx.allocate((rows + 1) * 4)
+    nnz = C.c_int64()
+    gCtx.call("sysml_b200_dense_to_csr", _p(in1.ptr), rows, cols, _p(tmp_rp), None, None, C.byref(nnz))
+    out = GPUObject(gCtx, rows, cols)
+    out.csr = CSRPointer(gCtx, nnz.value, rows)
+    gCtx.call("sysml_b200_dense_to_csr", _p(in1.ptr), rows, cols, _p(out.csr.rowPtr), _p(out.csr.colInd),
+              _p(out.csr.val), C.byref(nnz))
+    gCtx.cudaFreeHelper(tmp_rp)
+    return out
+
+
+def sparseToDense(gCtx, in1):
+    """GPUObject.sparseToDense (GPUObject.java:508-526)."""
+    out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
+    gCtx.call("sysml_b200_csr_to_dense", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val), in1.rows, in1.cols,
+              _p(out.ptr))
+    return out

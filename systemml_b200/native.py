@@ -1,0 +1,94 @@
+"""ctypes binding of libsystemml_b200.so (include/sysml_b200.h).
+
+This is the only place Python touches the native library.  There is NO fallback: if the shared
+library is missing or a symbol is absent, importing fails loudly.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libsystemml_b200.so")
+
+OK, E_INVALID, E_DIM, E_OOM, E_CUDA, E_UNSUPPORTED, E_LIMIT = 0, -1, -2, -3, -4, -5, -6
+
+vp, i64, u64, ci, dbl = C.c_void_p, C.c_int64, C.c_uint64, C.c_int, C.c_double
+pvp, pi64, pint, pdbl = C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_double)
+
+# name -> (restype, argtypes): mirrors include/sysml_b200.h declaration by declaration
+SIGNATURES = {
+    "sysml_b200_device_count": (ci, [pint]),
+    "sysml_b200_version": (C.c_char_p, []),
+    "sysml_b200_ctx_create": (ci, [ci, pvp]),
+    "sysml_b200_ctx_create_on_stream": (ci, [ci, vp, pvp]),
+    "sysml_b200_ctx_destroy": (ci, [vp]),
+    "sysml_b200_sync": (ci, [vp]),
+    "sysml_b200_last_error": (C.c_char_p, [vp]),
+    "sysml_b200_ctx_stream": (vp, [vp]),
+    "sysml_b200_ctx_device": (ci, [vp]),
+    "sysml_b200_ctx_sm_count": (ci, [vp]),
+    "sysml_b200_mem_info": (ci, [vp, pi64, pi64]),
+    "sysml_b200_launch_count": (i64, [vp]),
+    "sysml_b200_malloc": (ci, [vp, i64, pvp]),
+    "sysml_b200_free": (ci, [vp, vp]),
+    "sysml_b200_memset0": (ci, [vp, vp, i64]),
+    "sysml_b200_h2d": (ci, [vp, vp, vp, i64]),
+    "sysml_b200_d2h": (ci, [vp, vp, vp, i64]),
+    "sysml_b200_d2d": (ci, [vp, vp, vp, i64]),
+    "sysml_b200_host_alloc": (ci, [vp, i64, pvp]),
+    "sysml_b200_host_free": (ci, [vp, vp]),
+    "sysml_b200_timer_start": (ci, [vp]),
+    "sysml_b200_timer_stop_ms": (ci, [vp, pdbl]),
+    "sysml_b200_mmchain_dense": (ci, [vp, vp, vp, vp, vp, i64, i64, ci]),
+    "sysml_b200_mmchain_csr": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, ci]),
+    "sysml_b200_mmchain_dense_hostvec": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci]),
+    "sysml_b200_tsmm_dense": (ci, [vp, vp, vp, i64, i64, ci, pi64]),
+    "sysml_b200_tsmm_csr_left": (ci, [vp, vp, vp, vp, vp, i64, i64, pi64]),
+    "sysml_b200_matmult_dense": (ci, [vp, vp, vp, vp, i64, i64, i64, i64, ci, ci]),
+    "sysml_b200_matmult_csr_dense": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, ci]),
+    "sysml_b200_agg_unary_dense": (ci, [vp, vp, i64, i64, ci, ci, vp]),
+    "sysml_b200_agg_unary_csr": (ci, [vp, vp, vp, vp, i64, i64, ci, ci, vp]),
+    "sysml_b200_binary_mm": (ci, [vp, vp, vp, vp, i64, i64, ci, ci]),
+    "sysml_b200_binary_ms": (ci, [vp, vp, dbl, vp, i64, ci, ci]),
+    "sysml_b200_axpy": (ci, [vp, vp, vp, dbl, vp, i64, i64, ci]),
+    "sysml_b200_unary": (ci, [vp, vp, vp, i64, ci]),
+    "sysml_b200_fill": (ci, [vp, vp, i64, dbl]),
+    "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),
+    "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),
+    "sysml_b200_dense_to_csr": (ci, [vp, vp, i64, i64, vp, vp, vp, pi64]),
+    "sysml_b200_csr_to_dense": (ci, [vp, vp, vp, vp, i64, i64, vp]),
+    "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),
+}
+
+
+class NativeError(RuntimeError):
+    """The Python face of DMLRuntimeException for a failed native call."""
+
+    def __init__(self, code, msg):
+        super().__init__("sysml_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Loads the shared library and binds EVERY symbol the header declares (raises if one is missing)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(
+            "%s not found: build it with `python -m systemml_b200.build` (there is no CPU fallback)" % SO_PATH)
+    lib = C.CDLL(SO_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(ctx_handle, rc):
+    if rc != 0:
+        msg = load().sysml_b200_last_error(ctx_handle)
+        raise NativeError(rc, msg.decode("utf-8", "replace") if msg else "?")
