@@ -1,0 +1,437 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (driver contract: one JSON line on rank 0).
+
+Workload (BASELINE.json configs[1]): the CG inner iteration of GLM / LinearRegCG on a dense FP64
+X of 10,000,000 x 1000 (80 GB), row-sharded over the N GPUs of one box (strong scaling: the total is
+fixed; per-GPU rows = 10M / N in whole 1000-row blocks).  One "step" = one CG iteration:
+
+    q = t(X) %*% (w * (X %*% p))            <- mmchain XtwXv, ONE pass over the shard (the hot kernel)
+    [N > 1]  all-reduce(q) over NCCL / NVLink (m = 1000 doubles)
+    pq = t(p) %*% q ; a = nr2 / pq ; beta += a*p ; r += a*q ; nr2' = t(r) %*% r ; p = -r + (nr2'/nr2)*p
+
+all on the device through the C ABI of include/sysml_b200.h (no host synchronisation inside a step).
+
+  value   : CG iterations per second, whole job, inputs resident in HBM (CUDA events, max over ranks)
+  e2e     : the same iteration driven from HOST buffers through the reference-facing call shape: every
+            step copies p from pinned host memory to the device, runs mmchain (+ all-reduce), reads q back
+            to the host and does the m-vector CG algebra on the host, as SystemML's CP instructions do.
+            X stays resident on the device across steps, exactly as GPUObject caches it between
+            instructions (GPUObject.acquireDeviceRead copies host->device only when not resident,
+            GPUObject.java:528-545); e2e.cold additionally times the first-touch upload of X from pinned
+            host memory on a bounded row sample.
+  roofline: mmchain kernel, algorithmic bytes 8nm+16m+8n per launch / mean launch time (CUDA events around
+            every launch inside the timed region) against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline / --impl reference: the CPU restatement of LibMatrixMult.matrixMultChain (oracle/) with all
+            host threads on a bounded row sample (the JVM reference cannot run in this image).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_ROWS, N_COLS = 10_000_000, 1000
+METRIC = "cg_iterations_per_sec (GLM/LinearRegCG inner iteration: mmchain XtwXv on dense FP64 10M x 1000)"
+UNIT = "iters/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=N_ROWS)
+    ap.add_argument("--cols", type=int, default=N_COLS)
+    ap.add_argument("--no-tsmm", action="store_true", help="skip the auxiliary tsmm measurement")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def alg_bytes_mmchain(n, m, weighted=True):
+    return 8.0 * n * m + 16.0 * m + (8.0 * n if weighted else 0.0)
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks / throttle sampling during the timed region (pynvml, falls back to nvidia-smi)
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index):
+        self.index = index
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._t = None
+
+    def _loop(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            names = {
+                getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            while not self._stop.is_set():
+                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+                time.sleep(0.02)
+        except Exception:
+            try:
+                out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
+                                               "--format=csv,noheader,nounits"], text=True)
+                a, b = out.strip().split(",")
+                self.samples.append(int(a))
+                self.max_mhz = int(b)
+            except Exception:
+                pass
+
+    def start(self):
+        self._t = threading.Thread(target=self._loop, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=2)
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's mmchain (restatement of LibMatrixMult.matrixMultChain) on a bounded sample
+# --------------------------------------------------------------------------------------------------
+def cpu_cg_iterations(n_total, m, target_seconds=12.0, max_rows=2_000_000, steps=None):
+    """Times CG iterations (mmchain XtwXv + m-vector algebra) on the host cores on the first `rows` rows of the
+    same synthetic X; returns (iters/s scaled to n_total rows, cores, sample description, seconds per sample iter)."""
+    import numpy as np
+    from oracle import oracle as O
+    k = O.num_threads()
+    rows = min(max_rows, n_total)
+    X = O.rand_uniform(rows * m, seed=1).reshape(rows, m)
+    w = O.rand_uniform(rows, seed=4, lo=0.0, hi=1.0)
+    p = O.rand_uniform(m, seed=2)
+    r = -p.copy()
+    beta = np.zeros(m)
+    nr2 = float(r @ r)
+    t0 = time.perf_counter()
+    O.mmchain_dense(X, p, w, O.XtwXv, k)  # warm-up (page faults, thread pool)
+    warm = time.perf_counter() - t0
+    reps = steps if steps else max(3, min(50, int(target_seconds / max(warm, 1e-3))))
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        q = O.mmchain_dense(X, p, w, O.XtwXv, k)
+        pq = float(p @ q)
+        a = nr2 / pq if pq != 0 else 0.0
+        beta += a * p
+        r += a * q
+        nr2n = float(r @ r)
+        p = -r + (nr2n / nr2) * p if nr2 != 0 else -r
+        nr2 = nr2n
+        times.append(time.perf_counter() - t0)
+        if not np.isfinite(nr2) or nr2 == 0:
+            p = O.rand_uniform(m, seed=2)
+            r = -p.copy()
+            nr2 = float(r @ r)
+    times.sort()
+    med = times[len(times) // 2]
+    scaled = (rows / float(n_total)) / med
+    sample = "first %d of %d rows x %d cols, %d timed iterations, median; scaled to the full row count" % (rows, n_total, m, reps)
+    return scaled, k, sample, med, rows
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    t_start = time.perf_counter()
+    val, cores, sample, med, rows = cpu_cg_iterations(args.rows, args.cols, steps=max(args.steps, 1) + 0, max_rows=1_000_000)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1000.0 / val if val > 0 else None, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1])" % (args.rows, args.cols),
+                   "arm": "CPU restatement of LibMatrixMult.matrixMultChain (oracle/, k = all host threads); the JVM reference cannot run here"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "sample_gbs": alg_bytes_mmchain(rows, args.cols) / med / 1e9},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.perf_counter() - t_start,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import ctypes as C
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from systemml_b200 import GPUContext, GPUObject, LibMatrixB200 as L
+    from systemml_b200.sharding import row_shard
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    n, m = args.rows, args.cols
+    r0, r1 = row_shard(n, world, rank)
+    nloc = r1 - r0
+    # all library work is queued on torch's current stream so that torch events and NCCL see it in order
+    stream = torch.cuda.current_stream()
+    g = GPUContext(local_rank, stream=stream.cuda_stream)
+
+    def tensor(*shape):
+        return torch.empty(*shape, dtype=torch.float64, device=dev)
+
+    def obj(t, rows, cols):
+        return GPUObject.wrap(g, t.data_ptr(), rows, cols)
+
+    tX = tensor(max(nloc, 1) * m)
+    X = obj(tX, nloc, m)
+    g.call("sysml_b200_rand_uniform", C.c_void_p(X.ptr), nloc * m, 1, r0 * m, -1.0, 1.0)
+    tw = tensor(max(nloc, 1))
+    w = obj(tw, nloc, 1)
+    g.call("sysml_b200_rand_uniform", C.c_void_p(w.ptr), nloc, 4, r0, 0.0, 1.0)
+    vecs = {k: tensor(m) for k in ("p", "q", "r", "beta", "tmp")}
+    scal = {k: tensor(1) for k in ("pq", "a", "nr2", "nr2n", "b")}
+    P, Q, R, BETA, TMP = (obj(vecs[k], m, 1) for k in ("p", "q", "r", "beta", "tmp"))
+    PQ, A_, NR2, NR2N, B_ = (obj(scal[k], 1, 1) for k in ("pq", "a", "nr2", "nr2n", "b"))
+
+    def p_(o):
+        return C.c_void_p(o.ptr)
+
+    def reset_state():
+        g.call("sysml_b200_rand_uniform", p_(P), m, 2, 0, -1.0, 1.0)
+        g.call("sysml_b200_binary_ms", p_(P), -1.0, p_(R), m, L.BINARY_OPS["*"], 0)  # r = -p
+        g.call("sysml_b200_fill", p_(BETA), m, 0.0)
+        g.call("sysml_b200_matmult_dense", p_(R), p_(R), p_(NR2), 1, m, m, 1, 0, 0)   # nr2 = t(r) %*% r
+
+    ev_pairs = []
+
+    def cg_step(record):
+        if record:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+        g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+        if record:
+            e1.record(stream)
+            ev_pairs.append((e0, e1))
+        if world > 1:
+            dist.all_reduce(vecs["q"])
+        g.call("sysml_b200_matmult_dense", p_(P), p_(Q), p_(PQ), 1, m, m, 1, 0, 0)               # pq = t(p) %*% q
+        g.call("sysml_b200_binary_mm", p_(NR2), p_(PQ), p_(A_), 1, 1, 0, L.BINARY_OPS["/"])     # a = nr2 / pq
+        g.call("sysml_b200_binary_mm", p_(P), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+        g.call("sysml_b200_binary_mm", p_(BETA), p_(TMP), p_(BETA), m, 1, 0, L.BINARY_OPS["+"])  # beta += a*p
+        g.call("sysml_b200_binary_mm", p_(Q), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+        g.call("sysml_b200_binary_mm", p_(R), p_(TMP), p_(R), m, 1, 0, L.BINARY_OPS["+"])        # r += a*q
+        g.call("sysml_b200_matmult_dense", p_(R), p_(R), p_(NR2N), 1, m, m, 1, 0, 0)             # nr2' = t(r) %*% r
+        g.call("sysml_b200_binary_mm", p_(NR2N), p_(NR2), p_(B_), 1, 1, 0, L.BINARY_OPS["/"])   # b = nr2'/nr2
+        g.call("sysml_b200_binary_mm", p_(P), p_(B_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+        g.call("sysml_b200_binary_mm", p_(TMP), p_(R), p_(P), m, 1, 0, L.BINARY_OPS["-"])        # p = b*p - r
+        g.call("sysml_b200_d2d", p_(NR2), p_(NR2N), 8)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- resident run: `value` ----------------
+    reset_state()
+    for _ in range(max(args.warmup, 3)):
+        cg_step(False)
+    reset_state()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    launches0 = g.launch_count()
+    t_evt0, t_evt1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_evt0.record(stream)
+    for _ in range(args.steps):
+        cg_step(True)
+    t_evt1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    launches = g.launch_count() - launches0
+    total_ms = t_evt0.elapsed_time(t_evt1)
+    kern_ms = sum(a.elapsed_time(b) for a, b in ev_pairs) / max(len(ev_pairs), 1)
+    if world > 1:
+        t = torch.tensor([total_ms, kern_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, kern_ms = float(t[0]), float(t[1])
+    ms_per_step = total_ms / args.steps
+    value = 1000.0 / ms_per_step
+    finite = bool(torch.isfinite(vecs["beta"]).all().item())
+
+    # ---------------- host-driven run: `e2e` ----------------
+    e2e = None
+    if not args.no_e2e:
+        hp = torch.empty(m, dtype=torch.float64).pin_memory()
+        hq = torch.empty(m, dtype=torch.float64).pin_memory()
+        p_np, q_np = hp.numpy(), hq.numpy()
+        rng = np.random.default_rng(2)
+
+        def host_state():
+            p_np[:] = rng.uniform(-1, 1, m)
+            r = -p_np.copy()
+            return r, np.zeros(m), float(r @ r)
+
+        def e2e_step(state):
+            r, beta, nr2 = state
+            g.call("sysml_b200_h2d", p_(P), C.c_void_p(hp.data_ptr()), 8 * m)          # host -> device: p
+            g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+            if world > 1:
+                dist.all_reduce(vecs["q"])
+            g.call("sysml_b200_d2h", C.c_void_p(hq.data_ptr()), p_(Q), 8 * m)          # device -> host: q (syncs)
+            pq = float(p_np @ q_np)
+            a = nr2 / pq if pq != 0 else 0.0
+            beta += a * p_np
+            r += a * q_np
+            nr2n = float(r @ r)
+            p_np[:] = -r + (nr2n / nr2) * p_np
+            return r, beta, nr2n
+
+        st = host_state()
+        for _ in range(max(args.warmup, 3)):
+            st = e2e_step(st)
+        st = host_state()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            st = e2e_step(st)
+        barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1000.0 / args.steps
+        if world > 1:
+            t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t[0])
+        e2e = {"value": 1000.0 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": 8 * m, "d2h_bytes_per_step": 8 * m,
+               "ms_per_step": e2e_ms,
+               "note": "X and w resident on the device across steps (GPUObject cache semantics); p in / q out through pinned host memory every step"}
+        # cold first touch: upload a bounded row sample of X from pinned host memory, then one iteration on it
+        if rank == 0:
+            rows_c = min(nloc, 500_000)
+            hx = torch.empty(rows_c * m, dtype=torch.float64).pin_memory()
+            hx.uniform_(-1, 1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            g.call("sysml_b200_h2d", p_(X), C.c_void_p(hx.data_ptr()), 8 * rows_c * m)
+            g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), rows_c, m, L.XtwXv)
+            g.call("sysml_b200_d2h", C.c_void_p(hq.data_ptr()), p_(Q), 8 * m)
+            dt = time.perf_counter() - t0
+            e2e["cold"] = {"rows": rows_c, "seconds": dt, "h2d_gbs": 8.0 * rows_c * m / dt / 1e9,
+                           "iters_per_sec_if_X_uploaded_every_step": (rows_c / float(n)) / dt * world,
+                           "note": "bounded sample: first-touch upload of X (pinned host -> device) + one mmchain + q read-back"}
+            del hx
+            g.call("sysml_b200_rand_uniform", C.c_void_p(X.ptr), nloc * m, 1, r0 * m, -1.0, 1.0)  # restore X
+
+    # ---------------- auxiliary: tsmm FP64 TFLOP/s on this rank's shard (N = 1 only) ----------------
+    tsmm = None
+    if world == 1 and not args.no_tsmm:
+        tout = tensor(m * m)
+        g.call("sysml_b200_tsmm_dense", p_(X), C.c_void_p(tout.data_ptr()), nloc, m, 1, None)  # warm-up (+ workspace growth)
+        torch.cuda.synchronize()
+        reps = 3
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            g.call("sysml_b200_tsmm_dense", p_(X), C.c_void_p(tout.data_ptr()), nloc, m, 1, None)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        flops = float(nloc) * m * (m + 1)
+        tsmm = {"shape": [nloc, m], "ms": ms, "tflops_symmetric": flops / ms / 1e9, "tflops_gemm_equivalent": 2.0 * nloc * m * m / ms / 1e9,
+                "flops_counted": "n*m*(m+1) (upper triangle incl. diagonal, as the reference computes)"}
+        peaks = os.path.join(ROOT, "profiles", "fp64_peak.json")
+        if os.path.exists(peaks):
+            try:
+                pk = json.load(open(peaks))
+                tsmm["fp64_dmma_peak_tflops"] = pk["dmma_peak_tflops"]
+                tsmm["frac_of_measured_dmma_peak"] = tsmm["tflops_symmetric"] / pk["dmma_peak_tflops"]
+            except Exception:
+                pass
+        del tout
+
+    # ---------------- roofline + cpu baseline + output ----------------
+    peak, peak_src = measured_peak()
+    bytes_launch = alg_bytes_mmchain(nloc, m)
+    achieved = bytes_launch / (kern_ms * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "mmchain_traffic.json")
+    if os.path.exists(tp):
+        try:
+            tj = json.load(open(tp))
+            if tj.get("rows") == nloc and tj.get("cols") == m:
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    roofline = {"bound": "hbm", "kernel": "rowstream_kernel<CHAIN> (mmchain XtwXv)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_per_step}
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            val, cores, sample, med, rows = cpu_cg_iterations(n, m)
+            cpu = {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                   "sample_gbs": alg_bytes_mmchain(rows, m) / med / 1e9}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1]), row-sharded %d x %d rows/GPU"
+                       % (n, m, world, nloc), "parallelism": "row-shard x%d + all-reduce(m doubles)" % world,
+                       "l2": "inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush needed" % (8.0 * nloc * m / 1e9),
+                       "x_distribution": "U(-1,1) counter-based generator, seed 1"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+            "mmchain_gbs_aggregate": achieved * world, "result_finite": finite,
+        }
+        if tsmm:
+            line["tsmm"] = tsmm
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

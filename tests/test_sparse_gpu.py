@@ -1,0 +1,89 @@
+"""CSR kernels vs the CPU oracle: SpMV / SpMM / t(X)%*%y, sparse mmchain, sparse tsmm, sparse aggregates."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests.util import assert_equal_matrices
+
+pytestmark = pytest.mark.gpu
+
+
+def _csr(gctx, X):
+    rp, ci, va = O.dense_to_csr(X)
+    return gctx.csr(rp, ci, va, X.shape), (rp, ci, va)
+
+
+@pytest.mark.parametrize("rows,cols,sp", [(3471, 567, 0.1), (3471, 567, 0.7), (20000, 3000, 0.002), (1000, 10000, 0.001),
+                                          (50, 40, 0.5), (1, 100, 0.3), (5000, 200, 0.0)])
+@pytest.mark.parametrize("ct", [0, 1, 2])
+def test_sparse_mmchain(gctx, rows, cols, sp, ct):
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(rows, cols, 0, 1, sp, 7)
+    v = O.java_test_matrix(cols, 1, 0, 1, 0.7, 3)
+    w = O.java_test_matrix(rows, 1, 0, 1, max(sp, 0.1), 10)
+    dX, (rp, ci, va) = _csr(gctx, X)
+    exp = O.mmchain_csr(rp, ci, va, X.shape, v, w if ct else None, ct, 4)
+    out = L.mmchain(gctx, "mmchain", dX, gctx.dense(v), gctx.dense(w) if ct else None, ct)
+    got = out.to_host().reshape(-1)
+    scale = max(np.max(np.abs(exp)), 1e-300)
+    assert np.max(np.abs(exp - got)) <= 1e-9 * scale
+    if ct != 2:
+        assert_equal_matrices(exp, got, what="sparse mmchain")
+
+
+@pytest.mark.parametrize("rows,cols,sp,n", [(3471, 567, 0.1, 1), (3471, 567, 0.7, 1), (20000, 3000, 0.002, 1), (20000, 3000, 0.002, 20),
+                                            (999, 10000, 0.001, 1), (2000, 500, 0.05, 64), (2000, 500, 0.05, 130), (300, 80, 0.3, 7)])
+def test_spmv_spmm(gctx, rows, cols, sp, n):
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(rows, cols, 0, 1, sp, 7)
+    B = O.java_test_matrix(cols, n, 0, 1, 0.9, 5)
+    dX, (rp, ci, va) = _csr(gctx, X)
+    exp, _ = O.matmult_csr_dense(rp, ci, va, X.shape, B, 4)
+    got = L.matmult(gctx, "ba+*", dX, gctx.dense(B)).to_host()
+    assert_equal_matrices(exp, got, what="CSR x dense n=%d" % n)
+    # t(X) %*% Y (scatter form)
+    Y = O.java_test_matrix(rows, n, 0, 1, 0.9, 6)
+    exp2 = (X.astype(np.longdouble).T @ Y.astype(np.longdouble)).astype(np.float64)
+    got2 = L.matmult(gctx, "ba+*", dX, gctx.dense(Y), isLeftTransposed=True).to_host()
+    assert_equal_matrices(exp2, got2, rel=1e-9, what="t(CSR) x dense")
+
+
+def test_sparse_tsmm(gctx):
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(3500, 300, 0, 1, 0.1, 7)
+    dX, (rp, ci, va) = _csr(gctx, X)
+    exp, nnz = O.tsmm_csr_left(rp, ci, va, X.shape, 4)
+    out, gnnz = L.matmultTSMM(gctx, "tsmm", dX, True, with_nnz=True)
+    assert_equal_matrices(exp, out.to_host(), what="sparse tsmm")
+    assert gnnz == nnz
+
+
+@pytest.mark.parametrize("rows,cols,sp", [(1000, 50, 0.3), (2049, 130, 0.03), (500, 1000, 0.9), (64, 64, 0.0003)])
+def test_sparse_aggregates(gctx, rows, cols, sp):
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(rows, cols, -1, 1, sp, 42)
+    if not X.any():
+        X[1, 2] = -0.25
+    dX, (rp, ci, va) = _csr(gctx, X)
+    for opc, op, d, exact in (("uak+", O.SUM, O.ALL, False), ("uark+", O.SUM, O.ROW, False), ("uack+", O.SUM, O.COL, False),
+                              ("uasqk+", O.SUMSQ, O.ALL, False), ("uamax", O.MAX, O.ALL, True), ("uarmax", O.MAX, O.ROW, True),
+                              ("uacmax", O.MAX, O.COL, True), ("uamin", O.MIN, O.ALL, True), ("uarmin", O.MIN, O.ROW, True),
+                              ("uacmin", O.MIN, O.COL, True), ("uarimax", O.MAXINDEX, O.ROW, True), ("uarimin", O.MININDEX, O.ROW, True)):
+        exp = O.agg_unary_csr(rp, ci, va, X.shape, op, d, 1)
+        got = L.unaryAggregate(gctx, opc, dX, opc)
+        got = np.array([got]) if d == O.ALL else got.to_host().reshape(-1)
+        if exact:
+            assert np.array_equal(exp, got), opc
+        else:
+            assert np.max(np.abs(exp - got)) <= 1e-12 * max(1.0, np.max(np.abs(exp))), opc
+
+
+def test_sparse_rowindex_edge_cases(gctx):
+    from systemml_b200 import LibMatrixB200 as L
+    X = np.array([[1.0, 3.0, 3.0, 2.0], [-1.0, -2.0, -1.0, -3.0], [0.0, 0.0, 0.0, 0.0], [-5.0, 0.0, -2.0, 0.0],
+                  [0.0, -1.0, 0.0, -2.0], [0.0, 0.0, -1.0, -1.0], [2.0, 0.0, 0.0, 0.0]])
+    dX, (rp, ci, va) = _csr(gctx, X)
+    for opc, op in (("uarimax", O.MAXINDEX), ("uarimin", O.MININDEX)):
+        exp = O.agg_unary_csr(rp, ci, va, X.shape, op, O.ROW)
+        assert np.array_equal(exp, O.agg_unary_dense(X, op, O.ROW)), "oracle: sparse and dense must agree"
+        assert L.unaryAggregate(gctx, opc, dX, opc).to_host().reshape(-1).tolist() == exp.tolist()
