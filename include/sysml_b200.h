@@ -175,6 +175,21 @@ int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const double* X, const
                                      const double* h_w, const double* d_w, double* h_out, int64_t n,
                                      int64_t m, int chain_type);
 
+/* Allocation-free form of sysml_b200_mmchain_dense.  It has NO counterpart in the reference; it exists
+ * for callers that must not have device memory allocated on their behalf: a host runtime that budgets
+ * the whole card itself (SystemML's GPUMemoryManager is one) cannot have the library call cudaMalloc
+ * behind its back, and code running where the CUDA runtime may not be asked for memory cannot either.
+ * Same arguments, same result and same error codes as sysml_b200_mmchain_dense, with these differences:
+ *  - cols must be <= SYSML_B200_NOALLOC_MAX_COLS, otherwise SYSML_E_LIMIT is returned;
+ *  - the scratch is a fixed array inside the loaded library (about 2.4 MiB per GPU, held from load to
+ *    process exit); no cudaMalloc / cudaFree or other allocating routine is called;
+ *  - all calls on one GPU share that array: calls that overlap on the GPU race with each other;
+ *  - the first call on each device resolves the array's device address; issue it before starting any
+ *    stream capture. */
+#define SYSML_B200_NOALLOC_MAX_COLS 1024
+int sysml_b200_mmchain_dense_noalloc(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w,
+                                     double* out, int64_t n, int64_t m, int chain_type);
+
 /* ------------------------------------------------------------------------------------------------
  * tsmm.  Replaces LibMatrixCUDA.matmultTSMM (LibMatrixCUDA.java:477-524: cublasDsyrk + copy_u2l_dense)
  * called by MMTSJGPUInstruction.processInstruction (gpu/MMTSJGPUInstruction.java:78-89); CPU twin

@@ -472,3 +472,105 @@ extern "C" int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const doubl
   memcpy(h_out, p_out, (size_t)m * sizeof(double));
   return SYSML_OK;
 }
+
+// ================================================================================================
+// Allocation-free mmchain.
+//
+// sysml_b200_mmchain_dense does its cross-CTA reduction through scratch that the context obtains with
+// cudaMalloc the first time it is needed (and again whenever a larger request arrives).  Some callers
+// cannot tolerate that.  The typical one is a host runtime that has handed the whole device to its own
+// memory manager -- SystemML's GPUMemoryManager budgets the card up to sysml.gpu.memory.util.factor and
+// evicts matrices according to its own books -- so a cudaMalloc issued behind its back can fail on a
+// "full" device, or silently break the accounting it relies on to decide what to evict.  The same goes
+// for callers that run inside a region where the CUDA runtime must not be asked for memory at all
+// (cudaMalloc synchronises the whole device and is refused while a stream is being captured).
+//
+// For them this entry point keeps its scratch in a fixed array that is part of the loaded module: the
+// memory exists from the moment the library is loaded on a device until the process exits, whether or
+// not the function is ever called, and nothing is allocated or freed by the call itself.
+//   - limit: cols <= SYSML_B200_NOALLOC_MAX_COLS (1024); larger inputs are rejected with SYSML_E_LIMIT;
+//   - footprint: NOALLOC_DOUBLES*8 + 256 bytes (about 2.4 MiB) of device memory per GPU, permanently;
+//   - the array is shared by every call on that GPU and keeps whatever the previous call left in it; the
+//     one word that must start at zero (the arrival ticket) is cleared on the stream before each launch;
+//   - two calls that overlap on the same GPU (different streams / contexts / host threads) race on the
+//     array and produce garbage: serialise them;
+//   - the very first call on each device looks up the device address of the array
+//     (cudaGetSymbolAddress); make that first call before any stream capture begins.
+// ================================================================================================
+namespace {
+
+constexpr int NOALLOC_MAX_COLS = SYSML_B200_NOALLOC_MAX_COLS;
+constexpr size_t NOALLOC_DOUBLES = (size_t)304 * 1024;  // (CTAs x row-groups) x cols partial sums
+// [0, NOALLOC_DOUBLES): per-CTA column partials; the 256 bytes after them hold the arrival ticket
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES + 32];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};  // device address of the array, per device
+
+// `g_noalloc_scratch` named in host code is only a host-side handle for the symbol, not a device
+// address: the address a kernel can use has to be asked for, once per device, with that device current.
+int noalloc_scratch(sysml_b200_ctx* ctx, double** out) {
+  const int dev = ctx->device;
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return sysml_set_error(ctx, SYSML_E_LIMIT, "mmchain_noalloc: device index %d not supported", dev);
+  if (!g_noalloc_ptr[dev]) {
+    double* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p)
+      return sysml_set_error(ctx, SYSML_E_CUDA, "mmchain_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return SYSML_OK;
+}
+
+template <int NTC, int TC, int CPT, int RG, int STAGES>
+int launch_cfg_noalloc(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm, double* scratch) {
+  constexpr int G = NTC / TC;
+  constexpr int R = G * RG;
+  constexpr int NWG = TC / 32;
+  auto kern = rowstream_kernel<MODE_CHAIN, NTC, TC, CPT, RG, STAGES>;
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8;
+  SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  a.total_tiles = (a.n + R - 1) / R;
+  const size_t stage_bytes = (size_t)R * a.m * 8;
+  a.use_tma = ((reinterpret_cast<uintptr_t>(a.X) & 15) == 0) && (stage_bytes % 16 == 0) && (stage_bytes < (1u << 20));
+  i64 grid = (i64)ctx->sm_count * ctas_per_sm;
+  const i64 fit = (i64)(NOALLOC_DOUBLES / ((size_t)G * a.m));  // CTAs whose partials fit in the fixed array
+  if (grid > fit) grid = fit;
+  if (grid > a.total_tiles) grid = a.total_tiles;
+  if (grid < 1) grid = 1;
+  a.partial = scratch;
+  a.counter = reinterpret_cast<unsigned int*>(scratch + NOALLOC_DOUBLES);
+  SYSML_CUDA(ctx, cudaMemsetAsync(a.counter, 0, 256, ctx->stream));  // the ticket must start at zero
+  kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
+  SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel (noalloc)");
+  return SYSML_OK;
+}
+
+}  // namespace
+
+extern "C" int sysml_b200_mmchain_dense_noalloc(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w,
+                                                double* out, int64_t n, int64_t m, int chain_type) {
+  SYSML_ENTER(ctx);
+  int rc = validate_chain(ctx, X, v, w, out, n, m, chain_type);
+  if (rc) return rc;
+  if (m > NOALLOC_MAX_COLS)
+    return sysml_set_error(ctx, SYSML_E_LIMIT,
+                           "mmchain_noalloc: %lld columns exceed the fixed-scratch limit of %d; use sysml_b200_mmchain_dense",
+                           (long long)m, NOALLOC_MAX_COLS);
+  if (m == 0) return SYSML_OK;
+  if (n == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  double* scratch = nullptr;
+  rc = noalloc_scratch(ctx, &scratch);
+  if (rc) return rc;
+  StreamArgs a{};
+  a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type;
+  if (m <= 64) return launch_cfg_noalloc<128, 32, 2, 8, 4>(ctx, a, 2, scratch);
+  if (m <= 128) return launch_cfg_noalloc<128, 32, 4, 8, 3>(ctx, a, 2, scratch);
+  if (m <= 256) return launch_cfg_noalloc<128, 32, 8, 4, 3>(ctx, a, 2, scratch);
+  if (m <= 512) return launch_cfg_noalloc<128, 64, 8, 4, 3>(ctx, a, 2, scratch);
+  return launch_cfg_noalloc<128, 128, 8, 4, 3>(ctx, a, 2, scratch);
+}

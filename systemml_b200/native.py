@@ -39,6 +39,7 @@ SIGNATURES = {
     "sysml_b200_timer_start": (ci, [vp]),
     "sysml_b200_timer_stop_ms": (ci, [vp, pdbl]),
     "sysml_b200_mmchain_dense": (ci, [vp, vp, vp, vp, vp, i64, i64, ci]),
+    "sysml_b200_mmchain_dense_noalloc": (ci, [vp, vp, vp, vp, vp, i64, i64, ci]),
     "sysml_b200_mmchain_csr": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, ci]),
     "sysml_b200_mmchain_dense_hostvec": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci]),
     "sysml_b200_tsmm_dense": (ci, [vp, vp, vp, i64, i64, ci, pi64]),
