@@ -16,6 +16,8 @@
 //   - the contraction dimension (rows of X for tsmm: 10^7) is split across CTAs so that the grid is a
 //     multiple of the SM count; partials are reduced deterministically, not with atomics.
 // Algorithmic flops: tsmm n*m*(m+1); matmult 2*M*N*K.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m);
@@ -187,6 +189,217 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) dgemm_kernel(const Gemm
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Warp-specialised variant: one producer warp feeds the ring with 1-D bulk copies (cp.async.bulk, the
+// TMA engine, SASS UBLKCP) -- one copy per contiguous row segment, straight into the padded layout --
+// and signals mbarriers; the consumer warps do nothing but LDS + DMMA.  No __syncthreads and no address
+// arithmetic in the consumers' loop, so the DMMA pipe never waits for the loaders.
+// Requirements (checked on the host, otherwise the cp.async kernel above is used): 16-byte aligned
+// bases, even leading dimensions, even M and N.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bulk_g2s_plain(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// rows of the logical [R][CCOLS] tile are contiguous in global memory; copies `rvalid` rows of `cvalid`
+// columns (cvalid even) and, when zero_tail is set, clears what is not copied.  Returns bytes issued by
+// the whole warp (identical on every lane).
+template <int R, int CCOLS, int LD>
+__device__ __forceinline__ uint32_t tile_bytes(i64 rvalid, i64 cvalid) {
+  const i64 rv = rvalid < R ? (rvalid < 0 ? 0 : rvalid) : R;
+  const i64 cv = cvalid < CCOLS ? (cvalid < 0 ? 0 : cvalid) : CCOLS;
+  return (uint32_t)(rv * cv * 8);
+}
+template <int R, int CCOLS, int LD>
+__device__ __forceinline__ void tile_zero_tail(double* s, i64 rvalid, i64 cvalid, int lane) {
+  const int rv = (int)(rvalid < R ? (rvalid < 0 ? 0 : rvalid) : R);
+  const int cv = (int)(cvalid < CCOLS ? (cvalid < 0 ? 0 : cvalid) : CCOLS);
+  if (rv == R && cv == CCOLS) return;
+  for (int c = lane; c < R * CCOLS; c += 32) {
+    const int r = c / CCOLS, cc = c - r * CCOLS;
+    if (r >= rv || cc >= cv) s[r * LD + cc] = 0.0;
+  }
+}
+template <int R, int CCOLS, int LD>
+__device__ __forceinline__ void tile_issue(double* s, const double* src, i64 ld, i64 rvalid, i64 cvalid, uint64_t* bar, int lane) {
+  const int rv = (int)(rvalid < R ? (rvalid < 0 ? 0 : rvalid) : R);
+  const int cv = (int)(cvalid < CCOLS ? (cvalid < 0 ? 0 : cvalid) : CCOLS);
+  if (cv <= 0) return;
+  for (int r = lane; r < rv; r += 32) bulk_g2s_plain(s + r * LD, src + (i64)r * ld, (uint32_t)cv * 8u, bar);
+}
+
+// K-contiguous operands (rows of 16 doubles = 128 B): per-row bulk copies would be 128-byte requests,
+// which the TMA engine retires far too slowly; the producer warp uses 16-byte cp.async (LDGSTS) instead,
+// 8 lanes per row segment, zero-filling through the src-size operand, and lets the copies arrive on the
+// stage's mbarrier (cp.async.mbarrier.arrive.noinc).
+template <int R, int LD>
+__device__ __forceinline__ void tile_issue_cpasync(double* s, const double* src, i64 ld, i64 rvalid, i64 kvalid, int lane) {
+  const int r0 = lane >> 3, cc = (lane & 7) * 2;
+  i64 nb = (kvalid - cc) * 8;
+  nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+  const double* p = src + (i64)r0 * ld + cc;
+  double* d = s + r0 * LD + cc;
+  const i64 step = 4 * ld;
+#pragma unroll 4
+  for (int r = r0; r < R; r += 4) {
+    const int bytes = (r < rvalid) ? (int)nb : 0;
+    cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
+    p += step;
+    d += 4 * LD;
+  }
+}
+// rows-long tile [R][CCOLS] with SHORT rows (< 1 KB): same idea, 16-byte chunks spread over the warp
+template <int R, int CCOLS, int LD>
+__device__ __forceinline__ void tile_issue_cpasync_rows(double* s, const double* src, i64 ld, i64 rvalid, i64 cvalid, int lane) {
+  constexpr int CH = CCOLS / 2;
+#pragma unroll 2
+  for (int c = lane; c < R * CH; c += 32) {
+    const int r = c / CH, cc = (c - r * CH) * 2;
+    i64 nb = (r < rvalid) ? (cvalid - cc) * 8 : 0;
+    nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+    cp_async16(s + r * LD + cc, nb ? (const void*)(src + (i64)r * ld + cc) : (const void*)src, (int)nb);
+  }
+}
+__device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(const GemmArgs g) {
+  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  constexpr int NCW = WARPS_M * WARPS_N;  // consumer warps
+  constexpr int MT = Cfg::MT, NTL = Cfg::NTL, LDA = Cfg::LDA, LDB = Cfg::LDB;
+  constexpr bool A_BULK = TA && (BM * 8 >= 1024);
+  constexpr bool B_BULK = !TB && (BN * 8 >= 1024);
+  constexpr bool ANY_CPASYNC = !A_BULK || !B_BULK;
+  extern __shared__ __align__(16) double smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + STAGES;
+  double* As = smem + 16;  // 128 bytes reserved for the barriers
+  double* Bs = As + STAGES * Cfg::A_ELEMS;
+
+  int ti, tj;
+  if (g.sym) {
+    int t = blockIdx.x;
+    ti = 0;
+    while (t >= g.tiles_n - ti) {
+      t -= g.tiles_n - ti;
+      ti++;
+    }
+    tj = ti + t;
+  } else {
+    ti = blockIdx.x / g.tiles_n;
+    tj = blockIdx.x - ti * g.tiles_n;
+  }
+  const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+  const i64 kbeg = (i64)blockIdx.y * g.k_per_split;
+  const i64 kend = (kbeg + g.k_per_split < g.K) ? kbeg + g.k_per_split : g.K;
+  const int nkb = (int)((kend - kbeg + BK - 1) / BK);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // clear all tiles once: padding columns/rows that no copy ever writes must read as zero
+  for (int c = tid; c < STAGES * (Cfg::A_ELEMS + Cfg::B_ELEMS); c += (NCW + 1) * 32) As[c] = 0.0;
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(&full[s], ANY_CPASYNC ? 1 + 32 : 1);  // lane 0's expect_tx arrival (+ one cp.async arrival per producer lane)
+      mbar_init(&empty[s], NCW);
+    }
+    mbar_fence_init();
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+
+  if (warp == NCW) {
+    // ===================== producer warp =====================
+    for (int kb = 0; kb < nkb; kb++) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&empty[s], ph ^ 1u);
+      const i64 k0 = kbeg + (i64)kb * BK;
+      const i64 kvalid = kend - k0;
+      double* as = As + s * Cfg::A_ELEMS;
+      double* bs = Bs + s * Cfg::B_ELEMS;
+      // bulk copies only for operands whose tile rows are >= 1 KB; 16-byte cp.async for everything else
+      if (kvalid < BK) {  // ragged last k block: clear what the bulk copies below will not overwrite
+        if (A_BULK) tile_zero_tail<BK, BM, LDA>(as, kvalid, g.M - i0, lane);
+        if (B_BULK) tile_zero_tail<BK, BN, LDB>(bs, kvalid, g.N - j0, lane);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      }
+      uint32_t bytes = 0;
+      if (A_BULK) bytes += tile_bytes<BK, BM, LDA>(kvalid, g.M - i0);
+      if (B_BULK) bytes += tile_bytes<BK, BN, LDB>(kvalid, g.N - j0);
+      __syncwarp();
+      if (lane == 0) mbar_expect_tx(&full[s], bytes);
+      __syncwarp();
+      if (A_BULK)  tile_issue<BK, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, &full[s], lane);
+      else if (TA) tile_issue_cpasync_rows<BK, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, lane);
+      else         tile_issue_cpasync<BM, LDA>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, lane);
+      if (B_BULK)   tile_issue<BK, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, &full[s], lane);
+      else if (!TB) tile_issue_cpasync_rows<BK, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, lane);
+      else          tile_issue_cpasync<BN, LDB>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, lane);
+      if (ANY_CPASYNC) cp_async_mbar_arrive(&full[s]);
+    }
+    if (ANY_CPASYNC) cp_async_wait<0>();
+    return;
+  }
+
+  // ===================== consumer warps =====================
+  const int wm0 = (warp / WARPS_N) * Cfg::WM, wn0 = (warp % WARPS_N) * Cfg::WN;
+  const int gid = lane >> 2, tig = lane & 3;
+  double acc[MT][NTL][2];
+#pragma unroll
+  for (int a = 0; a < MT; a++)
+#pragma unroll
+    for (int b = 0; b < NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+  // per-thread fragment base offsets (constant over the whole loop)
+  const int a_off = TA ? (tig * LDA + wm0 + gid) : ((wm0 + gid) * LDA + tig);
+  const int b_off = TB ? ((wn0 + gid) * LDB + tig) : (tig * LDB + wn0 + gid);
+  constexpr int A_MT = TA ? 8 : 8 * LDA;       // step between m-tiles
+  constexpr int A_K4 = TA ? 4 * LDA : 4;       // step between k4 blocks
+  constexpr int B_NT = TB ? 8 * LDB : 8;
+  constexpr int B_K4 = TB ? 4 : 4 * LDB;
+
+  for (int kb = 0; kb < nkb; kb++) {
+    const int s = kb % STAGES;
+    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+    mbar_wait(&full[s], ph);
+    const double* as = As + s * Cfg::A_ELEMS + a_off;
+    const double* bs = Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+    for (int k4 = 0; k4 < BK / 4; k4++) {
+      double af[MT], bf[NTL];
+#pragma unroll
+      for (int a = 0; a < MT; a++) af[a] = as[k4 * A_K4 + a * A_MT];
+#pragma unroll
+      for (int b = 0; b < NTL; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+      for (int a = 0; a < MT; a++)
+#pragma unroll
+        for (int b = 0; b < NTL; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+
+  double* outp = g.out + (size_t)blockIdx.y * (size_t)g.M * (size_t)g.N;
+#pragma unroll
+  for (int a = 0; a < MT; a++) {
+    const i64 i = i0 + wm0 + a * 8 + gid;
+    if (i >= g.M) continue;
+#pragma unroll
+    for (int b = 0; b < NTL; b++) {
+      const i64 j = j0 + wn0 + b * 8 + 2 * tig;
+      if (j + 1 < g.N) {
+        *reinterpret_cast<double2*>(outp + i * g.N + j) = make_double2(acc[a][b][0], acc[a][b][1]);
+      } else if (j < g.N) {
+        outp[i * g.N + j] = acc[a][b][0];
+      }
+    }
+  }
+}
+
 // C[idx] = sum over splits (fixed order, compensated)
 __global__ void reduce_partials_kernel(const double* __restrict__ partial, int splits, i64 len, double* __restrict__ C) {
   const i64 stride = (i64)gridDim.x * blockDim.x;
@@ -286,8 +499,19 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
   } else {
     g.out = C;
   }
-  dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
-  SYSML_LAUNCH_CHECK(ctx, "dgemm_kernel");
+  // the warp-specialised bulk-copy kernel needs aligned, even-sized operands (see its header comment)
+  const bool ws_ok = g.vecA && g.vecB && (M % 2 == 0) && (N % 2 == 0) &&
+                     ((reinterpret_cast<uintptr_t>(g.out) & 15) == 0) && getenv("SYSML_B200_GEMM_NO_WS") == nullptr;
+  if (ws_ok) {
+    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+    const size_t smem_ws = Cfg::SMEM + 128;
+    SYSML_CUDA(ctx, cudaFuncSetAttribute(kws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ws));
+    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT + 32, smem_ws, ctx->stream>>>(g);
+    SYSML_LAUNCH_CHECK(ctx, "dgemm_ws_kernel");
+  } else {
+    dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
+    SYSML_LAUNCH_CHECK(ctx, "dgemm_kernel");
+  }
   if (direct) return SYSML_OK;
   const i64 len = M * N;
   i64 blocks = (len + 255) / 256;
@@ -314,6 +538,7 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
 template <bool TA, bool TB>
 int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
                   int64_t* h_nnz) {
+  if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
   if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
