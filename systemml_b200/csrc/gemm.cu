@@ -540,6 +540,7 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
                   int64_t* h_nnz) {
   if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
+  if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
