@@ -1,0 +1,85 @@
+/*
+ * sysml_b200_host.h -- C ABI of the host-side runtime that mirrors SystemML's GPU execution layer:
+ * instruction strings in, matrices out.  It is the C++ counterpart (the reference's toolchain, a JDK,
+ * is absent from the build image) of
+ *   - GPUInstructionParser.parseSingleInstruction   (J/runtime/instructions/GPUInstructionParser.java:147-205)
+ *   - the GPU instruction classes' processInstruction (J/runtime/instructions/gpu/ *GPUInstruction.java)
+ *   - ExecutionContext.*ForGPUInstruction            (J/runtime/controlprogram/context/ExecutionContext.java:304-452)
+ *   - GPUObject (locks, dirty bit, lazy H2D/D2H)     (J/runtime/instructions/gpu/context/GPUObject.java:528-946)
+ *   - GPUMemoryManager (free list by size, eviction) (J/runtime/instructions/gpu/context/GPUMemoryManager.java:157-322)
+ * with J/ = src/main/java/org/apache/sysml/.  All numeric work is delegated to the kernels behind
+ * include/sysml_b200.h; this layer only does what the Java classes do: parse, look up variables, move
+ * data lazily, set output metadata, call the library, release.
+ *
+ * Instruction strings are exactly what SystemML's compiler emits (lops/Lop.java:82-86): fields separated
+ * by OPERAND_DELIMITOR (U+00B0), operands written name<U+00B7>DATATYPE<U+00B7>VALUETYPE[<U+00B7>literal], e.g.
+ *   GPU°ba+*°A·MATRIX·DOUBLE°B·MATRIX·DOUBLE°C·MATRIX·DOUBLE°false°false
+ *   GPU°tsmm°X·MATRIX·DOUBLE°C·MATRIX·DOUBLE°LEFT
+ *   GPU°mmchain°X·MATRIX·DOUBLE°v·MATRIX·DOUBLE°w·MATRIX·DOUBLE°q·MATRIX·DOUBLE°XtwXv      (new on GPU)
+ *   GPU°uark+°X·MATRIX·DOUBLE°r·MATRIX·DOUBLE      GPU°uak+°X·MATRIX·DOUBLE°s·SCALAR·DOUBLE
+ *   GPU°*°A·MATRIX·DOUBLE°2.5·SCALAR·DOUBLE·true°C·MATRIX·DOUBLE
+ *   GPU°+*°A·MATRIX·DOUBLE°0.5·SCALAR·DOUBLE·true°B·MATRIX·DOUBLE°C·MATRIX·DOUBLE
+ * ASCII stand-ins are accepted too: ';' for the operand delimiter when no U+00B0 occurs in the string and
+ * ':' for U+00B7 likewise.
+ *
+ * Every function returns 0 or a negative SYSML_E_* code (sysml_b200.h); sysml_b200_ec_last_error() has
+ * the message -- the text a DMLRuntimeException would carry.
+ */
+#ifndef SYSML_B200_HOST_H
+#define SYSML_B200_HOST_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef struct sysml_b200_ec sysml_b200_ec;
+
+/* mem_util_factor: sysml.gpu.memory.util.factor (DMLConfig.java:138; 0.9 by default; <= 0 selects 0.9).
+ * eager_cuda_free : sysml.gpu.eager.cudaFree (false by default: freed pointers go to a size-keyed free list).
+ * memory_limit    : > 0 caps the device memory this context may hold (bytes) -- lets tests exercise the
+ *                   eviction path on a 180 GB card; 0 = use cudaMemGetInfo * factor. */
+int sysml_b200_ec_create(int device, double mem_util_factor, int eager_cuda_free, int64_t memory_limit,
+                         sysml_b200_ec** out);
+int sysml_b200_ec_destroy(sysml_b200_ec* ec);
+const char* sysml_b200_ec_last_error(sysml_b200_ec* ec);
+
+/* Variables (the symbol table of ExecutionContext).  Host data are copied; nothing goes to the device
+ * until a GPU instruction acquires the variable (GPUObject.acquireDeviceRead, GPUObject.java:528-545). */
+int sysml_b200_ec_set_matrix_dense(sysml_b200_ec* ec, const char* name, const double* h_data, int64_t rows,
+                                   int64_t cols);
+int sysml_b200_ec_set_matrix_csr(sysml_b200_ec* ec, const char* name, const int32_t* h_rowptr,
+                                 const int32_t* h_colind, const double* h_val, int64_t rows, int64_t cols);
+int sysml_b200_ec_set_scalar(sysml_b200_ec* ec, const char* name, double value);
+int sysml_b200_ec_remove(sysml_b200_ec* ec, const char* name); /* rmvar */
+
+/* Parses and runs ONE instruction (ProgramBlock.executeSingleInstruction, ProgramBlock.java:241-255). */
+int sysml_b200_ec_execute(sysml_b200_ec* ec, const char* instruction);
+/* Parse only (no device needed): writes "TYPE opcode in1 in2 ... out" into buf.  ec may be NULL. */
+int sysml_b200_parse_instruction(const char* instruction, char* buf, int buflen);
+
+int sysml_b200_ec_get_matrix_dims(sysml_b200_ec* ec, const char* name, int64_t* rows, int64_t* cols,
+                                  int64_t* nnz);
+/* CacheableData.acquireRead -> GPUObject.acquireHostRead: copies device -> host only when the device copy
+ * is dirty (GPUObject.java:593-607). */
+int sysml_b200_ec_get_matrix_dense(sysml_b200_ec* ec, const char* name, double* h_out);
+int sysml_b200_ec_get_scalar(sysml_b200_ec* ec, const char* name, double* value);
+
+/* GPUStatistics counters (J/utils/GPUStatistics.java:40-62), in this order:
+ * [0] executed GPU instructions, [1] H2D copies, [2] D2H copies, [3] cudaMalloc calls, [4] free-list reuses,
+ * [5] cudaFree calls, [6] evictions, [7] bytes currently allocated, [8] bytes in the free list. */
+int sysml_b200_ec_stats(sysml_b200_ec* ec, int64_t* out9);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SYSML_B200_HOST_H */

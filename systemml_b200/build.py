@@ -21,7 +21,7 @@ FLAGS = [
 
 
 def sources():
-    return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    return sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cpp")))
 
 
 def _newer(a, b):
@@ -32,11 +32,12 @@ def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     hdrs.append(os.path.join(HERE, "..", "include", "sysml_b200.h"))
+    hdrs.append(os.path.join(HERE, "..", "include", "sysml_b200_host.h"))
     hdr_time = max(os.path.getmtime(h) for h in hdrs)
     jobs = []
     for s in sources():
         src = os.path.join(CSRC, s)
-        obj = os.path.join(OBJ, s[:-3] + ".o")
+        obj = os.path.join(OBJ, os.path.splitext(s)[0] + ".o")
         if force or _newer(src, obj) or hdr_time > os.path.getmtime(obj):
             jobs.append((src, obj))
 
@@ -53,7 +54,7 @@ def build(force=False, verbose=False):
                     sys.stderr.write(out)
                 if rc:
                     raise RuntimeError("nvcc failed on %s" % src)
-    objs = [os.path.join(OBJ, s[:-3] + ".o") for s in sources()]
+    objs = [os.path.join(OBJ, os.path.splitext(s)[0] + ".o") for s in sources()]
     if jobs or not os.path.exists(SO):
         cmd = [NVCC, "-shared", "-o", SO] + objs + ["-ccbin", "/usr/bin/g++", "-Xlinker", "--no-undefined"]
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -58,6 +58,20 @@ SIGNATURES = {
     "sysml_b200_dense_to_csr": (ci, [vp, vp, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_csr_to_dense": (ci, [vp, vp, vp, vp, i64, i64, vp]),
     "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),
+    # ---- include/sysml_b200_host.h ----
+    "sysml_b200_ec_create": (ci, [ci, dbl, ci, i64, pvp]),
+    "sysml_b200_ec_destroy": (ci, [vp]),
+    "sysml_b200_ec_last_error": (C.c_char_p, [vp]),
+    "sysml_b200_ec_set_matrix_dense": (ci, [vp, C.c_char_p, vp, i64, i64]),
+    "sysml_b200_ec_set_matrix_csr": (ci, [vp, C.c_char_p, vp, vp, vp, i64, i64]),
+    "sysml_b200_ec_set_scalar": (ci, [vp, C.c_char_p, dbl]),
+    "sysml_b200_ec_remove": (ci, [vp, C.c_char_p]),
+    "sysml_b200_ec_execute": (ci, [vp, C.c_char_p]),
+    "sysml_b200_parse_instruction": (ci, [C.c_char_p, C.c_char_p, ci]),
+    "sysml_b200_ec_get_matrix_dims": (ci, [vp, C.c_char_p, pi64, pi64, pi64]),
+    "sysml_b200_ec_get_matrix_dense": (ci, [vp, C.c_char_p, vp]),
+    "sysml_b200_ec_get_scalar": (ci, [vp, C.c_char_p, pdbl]),
+    "sysml_b200_ec_stats": (ci, [vp, pi64]),
 }
 
 

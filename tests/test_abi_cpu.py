@@ -8,13 +8,16 @@ import subprocess
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "sysml_b200.h")
+HEADERS = [os.path.join(ROOT, "include", h) for h in ("sysml_b200.h", "sysml_b200_host.h")]
 
 
 def _declared():
-    txt = open(HEADER).read()
-    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    return sorted(set(re.findall(r"\b(sysml_b200_\w+)\s*\(", txt)))
+    names = set()
+    for h in HEADERS:
+        txt = open(h).read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        names |= set(re.findall(r"\b(sysml_b200_\w+)\s*\(", txt))
+    return sorted(names)
 
 
 @pytest.fixture(scope="module")
@@ -50,7 +53,7 @@ def test_ctypes_table_matches_header(so_path):
 
 def test_header_is_plain_c(tmp_path):
     src = tmp_path / "t.c"
-    src.write_text('#include "sysml_b200.h"\nint main(void){return SYSML_OK;}\n')
+    src.write_text('#include "sysml_b200.h"\n#include "sysml_b200_host.h"\nint main(void){return SYSML_OK;}\n')
     subprocess.check_call(["/usr/bin/gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
                            "-c", str(src), "-o", str(tmp_path / "t.o")])
 

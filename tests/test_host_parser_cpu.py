@@ -1,0 +1,46 @@
+"""GPUInstructionParser mirror (csrc/host_runtime.cpp): instruction strings as SystemML's lops emit them
+(lops/Lop.java:82-86; GPUInstructionParser.java:42-205).  Parsing needs no GPU."""
+import pytest
+
+from systemml_b200 import native
+from systemml_b200.execution_context import inst, literal, mat, parse_instruction, scalar_var
+
+
+def test_operand_and_field_layout():
+    s = inst("ba+*", mat("A"), mat("B"), mat("C"), "false", "true")
+    assert s == "GPU°ba+*°A·MATRIX·DOUBLE°B·MATRIX·DOUBLE°C·MATRIX·DOUBLE°false°true"
+    assert parse_instruction(s) == "AggregateBinary ba+* A:MATRIX B:MATRIX C:MATRIX [false] [true]"
+
+
+@pytest.mark.parametrize("ins,expect", [
+    (inst("tsmm", mat("X"), mat("C"), "LEFT"), "MMTSJ tsmm X:MATRIX C:MATRIX [LEFT]"),
+    (inst("mmchain", mat("X"), mat("v"), mat("q"), "XtXv", 16), "MMChain mmchain X:MATRIX v:MATRIX q:MATRIX [XtXv]"),
+    (inst("mmchain", mat("X"), mat("v"), mat("w"), mat("q"), "XtwXv"), "MMChain mmchain X:MATRIX v:MATRIX w:MATRIX q:MATRIX [XtwXv]"),
+    (inst("uark+", mat("X"), mat("r")), "AggregateUnary uark+ X:MATRIX r:MATRIX"),
+    (inst("uak+", mat("X"), scalar_var("s")), "AggregateUnary uak+ X:MATRIX s:SCALAR"),
+    (inst("uarimax", mat("X"), mat("r")), "AggregateUnary uarimax X:MATRIX r:MATRIX"),
+    (inst("*", mat("A"), literal(2.5), mat("C")), "ArithmeticBinary * A:MATRIX 2.5:SCALAR:lit C:MATRIX"),
+    (inst("+*", mat("A"), literal(0.5), mat("B"), mat("C")), "ArithmeticBinary +* A:MATRIX 0.5:SCALAR:lit B:MATRIX C:MATRIX"),
+    (inst("<=", mat("A"), mat("B"), mat("C")), "RelationalBinary <= A:MATRIX B:MATRIX C:MATRIX"),
+    (inst("max", mat("A"), mat("B"), mat("C")), "BuiltinBinary max A:MATRIX B:MATRIX C:MATRIX"),
+    (inst("exp", mat("A"), mat("C")), "BuiltinUnary exp A:MATRIX C:MATRIX"),
+    (inst("r'", mat("A"), mat("C")), "Reorg r' A:MATRIX C:MATRIX"),
+    ("GPU;ba+*;A:MATRIX:DOUBLE;B:MATRIX:DOUBLE;C:MATRIX:DOUBLE;true;false", "AggregateBinary ba+* A:MATRIX B:MATRIX C:MATRIX [true] [false]"),
+])
+def test_parse(ins, expect):
+    assert parse_instruction(ins) == expect
+
+
+@pytest.mark.parametrize("ins,code,frag", [
+    (inst("tsmm", mat("X"), mat("C"), "UP"), native.E_INVALID, "MMTSJType"),
+    (inst("ba+*", mat("A"), mat("B"), mat("C"), "false"), native.E_INVALID, "checkNumFields"),
+    ("CP°ba+*°A°B°C°false°false", native.E_INVALID, "Not a GPU instruction"),
+    (inst("conv2d", mat("A"), mat("B")), native.E_UNSUPPORTED, "Invalid GPU Instruction Type"),
+    (inst("mmchain", mat("X"), mat("v"), mat("q"), "XtwXv"), native.E_INVALID, "ChainType"),
+    (inst("+*", mat("A"), mat("S"), mat("B"), mat("C")), native.E_INVALID, "scalar"),
+    ("", native.E_INVALID, "empty"),
+])
+def test_parse_errors(ins, code, frag):
+    with pytest.raises(native.NativeError) as ei:
+        parse_instruction(ins)
+    assert ei.value.code == code and frag in str(ei.value)
