@@ -183,11 +183,23 @@ __global__ void agg_row_kernel(const double* __restrict__ X, i64 rows, i64 cols,
   const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
   for (i64 base = warp * rows_per_warp; base < rows; base += nwarps * rows_per_warp) {
     const i64 r = base + lane / W;
-    Acc<OP> a;
+    Acc<OP> a, b;
     a.init();
+    b.init();
     if (r < rows) {
       const double* row = X + r * cols;
-      for (i64 j = sub; j < cols; j += W) a.push(ldg_stream(row + j));
+      i64 j = sub;
+      // four independent loads in flight per lane, two accumulator chains
+      for (; j + 3 * W < cols; j += 4 * W) {
+        const double x0 = ldg_stream(row + j), x1 = ldg_stream(row + j + W);
+        const double x2 = ldg_stream(row + j + 2 * W), x3 = ldg_stream(row + j + 3 * W);
+        a.push(x0);
+        b.push(x1);
+        a.push(x2);
+        b.push(x3);
+      }
+      for (; j < cols; j += W) a.push(ldg_stream(row + j));
+      a.merge(b.hi, b.lo);
     }
     group_merge(a, W);
     if (r < rows && sub == 0) {
@@ -246,14 +258,23 @@ __global__ void __launch_bounds__(256) agg_col_kernel(const double* __restrict__
   if (active) {
     const i64 rstep = (i64)RPB * gridDim.y;
     i64 r = (i64)blockIdx.y * RPB + rl;
-    for (; r + rstep < rows; r += 2 * rstep) {
-      const double u = ldg_stream(X + r * cols + c);
-      const double w = ldg_stream(X + (r + rstep) * cols + c);
-      a0.push(u);
-      a1.push(w);
+    Acc<OP> a2, a3;
+    a2.init();
+    a3.init();
+    for (; r + 3 * rstep < rows; r += 4 * rstep) {
+      const double u0 = ldg_stream(X + r * cols + c);
+      const double u1 = ldg_stream(X + (r + rstep) * cols + c);
+      const double u2 = ldg_stream(X + (r + 2 * rstep) * cols + c);
+      const double u3 = ldg_stream(X + (r + 3 * rstep) * cols + c);
+      a0.push(u0);
+      a1.push(u1);
+      a2.push(u2);
+      a3.push(u3);
     }
-    if (r < rows) a0.push(ldg_stream(X + r * cols + c));
+    for (; r < rows; r += rstep) a0.push(ldg_stream(X + r * cols + c));
     a0.merge(a1.hi, a1.lo);
+    a2.merge(a3.hi, a3.lo);
+    a0.merge(a2.hi, a2.lo);
   }
   if (rl < RPB) {
     sh[rl * CPB + cl] = a0.hi;
@@ -267,18 +288,42 @@ __global__ void __launch_bounds__(256) agg_col_kernel(const double* __restrict__
   }
 }
 template <int OP>
-__global__ void agg_col_finish_kernel(const double* __restrict__ partial, int splits, i64 cols, double* __restrict__ out, double scale) {
-  const i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
-  Acc<OP> a;
+__global__ void __launch_bounds__(256) agg_col_finish_kernel(const double* __restrict__ partial, int splits, i64 cols, double* __restrict__ out, double scale) {
+  __shared__ double sh_hi[8][33], sh_lo[8][33];
+  const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  const i64 c = (i64)blockIdx.x * 32 + cl;
+  Acc<OP> a, b;
   a.init();
-  for (int s = 0; s < splits; s++) a.merge(partial[((size_t)s * 2) * cols + c], partial[((size_t)s * 2 + 1) * cols + c]);
-  double v = a.result();
-  if (scale != 1.0) v = __ddiv_rn(v, scale);
-  out[c] = v;
+  b.init();
+  if (c < cols) {
+    int s = sl;
+    for (; s + 8 < splits; s += 16) {
+      const double h0 = __ldcg(partial + ((size_t)s * 2) * cols + c), l0 = __ldcg(partial + ((size_t)s * 2 + 1) * cols + c);
+      const double h1 = __ldcg(partial + ((size_t)(s + 8) * 2) * cols + c), l1 = __ldcg(partial + ((size_t)(s + 8) * 2 + 1) * cols + c);
+      a.merge(h0, l0);
+      b.merge(h1, l1);
+    }
+    for (; s < splits; s += 8) a.merge(__ldcg(partial + ((size_t)s * 2) * cols + c), __ldcg(partial + ((size_t)s * 2 + 1) * cols + c));
+    a.merge(b.hi, b.lo);
+  }
+  sh_hi[sl][cl] = a.hi;
+  sh_lo[sl][cl] = a.lo;
+  __syncthreads();
+  if (sl == 0 && c < cols) {
+    for (int q = 1; q < 8; q++) a.merge(sh_hi[q][cl], sh_lo[q][cl]);
+    double v = a.result();
+    if (scale != 1.0) v = __ddiv_rn(v, scale);
+    out[c] = v;
+  }
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+// lanes cooperating on one row: about 8 elements per lane, so narrow matrices put several rows in a warp
+inline int lanes_per_row(i64 cols) {
+  int W = 1;
+  while (W < 32 && (i64)W * 8 < cols) W <<= 1;
+  return W;
+}
 
 template <int OP>
 int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, double* out, double scale) {
@@ -296,8 +341,7 @@ int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, d
     return SYSML_OK;
   }
   if (dir == SYSML_DIR_ROW) {
-    int W = 32;
-    while (W > 1 && (W >> 1) >= cols) W >>= 1;
+    const int W = lanes_per_row(cols);
     const i64 rows_per_block = (256 / 32) * (32 / W);
     i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
     const i64 cap = (i64)ctx->sm_count * 16;
@@ -321,7 +365,7 @@ int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, d
   dim3 grid((unsigned)ctiles, (unsigned)splits);
   agg_col_kernel<OP><<<grid, 256, 2 * RPB * CPB * sizeof(double), ctx->stream>>>(X, rows, cols, CPB, RPB, (double*)ws);
   SYSML_LAUNCH_CHECK(ctx, "agg_col_kernel");
-  agg_col_finish_kernel<OP><<<(unsigned)((cols + 127) / 128), 128, 0, ctx->stream>>>((double*)ws, (int)splits, cols, out, scale);
+  agg_col_finish_kernel<OP><<<(unsigned)((cols + 31) / 32), 256, 0, ctx->stream>>>((double*)ws, (int)splits, cols, out, scale);
   SYSML_LAUNCH_CHECK(ctx, "agg_col_finish_kernel");
   return SYSML_OK;
 }
@@ -348,8 +392,7 @@ extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, 
     case SYSML_AGG_MININDEX: {
       if (dir != SYSML_DIR_ROW)
         return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row (LibMatrixAgg.java:1318-1329)");
-      int W = 32;
-      while (W > 1 && (W >> 1) >= cols) W >>= 1;
+      const int W = lanes_per_row(cols);
       const i64 rows_per_block = (256 / 32) * (32 / W);
       i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
       const i64 cap = (i64)ctx->sm_count * 16;

@@ -15,8 +15,8 @@
 // tile into registers ONCE, use them for the X*v partial dot products (warp-shuffle reduction),
 // release the stage, and reuse the same registers for the t(X)*tmp update, accumulating their
 // columns of the result in registers across all tiles of the CTA.  Per-CTA column partials go to
-// a scratch buffer; the last CTA to finish (atomic ticket) adds them up with compensated
-// (two-sum) arithmetic in a fixed order, so the result is deterministic run to run.
+// a scratch buffer; a small second kernel adds them up with compensated (two-sum) arithmetic in
+// a fixed order, so the result is deterministic run to run.
 //
 // Algorithmic bytes per launch: 8*n*m (X once) + 8*m (v) + 8*m (out) [+ 8*n (w)];  flops 4*n*m.
 #include "common.cuh"
@@ -31,7 +31,6 @@ struct StreamArgs {
   const double* w;   // n-vector: weights / y (CHAIN ct 1,2; VM: the left vector)
   double* out;       // CHAIN, VM: m ; MV: n
   double* partial;   // [gridDim.x * G][m] scratch (CHAIN, VM)
-  unsigned int* counter;
   i64 n;
   int m;
   int ct;
@@ -201,7 +200,7 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
 
   if (MODE == MODE_MV) return;
 
-  // ---- per-CTA column partials -> scratch; last CTA reduces them in a fixed order ----
+  // ---- per-CTA column partials -> scratch; colpartial_reduce_kernel adds them up in a fixed order ----
   {
     double* prow = a.partial + ((size_t)blockIdx.x * G + g) * m;
 #pragma unroll
@@ -210,26 +209,46 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
       if (j < m) prow[j] = c[k];
     }
   }
-  __threadfence();
-  named_bar_sync(15, NTC);
-  __shared__ unsigned int s_ticket;
-  if (tid == 0) s_ticket = atomicAdd(a.counter, 1u);
-  named_bar_sync(15, NTC);
-  if (s_ticket != gridDim.x - 1) return;
-  __threadfence();
-  const int nparts = gridDim.x * G;
-  for (int j = tid; j < m; j += NTC) {
-    CompSum acc0, acc1;
-    int b = 0;
-    for (; b + 1 < nparts; b += 2) {
-      acc0.add(__ldcg(a.partial + (size_t)b * m + j));
-      acc1.add(__ldcg(a.partial + (size_t)(b + 1) * m + j));
+}
+
+// out[j] = sum over the P partial rows of partial[p][j], compensated (two-sum) and in a fixed order.
+// 32 columns x 8 row-slices per CTA: 8 x (P/8) loads deep instead of one thread walking all P rows, so the
+// reduction costs a few microseconds instead of P dependent L2 round trips inside the streaming kernel.
+__global__ void __launch_bounds__(256) colpartial_reduce_kernel(const double* __restrict__ partial, int P, int m, double* __restrict__ out) {
+  __shared__ double sh_hi[8][33], sh_lo[8][33];
+  const int c = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + c;
+  CompSum a0, a1, a2, a3;
+  if (j < m) {
+    int p = sl;
+    for (; p + 24 < P; p += 32) {
+      const double x0 = __ldcg(partial + (size_t)p * m + j);
+      const double x1 = __ldcg(partial + (size_t)(p + 8) * m + j);
+      const double x2 = __ldcg(partial + (size_t)(p + 16) * m + j);
+      const double x3 = __ldcg(partial + (size_t)(p + 24) * m + j);
+      a0.add(x0);
+      a1.add(x1);
+      a2.add(x2);
+      a3.add(x3);
     }
-    if (b < nparts) acc0.add(__ldcg(a.partial + (size_t)b * m + j));
-    acc0.add(acc1);
-    a.out[j] = acc0.value();
+    for (; p < P; p += 8) a0.add(__ldcg(partial + (size_t)p * m + j));
+    a0.add(a1);
+    a2.add(a3);
+    a0.add(a2);
   }
-  if (tid == 0) *a.counter = 0u;
+  sh_hi[sl][c] = a0.hi;
+  sh_lo[sl][c] = a0.lo;
+  __syncthreads();
+  if (sl == 0 && j < m) {
+#pragma unroll
+    for (int q = 1; q < 8; q++) {
+      CompSum t;
+      t.hi = sh_hi[q][c];
+      t.lo = sh_lo[q][c];
+      a0.add(t);
+    }
+    out[j] = a0.value();
+  }
 }
 
 template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES>
@@ -252,10 +271,13 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
     int rc = sysml_workspace(ctx, (size_t)grid * G * a.m * sizeof(double), &ws);
     if (rc) return rc;
     a.partial = (double*)ws;
-    a.counter = ctx->counters + 0;
   }
   kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
   SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel");
+  if (MODE != MODE_MV) {
+    colpartial_reduce_kernel<<<(unsigned)((a.m + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)(grid * G), a.m, a.out);
+    SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel");
+  }
   return SYSML_OK;
 }
 
@@ -360,8 +382,12 @@ int vm_wide(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, 
   dim3 grid((unsigned)ctiles, (unsigned)splits);
   vm_wide_kernel<<<grid, threads, 0, ctx->stream>>>(X, y, partial, n, m);
   SYSML_LAUNCH_CHECK(ctx, "vm_wide_kernel");
-  vm_wide_reduce_kernel<<<(unsigned)ctiles, threads, 0, ctx->stream>>>(partial, out, (int)splits, m);
-  SYSML_LAUNCH_CHECK(ctx, "vm_wide_reduce_kernel");
+  if (m <= 0x7fffffffLL) {
+    colpartial_reduce_kernel<<<(unsigned)((m + 31) / 32), 256, 0, ctx->stream>>>(partial, (int)splits, (int)m, out);
+  } else {
+    vm_wide_reduce_kernel<<<(unsigned)ctiles, threads, 0, ctx->stream>>>(partial, out, (int)splits, m);
+  }
+  SYSML_LAUNCH_CHECK(ctx, "vm_wide reduce");
   return SYSML_OK;
 }
 
@@ -490,8 +516,8 @@ extern "C" int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const doubl
 // not the function is ever called, and nothing is allocated or freed by the call itself.
 //   - limit: cols <= SYSML_B200_NOALLOC_MAX_COLS (1024); larger inputs are rejected with SYSML_E_LIMIT;
 //   - footprint: NOALLOC_DOUBLES*8 + 256 bytes (about 2.4 MiB) of device memory per GPU, permanently;
-//   - the array is shared by every call on that GPU and keeps whatever the previous call left in it; the
-//     one word that must start at zero (the arrival ticket) is cleared on the stream before each launch;
+//   - the array is shared by every call on that GPU and keeps whatever the previous call left in it; a
+//     call overwrites every partial-sum row it later reads, so nothing in it needs to be cleared first;
 //   - two calls that overlap on the same GPU (different streams / contexts / host threads) race on the
 //     array and produce garbage: serialise them;
 //   - the very first call on each device looks up the device address of the array
@@ -501,7 +527,7 @@ namespace {
 
 constexpr int NOALLOC_MAX_COLS = SYSML_B200_NOALLOC_MAX_COLS;
 constexpr size_t NOALLOC_DOUBLES = (size_t)304 * 1024;  // (CTAs x row-groups) x cols partial sums
-// [0, NOALLOC_DOUBLES): per-CTA column partials; the 256 bytes after them hold the arrival ticket
+// [0, NOALLOC_DOUBLES): per-CTA column partials (the 256 bytes after them are padding)
 static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES + 32];
 
 constexpr int NOALLOC_MAX_DEVICES = 64;
@@ -540,10 +566,11 @@ int launch_cfg_noalloc(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm, doubl
   if (grid > a.total_tiles) grid = a.total_tiles;
   if (grid < 1) grid = 1;
   a.partial = scratch;
-  a.counter = reinterpret_cast<unsigned int*>(scratch + NOALLOC_DOUBLES);
-  SYSML_CUDA(ctx, cudaMemsetAsync(a.counter, 0, 256, ctx->stream));  // the ticket must start at zero
   kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
   SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel (noalloc)");
+  // every partial row that is read below was written by the launch above: nothing has to start at zero
+  colpartial_reduce_kernel<<<(unsigned)((a.m + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)(grid * G), a.m, a.out);
+  SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel (noalloc)");
   return SYSML_OK;
 }
 

@@ -41,8 +41,8 @@ __device__ __forceinline__ double group_sum(double v) {
 
 inline int pick_lanes(i64 nnz, i64 rows) {
   const double mean = rows > 0 ? (double)nnz / (double)rows : 0.0;
-  int L = 2;
-  while (L < 32 && L < mean) L <<= 1;
+  int L = 2;  // largest power of two <= mean (at least 2): short rows share a warp, few lanes idle
+  while (L < 32 && 2 * L <= mean) L <<= 1;
   return L;
 }
 inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
@@ -306,73 +306,86 @@ __global__ void csr_to_dense_kernel(const int* __restrict__ rp, const int* __res
 }
 
 // ---------------- sparse aggregates ----------------
-// per-row: sum / sumsq (op 0/1), max / min (2/3) with the implicit-zero correction, rowIndexMax/Min (4/5)
+// per-row: sum / sumsq (op 0/1), max / min (2/3) with the implicit-zero correction, rowIndexMax/Min (4/5).
+// L lanes per row (L chosen like SpMV from the mean nnz/row), consecutive rows in consecutive lane groups.
+template <int L>
 __global__ void __launch_bounds__(256) csr_agg_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
                                                           const double* __restrict__ va, i64 rows, i64 cols, int op,
                                                           double* __restrict__ out) {
   const int lane = threadIdx.x & 31;
+  const int sub = lane & (L - 1);
+  constexpr int RPW = 32 / L;
   const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
-  for (i64 r = warp; r < rows; r += nwarps) {
-    const int lo = rp[r], hi = rp[r + 1];
+  for (i64 base = warp * RPW; base < rows; base += nwarps * RPW) {
+    const i64 r = base + lane / L;
+    int lo = 0, hi = 0;
+    if (r < rows) {
+      lo = __ldg(rp + r);
+      hi = __ldg(rp + r + 1);
+    }
     const int alen = hi - lo;
     if (op <= 1) {
       CompSum s;
-      for (int k = lo + lane; k < hi; k += 32) {
-        const double x = va[k];
+      for (int k = lo + sub; k < hi; k += L) {
+        const double x = ldg_stream(va + k);
         s.add(op == 1 ? __dmul_rn(x, x) : x);
       }
-      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int o = L >> 1; o > 0; o >>= 1) {
         CompSum t;
         t.hi = __shfl_xor_sync(0xffffffffu, s.hi, o);
         t.lo = __shfl_xor_sync(0xffffffffu, s.lo, o);
         s.add(t);
       }
-      if (lane == 0) out[r] = (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
+      if (r < rows && sub == 0) out[r] = (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
     } else if (op <= 3) {
       double t = (op == 2) ? -CUDART_INF : CUDART_INF;
-      for (int k = lo + lane; k < hi; k += 32) t = (op == 2) ? jmax(t, va[k]) : jmin(t, va[k]);
-      for (int o = 16; o > 0; o >>= 1) {
+      for (int k = lo + sub; k < hi; k += L) t = (op == 2) ? jmax(t, ldg_stream(va + k)) : jmin(t, ldg_stream(va + k));
+#pragma unroll
+      for (int o = L >> 1; o > 0; o >>= 1) {
         const double u = __shfl_xor_sync(0xffffffffu, t, o);
         t = (op == 2) ? jmax(t, u) : jmin(t, u);
       }
       if (alen < cols) t = (op == 2) ? jmax(t, 0.0) : jmin(t, 0.0);
-      if (lane == 0) out[r] = t;
+      if (r < rows && sub == 0) out[r] = t;
     } else {
       // LibMatrixAgg.s_uarimxx / s_uarimin (LibMatrixAgg.java:2536-2614)
       const bool ismax = (op == 4);
       double best = ismax ? -CUDART_INF : CUDART_INF;
       int idx = -1;  // position within the row
-      for (int k = lo + lane; k < hi; k += 32) {
-        const double x = va[k];
+      for (int k = lo + sub; k < hi; k += L) {
+        const double x = ldg_stream(va + k);
         const bool take = ismax ? (x >= best) : (x <= best);
         idx = take ? (k - lo) : idx;
         best = take ? x : best;
       }
-      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int o = L >> 1; o > 0; o >>= 1) {
         const double ob = __shfl_xor_sync(0xffffffffu, best, o);
         const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
         const bool other = (oi >= 0) && ((idx < 0) || (ismax ? (ob > best) : (ob < best)) || (ob == best && oi > idx));
         best = other ? ob : best;
         idx = other ? oi : idx;
       }
-      double res;
-      if (alen == 0) {
-        res = (double)cols;  // empty row: last column, value 0 (:2559-2563)
-      } else {
-        res = (idx >= 0) ? (double)ci[lo + idx] + 1.0 : 0.0;
-        const double bv = (idx >= 0) ? best : CUDART_NAN;
-        const bool zero_wins = ismax ? (0.0 > bv) : (0.0 < bv);  // strictly: Builtin.execute(0,v)==1
-        if (alen < cols && zero_wins) {
-          // last column that holds an implicit zero: walk back while the tail is densely occupied
-          // (all lanes compute the same answer; rows are short or the walk is short)
-          i64 ix = cols - 1;
-          for (int j = hi - 1; j >= lo; j--, ix--)
-            if (ci[j] != ix) break;
-          res = (double)(ix + 1);
+      if (r < rows && sub == 0) {
+        double res;
+        if (alen == 0) {
+          res = (double)cols;  // empty row: last column, value 0 (:2559-2563)
+        } else {
+          res = (idx >= 0) ? (double)ci[lo + idx] + 1.0 : 0.0;
+          const double bv = (idx >= 0) ? best : CUDART_NAN;
+          const bool zero_wins = ismax ? (0.0 > bv) : (0.0 < bv);  // strictly: Builtin.execute(0,v)==1
+          if (alen < cols && zero_wins) {
+            // last column that holds an implicit zero: walk back while the tail is densely occupied
+            i64 ix = cols - 1;
+            for (int j = hi - 1; j >= lo; j--, ix--)
+              if (ci[j] != ix) break;
+            res = (double)(ix + 1);
+          }
         }
+        out[r] = res;
       }
-      if (lane == 0) out[r] = res;
     }
   }
 }
@@ -645,7 +658,15 @@ extern "C" int sysml_b200_agg_unary_csr(sysml_b200_ctx* ctx, const int32_t* rowp
   if (!is_sum && !is_mm && !is_idx) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "agg_unary_csr: opcode %d on CSR input", op);
   if (is_idx && dir != SYSML_DIR_ROW) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row");
   if (dir == SYSML_DIR_ROW) {
-    csr_agg_row_kernel<<<warp_rows_grid(ctx, rows), 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out);
+    const int L = pick_lanes(nnz, rows);
+    const unsigned g = rows_grid(ctx, rows, L, 256);
+    switch (L) {
+      case 2: csr_agg_row_kernel<2><<<g, 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out); break;
+      case 4: csr_agg_row_kernel<4><<<g, 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out); break;
+      case 8: csr_agg_row_kernel<8><<<g, 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out); break;
+      case 16: csr_agg_row_kernel<16><<<g, 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out); break;
+      default: csr_agg_row_kernel<32><<<g, 256, 0, ctx->stream>>>(rowptr, colind, val, rows, cols, op, out); break;
+    }
     SYSML_LAUNCH_CHECK(ctx, "csr_agg_row_kernel");
     return SYSML_OK;
   }
