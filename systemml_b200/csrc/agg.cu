@@ -325,6 +325,278 @@ inline int lanes_per_row(i64 cols) {
   return W;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Streamed variants for matrices with short rows (cols <= 1024): a tile of R full rows is ONE contiguous
+// span, so a producer warp feeds a 3-deep shared-memory ring with 1-D bulk copies (cp.async.bulk, the
+// TMA engine) exactly like the mmchain kernel; bytes in flight no longer depend on how many loads the
+// reducing threads can issue, which is what held the direct-load kernels at ~50 % of HBM bandwidth on
+// 10M x 50 (ncu: long-scoreboard stalls, 37-43 % DRAM utilisation).
+//   ROWS : L lanes per row reduce out of shared memory (sum / sumsq / min / max / prod, rowIndexMax/Min)
+//   COLS : thread (column, row-lane) accumulators live in registers across all tiles of the CTA
+// ------------------------------------------------------------------------------------------------
+constexpr int AS_THREADS = 256;  // consumer threads (+32 producer)
+constexpr int AS_STAGES = 3;
+
+struct AggStreamArgs {
+  const double* X;
+  i64 rows;
+  int cols;
+  int R;            // rows per tile
+  int use_tma;
+  i64 total_tiles;
+  double* out;      // ROWS: rows results; COLS: unused
+  double* partial;  // COLS: [gridDim.x][2][cols]
+  double scale;
+  int L;            // ROWS: lanes per row
+};
+
+template <int OP, int KIND, int KC>  // KIND 0: per-row value, 1: per-row index (OP = K_MAX / K_MIN), 2: per-column (KC column chunks per thread)
+__global__ void __launch_bounds__(AS_THREADS + 32) aggstream_kernel(const AggStreamArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
+  uint64_t* empty = full + AS_STAGES;
+  double* tiles = reinterpret_cast<double*>(smem_raw + 128);
+  const int tid = threadIdx.x;
+  const int cols = a.cols, R = a.R;
+  const size_t stage_elems = (size_t)R * cols;
+  if (tid == 0) {
+    for (int s = 0; s < AS_STAGES; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], AS_THREADS);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (tid >= AS_THREADS) {  // producer warp
+    const int lane = tid - AS_THREADS;
+    const uint64_t pol = l2_policy_evict_first();
+    int it = 0;
+    for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+      const int s = it % AS_STAGES;
+      mbar_wait(&empty[s], ((uint32_t)(it / AS_STAGES) & 1u) ^ 1u);
+      const i64 r0 = tile * R;
+      const i64 nr = (a.rows - r0 < R) ? (a.rows - r0) : R;
+      double* dst = tiles + (size_t)s * stage_elems;
+      const double* src = a.X + r0 * (i64)cols;
+      if (a.use_tma && nr == R) {
+        if (lane == 0) {
+          const uint32_t bytes = (uint32_t)(stage_elems * sizeof(double));
+          mbar_expect_tx(&full[s], bytes);
+          bulk_g2s(dst, src, bytes, &full[s], pol);
+        }
+      } else {
+        const i64 valid = nr * (i64)cols;  // rows past the end are never read by the consumers
+        for (i64 i = lane; i < valid; i += 32) dst[i] = ldg_stream(src + i);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
+      }
+    }
+    return;
+  }
+
+  const int lane = tid & 31, warp = tid >> 5;
+  if (KIND == 2) {
+    // ---- per-column: thread owns column chunk(s) cl + CPB*k, row lane rl ----
+    const int CPB = cols < AS_THREADS ? cols : AS_THREADS;
+    const int RPB = AS_THREADS / CPB;
+    const int cl = tid % CPB, rl = tid / CPB;
+    Acc<OP> acc[KC], acc2[KC];  // two chains per column: even / odd rows of the thread
+#pragma unroll
+    for (int k = 0; k < KC; k++) {
+      acc[k].init();
+      acc2[k].init();
+    }
+    int it = 0;
+    for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+      const int s = it % AS_STAGES;
+      const i64 r0 = tile * R;
+      const int nr = (int)((a.rows - r0 < R) ? (a.rows - r0) : R);
+      mbar_wait(&full[s], (uint32_t)(it / AS_STAGES) & 1u);
+      const double* T = tiles + (size_t)s * stage_elems;
+      if (rl < RPB) {
+        int rr = rl;
+        for (; rr + RPB < nr; rr += 2 * RPB) {
+#pragma unroll
+          for (int k = 0; k < KC; k++) {
+            const int c = cl + CPB * k;
+            if (KC == 1 || c < cols) {
+              const double u = T[rr * cols + c], w = T[(rr + RPB) * cols + c];
+              acc[k].push(u);
+              acc2[k].push(w);
+            }
+          }
+        }
+        if (rr < nr) {
+#pragma unroll
+          for (int k = 0; k < KC; k++) {
+            const int c = cl + CPB * k;
+            if (KC == 1 || c < cols) acc[k].push(T[rr * cols + c]);
+          }
+        }
+      }
+      mbar_arrive(&empty[s]);
+    }
+#pragma unroll
+    for (int k = 0; k < KC; k++) acc[k].merge(acc2[k].hi, acc2[k].lo);
+    // combine the RPB row lanes through shared memory (reuse stage 0 after everyone is done with it)
+    named_bar_sync(1, AS_THREADS);
+    double* sh = tiles;  // [2][RPB][cols]
+    if (rl < RPB) {
+#pragma unroll
+      for (int k = 0; k < KC; k++) {
+        const int c = cl + CPB * k;
+        if (c < cols) {
+          sh[(size_t)rl * cols + c] = acc[k].hi;
+          sh[(size_t)(RPB + rl) * cols + c] = acc[k].lo;
+        }
+      }
+    }
+    named_bar_sync(1, AS_THREADS);
+    if (rl == 0) {
+#pragma unroll
+      for (int k = 0; k < KC; k++) {
+        const int c = cl + CPB * k;
+        if (c < cols) {
+          for (int q = 1; q < RPB; q++) acc[k].merge(sh[(size_t)q * cols + c], sh[(size_t)(RPB + q) * cols + c]);
+          a.partial[((size_t)blockIdx.x * 2) * cols + c] = acc[k].hi;
+          a.partial[((size_t)blockIdx.x * 2 + 1) * cols + c] = acc[k].lo;
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- per-row: L lanes per row ----
+  const int L = a.L;
+  const int sub = lane & (L - 1);
+  const int rpw = 32 / L;                      // rows per warp pass
+  const int rows_per_pass = rpw * (AS_THREADS / 32);
+  int it = 0;
+  for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
+    const int s = it % AS_STAGES;
+    const i64 r0 = tile * R;
+    const int nr = (int)((a.rows - r0 < R) ? (a.rows - r0) : R);
+    mbar_wait(&full[s], (uint32_t)(it / AS_STAGES) & 1u);
+    const double* T = tiles + (size_t)s * stage_elems;
+    for (int rb = warp * rpw; rb < nr; rb += 2 * rows_per_pass) {
+      // two rows per lane group per pass (independent chains hide the FP64 latency)
+      const int rr0 = rb + lane / L, rr1 = rr0 + rows_per_pass;
+      const bool live0 = rr0 < nr, live1 = rr1 < nr;
+      const double* row0 = T + (size_t)(live0 ? rr0 : 0) * cols;
+      const double* row1 = T + (size_t)(live1 ? rr1 : 0) * cols;
+      if (KIND == 0) {
+        Acc<OP> x0, x1;
+        x0.init();
+        x1.init();
+        for (int j = sub; j < cols; j += L) {
+          const double u = row0[j], w = row1[j];
+          if (live0) x0.push(u);
+          if (live1) x1.push(w);
+        }
+        group_merge(x0, L);
+        group_merge(x1, L);
+        if (sub == 0) {
+          if (live0) {
+            double v = x0.result();
+            if (a.scale != 1.0) v = __ddiv_rn(v, a.scale);
+            a.out[r0 + rr0] = v;
+          }
+          if (live1) {
+            double v = x1.result();
+            if (a.scale != 1.0) v = __ddiv_rn(v, a.scale);
+            a.out[r0 + rr1] = v;
+          }
+        }
+      } else {
+        constexpr bool ISMAX = (OP == K_MAX);
+        double best0 = ISMAX ? -CUDART_INF : CUDART_INF, best1 = best0;
+        int idx0 = -1, idx1 = -1;
+        for (int j = sub; j < cols; j += L) {
+          const double u = row0[j], w = row1[j];
+          const bool t0 = live0 && (ISMAX ? (u >= best0) : (u <= best0));
+          const bool t1 = live1 && (ISMAX ? (w >= best1) : (w <= best1));
+          idx0 = t0 ? j : idx0;
+          best0 = t0 ? u : best0;
+          idx1 = t1 ? j : idx1;
+          best1 = t1 ? w : best1;
+        }
+        for (int o = L >> 1; o > 0; o >>= 1) {
+          const double ob0 = __shfl_xor_sync(0xffffffffu, best0, o), ob1 = __shfl_xor_sync(0xffffffffu, best1, o);
+          const int oi0 = __shfl_xor_sync(0xffffffffu, idx0, o), oi1 = __shfl_xor_sync(0xffffffffu, idx1, o);
+          const bool b0 = (oi0 >= 0) && ((idx0 < 0) || (ISMAX ? (ob0 > best0) : (ob0 < best0)) || (ob0 == best0 && oi0 > idx0));
+          const bool b1 = (oi1 >= 0) && ((idx1 < 0) || (ISMAX ? (ob1 > best1) : (ob1 < best1)) || (ob1 == best1 && oi1 > idx1));
+          best0 = b0 ? ob0 : best0;
+          idx0 = b0 ? oi0 : idx0;
+          best1 = b1 ? ob1 : best1;
+          idx1 = b1 ? oi1 : idx1;
+        }
+        if (sub == 0) {
+          if (live0) a.out[r0 + rr0] = (double)(idx0 + 1);
+          if (live1) a.out[r0 + rr1] = (double)(idx1 + 1);
+        }
+      }
+    }
+    mbar_arrive(&empty[s]);
+  }
+}
+
+inline bool aggstream_ok(const double* X, i64 rows, i64 cols, bool per_row) {
+  // per-row results need enough rows per tile to keep all consumer warps busy: short rows only
+  return cols >= 1 && cols <= (per_row ? 128 : 2048) && rows * cols >= (i64)1 << 16 && (reinterpret_cast<uintptr_t>(X) & 7) == 0;
+}
+
+template <int OP, int KIND>
+int run_aggstream(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, double* out, double scale) {
+  AggStreamArgs a{};
+  a.X = X; a.rows = rows; a.cols = (int)cols; a.out = out; a.scale = scale;
+  // ~32 KB tiles, an even number of rows (16-byte multiples for the bulk copy), at least one pass of rows
+  int R = (int)((32 * 1024) / (cols * 8));
+  if (R < 2) R = 2;
+  R &= ~1;
+  if ((i64)R > rows) R = (int)((rows + 1) & ~(i64)1);
+  a.L = lanes_per_row(cols);
+  if (KIND != 2) {
+    // per-row kinds: every warp handles 2 * (32 / L) rows per pass; make the tile a whole number of passes
+    const int pass = 2 * (32 / a.L) * (AS_THREADS / 32);
+    if (R >= pass) R = (R / pass) * pass;
+    else if ((i64)pass * cols * 8 <= 64 * 1024) R = pass;
+  }
+  a.R = R;
+  a.total_tiles = (rows + R - 1) / R;
+  const size_t stage_bytes = (size_t)R * cols * 8;
+  a.use_tma = ((reinterpret_cast<uintptr_t>(X) & 15) == 0) && (stage_bytes % 16 == 0) && stage_bytes < (1u << 20);
+  const int CPB = (int)(cols < AS_THREADS ? cols : AS_THREADS), RPB = AS_THREADS / CPB;
+  size_t smem = 128 + AS_STAGES * stage_bytes;
+  if (KIND == 2 && (size_t)2 * RPB * cols * 8 > stage_bytes * AS_STAGES) smem = 128 + (size_t)2 * RPB * cols * 8;
+  const int kc_needed = (int)((cols + CPB - 1) / CPB);
+  void (*kern)(const AggStreamArgs) = aggstream_kernel<OP, KIND, 1>;
+  if (KIND == 2) {
+    if (kc_needed > 4) kern = aggstream_kernel<OP, 2, 8>;
+    else if (kc_needed > 2) kern = aggstream_kernel<OP, 2, 4>;
+    else if (kc_needed > 1) kern = aggstream_kernel<OP, 2, 2>;
+    else kern = aggstream_kernel<OP, 2, 1>;
+  }
+  SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  i64 grid = (i64)ctx->sm_count * 2;
+  if (grid > a.total_tiles) grid = a.total_tiles;
+  if (grid < 1) grid = 1;
+  if (KIND == 2) {
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)grid * 2 * cols * sizeof(double), &ws);
+    if (rc) return rc;
+    a.partial = (double*)ws;
+  }
+  kern<<<(unsigned)grid, AS_THREADS + 32, smem, ctx->stream>>>(a);
+  SYSML_LAUNCH_CHECK(ctx, "aggstream_kernel");
+  if (KIND == 2) {
+    agg_col_finish_kernel<OP><<<(unsigned)((cols + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)grid, cols, out, scale);
+    SYSML_LAUNCH_CHECK(ctx, "agg_col_finish_kernel");
+  }
+  return SYSML_OK;
+}
+
 template <int OP>
 int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, double* out, double scale) {
   const i64 len = rows * cols;
@@ -340,6 +612,8 @@ int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, d
     SYSML_LAUNCH_CHECK(ctx, "agg_all_kernel");
     return SYSML_OK;
   }
+  if (dir == SYSML_DIR_ROW && aggstream_ok(X, rows, cols, true)) return run_aggstream<OP, 0>(ctx, X, rows, cols, out, scale);
+  if (dir == SYSML_DIR_COL && aggstream_ok(X, rows, cols, false)) return run_aggstream<OP, 2>(ctx, X, rows, cols, out, scale);
   if (dir == SYSML_DIR_ROW) {
     const int W = lanes_per_row(cols);
     const i64 rows_per_block = (256 / 32) * (32 / W);
@@ -392,6 +666,8 @@ extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, 
     case SYSML_AGG_MININDEX: {
       if (dir != SYSML_DIR_ROW)
         return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row (LibMatrixAgg.java:1318-1329)");
+      if (aggstream_ok(X, rows, cols, true))
+        return op == SYSML_AGG_MAXINDEX ? run_aggstream<K_MAX, 1>(ctx, X, rows, cols, out, 1.0) : run_aggstream<K_MIN, 1>(ctx, X, rows, cols, out, 1.0);
       const int W = lanes_per_row(cols);
       const i64 rows_per_block = (256 / 32) * (32 / W);
       i64 blocks = (rows + rows_per_block - 1) / rows_per_block;

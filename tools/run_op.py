@@ -27,6 +27,11 @@ elif op == "matmult":
     else:
         A, B, o = g.rand(M, K, seed=1), g.rand(K, N, seed=2), g.empty(M, N)
         fn = lambda: g.call("sysml_b200_matmult_dense", p_(A), p_(B), p_(o), M, K, K, N, 0, 0)
+elif op == "agg":
+    n, m, aop, d = a
+    X = g.rand(n, m, seed=1)
+    o = g.empty(max(n, m), 1)
+    fn = lambda: g.call("sysml_b200_agg_unary_dense", p_(X), n, m, aop, d, p_(o))
 else:
     raise SystemExit("unknown op")
 for _ in range(3):
