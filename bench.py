@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--no-tsmm", action="store_true", help="skip the auxiliary tsmm measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
+                    help="N>1: 'fused' = sum exchange inside the mmchain finishing kernel over NVLink peer memory; 'nccl' = separate all-reduce")
     return ap.parse_args()
 
 
@@ -199,7 +201,8 @@ def main():
     import numpy as np
     import torch
     import torch.distributed as dist
-    from systemml_b200 import GPUContext, GPUObject, LibMatrixB200 as L
+    from systemml_b200 import Communicator, GPUContext, GPUObject, LibMatrixB200 as L
+    from systemml_b200.gpu_context import torch_exchange
     from systemml_b200.sharding import row_shard
 
     rank = int(os.environ.get("RANK", "0"))
@@ -221,6 +224,9 @@ def main():
     # all library work is queued on torch's current stream so that torch events and NCCL see it in order
     stream = torch.cuda.current_stream()
     g = GPUContext(local_rank, stream=stream.cuda_stream)
+    comm = None
+    if world > 1 and args.collective == "fused":
+        comm = Communicator(g, rank, world, max(m, 32), torch_exchange())
 
     def tensor(*shape):
         return torch.empty(*shape, dtype=torch.float64, device=dev)
@@ -254,11 +260,14 @@ def main():
         if record:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
-        g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+        if comm is not None:
+            g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+        else:
+            g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
         if record:
             e1.record(stream)
             ev_pairs.append((e0, e1))
-        if world > 1:
+        if world > 1 and comm is None:
             dist.all_reduce(vecs["q"])
         g.call("sysml_b200_matmult_dense", p_(P), p_(Q), p_(PQ), 1, m, m, 1, 0, 0)               # pq = t(p) %*% q
         g.call("sysml_b200_binary_mm", p_(NR2), p_(PQ), p_(A_), 1, 1, 0, L.BINARY_OPS["/"])     # a = nr2 / pq
@@ -320,9 +329,12 @@ def main():
         def e2e_step(state):
             r, beta, nr2 = state
             g.call("sysml_b200_h2d", p_(P), C.c_void_p(hp.data_ptr()), 8 * m)          # host -> device: p
-            g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
-            if world > 1:
-                dist.all_reduce(vecs["q"])
+            if comm is not None:
+                g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+            else:
+                g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+                if world > 1:
+                    dist.all_reduce(vecs["q"])
             g.call("sysml_b200_d2h", C.c_void_p(hq.data_ptr()), p_(Q), 8 * m)          # device -> host: q (syncs)
             pq = float(p_np @ q_np)
             a = nr2 / pq if pq != 0 else 0.0
@@ -420,7 +432,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
             "config": {"workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1]), row-sharded %d x %d rows/GPU"
-                       % (n, m, world, nloc), "parallelism": "row-shard x%d + all-reduce(m doubles)" % world,
+                       % (n, m, world, nloc), "parallelism": "row-shard x%d + all-reduce(m doubles) [%s]" % (world, ("fused into the mmchain finishing kernel over NVLink peer memory" if comm is not None else "NCCL") if world > 1 else "none"),
                        "l2": "inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush needed" % (8.0 * nloc * m / 1e9),
                        "x_distribution": "U(-1,1) counter-based generator, seed 1"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
@@ -430,7 +442,10 @@ def main():
             line["tsmm"] = tsmm
         print(json.dumps(line), flush=True)
     if world > 1:
+        torch.cuda.synchronize()
         dist.barrier()
+        if comm is not None:
+            comm.destroy()
         dist.destroy_process_group()
     return 0
 

@@ -265,6 +265,30 @@ int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
                             const double* val, int64_t rows, int64_t cols, double* X);
 
 /* ------------------------------------------------------------------------------------------------
+ * Multi-GPU sum exchange over NVLink peer memory (one process per GPU on one box, world <= 8).
+ * Replaces the aggregation step of SystemML's distributed tsmm / mmchain plan, RDDAggregateUtils.sumStable
+ * (J/runtime/instructions/spark/utils/RDDAggregateUtils.java:58-70, used by MapmmChainSPInstruction and
+ * TsmmSPInstruction): X is row-sharded, every rank computes on its shard, the m-sized partials are added.
+ * The reference has no GPU collective at all.  The sum is done INSIDE the kernel that finishes the local
+ * result (P2P stores into every peer's mailbox + per-CTA flags), not by a separate NCCL call.
+ *   comm_create : allocates this rank's mailbox (capacity max_values doubles per message) and returns its
+ *                 64-byte cudaIpcMemHandle in handle_out64; exchange the handles of all ranks by any means
+ *                 (the bench uses torch.distributed.all_gather) and pass them, in rank order, to comm_connect.
+ *   Every rank must issue the same sequence of collective calls with the same sizes.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct sysml_b200_comm sysml_b200_comm;
+int sysml_b200_comm_create(sysml_b200_ctx* ctx, int rank, int world, int64_t max_values,
+                           sysml_b200_comm** out, void* handle_out64);
+int sysml_b200_comm_connect(sysml_b200_comm* comm, const void* all_handles);
+int sysml_b200_comm_destroy(sysml_b200_comm* comm);
+/* buf[0..len) <- sum over ranks, in place, identical bits on every rank (len <= max_values). */
+int sysml_b200_allreduce_sum(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len);
+/* mmchain on the local row shard fused with the sum over ranks (m <= 4096). */
+int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X,
+                                       const double* v, const double* w, double* out, int64_t n,
+                                       int64_t m, int chain_type);
+
+/* ------------------------------------------------------------------------------------------------
  * Synthetic data (scripts/datagen/genRandData4LinearRegression.dml uses Rand(min,max,pdf=uniform,seed)).
  * Counter-based: cell i of the GLOBAL array gets hash(seed, offset + i), so any row shard equals the
  * same rows of the full matrix.  No reference GPU counterpart (RandGPU does not exist); the CPU twin is

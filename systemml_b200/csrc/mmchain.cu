@@ -21,6 +21,9 @@
 // Algorithmic bytes per launch: 8*n*m (X once) + 8*m (v) + 8*m (out) [+ 8*n (w)];  flops 4*n*m.
 #include "common.cuh"
 
+struct sysml_b200_comm;
+int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out);
+
 namespace {
 
 enum { MODE_CHAIN = 0, MODE_MV = 1, MODE_VM = 2 };
@@ -36,6 +39,7 @@ struct StreamArgs {
   int ct;
   i64 total_tiles;
   int use_tma;
+  sysml_b200_comm* comm;  // host side only: non-null -> the finishing kernel also does the cross-GPU sum
 };
 
 // NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
@@ -275,6 +279,7 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
   SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel");
   if (MODE != MODE_MV) {
+    if (a.comm) return sysml_launch_allreduce_finish(ctx, a.comm, a.partial, (int)(grid * G), a.m, a.out);
     colpartial_reduce_kernel<<<(unsigned)((a.m + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)(grid * G), a.m, a.out);
     SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel");
   }
@@ -457,6 +462,25 @@ extern "C" int sysml_b200_mmchain_dense(sysml_b200_ctx* ctx, const double* X, co
     SYSML_LAUNCH_CHECK(ctx, "apply_weights_kernel");
   }
   return vm_wide(ctx, X, t, out, n, m, tbytes);
+}
+
+// mmchain on this rank's row shard + sum over all ranks of the communicator, in one finishing kernel
+// (no NCCL call).  Every rank must make the call; out (m doubles) ends bit-identical on all of them.
+extern "C" int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X, const double* v,
+                                                  const double* w, double* out, int64_t n, int64_t m, int chain_type) {
+  SYSML_ENTER(ctx);
+  int rc = validate_chain(ctx, X, v, w, out, n, m, chain_type);
+  if (rc) return rc;
+  if (!comm) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_allreduce: null communicator");
+  if (m == 0) return SYSML_OK;
+  if (m > 4096) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_allreduce: more than 4096 columns; run mmchain_dense then allreduce_sum");
+  if (n == 0) {  // an empty shard still has to take part in the exchange
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
+    return sysml_launch_allreduce_finish(ctx, comm, out, 1, (int)m, out);
+  }
+  StreamArgs a{};
+  a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type; a.comm = comm;
+  return launch_rowstream<MODE_CHAIN>(ctx, a);
 }
 
 extern "C" int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const double* X, const double* h_v,

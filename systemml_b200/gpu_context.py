@@ -214,3 +214,50 @@ class GPUObject:
             self.csr = None
 
     free = clearData
+
+
+class Communicator:
+    """Sum exchange between the GPUs of one box through NVLink peer memory (csrc/comm.cu).
+
+    The 64-byte IPC handle of every rank's mailbox has to reach all ranks once; `exchange` is any callable
+    that maps this rank's bytes to the list of all ranks' bytes in rank order (e.g. built on
+    torch.distributed.all_gather)."""
+
+    def __init__(self, gctx, rank, world, max_values, exchange):
+        self.gctx = gctx
+        self.rank, self.world = rank, world
+        lib = gctx._lib
+        h = C.c_void_p()
+        handle = (C.c_ubyte * 64)()
+        native.check(gctx.handle, lib.sysml_b200_comm_create(gctx.handle, rank, world, int(max_values), C.byref(h), handle))
+        self.handle = h
+        blobs = exchange(bytes(handle))
+        assert len(blobs) == world and all(len(b) == 64 for b in blobs)
+        joined = b"".join(blobs)
+        buf = (C.c_ubyte * len(joined)).from_buffer_copy(joined)
+        native.check(gctx.handle, lib.sysml_b200_comm_connect(self.handle, buf))
+
+    def allreduce_sum(self, ptr, length):
+        self.gctx.call("sysml_b200_allreduce_sum", self.handle, C.c_void_p(ptr), int(length))
+
+    def destroy(self):
+        if self.handle:
+            self.gctx._lib.sysml_b200_comm_destroy(self.handle)
+            self.handle = None
+
+
+def torch_exchange(group=None):
+    """exchange callable for Communicator built on torch.distributed (any backend)."""
+    import torch
+    import torch.distributed as dist
+
+    def ex(mine):
+        world = dist.get_world_size(group)
+        backend = dist.get_backend(group)
+        dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+        t = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t, group=group)
+        return [bytes(o.cpu().tolist()) for o in outs]
+
+    return ex

@@ -58,6 +58,11 @@ SIGNATURES = {
     "sysml_b200_dense_to_csr": (ci, [vp, vp, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_csr_to_dense": (ci, [vp, vp, vp, vp, i64, i64, vp]),
     "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),
+    "sysml_b200_comm_create": (ci, [vp, ci, ci, i64, pvp, vp]),
+    "sysml_b200_comm_connect": (ci, [vp, vp]),
+    "sysml_b200_comm_destroy": (ci, [vp]),
+    "sysml_b200_allreduce_sum": (ci, [vp, vp, vp, i64]),
+    "sysml_b200_mmchain_dense_allreduce": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci]),
     # ---- include/sysml_b200_host.h ----
     "sysml_b200_ec_create": (ci, [ci, dbl, ci, i64, pvp]),
     "sysml_b200_ec_destroy": (ci, [vp]),
