@@ -8,8 +8,12 @@ fixed; per-GPU rows = 10M / N in whole 1000-row blocks).  One "step" = one CG it
     q = t(X) %*% (w * (X %*% p))            <- mmchain XtwXv, ONE pass over the shard (the hot kernel)
     [N > 1]  all-reduce(q) over NCCL / NVLink (m = 1000 doubles)
     pq = t(p) %*% q ; a = nr2 / pq ; beta += a*p ; r += a*q ; nr2' = t(r) %*% r ; p = -r + (nr2'/nr2)*p
+        (one fused kernel, sysml_b200_cg_vector_update; --unfused-tail runs it as the ~11 separate
+        m-sized instructions the reference's compiler would emit)
 
 all on the device through the C ABI of include/sysml_b200.h (no host synchronisation inside a step).
+For N > 1 the all-reduce is fused into the mmchain finishing kernel over NVLink peer memory
+(sysml_b200_mmchain_dense_allreduce); --collective nccl uses a separate NCCL all-reduce instead.
 
   value   : CG iterations per second, whole job, inputs resident in HBM (CUDA events, max over ranks)
   e2e     : the same iteration driven from HOST buffers through the reference-facing call shape: every
@@ -52,6 +56,7 @@ def parse():
     ap.add_argument("--no-tsmm", action="store_true", help="skip the auxiliary tsmm measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--unfused-tail", action="store_true", help="run the m-vector CG algebra as ~11 separate instructions instead of the fused kernel")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: 'fused' = sum exchange inside the mmchain finishing kernel over NVLink peer memory; 'nccl' = separate all-reduce")
     return ap.parse_args()
@@ -269,17 +274,21 @@ def main():
             ev_pairs.append((e0, e1))
         if world > 1 and comm is None:
             dist.all_reduce(vecs["q"])
-        g.call("sysml_b200_matmult_dense", p_(P), p_(Q), p_(PQ), 1, m, m, 1, 0, 0)               # pq = t(p) %*% q
-        g.call("sysml_b200_binary_mm", p_(NR2), p_(PQ), p_(A_), 1, 1, 0, L.BINARY_OPS["/"])     # a = nr2 / pq
-        g.call("sysml_b200_binary_mm", p_(P), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
-        g.call("sysml_b200_binary_mm", p_(BETA), p_(TMP), p_(BETA), m, 1, 0, L.BINARY_OPS["+"])  # beta += a*p
-        g.call("sysml_b200_binary_mm", p_(Q), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
-        g.call("sysml_b200_binary_mm", p_(R), p_(TMP), p_(R), m, 1, 0, L.BINARY_OPS["+"])        # r += a*q
-        g.call("sysml_b200_matmult_dense", p_(R), p_(R), p_(NR2N), 1, m, m, 1, 0, 0)             # nr2' = t(r) %*% r
-        g.call("sysml_b200_binary_mm", p_(NR2N), p_(NR2), p_(B_), 1, 1, 0, L.BINARY_OPS["/"])   # b = nr2'/nr2
-        g.call("sysml_b200_binary_mm", p_(P), p_(B_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
-        g.call("sysml_b200_binary_mm", p_(TMP), p_(R), p_(P), m, 1, 0, L.BINARY_OPS["-"])        # p = b*p - r
-        g.call("sysml_b200_d2d", p_(NR2), p_(NR2N), 8)
+        if args.unfused_tail:
+            g.call("sysml_b200_matmult_dense", p_(P), p_(Q), p_(PQ), 1, m, m, 1, 0, 0)               # pq = t(p) %*% q
+            g.call("sysml_b200_binary_mm", p_(NR2), p_(PQ), p_(A_), 1, 1, 0, L.BINARY_OPS["/"])     # a = nr2 / pq
+            g.call("sysml_b200_binary_mm", p_(P), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+            g.call("sysml_b200_binary_mm", p_(BETA), p_(TMP), p_(BETA), m, 1, 0, L.BINARY_OPS["+"])  # beta += a*p
+            g.call("sysml_b200_binary_mm", p_(Q), p_(A_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+            g.call("sysml_b200_binary_mm", p_(R), p_(TMP), p_(R), m, 1, 0, L.BINARY_OPS["+"])        # r += a*q
+            g.call("sysml_b200_matmult_dense", p_(R), p_(R), p_(NR2N), 1, m, m, 1, 0, 0)             # nr2' = t(r) %*% r
+            g.call("sysml_b200_binary_mm", p_(NR2N), p_(NR2), p_(B_), 1, 1, 0, L.BINARY_OPS["/"])   # b = nr2'/nr2
+            g.call("sysml_b200_binary_mm", p_(P), p_(B_), p_(TMP), m, 1, L.BCAST_ROW, L.BINARY_OPS["*"])
+            g.call("sysml_b200_binary_mm", p_(TMP), p_(R), p_(P), m, 1, 0, L.BINARY_OPS["-"])        # p = b*p - r
+            g.call("sysml_b200_d2d", p_(NR2), p_(NR2N), 8)
+        else:
+            # q += 0*p ; a = nr2/(p.q) ; beta += a p ; r += a q ; nr2' = r.r ; p = -r + (nr2'/nr2) p : one launch
+            g.call("sysml_b200_cg_vector_update", p_(P), p_(Q), p_(R), p_(BETA), p_(NR2), m, 0.0)
 
     def barrier():
         if world > 1:

@@ -250,6 +250,12 @@ int sysml_b200_axpy(sysml_b200_ctx* ctx, const double* A, const double* B, doubl
                     int64_t rows, int64_t cols, int bcast);
 int sysml_b200_unary(sysml_b200_ctx* ctx, const double* A, double* C, int64_t len, int op);
 int sysml_b200_fill(sysml_b200_ctx* ctx, double* A, int64_t len, double value);
+/* Fused m-vector tail of one CG iteration of LinearRegCG / GLM (scripts/algorithms/LinearRegCG.dml:183-195):
+ *   q += lambda*p; a = nr2 / sum(p*q); beta += a*p; r += a*q; nr2' = sum(r^2); p = -r + (nr2'/nr2)*p; nr2 = nr2'.
+ * Stands in for the ~10 m-sized instructions (ba+* dot products, +* axpys, host scalars) the reference
+ * compiles this block into; all operands are device pointers (nr2: one double), nothing returns to the host. */
+int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, double* r, double* beta, double* nr2,
+                                int64_t m, double lambda);
 /* C = t(A); replaces LibMatrixCUDA.transpose (java:1723-1729, cublasDgeam). */
 int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols);
 

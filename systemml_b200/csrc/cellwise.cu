@@ -213,6 +213,74 @@ __global__ void transpose_kernel(const double* __restrict__ A, double* __restric
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Fused m-vector tail of one conjugate-gradient iteration (scripts/algorithms/LinearRegCG.dml:183-195,
+// the same update GLM's inner CG uses, GLM.dml:1011-1030):
+//     q  += lambda * p                       (regularisation, LinearRegCG.dml:183)
+//     a   = nr2 / sum(p * q)
+//     beta += a * p ;  r += a * q
+//     nr2' = sum(r ^ 2) ;  p = -r + (nr2' / nr2) * p ;  nr2 = nr2'
+// The reference compiles this into ~10 separate m-sized instructions (dot products as ba+*, +* axpys,
+// scalar ops on the host).  On a B200 each of them is launch latency, nothing else: one CTA does them
+// all, with compensated block reductions, and leaves nr2 on the device so no host round trip is needed.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ double block_sum_1024(double v, double* sh) {
+  CompSum s;
+  s.add(v);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    CompSum t;
+    t.hi = __shfl_xor_sync(0xffffffffu, s.hi, o);
+    t.lo = __shfl_xor_sync(0xffffffffu, s.lo, o);
+    s.add(t);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) {
+    sh[warp] = s.hi;
+    sh[32 + warp] = s.lo;
+  }
+  __syncthreads();
+  CompSum t;
+  const int nw = blockDim.x >> 5;
+  for (int q = 0; q < nw; q++) {  // every thread adds the warp sums in the same order: identical result
+    CompSum u;
+    u.hi = sh[q];
+    u.lo = sh[32 + q];
+    t.add(u);
+  }
+  return t.value();
+}
+
+__global__ void __launch_bounds__(1024) cg_vector_update_kernel(double* __restrict__ p, double* __restrict__ q, double* __restrict__ r,
+                                                                double* __restrict__ beta, double* __restrict__ nr2, i64 m, double lambda) {
+  __shared__ double sh[64];
+  const double nr2_old = *nr2;
+  double part = 0.0;
+  for (i64 j = threadIdx.x; j < m; j += blockDim.x) {
+    const double pj = p[j];
+    const double qj = __dadd_rn(q[j], __dmul_rn(lambda, pj));
+    q[j] = qj;
+    part = fma(pj, qj, part);
+  }
+  const double pq = block_sum_1024(part, sh);
+  const double a = __ddiv_rn(nr2_old, pq);
+  part = 0.0;
+  for (i64 j = threadIdx.x; j < m; j += blockDim.x) {
+    const double pj = p[j];
+    beta[j] = __dadd_rn(beta[j], __dmul_rn(a, pj));
+    const double rj = __dadd_rn(r[j], __dmul_rn(a, q[j]));
+    r[j] = rj;
+    part = fma(rj, rj, part);
+  }
+  const double nr2_new = block_sum_1024(part, sh);
+  const double b = __ddiv_rn(nr2_new, nr2_old);
+  for (i64 j = threadIdx.x; j < m; j += blockDim.x) p[j] = __dadd_rn(-r[j], __dmul_rn(b, p[j]));
+  __syncthreads();
+  if (threadIdx.x == 0) *nr2 = nr2_new;
+}
+
 inline unsigned grid_for(sysml_b200_ctx* ctx, i64 work_items, int threads, int per_sm) {
   i64 blocks = (work_items + threads - 1) / threads;
   const i64 cap = (i64)ctx->sm_count * per_sm;
@@ -347,5 +415,15 @@ extern "C" int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double
   if (blocks > cap) blocks = cap;
   transpose_kernel<<<(unsigned)blocks, dim3(32, 8), 0, ctx->stream>>>(A, C, rows, cols);
   SYSML_LAUNCH_CHECK(ctx, "transpose_kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, double* r, double* beta, double* nr2,
+                                           int64_t m, double lambda) {
+  SYSML_ENTER(ctx);
+  if (m <= 0 || !p || !q || !r || !beta || !nr2) return sysml_set_error(ctx, SYSML_E_INVALID, "cg_vector_update: bad arguments");
+  if (m > (1 << 22)) return sysml_set_error(ctx, SYSML_E_LIMIT, "cg_vector_update: single-CTA kernel, m <= 4M");
+  cg_vector_update_kernel<<<1, 1024, 0, ctx->stream>>>(p, q, r, beta, nr2, m, lambda);
+  SYSML_LAUNCH_CHECK(ctx, "cg_vector_update_kernel");
   return SYSML_OK;
 }

@@ -52,6 +52,7 @@ SIGNATURES = {
     "sysml_b200_binary_ms": (ci, [vp, vp, dbl, vp, i64, ci, ci]),
     "sysml_b200_axpy": (ci, [vp, vp, vp, dbl, vp, i64, i64, ci]),
     "sysml_b200_unary": (ci, [vp, vp, vp, i64, ci]),
+    "sysml_b200_cg_vector_update": (ci, [vp, vp, vp, vp, vp, vp, i64, dbl]),
     "sysml_b200_fill": (ci, [vp, vp, i64, dbl]),
     "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),
     "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),

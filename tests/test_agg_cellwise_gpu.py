@@ -176,3 +176,24 @@ def test_nnz_and_conversions(gctx):
     assert np.array_equal(rp, erp.astype(np.int32)) and np.array_equal(ci, eci) and np.array_equal(va, eva, equal_nan=True)
     back = L.sparseToDense(gctx, S).to_host()
     assert np.array_equal(np.nan_to_num(back, nan=123.0), np.nan_to_num(np.where(X == 0, 0.0, X), nan=123.0))
+
+
+def test_fused_cg_vector_update(gctx):
+    """sysml_b200_cg_vector_update against the same block written out in numpy (LinearRegCG.dml:183-195)."""
+    import ctypes as C
+    m, lam = 1000, 0.01
+    rng = np.random.default_rng(5)
+    p, q, r, beta = (rng.uniform(-1, 1, (m, 1)) for _ in range(4))
+    nr2 = np.array([[float((r * r).sum())]])
+    dp, dq, dr, db, dn = (gctx.dense(x) for x in (p, q, r, beta, nr2))
+    gctx.call("sysml_b200_cg_vector_update", *(C.c_void_p(o.ptr) for o in (dp, dq, dr, db, dn)), m, lam)
+    q2 = q + lam * p
+    a = nr2[0, 0] / float((p * q2).sum())
+    beta2, r2 = beta + a * p, r + a * q2
+    nr2n = float((r2 * r2).sum())
+    p2 = -r2 + (nr2n / nr2[0, 0]) * p
+    assert_equal_matrices(q2, dq.to_host(), rel=1e-14)
+    assert_equal_matrices(beta2, db.to_host(), rel=1e-12)
+    assert_equal_matrices(r2, dr.to_host(), rel=1e-12)
+    assert_equal_matrices(p2, dp.to_host(), rel=1e-11)
+    assert abs(dn.to_host()[0, 0] - nr2n) <= 1e-12 * nr2n
