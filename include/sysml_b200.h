@@ -220,6 +220,21 @@ int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, con
                                  const double* val, const double* B, double* C, int64_t a_rows,
                                  int64_t a_cols, int64_t b_rows, int64_t b_cols, int trans_a);
 
+/* Remaining sparsity combinations of ba+* (LibMatrixCuMatMult.matmult :150-195: cusparseDcsrgemm for
+ * sparse x sparse, the dense x sparse branch; CPU LibMatrixMult.matrixMultDenseSparse :1105-1168 and
+ * matrixMultSparseSparse :1397-1500).  C is always written dense and row-major. */
+int sysml_b200_matmult_dense_csr(sysml_b200_ctx* ctx, const double* A, const int32_t* rowptr,
+                                 const int32_t* colind, const double* val, double* C, int64_t a_rows,
+                                 int64_t a_cols, int64_t b_rows, int64_t b_cols, int trans_a);
+int sysml_b200_matmult_csr_csr(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind,
+                               const double* a_val, const int32_t* b_rowptr, const int32_t* b_colind,
+                               const double* b_val, double* C, int64_t a_rows, int64_t a_cols,
+                               int64_t b_rows, int64_t b_cols);
+/* X %*% t(X) for CSR X (LibMatrixMult.prepMatrixMultTransposeSelfInput :3679-3685 + the RIGHT kernel). */
+int sysml_b200_tsmm_csr_right(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                              const double* val, double* out, int64_t rows, int64_t cols,
+                              int64_t* h_nnz_out);
+
 /* ------------------------------------------------------------------------------------------------
  * Aggregate-unary.  Replaces LibMatrixCUDA.unaryAggregate (LibMatrixCUDA.java:573-894) called by
  * AggregateUnaryGPUInstruction.processInstruction (gpu/AggregateUnaryGPUInstruction.java:67-101);

@@ -19,7 +19,7 @@ lp = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
 
 XtXv, XtwXv, XtXvy = 0, 1, 2
 # aggregate opcodes / directions (same numbering as include/sysml_b200.h)
-SUM, SUMSQ, MAX, MIN, MAXINDEX, MININDEX, MEAN, PROD = range(8)
+SUM, SUMSQ, MAX, MIN, MAXINDEX, MININDEX, MEAN, PROD, VAR = range(9)
 ALL, ROW, COL = 0, 1, 2
 
 

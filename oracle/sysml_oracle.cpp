@@ -1018,7 +1018,33 @@ static void agg_driver(i64 rows, i64 cols, i64 nnz, int op, int dir, double* out
 
 extern "C" {
 
+// VARIANCE: Welford-style update with Kahan-compensated mean and m2 (FO/CM.java:166-176), result
+// m2/(w-1), 0 for a single value (instructions/cp/CM_COV_Object.java:169-170).  Sequential form.
+static double var_seq(const double* p, i64 len, i64 stride) {
+  Kahan mean, m2;
+  double w = 0;
+  for (i64 i = 0; i < len; i++) {
+    const double x = p[i * stride];
+    const double w1 = w + 1;
+    const double d = x - mean.sum;
+    kahan_add(mean, d / w1);
+    const double t1 = w / w1 * d;
+    kahan_add(m2, t1 * d);
+    w = w1;
+  }
+  return w == 1.0 ? 0.0 : m2.sum / (w - 1);
+}
+
 void orc_agg_unary_dense(const double* a, i64 rows, i64 cols, int op, int dir, double* out, double* corr, int k) {
+  if (op == 8) {
+    if (dir == 0)
+      out[0] = var_seq(a, rows * cols, 1);
+    else if (dir == 1)
+      for (i64 i = 0; i < rows; i++) out[i] = var_seq(a + i * cols, cols, 1);
+    else
+      for (i64 j = 0; j < cols; j++) out[j] = var_seq(a + j, rows, cols);
+    return;
+  }
   if (op == 6) {  // MEAN: incremental Kahan mean, d_uamean/d_uarmean/d_uacmean LMA:1940-2010 with
                   // mean() LMA:2962-2966 and FO/Mean.java:60-64.  Sequential form only (k ignored).
     auto mean_seq = [](const double* p, i64 len, i64 stride) {  // Mean.execute: FO/Mean.java

@@ -644,6 +644,137 @@ int run_agg(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, d
   return SYSML_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Variance (uavar / uarvar / uacvar): two passes -- the compensated mean first, then the compensated sum
+// of squared deviations, divided by n-1 (0 for n == 1, CM_COV_Object.java:169-170).  The reference runs a
+// one-pass Welford/Kahan update (functionobjects/CM.java:166-176); both are stable and agree to ~1e-15.
+// mode: 0 one mean for everything, 1 mean per row, 2 mean per column.
+// ------------------------------------------------------------------------------------------------
+__global__ void var_all_kernel(const double* __restrict__ X, i64 len, const double* __restrict__ mean, double* __restrict__ partial) {
+  const double mu = *mean;
+  Acc<K_SUM> a;
+  a.init();
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < len; i += stride) {
+    const double d = __dsub_rn(ldg_stream(X + i), mu);
+    a.push(__dmul_rn(d, d));
+  }
+  warp_merge(a);
+  __shared__ double sh[2][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    sh[0][warp] = a.hi;
+    sh[1][warp] = a.lo;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    Acc<K_SUM> b;
+    b.init();
+    if (lane < (int)(blockDim.x >> 5)) {
+      b.hi = sh[0][lane];
+      b.lo = sh[1][lane];
+    }
+    warp_merge(b);
+    if (lane == 0) {
+      partial[2 * blockIdx.x] = b.hi;
+      partial[2 * blockIdx.x + 1] = b.lo;
+    }
+  }
+}
+__global__ void var_all_finish_kernel(const double* __restrict__ partial, int nparts, double denom, double* __restrict__ out) {
+  Acc<K_SUM> b;
+  b.init();
+  for (int i = threadIdx.x; i < nparts; i += 32) b.merge(partial[2 * i], partial[2 * i + 1]);
+  warp_merge(b);
+  if (threadIdx.x == 0) out[0] = denom > 0.0 ? __ddiv_rn(b.result(), denom) : 0.0;
+}
+__global__ void var_row_kernel(const double* __restrict__ X, i64 rows, i64 cols, int W, const double* __restrict__ mean, double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int sub = lane & (W - 1);
+  const int rows_per_warp = 32 / W;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 base = warp * rows_per_warp; base < rows; base += nwarps * rows_per_warp) {
+    const i64 r = base + lane / W;
+    Acc<K_SUM> a;
+    a.init();
+    if (r < rows) {
+      const double mu = mean[r];
+      for (i64 j = sub; j < cols; j += W) {
+        const double d = __dsub_rn(ldg_stream(X + r * cols + j), mu);
+        a.push(__dmul_rn(d, d));
+      }
+    }
+    group_merge(a, W);
+    if (r < rows && sub == 0) out[r] = cols > 1 ? __ddiv_rn(a.result(), (double)(cols - 1)) : 0.0;
+  }
+}
+__global__ void var_col_kernel(const double* __restrict__ X, i64 rows, i64 cols, const double* __restrict__ mean, double* __restrict__ partial) {
+  const i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  const double mu = mean[c];
+  Acc<K_SUM> a;
+  a.init();
+  for (i64 r = blockIdx.y; r < rows; r += gridDim.y) {
+    const double d = __dsub_rn(ldg_stream(X + r * cols + c), mu);
+    a.push(__dmul_rn(d, d));
+  }
+  partial[((size_t)blockIdx.y * 2) * cols + c] = a.hi;
+  partial[((size_t)blockIdx.y * 2 + 1) * cols + c] = a.lo;
+}
+
+int run_var(sysml_b200_ctx* ctx, const double* X, i64 rows, i64 cols, int dir, double* out) {
+  // pass 1: means, into the output buffer itself (overwritten by pass 2 only after it has been read)
+  const i64 outlen = dir == SYSML_DIR_ALL ? 1 : (dir == SYSML_DIR_ROW ? rows : cols);
+  int rc = SYSML_OK;
+  double* mean = nullptr;
+  SYSML_CUDA(ctx, cudaMalloc((void**)&mean, (size_t)outlen * sizeof(double)));
+  const double cnt = dir == SYSML_DIR_ALL ? (double)rows * (double)cols : (dir == SYSML_DIR_ROW ? (double)cols : (double)rows);
+  rc = run_agg<K_SUM>(ctx, X, rows, cols, dir, mean, cnt);
+  if (!rc) {
+    if (dir == SYSML_DIR_ALL) {
+      i64 blocks = (rows * cols + 2047) / 2048;
+      const i64 cap = (i64)ctx->sm_count * 8;
+      if (blocks > cap) blocks = cap;
+      void* ws = nullptr;
+      rc = sysml_workspace(ctx, (size_t)blocks * 2 * sizeof(double), &ws);
+      if (!rc) {
+        var_all_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(X, rows * cols, mean, (double*)ws);
+        var_all_finish_kernel<<<1, 32, 0, ctx->stream>>>((double*)ws, (int)blocks, cnt - 1.0, out);
+        ctx->launches += 2;
+      }
+    } else if (dir == SYSML_DIR_ROW) {
+      const int W = lanes_per_row(cols);
+      const i64 rows_per_block = (256 / 32) * (32 / W);
+      i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
+      const i64 cap = (i64)ctx->sm_count * 16;
+      if (blocks > cap) blocks = cap;
+      var_row_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(X, rows, cols, W, mean, out);
+      ctx->launches++;
+    } else {
+      const i64 ctiles = (cols + 127) / 128;
+      i64 splits = ((i64)ctx->sm_count * 8 + ctiles - 1) / ctiles;
+      if (splits > (rows + 63) / 64) splits = (rows + 63) / 64;
+      if (splits < 1) splits = 1;
+      if (splits > 65535) splits = 65535;
+      void* ws = nullptr;
+      rc = sysml_workspace(ctx, (size_t)splits * 2 * cols * sizeof(double), &ws);
+      if (!rc) {
+        var_col_kernel<<<dim3((unsigned)ctiles, (unsigned)splits), 128, 0, ctx->stream>>>(X, rows, cols, mean, (double*)ws);
+        agg_col_finish_kernel<K_SUM><<<(unsigned)((cols + 31) / 32), 256, 0, ctx->stream>>>((double*)ws, (int)splits, cols, out, rows > 1 ? (double)(rows - 1) : 1.0);
+        ctx->launches += 2;
+      }
+    }
+  }
+  cudaError_t e = cudaGetLastError();
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(mean);
+  if (rc) return rc;
+  if (e != cudaSuccess) return sysml_set_error(ctx, SYSML_E_CUDA, "variance kernels: %s", cudaGetErrorString(e));
+  return SYSML_OK;
+}
+
 }  // namespace
 
 extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, int64_t rows, int64_t cols, int op, int dir,
@@ -680,7 +811,7 @@ extern "C" int sysml_b200_agg_unary_dense(sysml_b200_ctx* ctx, const double* X, 
       SYSML_LAUNCH_CHECK(ctx, "agg_rowindex_kernel");
       return SYSML_OK;
     }
-    case SYSML_AGG_VAR: return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "variance is not implemented yet");
+    case SYSML_AGG_VAR: return run_var(ctx, X, rows, cols, dir, out);
   }
   return sysml_set_error(ctx, SYSML_E_INVALID, "agg_unary: unknown opcode %d", op);
 }

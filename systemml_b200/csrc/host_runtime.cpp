@@ -591,12 +591,15 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
       const bool lt = pi.extras[0] == "true", rt = pi.extras[1] == "true";
       const i64 rlen = lt ? m1->cols : m1->rows, clen = rt ? m2->rows : m2->cols;
       GPUObject *g1 = m1->gpu.get(), *g2 = m2->gpu.get();
-      if (g2->isSparse() || (g1->isSparse() && rt)) {
-        fail(SYSML_E_UNSUPPORTED, "GPU : ba+* with a sparse right-hand side (or CSR %%*%% t(dense)) is not implemented yet");
-      }
+      if ((g2->isSparse() && (rt || (g1->isSparse() && lt))) || (g1->isSparse() && !g2->isSparse() && rt))
+        fail(SYSML_E_UNSUPPORTED, "GPU : ba+* with a transposed sparse operand in this combination is not implemented yet");
       MatrixObject* out = L.out(pi.ops[2].name, rlen, clen, opc);
       int rc;
-      if (g1->isSparse()) {
+      if (g2->isSparse() && g1->isSparse()) {
+        rc = sysml_b200_matmult_csr_csr(ctx, g1->rowptr, g1->colind, g1->val, g2->rowptr, g2->colind, g2->val, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols);
+      } else if (g2->isSparse()) {
+        rc = sysml_b200_matmult_dense_csr(ctx, g1->dense, g2->rowptr, g2->colind, g2->val, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt);
+      } else if (g1->isSparse()) {
         rc = sysml_b200_matmult_csr_dense(ctx, g1->rowptr, g1->colind, g1->val, g2->dense, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt);
       } else {
         rc = sysml_b200_matmult_dense(ctx, g1->dense, g2->dense, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt, rt);
@@ -613,12 +616,11 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
       int rc;
       if (mat->gpu->isSparse()) {
         rc = left ? sysml_b200_tsmm_csr_left(ctx, mat->gpu->rowptr, mat->gpu->colind, mat->gpu->val, out->gpu->dense, mat->rows, mat->cols, &nnz)
-                  : SYSML_E_UNSUPPORTED;
+                  : sysml_b200_tsmm_csr_right(ctx, mat->gpu->rowptr, mat->gpu->colind, mat->gpu->val, out->gpu->dense, mat->rows, mat->cols, &nnz);
       } else {
         rc = sysml_b200_tsmm_dense(ctx, mat->gpu->dense, out->gpu->dense, mat->rows, mat->cols, left ? 1 : 0, &nnz);
       }
       out->nnz = nnz;  // ret.setNonZeros(copyUpperToLowerTriangle(ret)), LibMatrixMult.java:352-353
-      if (rc == SYSML_E_UNSUPPORTED) fail(rc, "GPU : tsmm RIGHT on a sparse input is not implemented yet");
       check(rc);
       break;
     }

@@ -212,6 +212,52 @@ __global__ void mirror_count_kernel(double* __restrict__ C, i64 n, unsigned long
   if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(nnz, cnt);
 }
 
+
+// ---------------- remaining sparsity combinations (dense output) ----------------
+// C[i, :] = sum_k A[i,k] * B[k, :] with B in CSR: one warp per output row, k sequential, lanes over the
+// non-zeros of B's row k (distinct columns within a row, so no atomics; __syncwarp orders the k steps).
+// LibMatrixMult.matrixMultDenseSparse (LibMatrixMult.java:1105-1168).
+__global__ void __launch_bounds__(256) dense_csr_mm_kernel(const double* __restrict__ A, const int* __restrict__ rp, const int* __restrict__ ci,
+                                                           const double* __restrict__ va, double* __restrict__ C, i64 m, i64 k, i64 n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 i = warp; i < m; i += nwarps) {
+    double* crow = C + i * n;
+    for (i64 j = lane; j < n; j += 32) crow[j] = 0.0;
+    __syncwarp();
+    for (i64 kk = 0; kk < k; kk++) {
+      const double a = __ldg(A + i * k + kk);
+      if (a == 0.0) continue;  // warp-uniform: every lane reads the same a
+      const int lo = __ldg(rp + kk), hi = __ldg(rp + kk + 1);
+      for (int q = lo + lane; q < hi; q += 32) crow[ci[q]] += a * va[q];
+      __syncwarp();
+    }
+  }
+}
+// C[i, :] = sum over non-zeros (k, a) of A's row i of a * B[k, :], A and B in CSR.
+// LibMatrixMult.matrixMultSparseSparse (LibMatrixMult.java:1397-1500); the result is written dense.
+__global__ void __launch_bounds__(256) csr_csr_mm_kernel(const int* __restrict__ arp, const int* __restrict__ aci, const double* __restrict__ ava,
+                                                         const int* __restrict__ brp, const int* __restrict__ bci, const double* __restrict__ bva,
+                                                         double* __restrict__ C, i64 m, i64 n) {
+  const int lane = threadIdx.x & 31;
+  const i64 warp = ((i64)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const i64 nwarps = ((i64)gridDim.x * blockDim.x) >> 5;
+  for (i64 i = warp; i < m; i += nwarps) {
+    double* crow = C + i * n;
+    for (i64 j = lane; j < n; j += 32) crow[j] = 0.0;
+    __syncwarp();
+    const int alo = __ldg(arp + i), ahi = __ldg(arp + i + 1);
+    for (int p = alo; p < ahi; p++) {
+      const double a = __ldg(ava + p);
+      const int kk = __ldg(aci + p);
+      const int lo = __ldg(brp + kk), hi = __ldg(brp + kk + 1);
+      for (int q = lo + lane; q < hi; q += 32) crow[bci[q]] += a * bva[q];
+      __syncwarp();
+    }
+  }
+}
+
 // ---------------- nnz / conversions ----------------
 __global__ void count_nnz_kernel(const double* __restrict__ X, i64 len, unsigned long long* __restrict__ out) {
   const i64 stride = (i64)gridDim.x * blockDim.x;
@@ -712,4 +758,73 @@ extern "C" int sysml_b200_agg_unary_csr(sysml_b200_ctx* ctx, const int32_t* rowp
   csr_agg_col_minmax_finish<<<(unsigned)((cols + 255) / 256), 256, 0, ctx->stream>>>(out, (int*)ws, cols, rows, op == SYSML_AGG_MAX);
   SYSML_LAUNCH_CHECK(ctx, "csr_agg_col_minmax_finish");
   return SYSML_OK;
+}
+
+extern "C" int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols);
+extern "C" int sysml_b200_tsmm_dense(sysml_b200_ctx* ctx, const double* X, double* out, int64_t rows, int64_t cols, int left, int64_t* h_nnz_out);
+
+extern "C" int sysml_b200_matmult_dense_csr(sysml_b200_ctx* ctx, const double* A, const int32_t* rowptr, const int32_t* colind,
+                                            const double* val, double* C, int64_t a_rows, int64_t a_cols, int64_t b_rows,
+                                            int64_t b_cols, int trans_a) {
+  SYSML_ENTER(ctx);
+  if (a_rows < 0 || a_cols < 0 || b_rows < 0 || b_cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_dense_csr: negative dimension");
+  const i64 m = trans_a ? a_cols : a_rows, k = trans_a ? a_rows : a_cols;
+  if (k != b_rows) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_dense_csr: inner dimensions %lld vs %lld", (long long)k, (long long)b_rows);
+  const i64 n = b_cols;
+  if (m * n == 0) return SYSML_OK;
+  if (!C) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_dense_csr: C is null");
+  if (k == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(m * n) * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (!A || !rowptr) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_dense_csr: null operand");
+  const double* Ause = A;
+  if (trans_a) {  // materialise t(A) once in scratch (the reference's r' + ba+*, LibMatrixCUDA.java:1723-1729)
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)(m * k) * sizeof(double), &ws);
+    if (rc) return rc;
+    rc = sysml_b200_transpose(ctx, A, (double*)ws, a_rows, a_cols);
+    if (rc) return rc;
+    Ause = (const double*)ws;
+  }
+  dense_csr_mm_kernel<<<warp_rows_grid(ctx, m), 256, 0, ctx->stream>>>(Ause, rowptr, colind, val, C, m, k, n);
+  SYSML_LAUNCH_CHECK(ctx, "dense_csr_mm_kernel");
+  return SYSML_OK;
+}
+
+extern "C" int sysml_b200_matmult_csr_csr(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind, const double* a_val,
+                                          const int32_t* b_rowptr, const int32_t* b_colind, const double* b_val, double* C,
+                                          int64_t a_rows, int64_t a_cols, int64_t b_rows, int64_t b_cols) {
+  SYSML_ENTER(ctx);
+  if (a_rows < 0 || a_cols < 0 || b_rows < 0 || b_cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_csr_csr: negative dimension");
+  if (a_cols != b_rows) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_csr_csr: inner dimensions %lld vs %lld", (long long)a_cols, (long long)b_rows);
+  if (a_rows * b_cols == 0) return SYSML_OK;
+  if (!C || !a_rowptr || !b_rowptr) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_csr_csr: null pointer");
+  csr_csr_mm_kernel<<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(a_rowptr, a_colind, a_val, b_rowptr, b_colind, b_val, C, a_rows, b_cols);
+  SYSML_LAUNCH_CHECK(ctx, "csr_csr_mm_kernel");
+  return SYSML_OK;
+}
+
+// X %*% t(X) for CSR X: the reference transposes first and runs the LEFT kernel on t(X)
+// (prepMatrixMultTransposeSelfInput, LibMatrixMult.java:3679-3685); here the (rows x rows) result is
+// formed from a dense copy of X in scratch, which is only sensible while rows*cols fits comfortably.
+extern "C" int sysml_b200_tsmm_csr_right(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                         double* out, int64_t rows, int64_t cols, int64_t* h_nnz_out) {
+  SYSML_ENTER(ctx);
+  if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "tsmm_csr_right: negative dimension");
+  if (h_nnz_out) *h_nnz_out = 0;
+  if (rows == 0) return SYSML_OK;
+  if (!out || !rowptr) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm_csr_right: null pointer");
+  if (cols == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)(rows * rows) * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if ((double)rows * (double)cols * 8.0 > 32e9) return sysml_set_error(ctx, SYSML_E_LIMIT, "tsmm_csr_right: dense copy of X would need more than 32 GB");
+  double* dense = nullptr;
+  SYSML_CUDA(ctx, cudaMalloc((void**)&dense, (size_t)(rows * cols) * sizeof(double)));
+  int rc = sysml_b200_csr_to_dense(ctx, rowptr, colind, val, rows, cols, dense);
+  if (!rc) rc = sysml_b200_tsmm_dense(ctx, dense, out, rows, cols, 0, h_nnz_out);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(dense);
+  return rc;
 }

@@ -98,10 +98,8 @@ def matmultTSMM(gCtx, instName, left, isLeftTransposed=True, with_nnz=False):
     nnz = C.c_int64(-1)
     pn = C.byref(nnz) if with_nnz else None
     if left.isSparse():
-        if not isLeftTransposed:
-            raise native.NativeError(native.E_UNSUPPORTED, "tsmm RIGHT on CSR input")
-        gCtx.call("sysml_b200_tsmm_csr_left", _p(left.csr.rowPtr), _p(left.csr.colInd), _p(left.csr.val),
-                  _p(out.ptr), left.rows, left.cols, pn)
+        gCtx.call("sysml_b200_tsmm_csr_left" if isLeftTransposed else "sysml_b200_tsmm_csr_right", _p(left.csr.rowPtr),
+                  _p(left.csr.colInd), _p(left.csr.val), _p(out.ptr), left.rows, left.cols, pn)
     else:
         gCtx.call("sysml_b200_tsmm_dense", _p(left.ptr), _p(out.ptr), left.rows, left.cols,
                   1 if isLeftTransposed else 0, pn)
@@ -116,9 +114,18 @@ def matmult(gCtx, instName, left, right, isLeftTransposed=False, isRightTranspos
     n = right.rows if isRightTransposed else right.cols
     if k1 != k2:
         _dim_error("matmult: incompatible dimensions %d vs %d" % (k1, k2))
-    if right.isSparse():
-        raise native.NativeError(native.E_UNSUPPORTED, "matmult with sparse right-hand side")
     out = GPUObject.allocate_dense(gCtx, m, n)
+    if right.isSparse():
+        if isRightTransposed or (left.isSparse() and isLeftTransposed):
+            raise native.NativeError(native.E_UNSUPPORTED, "transposed sparse operand in this combination")
+        if left.isSparse():
+            gCtx.call("sysml_b200_matmult_csr_csr", _p(left.csr.rowPtr), _p(left.csr.colInd), _p(left.csr.val),
+                      _p(right.csr.rowPtr), _p(right.csr.colInd), _p(right.csr.val), _p(out.ptr), left.rows, left.cols,
+                      right.rows, right.cols)
+        else:
+            gCtx.call("sysml_b200_matmult_dense_csr", _p(left.ptr), _p(right.csr.rowPtr), _p(right.csr.colInd),
+                      _p(right.csr.val), _p(out.ptr), left.rows, left.cols, right.rows, right.cols, int(isLeftTransposed))
+        return out
     if left.isSparse():
         if isRightTransposed:
             raise native.NativeError(native.E_UNSUPPORTED, "CSR x t(dense)")

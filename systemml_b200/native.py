@@ -46,6 +46,9 @@ SIGNATURES = {
     "sysml_b200_tsmm_csr_left": (ci, [vp, vp, vp, vp, vp, i64, i64, pi64]),
     "sysml_b200_matmult_dense": (ci, [vp, vp, vp, vp, i64, i64, i64, i64, ci, ci]),
     "sysml_b200_matmult_csr_dense": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, ci]),
+    "sysml_b200_matmult_dense_csr": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, ci]),
+    "sysml_b200_matmult_csr_csr": (ci, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, i64, i64]),
+    "sysml_b200_tsmm_csr_right": (ci, [vp, vp, vp, vp, vp, i64, i64, pi64]),
     "sysml_b200_agg_unary_dense": (ci, [vp, vp, i64, i64, ci, ci, vp]),
     "sysml_b200_agg_unary_csr": (ci, [vp, vp, vp, vp, i64, i64, ci, ci, vp]),
     "sysml_b200_binary_mm": (ci, [vp, vp, vp, vp, i64, i64, ci, ci]),

@@ -197,3 +197,17 @@ def test_fused_cg_vector_update(gctx):
     assert_equal_matrices(r2, dr.to_host(), rel=1e-12)
     assert_equal_matrices(p2, dp.to_host(), rel=1e-11)
     assert abs(dn.to_host()[0, 0] - nr2n) <= 1e-12 * nr2n
+
+
+@pytest.mark.parametrize("rows,cols", [(1, 1), (64, 130), (2049, 21), (1000, 1), (1, 777), (50_000, 50)])
+def test_variance(gctx, rows, cols):
+    """uavar / uarvar / uacvar (AggregateUnaryOpTests.var, rel 1e-9) vs the restated CM update."""
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(rows, cols, -1, 1, 0.9, 42) + 3.0
+    dX = gctx.dense(X)
+    for opc, d in (("uavar", O.ALL), ("uarvar", O.ROW), ("uacvar", O.COL)):
+        exp = O.agg_unary_dense(X, O.VAR, d, 1)
+        got = L.unaryAggregate(gctx, opc, dX, opc)
+        got = np.array([got]) if d == O.ALL else got.to_host().reshape(-1)
+        assert_equal_matrices(exp, got, rel=1e-9, what=opc)
+    dX.free()

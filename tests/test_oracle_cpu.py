@@ -164,3 +164,12 @@ def test_rand_generator_is_shardable():
     full = O.rand_uniform(1000, seed=9)
     assert np.array_equal(full[300:700], O.rand_uniform(400, seed=9, offset=300))
     assert full.min() >= -1 and full.max() < 1 and abs(full.mean()) < 0.1
+
+
+def test_variance_matches_two_pass_longdouble():
+    X = O.java_test_matrix(500, 40, -1, 1, 0.9, 42) + 3.0
+    Xl = X.astype(np.longdouble)
+    assert abs(O.agg_unary_dense(X, O.VAR, O.ALL)[0] - float(Xl.var(ddof=1))) < 1e-13
+    assert np.max(np.abs(O.agg_unary_dense(X, O.VAR, O.ROW) - Xl.var(axis=1, ddof=1).astype(np.float64))) < 1e-13
+    assert np.max(np.abs(O.agg_unary_dense(X, O.VAR, O.COL) - Xl.var(axis=0, ddof=1).astype(np.float64))) < 1e-13
+    assert O.agg_unary_dense(np.array([[5.0]]), O.VAR, O.ALL)[0] == 0.0  # w == 1 -> 0 (CM_COV_Object.java:170)

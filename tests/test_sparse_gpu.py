@@ -87,3 +87,32 @@ def test_sparse_rowindex_edge_cases(gctx):
         exp = O.agg_unary_csr(rp, ci, va, X.shape, op, O.ROW)
         assert np.array_equal(exp, O.agg_unary_dense(X, op, O.ROW)), "oracle: sparse and dense must agree"
         assert L.unaryAggregate(gctx, opc, dX, opc).to_host().reshape(-1).tolist() == exp.tolist()
+
+
+@pytest.mark.parametrize("m,k,n,spa,spb", [(300, 500, 200, 0.1, 0.05), (1, 400, 300, 1.0, 0.1), (700, 50, 1200, 0.02, 0.3), (64, 64, 64, 0.5, 0.0)])
+def test_remaining_sparsity_combinations(gctx, m, k, n, spa, spb):
+    """dense x sparse, sparse x sparse (FullMatrixMultiplicationTest's sparsity grid) and t(dense) x sparse."""
+    from systemml_b200 import LibMatrixB200 as L
+    A = O.java_test_matrix(m, k, -1, 1, spa, 11)
+    B = O.java_test_matrix(k, n, -1, 1, spb, 12)
+    exp = (A.astype(np.longdouble) @ B.astype(np.longdouble)).astype(np.float64)
+    dB, _ = _csr(gctx, B)
+    scale = max(np.max(np.abs(exp)), 1e-300)
+    got = L.matmult(gctx, "ba+*", gctx.dense(A), dB).to_host()            # dense x CSR
+    assert np.max(np.abs(exp - got)) <= 1e-12 * scale
+    dA, _ = _csr(gctx, A)
+    got = L.matmult(gctx, "ba+*", dA, dB).to_host()                        # CSR x CSR
+    assert np.max(np.abs(exp - got)) <= 1e-12 * scale
+    At = np.ascontiguousarray(A.T)
+    got = L.matmult(gctx, "ba+*", gctx.dense(At), dB, isLeftTransposed=True).to_host()  # t(dense) x CSR
+    assert np.max(np.abs(exp - got)) <= 1e-12 * scale
+
+
+def test_sparse_tsmm_right(gctx):
+    from systemml_b200 import LibMatrixB200 as L
+    X = O.java_test_matrix(300, 2000, 0, 1, 0.1, 7)
+    dX, _ = _csr(gctx, X)
+    exp, nnz = O.tsmm_dense(X, False, 4)
+    out, gnnz = L.matmultTSMM(gctx, "tsmm", dX, False, with_nnz=True)
+    assert_equal_matrices(exp, out.to_host(), what="sparse tsmm RIGHT")
+    assert gnnz == nnz
