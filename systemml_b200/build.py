@@ -43,9 +43,22 @@ def build(force=False, verbose=False):
 
     def compile_one(job):
         src, obj = job
-        cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]
+        cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if src.endswith(".cu") else []) + ["-c", src, "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
-        return src, r.returncode, r.stdout + r.stderr
+        out = r.stdout + r.stderr
+        rc = r.returncode
+        # ptxas occasionally falls off a cliff on the warp-specialised kernels (32 registers, kilobytes of
+        # spills); a kernel that spills is a build failure, not a slow kernel
+        spills = [l for l in out.splitlines() if "bytes spill stores" in l and not l.strip().startswith("0 bytes stack frame, 0 bytes spill stores")]
+        spills = [l for l in spills if ", 0 bytes spill stores" not in l]
+        if rc == 0 and spills:
+            out += "\nERROR: register spills in %s:\n%s\n" % (src, "\n".join(spills[:5]))
+            rc = 1
+            if os.path.exists(obj):
+                os.remove(obj)
+        if not verbose and rc == 0:
+            out = ""
+        return src, rc, out
 
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:

@@ -76,16 +76,16 @@ __device__ __forceinline__ void load_tile(double* s, const double* src, i64 ld, 
   }
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES>
 struct GemmCfg {
   static constexpr int NT = WARPS_M * WARPS_N * 32;
   static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
   static constexpr int MT = WM / 8, NTL = WN / 8;
-  static constexpr int LDA = TA ? (BM + 4) : (BK + 4);
-  static constexpr int LDB = TB ? (BK + 4) : (BN + 4);
-  static constexpr int A_ELEMS = TA ? BK * LDA : BM * LDA;
-  static constexpr int B_ELEMS = TB ? BN * LDB : BK * LDB;
-  static constexpr size_t SMEM = (size_t)STAGES * (A_ELEMS + B_ELEMS) * sizeof(double);
+  static constexpr int LDA = TA ? (BM + 4) : (BKT + 4);
+  static constexpr int LDB = TB ? (BKT + 4) : (BN + 4);
+  static constexpr int A_ELEMS = TA ? BKT * LDA : BM * LDA;
+  static constexpr int B_ELEMS = TB ? BN * LDB : BKT * LDB;
+  static constexpr size_t SMEM = (size_t)NST * (A_ELEMS + B_ELEMS) * sizeof(double);
 };
 
 template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
@@ -234,20 +234,38 @@ __device__ __forceinline__ void tile_issue(double* s, const double* src, i64 ld,
 // which the TMA engine retires far too slowly; the producer warp uses 16-byte cp.async (LDGSTS) instead,
 // 8 lanes per row segment, zero-filling through the src-size operand, and lets the copies arrive on the
 // stage's mbarrier (cp.async.mbarrier.arrive.noinc).
-template <int R, int LD>
+template <int R, int LD, int KC>  // KC doubles (KC/2 16-byte chunks) per row
 __device__ __forceinline__ void tile_issue_cpasync(double* s, const double* src, i64 ld, i64 rvalid, i64 kvalid, int lane) {
-  const int r0 = lane >> 3, cc = (lane & 7) * 2;
-  i64 nb = (kvalid - cc) * 8;
-  nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
-  const double* p = src + (i64)r0 * ld + cc;
-  double* d = s + r0 * LD + cc;
-  const i64 step = 4 * ld;
+  if constexpr (KC == 16) {
+    // 8 chunks per row, 4 rows per warp instruction
+    const int r0 = lane >> 3, cc = (lane & 7) * 2;
+    i64 nb = (kvalid - cc) * 8;
+    nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+    const double* p = src + (i64)r0 * ld + cc;
+    double* d = s + r0 * LD + cc;
+    const i64 step = 4 * ld;
 #pragma unroll 4
-  for (int r = r0; r < R; r += 4) {
-    const int bytes = (r < rvalid) ? (int)nb : 0;
-    cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
-    p += step;
-    d += 4 * LD;
+    for (int r = r0; r < R; r += 4) {
+      const int bytes = (r < rvalid) ? (int)nb : 0;
+      cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
+      p += step;
+      d += 4 * LD;
+    }
+  } else {
+    // KC == 64: 32 chunks per row, one row (512 contiguous bytes) per warp instruction
+    static_assert(KC == 64, "K-contiguous tiles are 16 or 64 deep");
+    const int cc = lane * 2;
+    i64 nb = (kvalid - cc) * 8;
+    nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+    const double* p = src + cc;
+    double* d = s + cc;
+#pragma unroll 4
+    for (int r = 0; r < R; r++) {
+      const int bytes = (r < rvalid) ? (int)nb : 0;
+      cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
+      p += ld;
+      d += LD;
+    }
   }
 }
 // rows-long tile [R][CCOLS] with SHORT rows (< 1 KB): same idea, 16-byte chunks spread over the warp
@@ -266,9 +284,9 @@ __device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST>
 __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(const GemmArgs g) {
-  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
   constexpr int NCW = WARPS_M * WARPS_N;  // consumer warps
   constexpr int MT = Cfg::MT, NTL = Cfg::NTL, LDA = Cfg::LDA, LDB = Cfg::LDB;
   constexpr bool A_BULK = TA && (BM * 8 >= 1024);
@@ -276,9 +294,9 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   constexpr bool ANY_CPASYNC = !A_BULK || !B_BULK;
   extern __shared__ __align__(16) double smem[];
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint64_t* empty = full + STAGES;
+  uint64_t* empty = full + NST;
   double* As = smem + 16;  // 128 bytes reserved for the barriers
-  double* Bs = As + STAGES * Cfg::A_ELEMS;
+  double* Bs = As + NST * Cfg::A_ELEMS;
 
   int ti, tj;
   if (g.sym) {
@@ -296,13 +314,13 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
   const i64 kbeg = (i64)blockIdx.y * g.k_per_split;
   const i64 kend = (kbeg + g.k_per_split < g.K) ? kbeg + g.k_per_split : g.K;
-  const int nkb = (int)((kend - kbeg + BK - 1) / BK);
+  const int nkb = (int)((kend - kbeg + BKT - 1) / BKT);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // clear all tiles once: padding columns/rows that no copy ever writes must read as zero
-  for (int c = tid; c < STAGES * (Cfg::A_ELEMS + Cfg::B_ELEMS); c += (NCW + 1) * 32) As[c] = 0.0;
+  for (int c = tid; c < NST * (Cfg::A_ELEMS + Cfg::B_ELEMS); c += (NCW + 1) * 32) As[c] = 0.0;
   if (tid == 0) {
-    for (int s = 0; s < STAGES; s++) {
+    for (int s = 0; s < NST; s++) {
       mbar_init(&full[s], ANY_CPASYNC ? 1 + 32 : 1);  // lane 0's expect_tx arrival (+ one cp.async arrival per producer lane)
       mbar_init(&empty[s], NCW);
     }
@@ -314,31 +332,31 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   if (warp == NCW) {
     // ===================== producer warp =====================
     for (int kb = 0; kb < nkb; kb++) {
-      const int s = kb % STAGES;
-      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      const int s = kb % NST;
+      const uint32_t ph = (uint32_t)(kb / NST) & 1u;
       mbar_wait(&empty[s], ph ^ 1u);
-      const i64 k0 = kbeg + (i64)kb * BK;
+      const i64 k0 = kbeg + (i64)kb * BKT;
       const i64 kvalid = kend - k0;
       double* as = As + s * Cfg::A_ELEMS;
       double* bs = Bs + s * Cfg::B_ELEMS;
       // bulk copies only for operands whose tile rows are >= 1 KB; 16-byte cp.async for everything else
-      if (kvalid < BK) {  // ragged last k block: clear what the bulk copies below will not overwrite
-        if (A_BULK) tile_zero_tail<BK, BM, LDA>(as, kvalid, g.M - i0, lane);
-        if (B_BULK) tile_zero_tail<BK, BN, LDB>(bs, kvalid, g.N - j0, lane);
+      if (kvalid < BKT) {  // ragged last k block: clear what the bulk copies below will not overwrite
+        if (A_BULK) tile_zero_tail<BKT, BM, LDA>(as, kvalid, g.M - i0, lane);
+        if (B_BULK) tile_zero_tail<BKT, BN, LDB>(bs, kvalid, g.N - j0, lane);
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       }
       uint32_t bytes = 0;
-      if (A_BULK) bytes += tile_bytes<BK, BM, LDA>(kvalid, g.M - i0);
-      if (B_BULK) bytes += tile_bytes<BK, BN, LDB>(kvalid, g.N - j0);
+      if (A_BULK) bytes += tile_bytes<BKT, BM, LDA>(kvalid, g.M - i0);
+      if (B_BULK) bytes += tile_bytes<BKT, BN, LDB>(kvalid, g.N - j0);
       __syncwarp();
       if (lane == 0) mbar_expect_tx(&full[s], bytes);
       __syncwarp();
-      if (A_BULK)  tile_issue<BK, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, &full[s], lane);
-      else if (TA) tile_issue_cpasync_rows<BK, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, lane);
-      else         tile_issue_cpasync<BM, LDA>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, lane);
-      if (B_BULK)   tile_issue<BK, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, &full[s], lane);
-      else if (!TB) tile_issue_cpasync_rows<BK, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, lane);
-      else          tile_issue_cpasync<BN, LDB>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, lane);
+      if (A_BULK)  tile_issue<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, &full[s], lane);
+      else if (TA) tile_issue_cpasync_rows<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, lane);
+      else         tile_issue_cpasync<BM, LDA, BKT>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, lane);
+      if (B_BULK)   tile_issue<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, &full[s], lane);
+      else if (!TB) tile_issue_cpasync_rows<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, lane);
+      else          tile_issue_cpasync<BN, LDB, BKT>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, lane);
       if (ANY_CPASYNC) cp_async_mbar_arrive(&full[s]);
     }
     if (ANY_CPASYNC) cp_async_wait<0>();
@@ -362,13 +380,13 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   constexpr int B_K4 = TB ? 4 : 4 * LDB;
 
   for (int kb = 0; kb < nkb; kb++) {
-    const int s = kb % STAGES;
-    const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+    const int s = kb % NST;
+    const uint32_t ph = (uint32_t)(kb / NST) & 1u;
     mbar_wait(&full[s], ph);
     const double* as = As + s * Cfg::A_ELEMS + a_off;
     const double* bs = Bs + s * Cfg::B_ELEMS + b_off;
 #pragma unroll
-    for (int k4 = 0; k4 < BK / 4; k4++) {
+    for (int k4 = 0; k4 < BKT / 4; k4++) {
       double af[MT], bf[NTL];
 #pragma unroll
       for (int a = 0; a < MT; a++) af[a] = as[k4 * A_K4 + a * A_MT];
@@ -448,15 +466,15 @@ struct Plan {
   int tiles_m, tiles_n, ntiles, splits;
   i64 k_per_split;
 };
-inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, bool sym) {
+inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, bool sym, int bk) {
   Plan p;
   p.tiles_m = (int)((M + BM - 1) / BM);
   p.tiles_n = (int)((N + BN - 1) / BN);
   p.ntiles = sym ? p.tiles_n * (p.tiles_n + 1) / 2 : p.tiles_m * p.tiles_n;
-  const i64 kblocks = (K + BK - 1) / BK;
+  const i64 kblocks = (K + bk - 1) / bk;
   // aim at ~6 waves of CTAs (1 CTA per SM) but keep >= 32 k-blocks (512 contraction steps) per CTA
   i64 want = ((i64)ctx->sm_count * 6 + p.ntiles - 1) / p.ntiles;
-  i64 maxs = kblocks / 32;
+  i64 maxs = kblocks * bk / 512;
   if (maxs < 1) maxs = 1;
   if (want > maxs) want = maxs;
   if (want < 1) want = 1;
@@ -468,19 +486,20 @@ inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, 
   }
   if (want > 65535) want = 65535;
   i64 kbs = (kblocks + want - 1) / want;
-  p.k_per_split = kbs * BK;
+  p.k_per_split = kbs * bk;
   p.splits = (int)((K + p.k_per_split - 1) / p.k_per_split);
   if (p.splits < 1) p.splits = 1;
   return p;
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N>
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES>
 int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
              int64_t* h_nnz) {
-  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;
+  using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;           // legacy cp.async kernel (BK = 16, 4 stages)
+  using WsCfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;  // warp-specialised kernel
   auto kern = dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N>;
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-  const Plan p = make_plan(ctx, M, N, K, BM, BN, sym);
+  const Plan p = make_plan(ctx, M, N, K, BM, BN, sym, BKT);
   const bool direct = (p.splits == 1) && !sym;
   GemmArgs g{};
   g.A = A; g.B = B; g.M = M; g.N = N; g.K = K; g.lda = lda; g.ldb = ldb;
@@ -503,10 +522,10 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
   const bool ws_ok = g.vecA && g.vecB && (M % 2 == 0) && (N % 2 == 0) &&
                      ((reinterpret_cast<uintptr_t>(g.out) & 15) == 0) && getenv("SYSML_B200_GEMM_NO_WS") == nullptr;
   if (ws_ok) {
-    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N>;
-    const size_t smem_ws = Cfg::SMEM + 128;
+    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
+    const size_t smem_ws = WsCfg::SMEM + 128;
     SYSML_CUDA(ctx, cudaFuncSetAttribute(kws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ws));
-    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT + 32, smem_ws, ctx->stream>>>(g);
+    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), WsCfg::NT + 32, smem_ws, ctx->stream>>>(g);
     SYSML_LAUNCH_CHECK(ctx, "dgemm_ws_kernel");
   } else {
     dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
@@ -541,11 +560,18 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
   if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
   if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  // Note (measured, profiles/r01_ncu_xv_summary.txt): for a K-contiguous A with a skinny output (MultiLogReg's
+  // X %*% V, 1M x 5000 x 20) the 256-row tile reaches only ~2.8 TB/s: 256 row segments per stage land in as
+  // many DRAM pages.  64-deep k blocks (512-byte segments, 128-row tile, 2 stages) were tried and were slower
+  // (17.5 ms vs 14.2 ms): the effective DRAM latency stays ~5 us either way.  Next step: rows-contiguous tiles
+  // (few rows x long k) with the k range split across the warps of a CTA.
   if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 32) return run_gemm<TA, TB, 256, 32, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 40) return run_gemm<TA, TB, 256, 40, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 48) return run_gemm<TA, TB, 256, 48, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 56) return run_gemm<TA, TB, 256, 56, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   return run_gemm<TA, TB, 256, 64, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
 }
 
