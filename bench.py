@@ -387,6 +387,40 @@ def main():
             del hx
             g.call("sysml_b200_rand_uniform", C.c_void_p(X.ptr), nloc * m, 1, r0 * m, -1.0, 1.0)  # restore X
 
+    # ---------------- e2e through instruction strings (N = 1): the call shape SystemML itself uses ----------------
+    if e2e is not None and world == 1:
+        from systemml_b200.execution_context import ExecutionContext, inst, mat
+        torch.cuda.synchronize()
+        ecx = ExecutionContext(local_rank)
+        ecx.setMatrixDevice("X", X.ptr, nloc, m)
+        ecx.setMatrixDevice("w", w.ptr, nloc, 1)
+        ins = inst("mmchain", mat("X"), mat("p"), mat("w"), mat("q"), "XtwXv", 16)
+
+        def ec_step(state):
+            r, beta, nr2 = state
+            ecx.setMatrix("p", p_np)                 # host block; uploaded when the instruction acquires it
+            ecx.execute(ins)                          # GPU°mmchain°X°p°w°q°XtwXv°16 (+ sync.postProcess)
+            q_h = ecx.getMatrix("q").reshape(-1)      # acquireHostRead: device -> host
+            pq = float(p_np @ q_h)
+            a = nr2 / pq if pq != 0 else 0.0
+            beta += a * p_np
+            r += a * q_h
+            nr2n = float(r @ r)
+            p_np[:] = -r + (nr2n / nr2) * p_np
+            return r, beta, nr2n
+
+        st = host_state()
+        for _ in range(3):
+            st = ec_step(st)
+        st = host_state()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            st = ec_step(st)
+        ms_i = (time.perf_counter() - t0) * 1000.0 / args.steps
+        e2e["instruction_level"] = {"value": 1000.0 / ms_i, "unit": UNIT, "ms_per_step": ms_i,
+                                    "note": "same iteration through sysml_b200_ec_execute('GPU°mmchain°X°p°w°q°XtwXv°16'): parser, GPUObject locks, lazy H2D of p, D2H of q, sync after the instruction"}
+        ecx.destroy()
+
     # ---------------- auxiliary: tsmm FP64 TFLOP/s on this rank's shard (N = 1 only) ----------------
     tsmm = None
     if world == 1 and not args.no_tsmm:

@@ -55,6 +55,10 @@ int sysml_b200_ec_set_matrix_dense(sysml_b200_ec* ec, const char* name, const do
                                    int64_t cols);
 int sysml_b200_ec_set_matrix_csr(sysml_b200_ec* ec, const char* name, const int32_t* h_rowptr,
                                  const int32_t* h_colind, const double* h_val, int64_t rows, int64_t cols);
+/* Binds a dense matrix that already lives on the device (row-major, on this context's device).  The block
+ * stays owned by the caller: it is never freed or evicted here (a GPUObject whose pointer came from outside). */
+int sysml_b200_ec_set_matrix_device(sysml_b200_ec* ec, const char* name, double* d_data, int64_t rows,
+                                    int64_t cols);
 int sysml_b200_ec_set_scalar(sysml_b200_ec* ec, const char* name, double value);
 int sysml_b200_ec_remove(sysml_b200_ec* ec, const char* name); /* rmvar */
 

@@ -146,6 +146,7 @@ struct GPUObject {
   double* val = nullptr;
   i64 csr_nnz = 0;
   bool dirty = false;
+  bool borrowed = false;  // device block owned by the caller: never freed, never evicted
   int readLocks = 0;
   bool writeLock = false;
   i64 timestamp = 0;
@@ -222,6 +223,11 @@ struct GPUObject {
     if (isAllocated() && dirty) copyFromDeviceToHost();
   }
   void clearData(bool eager) {  // GPUObject.java:948-970
+    if (borrowed) {
+      dense = nullptr;
+      dirty = false;
+      return;
+    }
     mm->free(dense, eager);
     mm->free(rowptr, eager);
     mm->free(colind, eager);
@@ -267,7 +273,7 @@ void* GPUMemoryManager::malloc(const char* opcode, i64 size) {
   if (!A) {
     std::vector<GPUObject*> cand;
     for (GPUObject* o : objects)
-      if (o->isAllocated() && !o->isLocked()) cand.push_back(o);
+      if (o->isAllocated() && !o->isLocked() && !o->borrowed) cand.push_back(o);
     std::sort(cand.begin(), cand.end(), [](GPUObject* a, GPUObject* b) { return a->timestamp < b->timestamp; });
     for (GPUObject* o : cand) {
       if (size <= getAvailableMemory()) break;
@@ -831,6 +837,23 @@ int sysml_b200_ec_set_matrix_csr(sysml_b200_ec* ec, const char* name, const int3
     mo->host_sparse = true;
     mo->host_valid = true;
     ec->matrices[name] = std::move(mo);
+  })
+}
+
+int sysml_b200_ec_set_matrix_device(sysml_b200_ec* ec, const char* name, double* d_data, int64_t rows, int64_t cols) {
+  if (!ec || !name || rows < 0 || cols < 0 || (rows * cols > 0 && !d_data)) return SYSML_E_INVALID;
+  EC_TRY(ec, {
+    ec->removeMatrix(name);
+    std::unique_ptr<MatrixObject> mo(new MatrixObject());
+    mo->name = name;
+    mo->rows = rows;
+    mo->cols = cols;
+    MatrixObject* p = mo.get();
+    ec->matrices[name] = std::move(mo);
+    GPUObject* g = ec->gpuObject(p);
+    g->dense = d_data;
+    g->borrowed = true;
+    g->dirty = true;  // the device copy is the only one
   })
 }
 

@@ -72,6 +72,10 @@ class ExecutionContext:
         self._check(self._lib.sysml_b200_ec_set_matrix_csr(self.handle, name.encode(), rp.ctypes.data_as(C.c_void_p),
                                                            ci.ctypes.data_as(C.c_void_p), va.ctypes.data_as(C.c_void_p), shape[0], shape[1]))
 
+    def setMatrixDevice(self, name, dptr, rows, cols):
+        """Bind a dense matrix that already lives on the device (borrowed, never freed here)."""
+        self._check(self._lib.sysml_b200_ec_set_matrix_device(self.handle, name.encode(), C.c_void_p(dptr), rows, cols))
+
     def setScalar(self, name, value):
         self._check(self._lib.sysml_b200_ec_set_scalar(self.handle, name.encode(), float(value)))
 

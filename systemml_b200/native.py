@@ -73,6 +73,7 @@ SIGNATURES = {
     "sysml_b200_ec_last_error": (C.c_char_p, [vp]),
     "sysml_b200_ec_set_matrix_dense": (ci, [vp, C.c_char_p, vp, i64, i64]),
     "sysml_b200_ec_set_matrix_csr": (ci, [vp, C.c_char_p, vp, vp, vp, i64, i64]),
+    "sysml_b200_ec_set_matrix_device": (ci, [vp, C.c_char_p, vp, i64, i64]),
     "sysml_b200_ec_set_scalar": (ci, [vp, C.c_char_p, dbl]),
     "sysml_b200_ec_remove": (ci, [vp, C.c_char_p]),
     "sysml_b200_ec_execute": (ci, [vp, C.c_char_p]),

@@ -185,3 +185,19 @@ def test_error_paths(ec):
     ec.execute(inst("uak+", mat("A"), scalar_var("s")))
     assert ec.getScalar("s") == 12.0
     ec.removeVariable("A")
+
+
+def test_borrowed_device_matrix(gctx, ec):
+    """A matrix that already lives on the device (e.g. produced by another library) is bound, used and left alone."""
+    X = gctx.rand(5000, 300, seed=3)
+    Xh = X.to_host()
+    ec.setMatrixDevice("X", X.ptr, 5000, 300)
+    v = O.rand_uniform(300, seed=4).reshape(300, 1)
+    ec.setMatrix("v", v)
+    ec.execute(inst("mmchain", mat("X"), mat("v"), mat("q"), "XtXv"))
+    assert_equal_matrices(O.mmchain_dense(Xh, v, None, 0, 4), ec.getMatrix("q"))
+    assert np.array_equal(ec.getMatrix("X"), Xh)
+    ec.removeVariable("X")                      # must NOT free the caller's block
+    assert np.array_equal(X.to_host(), Xh)
+    assert ec.stats()["h2d"] == 1               # only v was uploaded
+    X.free()
