@@ -49,8 +49,12 @@ def build(force=False, verbose=False):
         rc = r.returncode
         # ptxas occasionally falls off a cliff on the warp-specialised kernels (32 registers, kilobytes of
         # spills); a kernel that spills is a build failure, not a slow kernel
-        spills = [l for l in out.splitlines() if "bytes spill stores" in l and not l.strip().startswith("0 bytes stack frame, 0 bytes spill stores")]
-        spills = [l for l in spills if ", 0 bytes spill stores" not in l]
+        import re as _re
+        spills = []
+        for l in out.splitlines():
+            mm = _re.search(r"(\d+) bytes spill stores", l)
+            if mm and int(mm.group(1)) > 64:  # a handful of bytes is harmless; kilobytes mean ptxas gave up
+                spills.append(l)
         if rc == 0 and spills:
             out += "\nERROR: register spills in %s:\n%s\n" % (src, "\n".join(spills[:5]))
             rc = 1

@@ -398,6 +398,13 @@ int vm_wide(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, 
 
 }  // namespace
 
+// sums P partial rows of length m (fixed order, compensated); used by sparse.cu for its replicated outputs
+int sysml_reduce_partial_rows(sysml_b200_ctx* ctx, const double* partial, int P, int m, double* out) {
+  colpartial_reduce_kernel<<<(unsigned)((m + 31) / 32), 256, 0, ctx->stream>>>(partial, P, m, out);
+  SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel");
+  return SYSML_OK;
+}
+
 // internal entry points used by matmult.cu as well
 int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m) {
   if (m <= 4096) {

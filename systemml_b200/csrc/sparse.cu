@@ -18,6 +18,8 @@
 
 #include "common.cuh"
 
+int sysml_reduce_partial_rows(sysml_b200_ctx* ctx, const double* partial, int P, int m, double* out);
+
 namespace {
 
 __device__ __forceinline__ double jmax(double a, double b) {
@@ -46,7 +48,7 @@ inline int pick_lanes(i64 nnz, i64 rows) {
   return L;
 }
 inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
-  const i64 rows_per_block = (threads / 32) * (32 / L);
+  const i64 rows_per_block = (threads / 32) * (32 / L);  // per pass; kernels that unroll passes just loop less
   i64 blocks = (rows + rows_per_block - 1) / rows_per_block;
   const i64 cap = (i64)ctx->sm_count * 16;
   if (blocks > cap) blocks = cap;
@@ -60,7 +62,11 @@ inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
 template <int L, int MODE>
 __global__ void __launch_bounds__(256) csr_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
                                                       const double* __restrict__ va, const double* __restrict__ v,
-                                                      const double* __restrict__ w, double* __restrict__ out, i64 rows, int ct) {
+                                                      const double* __restrict__ w, double* __restrict__ out, i64 rows, int ct,
+                                                      int replicas, i64 out_len) {
+  // scatter modes: the L2 serialises atomics that hit the same address, and the output vector is small and
+  // hot -- each CTA therefore adds into one of `replicas` copies of it (summed afterwards in a fixed order)
+  if (MODE != 0 && replicas > 1) out += (i64)(blockIdx.x % replicas) * out_len;
   const int lane = threadIdx.x & 31;
   const int sub = lane & (L - 1);
   constexpr int RPW = 32 / L;
@@ -510,19 +516,38 @@ inline unsigned warp_rows_grid(sysml_b200_ctx* ctx, i64 rows) {
   return (unsigned)blocks;
 }
 
+inline int sysml_reduce_partial_rows_fwd(sysml_b200_ctx* ctx, const double* partial, int P, int m, double* out) {
+  return ::sysml_reduce_partial_rows(ctx, partial, P, m, out);
+}
+
 template <int MODE>
 int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const double* va, const double* v, const double* w,
-                   double* out, i64 rows, i64 nnz, int ct) {
+                   double* out, i64 rows, i64 nnz, int ct, i64 out_len) {
   const int L = pick_lanes(nnz, rows);
   const unsigned g = rows_grid(ctx, rows, L, 256);
+  int replicas = 1;
+  double* target = out;
+  if (MODE != 0 && out_len <= (1 << 20) && nnz > 64 * out_len) {
+    replicas = 32;
+    while (replicas > 1 && (i64)replicas * out_len * 8 > (64ll << 20)) replicas >>= 1;
+    if ((unsigned)replicas > g) replicas = (int)g;
+  }
+  if (replicas > 1) {
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)replicas * out_len * sizeof(double), &ws);
+    if (rc) return rc;
+    target = (double*)ws;
+    SYSML_CUDA(ctx, cudaMemsetAsync(target, 0, (size_t)replicas * out_len * sizeof(double), ctx->stream));
+  }
   switch (L) {
-    case 2: csr_row_kernel<2, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
-    case 4: csr_row_kernel<4, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
-    case 8: csr_row_kernel<8, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
-    case 16: csr_row_kernel<16, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
-    default: csr_row_kernel<32, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, out, rows, ct); break;
+    case 2: csr_row_kernel<2, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
+    case 4: csr_row_kernel<4, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
+    case 8: csr_row_kernel<8, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
+    case 16: csr_row_kernel<16, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
+    default: csr_row_kernel<32, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
   }
   SYSML_LAUNCH_CHECK(ctx, "csr_row_kernel");
+  if (replicas > 1) return sysml_reduce_partial_rows_fwd(ctx, target, replicas, (int)out_len, out);
   return SYSML_OK;
 }
 
@@ -553,7 +578,7 @@ extern "C" int sysml_b200_mmchain_csr(sysml_b200_ctx* ctx, const int32_t* rowptr
   int rc = fetch_nnz(ctx, rowptr, n, &nnz);
   if (rc) return rc;
   if (nnz == 0) return SYSML_OK;
-  return launch_csr_row<1>(ctx, rowptr, colind, val, v, w, out, n, nnz, chain_type);
+  return launch_csr_row<1>(ctx, rowptr, colind, val, v, w, out, n, nnz, chain_type, m);
 }
 
 extern "C" int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
@@ -578,12 +603,12 @@ extern "C" int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* 
   if (trans_a) {
     SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(m * n) * sizeof(double), ctx->stream));
     if (nnz == 0) return SYSML_OK;
-    if (n == 1) return launch_csr_row<2>(ctx, rowptr, colind, val, nullptr, B, C, a_rows, nnz, 0);
+    if (n == 1) return launch_csr_row<2>(ctx, rowptr, colind, val, nullptr, B, C, a_rows, nnz, 0, m);
     csr_tspmm_kernel<<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, n);
     SYSML_LAUNCH_CHECK(ctx, "csr_tspmm_kernel");
     return SYSML_OK;
   }
-  if (n == 1) return launch_csr_row<0>(ctx, rowptr, colind, val, B, nullptr, C, a_rows, nnz, 0);
+  if (n == 1) return launch_csr_row<0>(ctx, rowptr, colind, val, B, nullptr, C, a_rows, nnz, 0, a_rows);
   if (n <= 32) {
     csr_spmm_skinny_kernel<1><<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, (int)n);
   } else if (n <= 64) {

@@ -27,6 +27,16 @@ elif op == "matmult":
     else:
         A, B, o = g.rand(M, K, seed=1), g.rand(K, N, seed=2), g.empty(M, N)
         fn = lambda: g.call("sysml_b200_matmult_dense", p_(A), p_(B), p_(o), M, K, K, N, 0, 0)
+elif op == "spmv":
+    import numpy as np
+    rows, cols, per = a
+    rng = np.random.default_rng(2)
+    ci = (np.arange(per, dtype=np.int64)[None, :] * (cols // per) + rng.integers(0, cols // per, size=(rows, per))).astype(np.int32).reshape(-1)
+    va = rng.uniform(-1, 1, rows * per)
+    rp = (np.arange(rows + 1, dtype=np.int64) * per).astype(np.int32)
+    S = g.csr(rp, ci, va, (rows, cols))
+    v, o = g.rand(cols, 1, seed=2), g.empty(rows, 1)
+    fn = lambda: g.call("sysml_b200_matmult_csr_dense", C.c_void_p(S.csr.rowPtr), C.c_void_p(S.csr.colInd), C.c_void_p(S.csr.val), p_(v), p_(o), rows, cols, cols, 1, 0)
 elif op == "agg":
     n, m, aop, d = a
     X = g.rand(n, m, seed=1)
