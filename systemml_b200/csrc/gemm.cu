@@ -235,21 +235,22 @@ __device__ __forceinline__ void tile_issue(double* s, const double* src, i64 ld,
 // 8 lanes per row segment, zero-filling through the src-size operand, and lets the copies arrive on the
 // stage's mbarrier (cp.async.mbarrier.arrive.noinc).
 template <int R, int LD, int KC>  // KC doubles (KC/2 16-byte chunks) per row
-__device__ __forceinline__ void tile_issue_cpasync(double* s, const double* src, i64 ld, i64 rvalid, i64 kvalid, int lane) {
+__device__ __forceinline__ void tile_issue_cpasync(double* s, const double* src, i64 ld, i64 rvalid, i64 kvalid, int lane, int pw, int npw) {
   if constexpr (KC == 16) {
     // 8 chunks per row, 4 rows per warp instruction
-    const int r0 = lane >> 3, cc = (lane & 7) * 2;
+    const int r0 = pw * 4 + (lane >> 3), cc = (lane & 7) * 2;  // producer warp pw takes rows pw*4.., step 4*npw
     i64 nb = (kvalid - cc) * 8;
     nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
     const double* p = src + (i64)r0 * ld + cc;
     double* d = s + r0 * LD + cc;
-    const i64 step = 4 * ld;
+    const i64 step = (i64)4 * npw * ld;
+    const int dstep = 4 * npw * LD;
 #pragma unroll 4
-    for (int r = r0; r < R; r += 4) {
+    for (int r = r0; r < R; r += 4 * npw) {
       const int bytes = (r < rvalid) ? (int)nb : 0;
       cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
       p += step;
-      d += 4 * LD;
+      d += dstep;
     }
   } else {
     // KC == 64: 32 chunks per row, one row (512 contiguous bytes) per warp instruction
@@ -257,23 +258,23 @@ __device__ __forceinline__ void tile_issue_cpasync(double* s, const double* src,
     const int cc = lane * 2;
     i64 nb = (kvalid - cc) * 8;
     nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
-    const double* p = src + cc;
-    double* d = s + cc;
+    const double* p = src + (i64)pw * ld + cc;
+    double* d = s + pw * LD + cc;
 #pragma unroll 4
-    for (int r = 0; r < R; r++) {
+    for (int r = pw; r < R; r += npw) {
       const int bytes = (r < rvalid) ? (int)nb : 0;
       cp_async16(d, bytes ? (const void*)p : (const void*)src, bytes);
-      p += ld;
-      d += LD;
+      p += (i64)npw * ld;
+      d += npw * LD;
     }
   }
 }
 // rows-long tile [R][CCOLS] with SHORT rows (< 1 KB): same idea, 16-byte chunks spread over the warp
 template <int R, int CCOLS, int LD>
-__device__ __forceinline__ void tile_issue_cpasync_rows(double* s, const double* src, i64 ld, i64 rvalid, i64 cvalid, int lane) {
+__device__ __forceinline__ void tile_issue_cpasync_rows(double* s, const double* src, i64 ld, i64 rvalid, i64 cvalid, int lane, int pw, int npw) {
   constexpr int CH = CCOLS / 2;
 #pragma unroll 2
-  for (int c = lane; c < R * CH; c += 32) {
+  for (int c = pw * 32 + lane; c < R * CH; c += 32 * npw) {
     const int r = c / CH, cc = (c - r * CH) * 2;
     i64 nb = (r < rvalid) ? (cvalid - cc) * 8 : 0;
     nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
@@ -284,8 +285,8 @@ __device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST>
-__global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(const GemmArgs g) {
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST, int NPW>
+__global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kernel(const GemmArgs g) {
   using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
   constexpr int NCW = WARPS_M * WARPS_N;  // consumer warps
   constexpr int MT = Cfg::MT, NTL = Cfg::NTL, LDA = Cfg::LDA, LDB = Cfg::LDB;
@@ -318,10 +319,10 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
   // clear all tiles once: padding columns/rows that no copy ever writes must read as zero
-  for (int c = tid; c < NST * (Cfg::A_ELEMS + Cfg::B_ELEMS); c += (NCW + 1) * 32) As[c] = 0.0;
+  for (int c = tid; c < NST * (Cfg::A_ELEMS + Cfg::B_ELEMS); c += (NCW + NPW) * 32) As[c] = 0.0;
   if (tid == 0) {
     for (int s = 0; s < NST; s++) {
-      mbar_init(&full[s], ANY_CPASYNC ? 1 + 32 : 1);  // lane 0's expect_tx arrival (+ one cp.async arrival per producer lane)
+      mbar_init(&full[s], ANY_CPASYNC ? 1 + 32 * NPW : 1);  // lane 0's expect_tx arrival (+ one cp.async arrival per producer lane)
       mbar_init(&empty[s], NCW);
     }
     mbar_fence_init();
@@ -329,8 +330,9 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
 
-  if (warp == NCW) {
-    // ===================== producer warp =====================
+  if (warp >= NCW) {
+    // ===================== producer warps (warp NCW does the bulk copies; all NPW share the cp.async rows) =====================
+    const int pw = warp - NCW;
     for (int kb = 0; kb < nkb; kb++) {
       const int s = kb % NST;
       const uint32_t ph = (uint32_t)(kb / NST) & 1u;
@@ -340,23 +342,29 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + 1) * 32) dgemm_ws_kernel(
       double* as = As + s * Cfg::A_ELEMS;
       double* bs = Bs + s * Cfg::B_ELEMS;
       // bulk copies only for operands whose tile rows are >= 1 KB; 16-byte cp.async for everything else
-      if (kvalid < BKT) {  // ragged last k block: clear what the bulk copies below will not overwrite
-        if (A_BULK) tile_zero_tail<BKT, BM, LDA>(as, kvalid, g.M - i0, lane);
-        if (B_BULK) tile_zero_tail<BKT, BN, LDB>(bs, kvalid, g.N - j0, lane);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      if (pw == 0) {
+        if (kvalid < BKT) {  // ragged last k block: clear what the bulk copies below will not overwrite
+          if (A_BULK) tile_zero_tail<BKT, BM, LDA>(as, kvalid, g.M - i0, lane);
+          if (B_BULK) tile_zero_tail<BKT, BN, LDB>(bs, kvalid, g.N - j0, lane);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        uint32_t bytes = 0;
+        if (A_BULK) bytes += tile_bytes<BKT, BM, LDA>(kvalid, g.M - i0);
+        if (B_BULK) bytes += tile_bytes<BKT, BN, LDB>(kvalid, g.N - j0);
+        __syncwarp();
+        if (lane == 0) mbar_expect_tx(&full[s], bytes);
+        __syncwarp();
+        if (A_BULK) tile_issue<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, &full[s], lane);
+        if (B_BULK) tile_issue<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, &full[s], lane);
       }
-      uint32_t bytes = 0;
-      if (A_BULK) bytes += tile_bytes<BKT, BM, LDA>(kvalid, g.M - i0);
-      if (B_BULK) bytes += tile_bytes<BKT, BN, LDB>(kvalid, g.N - j0);
-      __syncwarp();
-      if (lane == 0) mbar_expect_tx(&full[s], bytes);
-      __syncwarp();
-      if (A_BULK)  tile_issue<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, &full[s], lane);
-      else if (TA) tile_issue_cpasync_rows<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, lane);
-      else         tile_issue_cpasync<BM, LDA, BKT>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, lane);
-      if (B_BULK)   tile_issue<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, &full[s], lane);
-      else if (!TB) tile_issue_cpasync_rows<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, lane);
-      else          tile_issue_cpasync<BN, LDB, BKT>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, lane);
+      if (!A_BULK) {
+        if (TA) tile_issue_cpasync_rows<BKT, BM, LDA>(as, g.A + k0 * g.lda + i0, g.lda, kvalid, g.M - i0, lane, pw, NPW);
+        else    tile_issue_cpasync<BM, LDA, BKT>(as, g.A + i0 * g.lda + k0, g.lda, g.M - i0, kvalid, lane, pw, NPW);
+      }
+      if (!B_BULK) {
+        if (!TB) tile_issue_cpasync_rows<BKT, BN, LDB>(bs, g.B + k0 * g.ldb + j0, g.ldb, kvalid, g.N - j0, lane, pw, NPW);
+        else     tile_issue_cpasync<BN, LDB, BKT>(bs, g.B + j0 * g.ldb + k0, g.ldb, g.N - j0, kvalid, lane, pw, NPW);
+      }
       if (ANY_CPASYNC) cp_async_mbar_arrive(&full[s]);
     }
     if (ANY_CPASYNC) cp_async_wait<0>();
@@ -492,7 +500,7 @@ inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, 
   return p;
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES>
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES, int NPW = 1>
 int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
              int64_t* h_nnz) {
   using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;           // legacy cp.async kernel (BK = 16, 4 stages)
@@ -522,10 +530,10 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
   const bool ws_ok = g.vecA && g.vecB && (M % 2 == 0) && (N % 2 == 0) &&
                      ((reinterpret_cast<uintptr_t>(g.out) & 15) == 0) && getenv("SYSML_B200_GEMM_NO_WS") == nullptr;
   if (ws_ok) {
-    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
+    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST, NPW>;
     const size_t smem_ws = WsCfg::SMEM + 128;
     SYSML_CUDA(ctx, cudaFuncSetAttribute(kws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ws));
-    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), WsCfg::NT + 32, smem_ws, ctx->stream>>>(g);
+    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
     SYSML_LAUNCH_CHECK(ctx, "dgemm_ws_kernel");
   } else {
     dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
@@ -565,14 +573,17 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
   // many DRAM pages.  64-deep k blocks (512-byte segments, 128-row tile, 2 stages) were tried and were slower
   // (17.5 ms vs 14.2 ms): the effective DRAM latency stays ~5 us either way.  Next step: rows-contiguous tiles
   // (few rows x long k) with the k range split across the warps of a CTA.
-  if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 32) return run_gemm<TA, TB, 256, 32, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 40) return run_gemm<TA, TB, 256, 40, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 48) return run_gemm<TA, TB, 256, 48, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 56) return run_gemm<TA, TB, 256, 56, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  return run_gemm<TA, TB, 256, 64, 8, 1>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  // K-contiguous A (no bulk copies possible): one producer warp cannot keep enough cp.async in flight
+  // (measured ~28 KB per SM), so four producer warps share the rows of every stage
+  constexpr int NP = TA ? 1 : 4;
+  if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 32) return run_gemm<TA, TB, 256, 32, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 40) return run_gemm<TA, TB, 256, 40, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 48) return run_gemm<TA, TB, 256, 48, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 56) return run_gemm<TA, TB, 256, 56, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  return run_gemm<TA, TB, 256, 64, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
 }
 
 }  // namespace
