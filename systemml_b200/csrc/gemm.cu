@@ -285,6 +285,20 @@ __device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+__device__ __forceinline__ void tile_coords(const GemmArgs& g, int t, int& ti, int& tj) {
+  if (g.sym) {  // upper-triangular tile list, row by row
+    ti = 0;
+    while (t >= g.tiles_n - ti) {
+      t -= g.tiles_n - ti;
+      ti++;
+    }
+    tj = ti + t;
+  } else {
+    ti = t / g.tiles_n;
+    tj = t - ti * g.tiles_n;
+  }
+}
+
 template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST, int NPW>
 __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kernel(const GemmArgs g) {
   using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
@@ -299,20 +313,9 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   double* As = smem + 16;  // 128 bytes reserved for the barriers
   double* Bs = As + NST * Cfg::A_ELEMS;
 
-  int ti, tj;
-  if (g.sym) {
-    int t = blockIdx.x;
-    ti = 0;
-    while (t >= g.tiles_n - ti) {
-      t -= g.tiles_n - ti;
-      ti++;
-    }
-    tj = ti + t;
-  } else {
-    ti = blockIdx.x / g.tiles_n;
-    tj = blockIdx.x - ti * g.tiles_n;
-  }
-  const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+  // output tiles are walked with a grid stride: with gridDim.x == ntiles this is one tile per CTA; the direct
+  // (no split-K) launches use one CTA per SM slot so that the copy pipeline never drains between tiles
+  const int ntiles = g.sym ? g.tiles_n * (g.tiles_n + 1) / 2 : g.tiles_m * g.tiles_n;
   const i64 kbeg = (i64)blockIdx.y * g.k_per_split;
   const i64 kend = (kbeg + g.k_per_split < g.K) ? kbeg + g.k_per_split : g.K;
   const int nkb = (int)((kend - kbeg + BKT - 1) / BKT);
@@ -333,9 +336,14 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   if (warp >= NCW) {
     // ===================== producer warps (warp NCW does the bulk copies; all NPW share the cp.async rows) =====================
     const int pw = warp - NCW;
-    for (int kb = 0; kb < nkb; kb++) {
-      const int s = kb % NST;
-      const uint32_t ph = (uint32_t)(kb / NST) & 1u;
+    uint32_t it = 0;  // k blocks issued so far, over all tiles of this CTA
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    int ti, tj;
+    tile_coords(g, tile, ti, tj);
+    const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+    for (int kb = 0; kb < nkb; kb++, it++) {
+      const int s = it % NST;
+      const uint32_t ph = (it / NST) & 1u;
       mbar_wait(&empty[s], ph ^ 1u);
       const i64 k0 = kbeg + (i64)kb * BKT;
       const i64 kvalid = kend - k0;
@@ -367,6 +375,7 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
       }
       if (ANY_CPASYNC) cp_async_mbar_arrive(&full[s]);
     }
+    }
     if (ANY_CPASYNC) cp_async_wait<0>();
     return;
   }
@@ -374,11 +383,6 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   // ===================== consumer warps =====================
   const int wm0 = (warp / WARPS_N) * Cfg::WM, wn0 = (warp % WARPS_N) * Cfg::WN;
   const int gid = lane >> 2, tig = lane & 3;
-  double acc[MT][NTL][2];
-#pragma unroll
-  for (int a = 0; a < MT; a++)
-#pragma unroll
-    for (int b = 0; b < NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
   // per-thread fragment base offsets (constant over the whole loop)
   const int a_off = TA ? (tig * LDA + wm0 + gid) : ((wm0 + gid) * LDA + tig);
   const int b_off = TB ? ((wn0 + gid) * LDB + tig) : (tig * LDB + wn0 + gid);
@@ -387,9 +391,19 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   constexpr int B_NT = TB ? 8 * LDB : 8;
   constexpr int B_K4 = TB ? 4 : 4 * LDB;
 
-  for (int kb = 0; kb < nkb; kb++) {
-    const int s = kb % NST;
-    const uint32_t ph = (uint32_t)(kb / NST) & 1u;
+  uint32_t it = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  int ti, tj;
+  tile_coords(g, tile, ti, tj);
+  const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+  double acc[MT][NTL][2];
+#pragma unroll
+  for (int a = 0; a < MT; a++)
+#pragma unroll
+    for (int b = 0; b < NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
+  for (int kb = 0; kb < nkb; kb++, it++) {
+    const int s = it % NST;
+    const uint32_t ph = (it / NST) & 1u;
     mbar_wait(&full[s], ph);
     const double* as = As + s * Cfg::A_ELEMS + a_off;
     const double* bs = Bs + s * Cfg::B_ELEMS + b_off;
@@ -423,6 +437,7 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
         outp[i * g.N + j] = acc[a][b][0];
       }
     }
+  }
   }
 }
 
@@ -533,7 +548,14 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
     auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST, NPW>;
     const size_t smem_ws = WsCfg::SMEM + 128;
     SYSML_CUDA(ctx, cudaFuncSetAttribute(kws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ws));
-    kws<<<dim3((unsigned)p.ntiles, (unsigned)p.splits), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
+    int gx = p.ntiles;
+    if (direct) {  // persistent over tiles: one CTA per resident slot
+      int per_sm = 1;
+      SYSML_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kws, WsCfg::NT + 32 * NPW, smem_ws));
+      if (per_sm < 1) per_sm = 1;
+      if (gx > per_sm * ctx->sm_count) gx = per_sm * ctx->sm_count;
+    }
+    kws<<<dim3((unsigned)gx, (unsigned)p.splits), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
     SYSML_LAUNCH_CHECK(ctx, "dgemm_ws_kernel");
   } else {
     dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
@@ -568,11 +590,6 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
   if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
   if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  // Note (measured, profiles/r01_ncu_xv_summary.txt): for a K-contiguous A with a skinny output (MultiLogReg's
-  // X %*% V, 1M x 5000 x 20) the 256-row tile reaches only ~2.8 TB/s: 256 row segments per stage land in as
-  // many DRAM pages.  64-deep k blocks (512-byte segments, 128-row tile, 2 stages) were tried and were slower
-  // (17.5 ms vs 14.2 ms): the effective DRAM latency stays ~5 us either way.  Next step: rows-contiguous tiles
-  // (few rows x long k) with the k range split across the warps of a CTA.
   // K-contiguous A (no bulk copies possible): one producer warp cannot keep enough cp.async in flight
   // (measured ~28 KB per SM), so four producer warps share the rows of every stage
   constexpr int NP = TA ? 1 : 4;
