@@ -60,7 +60,7 @@ inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
 // MODE 1: c[col] += (w-adjusted A[r,:].v) * A[r,col] (sparse mmchain), ct as in SYSML_CHAIN_*
 // MODE 2: c[col] += y[r] * A[r,col]                 (t(A) %*% y)
 template <int L, int MODE>
-__global__ void __launch_bounds__(256) csr_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
+__global__ void __launch_bounds__(256, 8) csr_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
                                                       const double* __restrict__ va, const double* __restrict__ v,
                                                       const double* __restrict__ w, double* __restrict__ out, i64 rows, int ct,
                                                       int replicas, i64 out_len) {
@@ -99,6 +99,218 @@ __global__ void __launch_bounds__(256) csr_row_kernel(const int* __restrict__ rp
     }
     if (t == 0.0) continue;  // LibMatrixMult.java:1680 / VM skips zero entries of the left vector (:978)
     for (int k = lo + sub; k < hi; k += L) atomicAdd(out + __ldg(ci + k), t * va[k]);
+  }
+}
+
+// ---- streamed CSR row kernel (large matrices, short rows) ------------------------------------------------
+// The row-at-a-time kernel above is latency-bound on short rows (three dependent loads per row: rowptr ->
+// colind/val -> v; measured 0.41 of the HBM copy rate at 10 nnz/row).  rowptr, colind and val of a range of
+// rows are CONTIGUOUS in CSR, so here a producer thread streams them with 1-D bulk copies (TMA engine) into a
+// ring of shared-memory stages -- tens of KB in flight per SM whatever the consumers do -- and the 16 consumer
+// warps work out of shared memory: L lanes per row (L ~ mean/4, so a lane holds up to four independent gathers
+// of v), every consumer thread owns one (row, lane) slot of the tile, warps never wait for each other.
+// Tiles that do not fit a stage (a run of very long rows), the ragged last tile, and tiles whose aligned
+// copy would run past the arrays are flagged "slow" and processed straight from global memory, one warp per row.
+// NC consumer threads (896 = 28 warps, or 512 when only the smaller tiles fit beside v / out); a tile has NC / L rows
+
+struct CsrStreamArgs {
+  const int* rp;
+  const int* ci;
+  const double* va;
+  const double* v;
+  const double* w;
+  double* out;
+  i64 rows, nnz, out_len;
+  int ct, replicas, cap, nst, ntiles;
+  int v_smem;    // > 0: v (that many doubles) is copied into shared memory once per CTA and gathered from there
+  int out_smem;  // > 0: scatter modes accumulate into a per-CTA shared-memory copy of out, written to partial row blockIdx.x at the end
+  // Shared-memory fp64 atomics are CAS loops (~0.8 per clock per SM measured) and L2 fp64 reductions top out near
+  // 150 G/s for the whole chip; they are different units, so red_eighths of every 8 tiles scatter with L2
+  // reductions into red_out (red_replicas zeroed copies of out) while the others use the shared-memory copy.
+  double* red_out;
+  int red_replicas, red_eighths;
+};
+
+template <int L, int MODE, int NC>
+__global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamArgs a) {
+  constexpr int TR = NC / L;     // rows per tile
+  constexpr int RPB = (TR + 4) * 4;   // bytes of a stage's rowptr slice (TR+1 entries, padded to 16 B)
+  extern __shared__ __align__(16) unsigned char cs_smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(cs_smem);
+  uint64_t* empty = full + 8;
+  int4* meta = reinterpret_cast<int4*>(cs_smem + 128);  // per stage: {aligned first k, fast?, -, -}
+  const int cap = a.cap, nst = a.nst;
+  const size_t stage_bytes = (size_t)RPB + TR * 8 + (size_t)cap * 12;
+  unsigned char* stages = cs_smem + 256;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) {
+    for (int s = 0; s < nst; s++) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], NC / 32);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const bool have_w = (MODE == 2) || (MODE == 1 && a.ct != SYSML_CHAIN_XtXv);
+
+  if (warp == NC / 32) {
+    // ===================== producer =====================
+    if (lane != 0) return;
+    const uint64_t pol = l2_policy_evict_first();
+    int tile = blockIdx.x;
+    int nk0 = 0, nk1 = 0;
+    if (tile < a.ntiles) {
+      const i64 r0 = (i64)tile * TR;
+      const i64 r1 = (r0 + TR < a.rows) ? r0 + TR : a.rows;
+      nk0 = __ldg(a.rp + r0);
+      nk1 = __ldg(a.rp + r1);
+    }
+    for (uint32_t it = 0; tile < a.ntiles; tile += gridDim.x, it++) {
+      const int k0 = nk0, k1 = nk1;
+      const int nt = tile + gridDim.x;
+      if (nt < a.ntiles) {  // boundaries of the next tile: in flight while this one waits for its stage
+        const i64 q0 = (i64)nt * TR;
+        const i64 q1 = (q0 + TR < a.rows) ? q0 + TR : a.rows;
+        nk0 = __ldg(a.rp + q0);
+        nk1 = __ldg(a.rp + q1);
+      }
+      const int s = it % nst;
+      const uint32_t ph = (it / nst) & 1u;
+      mbar_wait(&empty[s], ph ^ 1u);
+      const i64 r0 = (i64)tile * TR;
+      const int ka = k0 & ~3, kb = (k1 + 3) & ~3;
+      const bool fast = (r0 + TR + 3 <= a.rows) && ((i64)kb <= a.nnz) && (kb - ka <= cap);
+      meta[s] = make_int4(ka, fast ? 1 : 0, 0, 0);
+      if (fast) {
+        unsigned char* st = stages + (size_t)s * stage_bytes;
+        const uint32_t nk = (uint32_t)(kb - ka);
+        mbar_expect_tx(&full[s], RPB + (have_w ? TR * 8 : 0) + nk * 12u);
+        bulk_g2s(st, a.rp + r0, RPB, &full[s], pol);
+        if (have_w) bulk_g2s(st + RPB, a.w + r0, TR * 8, &full[s], pol);
+        if (nk) {
+          bulk_g2s(st + RPB + TR * 8, a.va + ka, nk * 8u, &full[s], pol);
+          bulk_g2s(st + RPB + TR * 8 + (size_t)cap * 8, a.ci + ka, nk * 4u, &full[s], pol);
+        }
+      } else {
+        mbar_arrive(&full[s]);
+      }
+    }
+    return;
+  }
+
+  // ===================== consumers =====================
+  double* out = a.out;
+  if (MODE != 0 && a.replicas > 1) out += (i64)(blockIdx.x % a.replicas) * a.out_len;
+  // Random 8-byte gathers of v from L2 cost a 32-byte sector each -- more L2 traffic than the matrix stream
+  // itself -- and the stages leave little L1.  A v that fits is therefore staged in shared memory, and so is
+  // the scatter target of modes 1/2 (shared-memory fp64 atomics instead of L2 atomics).
+  double* v_s = reinterpret_cast<double*>(stages + (size_t)nst * stage_bytes);
+  double* out_s = v_s + a.v_smem;
+  const double* vsrc = a.v;
+  if (MODE != 2 && a.v_smem > 0) {
+    for (int i = tid; i < a.v_smem; i += NC) v_s[i] = __ldg(a.v + i);
+    vsrc = v_s;
+  }
+  double* const out_g = out;  // global target (replica) of the scatter modes
+  if (MODE != 0 && a.out_smem > 0) {
+    for (int i = tid; i < a.out_smem; i += NC) out_s[i] = 0.0;
+  }
+  if ((MODE != 2 && a.v_smem > 0) || (MODE != 0 && a.out_smem > 0)) named_bar_sync(1, NC);
+  const int sub = lane & (L - 1);
+  const int row = tid / L;  // this thread's row of every tile
+  uint32_t it = 0;
+  for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, it++) {
+    const int s = it % nst;
+    const uint32_t ph = (it / nst) & 1u;
+    mbar_wait(&full[s], ph);
+    const int4 mt = meta[s];
+    const i64 r0 = (i64)tile * TR;
+    if (mt.y) {
+      const unsigned char* st = stages + (size_t)s * stage_bytes;
+      const int* rp_s = reinterpret_cast<const int*>(st);
+      const double* w_s = reinterpret_cast<const double*>(st + RPB);
+      const double* va_s = reinterpret_cast<const double*>(st + RPB + TR * 8);
+      const int* ci_s = reinterpret_cast<const int*>(st + RPB + TR * 8 + (size_t)cap * 8);
+      const int lo = rp_s[row] - mt.x, hi = rp_s[row + 1] - mt.x;
+      double p = 0.0;
+      if (MODE != 2) {
+        if (a.v_smem > 0) {  // shared-memory gathers: short latency, a plain loop is cheapest
+          for (int k = lo + sub; k < hi; k += L) p = fma(va_s[k], v_s[ci_s[k]], p);
+        } else {
+          for (int k = lo + sub; k < hi; k += 4 * L) {  // up to four independent L1/L2 gathers in flight per lane
+            const int k1 = k + L, k2 = k + 2 * L, k3 = k + 3 * L;
+            const double x0 = __ldg(a.v + ci_s[k]);
+            const double x1 = (k1 < hi) ? __ldg(a.v + ci_s[k1]) : 0.0;
+            const double x2 = (k2 < hi) ? __ldg(a.v + ci_s[k2]) : 0.0;
+            const double x3 = (k3 < hi) ? __ldg(a.v + ci_s[k3]) : 0.0;
+            p = fma(va_s[k], x0, p);
+            if (k1 < hi) p = fma(va_s[k1], x1, p);
+            if (k2 < hi) p = fma(va_s[k2], x2, p);
+            if (k3 < hi) p = fma(va_s[k3], x3, p);
+          }
+        }
+        p = group_sum<L>(p);
+      }
+      if (MODE == 0) {
+        if (sub == 0) out[r0 + row] = p;
+      } else if (hi > lo) {
+        double t;
+        bool skip = false;
+        if (MODE == 1) {
+          const double wr = have_w ? w_s[row] : 0.0;
+          skip = (a.ct == SYSML_CHAIN_XtwXv && wr == 0.0);  // LibMatrixMult.java:1667
+          t = (a.ct == SYSML_CHAIN_XtwXv) ? p * wr : ((a.ct == SYSML_CHAIN_XtXvy) ? p - wr : p);
+        } else {
+          t = w_s[row];
+        }
+        if (!skip && t != 0.0) {
+          // two loops so that each atomic has a known address space (a generic-address atomic is much slower)
+          if (a.out_smem > 0 && (int)(it & 7u) >= a.red_eighths) {
+            for (int k = lo + sub; k < hi; k += L) atomicAdd(out_s + ci_s[k], t * va_s[k]);
+          } else {
+            double* o = (a.out_smem > 0) ? a.red_out + (i64)(blockIdx.x % a.red_replicas) * a.out_len : out_g;
+            for (int k = lo + sub; k < hi; k += L) atomicAdd(o + ci_s[k], t * va_s[k]);
+          }
+        }
+      }
+    } else {
+      // slow tile: straight from global memory, one warp per row
+      const i64 rend = (r0 + TR < a.rows) ? r0 + TR : a.rows;
+      for (i64 r = r0 + warp; r < rend; r += NC / 32) {
+        const int lo = __ldg(a.rp + r), hi = __ldg(a.rp + r + 1);
+        double p = 0.0;
+        if (MODE != 2) {
+          for (int k = lo + lane; k < hi; k += 32) p = fma(ldg_stream(a.va + k), vsrc[__ldg(a.ci + k)], p);
+          p = group_sum<32>(p);
+        }
+        if (MODE == 0) {
+          if (lane == 0) out[r] = p;
+          continue;
+        }
+        if (hi == lo) continue;
+        double t;
+        if (MODE == 1) {
+          const double wr = have_w ? __ldg(a.w + r) : 0.0;
+          if (a.ct == SYSML_CHAIN_XtwXv && wr == 0.0) continue;
+          t = (a.ct == SYSML_CHAIN_XtwXv) ? p * wr : ((a.ct == SYSML_CHAIN_XtXvy) ? p - wr : p);
+        } else {
+          t = __ldg(a.w + r);
+        }
+        if (t == 0.0) continue;
+        if (a.out_smem > 0) {
+          for (int k = lo + lane; k < hi; k += 32) atomicAdd(out_s + __ldg(a.ci + k), t * a.va[k]);
+        } else {
+          for (int k = lo + lane; k < hi; k += 32) atomicAdd(out_g + __ldg(a.ci + k), t * a.va[k]);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty[s]);
+  }
+  if (MODE != 0 && a.out_smem > 0) {
+    named_bar_sync(1, NC);
+    double* dst = a.out + (i64)blockIdx.x * a.out_len;
+    for (int i = tid; i < a.out_smem; i += NC) dst[i] = out_s[i];
   }
 }
 
@@ -522,22 +734,109 @@ inline int sysml_reduce_partial_rows_fwd(sysml_b200_ctx* ctx, const double* part
 
 template <int MODE>
 int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const double* va, const double* v, const double* w,
-                   double* out, i64 rows, i64 nnz, int ct, i64 out_len) {
+                   double* out, i64 rows, i64 nnz, int ct, i64 out_len, i64 vlen) {
   const int L = pick_lanes(nnz, rows);
-  const unsigned g = rows_grid(ctx, rows, L, 256);
+  unsigned g = rows_grid(ctx, rows, L, 256);
+  // streamed kernel: big matrices with short rows and 16-byte aligned arrays (bulk copies)
+  CsrStreamArgs sa{};
+  bool stream = false;
+  size_t stream_smem = 0;
+  int SL = 1;  // lanes per row in the streamed kernel: smallest power of two >= mean/4
+  int NC = 512;
+  {
+    const bool has_w = (MODE == 2) || (MODE == 1 && ct != SYSML_CHAIN_XtXv);
+    const uintptr_t al = reinterpret_cast<uintptr_t>(rp) | reinterpret_cast<uintptr_t>(ci) | reinterpret_cast<uintptr_t>(va) |
+                         (has_w ? reinterpret_cast<uintptr_t>(w) : 0);
+    const double mean = (double)nnz / (double)rows;
+    while (SL < 32 && 4 * SL < mean) SL <<= 1;
+    if ((al & 15) == 0 && nnz >= (1 << 20) && rows >= (i64)(896 / SL) * ctx->sm_count && mean <= 256.0 &&
+        getenv("SYSML_B200_CSR_NO_STREAM") == nullptr) {
+      const size_t all = (size_t)ctx->max_smem_optin;
+      auto stage_of = [&](int nc, int* cap) {
+        const int TR = nc / SL;
+        *cap = (int)(((i64)(TR * mean * 1.25) + 64 + 3) & ~3ll);
+        return (size_t)(TR + 4) * 4 + (size_t)TR * 8 + (size_t)*cap * 12;
+      };
+      // Streaming pays only with v (modes 0/1) and the scatter target (modes 1/2) resident in shared memory
+      // (measured: without them the row-at-a-time kernel, which has the whole L1 for v, is faster): one CTA per
+      // SM with 896 consumers, or 512 when only the smaller tiles leave room for three stages.
+      const size_t need = (MODE != 2 ? (size_t)vlen * 8 : 0) + (MODE != 0 ? (size_t)out_len * 8 : 0);
+      const size_t fixed = 256 + need;
+      int cap = 0, nst = 0;
+      size_t stage = stage_of(896, &cap);
+      NC = 896;
+      if (fixed + 3 * stage > all) {
+        stage = stage_of(512, &cap);
+        NC = 512;
+      }
+      if (fixed + 3 * stage <= all) {
+        nst = (int)((all - fixed) / stage);
+        if (MODE != 2) sa.v_smem = (int)vlen;
+        if (MODE != 0) sa.out_smem = (int)out_len;
+      }
+      if (nst > 6) nst = 6;
+      if (nst >= 2) {
+        stream = true;
+        stream_smem = fixed + (size_t)nst * stage;
+        const int TR = NC / SL;
+        sa.rp = rp; sa.ci = ci; sa.va = va; sa.v = v; sa.w = w; sa.rows = rows; sa.nnz = nnz; sa.out_len = out_len;
+        sa.ct = ct; sa.cap = cap; sa.nst = nst; sa.ntiles = (int)((rows + TR - 1) / TR);
+        g = (unsigned)ctx->sm_count;
+        if ((i64)g > sa.ntiles) g = (unsigned)sa.ntiles;
+      }
+    }
+  }
   int replicas = 1;
   double* target = out;
-  if (MODE != 0 && out_len <= (1 << 20) && nnz > 64 * out_len) {
+  if (stream && MODE != 0 && sa.out_smem > 0) {
+    // one partial row per CTA (every cell written by the kernel) + 32 zeroed rows for the L2-reduction share
+    sa.red_replicas = 32;
+    sa.red_eighths = 3;
+    if (const char* e = getenv("SYSML_B200_CSR_RED_EIGHTHS")) sa.red_eighths = atoi(e);
+    replicas = (int)g + sa.red_replicas;
+    void* ws = nullptr;
+    int rc = sysml_workspace(ctx, (size_t)replicas * out_len * sizeof(double), &ws);
+    if (rc) return rc;
+    target = (double*)ws;
+    sa.red_out = target + (size_t)g * out_len;
+    SYSML_CUDA(ctx, cudaMemsetAsync(sa.red_out, 0, (size_t)sa.red_replicas * out_len * sizeof(double), ctx->stream));
+  } else if (MODE != 0 && out_len <= (1 << 20) && nnz > 64 * out_len) {
     replicas = 32;
     while (replicas > 1 && (i64)replicas * out_len * 8 > (64ll << 20)) replicas >>= 1;
     if ((unsigned)replicas > g) replicas = (int)g;
   }
-  if (replicas > 1) {
+  if (replicas > 1 && target == out) {
     void* ws = nullptr;
     int rc = sysml_workspace(ctx, (size_t)replicas * out_len * sizeof(double), &ws);
     if (rc) return rc;
     target = (double*)ws;
     SYSML_CUDA(ctx, cudaMemsetAsync(target, 0, (size_t)replicas * out_len * sizeof(double), ctx->stream));
+  }
+  if (stream) {
+    sa.out = target;
+    sa.replicas = replicas;
+#define CS_LAUNCH2(LL, NCC)                                                                                             \
+  {                                                                                                                     \
+    auto k = csr_stream_kernel<LL, MODE, NCC>;                                                                          \
+    SYSML_CUDA(ctx, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stream_smem));            \
+    k<<<g, NCC + 32, stream_smem, ctx->stream>>>(sa);                                                                   \
+  }
+#define CS_LAUNCH(LL)              \
+  if (NC == 896) CS_LAUNCH2(LL, 896) \
+  else CS_LAUNCH2(LL, 512)
+    switch (SL) {
+      case 1: CS_LAUNCH(1) break;
+      case 2: CS_LAUNCH(2) break;
+      case 4: CS_LAUNCH(4) break;
+      case 8: CS_LAUNCH(8) break;
+      case 16: CS_LAUNCH(16) break;
+      default: CS_LAUNCH(32) break;
+    }
+#undef CS_LAUNCH2
+#undef CS_LAUNCH
+    SYSML_LAUNCH_CHECK(ctx, "csr_stream_kernel");
+    if (replicas > 1) return sysml_reduce_partial_rows_fwd(ctx, target, replicas, (int)out_len, out);
+    return SYSML_OK;
   }
   switch (L) {
     case 2: csr_row_kernel<2, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
@@ -578,7 +877,7 @@ extern "C" int sysml_b200_mmchain_csr(sysml_b200_ctx* ctx, const int32_t* rowptr
   int rc = fetch_nnz(ctx, rowptr, n, &nnz);
   if (rc) return rc;
   if (nnz == 0) return SYSML_OK;
-  return launch_csr_row<1>(ctx, rowptr, colind, val, v, w, out, n, nnz, chain_type, m);
+  return launch_csr_row<1>(ctx, rowptr, colind, val, v, w, out, n, nnz, chain_type, m, m);
 }
 
 extern "C" int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
@@ -603,12 +902,12 @@ extern "C" int sysml_b200_matmult_csr_dense(sysml_b200_ctx* ctx, const int32_t* 
   if (trans_a) {
     SYSML_CUDA(ctx, cudaMemsetAsync(C, 0, (size_t)(m * n) * sizeof(double), ctx->stream));
     if (nnz == 0) return SYSML_OK;
-    if (n == 1) return launch_csr_row<2>(ctx, rowptr, colind, val, nullptr, B, C, a_rows, nnz, 0, m);
+    if (n == 1) return launch_csr_row<2>(ctx, rowptr, colind, val, nullptr, B, C, a_rows, nnz, 0, m, 0);
     csr_tspmm_kernel<<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, n);
     SYSML_LAUNCH_CHECK(ctx, "csr_tspmm_kernel");
     return SYSML_OK;
   }
-  if (n == 1) return launch_csr_row<0>(ctx, rowptr, colind, val, B, nullptr, C, a_rows, nnz, 0, a_rows);
+  if (n == 1) return launch_csr_row<0>(ctx, rowptr, colind, val, B, nullptr, C, a_rows, nnz, 0, a_rows, a_cols);
   if (n <= 32) {
     csr_spmm_skinny_kernel<1><<<warp_rows_grid(ctx, a_rows), 256, 0, ctx->stream>>>(rowptr, colind, val, B, C, a_rows, (int)n);
   } else if (n <= 64) {

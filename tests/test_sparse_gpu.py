@@ -116,3 +116,59 @@ def test_sparse_tsmm_right(gctx):
     out, gnnz = L.matmultTSMM(gctx, "tsmm", dX, False, with_nnz=True)
     assert_equal_matrices(exp, out.to_host(), what="sparse tsmm RIGHT")
     assert gnnz == nnz
+
+
+def _big_csr(rows, cols, mean, seed, full_rows=(), empty_every=0):
+    """CSR arrays built directly (no dense detour): ~Poisson(mean) entries per row, sorted distinct columns."""
+    rng = np.random.default_rng(seed)
+    cnt = np.minimum(rng.poisson(mean, rows), cols).astype(np.int64)
+    if empty_every:
+        cnt[::empty_every] = 0
+    for r in full_rows:
+        cnt[r] = cols
+    rp = np.zeros(rows + 1, dtype=np.int64)  # the oracle takes int64 row pointers; the device copy is int32
+    rp[1:] = np.cumsum(cnt)
+    ci = np.empty(rp[-1], dtype=np.int32)
+    for r in range(rows):
+        c = cnt[r]
+        if c:
+            ci[rp[r]:rp[r + 1]] = np.sort(rng.choice(cols, size=c, replace=False)) if c < cols else np.arange(cols)
+    va = rng.uniform(-1, 1, rp[-1])
+    va[va == 0] = 0.5
+    return rp, ci, va
+
+
+@pytest.mark.parametrize("rows,cols,mean,full_rows,empty_every", [
+    (40001, 3000, 30, (), 0),                       # ragged last tile
+    (40960, 3000, 30, (5, 20000, 40959), 7),        # tiles that overflow a stage + empty rows
+    (150000, 10000, 10, (), 0),                     # the L2SVM shape class: 10 per row
+    (400000, 500, 3, (), 0),                        # very short rows: one lane per row
+])
+def test_csr_streamed_rows(gctx, rows, cols, mean, full_rows, empty_every, monkeypatch):
+    """The bulk-copy streamed CSR kernel (rows >= 128 x #SMs, nnz >= 2^20) for SpMV, t(X)%*%y and the three
+    sparse mmchain types, against the oracle and against the row-at-a-time kernel."""
+    from systemml_b200 import LibMatrixB200 as L
+    rp, ci, va = _big_csr(rows, cols, mean, 11, full_rows, empty_every)
+    assert rp[-1] >= (1 << 20) or rows * mean < (1 << 20)
+    shape = (rows, cols)
+    dX = gctx.csr(rp, ci, va, shape)
+    rng = np.random.default_rng(5)
+    v = rng.uniform(-1, 1, (cols, 1))
+    y = rng.uniform(-1, 1, (rows, 1))
+    y[::5] = 0.0  # zero weights are skipped (LibMatrixMult.java:1667)
+    exp, _ = O.matmult_csr_dense(rp, ci, va, shape, v, 4)
+    got = L.matmult(gctx, "ba+*", dX, gctx.dense(v)).to_host()
+    assert_equal_matrices(exp, got, what="streamed SpMV")
+    monkeypatch.setenv("SYSML_B200_CSR_NO_STREAM", "1")
+    got_row = L.matmult(gctx, "ba+*", dX, gctx.dense(v)).to_host()
+    monkeypatch.delenv("SYSML_B200_CSR_NO_STREAM")
+    assert_equal_matrices(got_row, got, rel=1e-9, what="streamed vs row kernel")
+    for ct in (0, 1, 2):
+        e = O.mmchain_csr(rp, ci, va, shape, v, y if ct else None, ct, 4)
+        g = L.mmchain(gctx, "mmchain", dX, gctx.dense(v), gctx.dense(y) if ct else None, ct).to_host().reshape(-1)
+        assert np.max(np.abs(e - g)) <= 1e-9 * max(np.max(np.abs(e)), 1e-300), ct
+    # t(X) %*% y: exact column sums in extended precision
+    e2 = np.zeros(cols, dtype=np.longdouble)
+    np.add.at(e2, ci, va.astype(np.longdouble) * np.repeat(y.reshape(-1), np.diff(rp)).astype(np.longdouble))
+    g2 = L.matmult(gctx, "ba+*", dX, gctx.dense(y), isLeftTransposed=True).to_host().reshape(-1)
+    assert np.max(np.abs(e2.astype(np.float64) - g2)) <= 1e-9 * max(float(np.max(np.abs(e2))), 1e-300)

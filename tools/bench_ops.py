@@ -152,18 +152,15 @@ def main():
         for x in (X, o_n, o_m, o_1):
             x.free()
 
-    # ---------------- CSR (C3 scaled: rows x 10k, 10 nnz/row) ----------------
+    # ---------------- CSR (C3 scaled: 20M x 10k, ~Poisson(10) nnz/row) ----------------
     if want("csr"):
-        rows, cols, per = int(5_000_000 * S), 10_000, 10
-        rng = np.random.default_rng(2)
-        # stratified columns: sorted and distinct by construction
-        ci = (np.arange(per, dtype=np.int64)[None, :] * (cols // per) + rng.integers(0, cols // per, size=(rows, per))).astype(np.int32).reshape(-1)
-        va = rng.uniform(-1, 1, rows * per)
-        rp = (np.arange(rows + 1, dtype=np.int64) * per).astype(np.int32)
+        rows, cols, per = int(20_000_000 * S), 10_000, 10
+        from csr_gen import poisson_rows_csr
+        rp, ci, va = poisson_rows_csr(rows, cols, per, 2)  # row lengths ~Poisson(10), as C3's Bernoulli cells give
         Xs = g.csr(rp, ci, va, (rows, cols))
         v, y, w = g.rand(cols, 1, seed=2), g.rand(rows, 1, seed=3), g.rand(rows, 1, seed=4, lo=0.0, hi=1.0)
         o_r, o_c = g.empty(rows, 1), g.empty(cols, 1)
-        nnz = rows * per
+        nnz = int(rp[-1])
         spb = 12.0 * nnz + 4 * (rows + 1) + 8 * cols + 8 * rows
         args_csr = (p_(GPUObject.wrap(g, Xs.csr.rowPtr, 1, 1)), p_(GPUObject.wrap(g, Xs.csr.colInd, 1, 1)), p_(GPUObject.wrap(g, Xs.csr.val, 1, 1)))
         b, a = timeit(g, lambda: g.call("sysml_b200_matmult_csr_dense", *args_csr, p_(v), p_(o_r), rows, cols, cols, 1, 0), args.reps)

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta"""
+"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta | spmv rows cols per [mode] | agg n m op dir"""
 import ctypes as C
 import os
 import sys
@@ -29,14 +29,20 @@ elif op == "matmult":
         fn = lambda: g.call("sysml_b200_matmult_dense", p_(A), p_(B), p_(o), M, K, K, N, 0, 0)
 elif op == "spmv":
     import numpy as np
-    rows, cols, per = a
-    rng = np.random.default_rng(2)
-    ci = (np.arange(per, dtype=np.int64)[None, :] * (cols // per) + rng.integers(0, cols // per, size=(rows, per))).astype(np.int32).reshape(-1)
-    va = rng.uniform(-1, 1, rows * per)
-    rp = (np.arange(rows + 1, dtype=np.int64) * per).astype(np.int32)
+    rows, cols, per = a[:3]
+    mode = a[3] if len(a) > 3 else 0  # 0 X%*%v, 1 t(X)%*%y, 2 mmchain XtwXv
+    from csr_gen import poisson_rows_csr
+    rp, ci, va = poisson_rows_csr(rows, cols, per, 2)
     S = g.csr(rp, ci, va, (rows, cols))
     v, o = g.rand(cols, 1, seed=2), g.empty(rows, 1)
-    fn = lambda: g.call("sysml_b200_matmult_csr_dense", C.c_void_p(S.csr.rowPtr), C.c_void_p(S.csr.colInd), C.c_void_p(S.csr.val), p_(v), p_(o), rows, cols, cols, 1, 0)
+    y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
+    csr3 = (C.c_void_p(S.csr.rowPtr), C.c_void_p(S.csr.colInd), C.c_void_p(S.csr.val))
+    if mode == 0:
+        fn = lambda: g.call("sysml_b200_matmult_csr_dense", *csr3, p_(v), p_(o), rows, cols, cols, 1, 0)
+    elif mode == 1:
+        fn = lambda: g.call("sysml_b200_matmult_csr_dense", *csr3, p_(y), p_(oc), rows, cols, rows, 1, 1)
+    else:
+        fn = lambda: g.call("sysml_b200_mmchain_csr", *csr3, p_(v), p_(y), p_(oc), rows, cols, 1)
 elif op == "agg":
     n, m, aop, d = a
     X = g.rand(n, m, seed=1)
