@@ -338,6 +338,81 @@ inline int lanes_per_row(i64 cols) {
 constexpr int AS_THREADS = 256;  // consumer threads (+32 producer)
 constexpr int AS_STAGES = 3;
 
+// Per-row accumulator of the streamed kernel.  Sums/products reuse Acc; max/min use a branch-free form: the
+// loop keeps a plain compare-select plus two sticky flags (a NaN was seen; a zero of the winning sign was seen)
+// and the Math.max/min corner cases (NaN propagates, -0.0 < +0.0; Builtin.java:356-361) are settled once per row.
+template <int OP>
+struct RowAcc {
+  Acc<OP> a;
+  __device__ __forceinline__ void init() { a.init(); }
+  __device__ __forceinline__ void push(double x) { a.push(x); }
+  __device__ __forceinline__ RowAcc from_lane_xor(int o) const {
+    RowAcc r;
+    r.a.hi = __shfl_xor_sync(0xffffffffu, a.hi, o);
+    r.a.lo = __shfl_xor_sync(0xffffffffu, a.lo, o);
+    return r;
+  }
+  __device__ __forceinline__ void merge(const RowAcc& b) { a.merge(b.a.hi, b.a.lo); }
+  __device__ __forceinline__ double result() const { return a.result(); }
+};
+template <bool ISMAX>
+struct RowAccMinMax {
+  double v;
+  int fl;  // bit 0: NaN seen, bit 1: +0.0 (max) / -0.0 (min) seen
+  __device__ __forceinline__ void init() {
+    v = ISMAX ? -CUDART_INF : CUDART_INF;
+    fl = 0;
+  }
+  __device__ __forceinline__ void push(double x) {
+    const long long b = __double_as_longlong(x);
+    fl |= (x != x) ? 1 : 0;
+    fl |= (b == (ISMAX ? 0ll : (long long)0x8000000000000000ull)) ? 2 : 0;
+    v = (ISMAX ? (x > v) : (x < v)) ? x : v;
+  }
+  __device__ __forceinline__ RowAccMinMax from_lane_xor(int o) const {
+    RowAccMinMax r;
+    r.v = __shfl_xor_sync(0xffffffffu, v, o);
+    r.fl = __shfl_xor_sync(0xffffffffu, fl, o);
+    return r;
+  }
+  __device__ __forceinline__ void merge(const RowAccMinMax& b) {
+    fl |= b.fl;
+    v = (ISMAX ? (b.v > v) : (b.v < v)) ? b.v : v;
+  }
+  __device__ __forceinline__ double result() const {
+    if (fl & 1) return CUDART_NAN;
+    if (v == 0.0 && (fl & 2)) return ISMAX ? 0.0 : -0.0;
+    return v;
+  }
+};
+template <>
+struct RowAcc<K_MAX> : RowAccMinMax<true> {};
+template <>
+struct RowAcc<K_MIN> : RowAccMinMax<false> {};
+
+// Reduces two per-lane accumulators (rows r0, r1 of an L-lane group, L >= 2) with half the shuffles of two
+// separate butterflies: in the first step even lanes keep row r0 and odd lanes row r1, each receiving the
+// partner's share of the row it keeps; the remaining steps stay within lanes of equal parity.  Afterwards
+// x0 of lane sub==0 is row r0 and x0 of lane sub==1 is row r1.
+template <class A>
+__device__ __forceinline__ void pair_group_merge(A& x0, A& x1, int lane, int L) {
+  const bool odd = lane & 1;
+  A keep = odd ? x1 : x0;
+  const A send = odd ? x0 : x1;
+  keep.merge(send.from_lane_xor(1));
+  for (int o = L >> 1; o > 1; o >>= 1) keep.merge(keep.from_lane_xor(o));
+  x0 = keep;
+}
+
+// kept out of line: the compiler otherwise if-converts the rarely taken division (mean only) into every row
+__device__ __noinline__ double div_by_scale(double v, double s) { return __ddiv_rn(v, s); }
+
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+
 struct AggStreamArgs {
   const double* X;
   i64 rows;
@@ -473,6 +548,9 @@ __global__ void __launch_bounds__(AS_THREADS + 32) aggstream_kernel(const AggStr
   const int sub = lane & (L - 1);
   const int rpw = 32 / L;                      // rows per warp pass
   const int rows_per_pass = rpw * (AS_THREADS / 32);
+  const int n_it = (cols - sub + L - 1) / L;  // elements of a row this lane visits
+  const uint32_t step = (uint32_t)L * 8u;
+  const bool scaled = a.scale != 1.0;
   int it = 0;
   for (i64 tile = blockIdx.x; tile < a.total_tiles; tile += gridDim.x, ++it) {
     const int s = it % AS_STAGES;
@@ -487,25 +565,34 @@ __global__ void __launch_bounds__(AS_THREADS + 32) aggstream_kernel(const AggStr
       const double* row0 = T + (size_t)(live0 ? rr0 : 0) * cols;
       const double* row1 = T + (size_t)(live1 ? rr1 : 0) * cols;
       if (KIND == 0) {
-        Acc<OP> x0, x1;
+        // shared-window addresses and the trip count are hoisted: the loop body is two LDS and the two updates
+        // (rows past the end of the tile read row 0 and are discarded)
+        RowAcc<OP> x0, x1;
         x0.init();
         x1.init();
-        for (int j = sub; j < cols; j += L) {
-          const double u = row0[j], w = row1[j];
-          if (live0) x0.push(u);
-          if (live1) x1.push(w);
+        uint32_t p0 = smem_u32(row0 + sub), p1 = smem_u32(row1 + sub);
+#pragma unroll 2
+        for (int i = 0; i < n_it; i++, p0 += step, p1 += step) {
+          x0.push(lds_f64(p0));
+          x1.push(lds_f64(p1));
         }
-        group_merge(x0, L);
-        group_merge(x1, L);
-        if (sub == 0) {
+        if (L >= 2) {
+          pair_group_merge(x0, x1, lane, L);
+          const bool mine = (sub == 0) ? live0 : live1;
+          if (sub < 2 && mine) {
+            double v = x0.result();
+            if (scaled) v = div_by_scale(v, a.scale);
+            a.out[r0 + (sub == 0 ? rr0 : rr1)] = v;
+          }
+        } else {
           if (live0) {
             double v = x0.result();
-            if (a.scale != 1.0) v = __ddiv_rn(v, a.scale);
+            if (scaled) v = div_by_scale(v, a.scale);
             a.out[r0 + rr0] = v;
           }
           if (live1) {
             double v = x1.result();
-            if (a.scale != 1.0) v = __ddiv_rn(v, a.scale);
+            if (scaled) v = div_by_scale(v, a.scale);
             a.out[r0 + rr1] = v;
           }
         }
