@@ -271,6 +271,32 @@ int sysml_b200_fill(sysml_b200_ctx* ctx, double* A, int64_t len, double value);
  * compiles this block into; all operands are device pointers (nr2: one double), nothing returns to the host. */
 int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, double* r, double* beta, double* nr2,
                                 int64_t m, double lambda);
+/* Fused cellwise chain: out = f(inputs, consts) cell by cell in ONE pass over HBM, optionally reduced by
+ * sum / rowSums / colSums in the same pass.  Stands in for a run of matrixMatrixArithmetic / matrixScalarArithmetic
+ * / unaryOp launches and the unaryAggregate after them (LibMatrixCUDA.java:1126-1270, 1969-2290, 573-894), each
+ * of which round-trips a temporary through HBM; the reference's own fused form is the code generator's cellwise
+ * template (runtime/codegen/SpoofCellwise.java: NO_AGG / FULL_AGG / ROW_AGG / COL_AGG).
+ *   inputs[i]      device pointers; input_kinds[i] = SYSML_BCAST_NONE (rows x cols), _COL (rows x 1), _ROW (1 x cols)
+ *   program        postfix tokens SYSML_FUSED_TOKEN(kind, arg); binary/unary args are SYSML_OP_* / SYSML_UN_*
+ *   agg            SYSML_FUSED_AGG_*; out holds rows*cols, 1, rows or cols doubles accordingly
+ * The chain is compiled to a kernel on first use (NVRTC, sm_100a) and cached by program; every operator has the
+ * arithmetic of its unfused kernel, so without an aggregate the result is bit-identical to the unfused sequence.
+ * Fails with SYSML_E_UNSUPPORTED when NVRTC or the driver library cannot be loaded (no CPU path). */
+#define SYSML_FUSED_IN 0     /* push inputs[arg] at the current cell */
+#define SYSML_FUSED_CONST 1  /* push consts[arg] */
+#define SYSML_FUSED_BINARY 2 /* pop y, pop x, push x <SYSML_OP_arg> y */
+#define SYSML_FUSED_UNARY 3  /* pop x, push SYSML_UN_arg(x) */
+#define SYSML_FUSED_TOKEN(kind, arg) (((kind) << 24) | (arg))
+#define SYSML_FUSED_AGG_NONE 0
+#define SYSML_FUSED_AGG_SUM 1
+#define SYSML_FUSED_AGG_ROWSUMS 2
+#define SYSML_FUSED_AGG_COLSUMS 3
+#define SYSML_FUSED_MAX_INPUTS 8
+#define SYSML_FUSED_MAX_CONSTS 8
+#define SYSML_FUSED_MAX_TOKENS 64
+int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
+                              const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
+                              int64_t cols, int agg, double* out);
 /* C = t(A); replaces LibMatrixCUDA.transpose (java:1723-1729, cublasDgeam). */
 int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols);
 

@@ -207,6 +207,56 @@ def axpy(A, B, alpha):
     return out
 
 
+_UNARY_NP = {
+    0: np.exp, 1: np.sqrt, 2: lambda x: np.floor(x + 0.5), 3: np.abs, 4: np.log, 5: np.floor, 6: np.ceil, 7: np.sign,
+    8: lambda x: 1.0 / (1.0 + np.exp(-x)), 9: np.sin, 10: np.cos, 11: np.tan, 12: np.tanh,
+}
+
+
+def fused_cellwise(inputs, consts, tokens, rows, cols, agg=0):
+    """The UNFUSED reference evaluation of a postfix cellwise program (tokens as SYSML_FUSED_TOKEN): one
+    LibMatrixBincell op per binary token (bincellOp, LibMatrixBincell.java:87-339), numpy for the unary builtins,
+    then LibMatrixAgg sum / rowSums / colSums (agg 1/2/3).  Operands broadcast like the reference: rows x 1 and
+    1 x cols vectors against rows x cols."""
+    stack = []
+
+    def full(x):
+        if np.isscalar(x):
+            return np.full((rows, cols), float(x))
+        return np.ascontiguousarray(np.broadcast_to(x, (rows, cols)))
+
+    with np.errstate(all="ignore"):
+        for t in tokens:
+            kind, arg = (t >> 24) & 0xFF, t & 0xFFFFFF
+            if kind == 0:
+                stack.append(np.asarray(inputs[arg], dtype=np.float64))
+            elif kind == 1:
+                stack.append(float(consts[arg]))
+            elif kind == 2:
+                y = stack.pop()
+                x = stack.pop()
+                if np.isscalar(x) and np.isscalar(y):
+                    stack.append(binary_scalar(x, y, arg))
+                elif np.isscalar(y):
+                    stack.append(binary_ms(np.ascontiguousarray(x), y, arg, False))
+                elif np.isscalar(x):
+                    stack.append(binary_ms(np.ascontiguousarray(y), x, arg, True))
+                elif x.shape == y.shape or y.shape in ((x.shape[0], 1), (1, x.shape[1])):
+                    stack.append(binary_mm(np.ascontiguousarray(x), y, arg))
+                else:  # vector on the left or two different vectors: materialise both (outer / reversed broadcast)
+                    stack.append(binary_mm(full(x), full(y), arg))
+            elif kind == 3:
+                x = stack.pop()
+                stack.append(_UNARY_NP[arg](np.asarray(x, dtype=np.float64)) if not np.isscalar(x) else float(_UNARY_NP[arg](np.float64(x))))
+            else:
+                raise ValueError("bad token")
+    assert len(stack) == 1
+    res = full(stack[0])
+    if agg == 0:
+        return res
+    return agg_unary_dense(res, SUM, {1: ALL, 2: ROW, 3: COL}[agg], 1)
+
+
 def count_nnz(A):
     return lib().orc_count_nnz(np.ascontiguousarray(A).reshape(-1), A.size)
 

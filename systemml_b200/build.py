@@ -28,9 +28,20 @@ def _newer(a, b):
     return (not os.path.exists(b)) or os.path.getmtime(a) > os.path.getmtime(b)
 
 
+def embed_ops_header():
+    """cellwise_ops.cuh as a C++ raw string literal, for the NVRTC-compiled fused cellwise kernels (fused.cu)."""
+    src = os.path.join(CSRC, "cellwise_ops.cuh")
+    dst = os.path.join(CSRC, "cellwise_ops_embed.inc")
+    text = 'R"SYSMLOPS(' + open(src).read() + ')SYSMLOPS"\n'
+    if not os.path.exists(dst) or open(dst).read() != text:
+        with open(dst, "w") as f:
+            f.write(text)
+
+
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
-    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    embed_ops_header()
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".inc"))]
     hdrs.append(os.path.join(HERE, "..", "include", "sysml_b200.h"))
     hdrs.append(os.path.join(HERE, "..", "include", "sysml_b200_host.h"))
     hdr_time = max(os.path.getmtime(h) for h in hdrs)
@@ -73,7 +84,7 @@ def build(force=False, verbose=False):
                     raise RuntimeError("nvcc failed on %s" % src)
     objs = [os.path.join(OBJ, os.path.splitext(s)[0] + ".o") for s in sources()]
     if jobs or not os.path.exists(SO):
-        cmd = [NVCC, "-shared", "-o", SO] + objs + ["-ccbin", "/usr/bin/g++", "-Xlinker", "--no-undefined"]
+        cmd = [NVCC, "-shared", "-o", SO] + objs + ["-ccbin", "/usr/bin/g++", "-Xlinker", "--no-undefined", "-ldl"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode:
             sys.stderr.write(r.stdout + r.stderr)

@@ -198,6 +198,81 @@ def unaryOp(gCtx, instName, in1, op):
     return out
 
 
+FUSED_AGG = {None: 0, "none": 0, "sum": 1, "rowSums": 2, "colSums": 3}
+
+
+class Expr:
+    """Tiny expression builder for fusedCellwise: Expr.input(0) * Expr.const(0) ... -> postfix tokens of
+    include/sysml_b200.h (SYSML_FUSED_TOKEN)."""
+
+    def __init__(self, tokens):
+        self.tokens = list(tokens)
+
+    @staticmethod
+    def input(i):
+        return Expr([(0 << 24) | i])
+
+    @staticmethod
+    def const(i):
+        return Expr([(1 << 24) | i])
+
+    def binary(self, other, op):
+        opc = BINARY_OPS[op] if isinstance(op, str) else int(op)
+        return Expr(self.tokens + other.tokens + [(2 << 24) | opc])
+
+    def unary(self, op):
+        opc = UNARY_OPS[op] if isinstance(op, str) else int(op)
+        return Expr(self.tokens + [(3 << 24) | opc])
+
+    def __add__(self, o):
+        return self.binary(o, "+")
+
+    def __sub__(self, o):
+        return self.binary(o, "-")
+
+    def __mul__(self, o):
+        return self.binary(o, "*")
+
+    def __truediv__(self, o):
+        return self.binary(o, "/")
+
+
+def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None):
+    """One-pass evaluation of a cellwise chain over `inputs` (GPUObjects: rows x cols matrices, rows x 1 column
+    vectors or 1 x cols row vectors), optionally reduced by sum / rowSums / colSums -- the GPU twin of the code
+    generator's cellwise template (runtime/codegen/SpoofCellwise.java).  Returns a GPUObject, or a float for
+    agg="sum" (read back like LibMatrixCUDA.unaryAggregate does for scalars, LibMatrixCUDA.java:692-693)."""
+    if rows is None:
+        rows = max(i.rows for i in inputs)
+    if cols is None:
+        cols = max(i.cols for i in inputs)
+    kinds = []
+    for i in inputs:
+        if (i.rows, i.cols) == (rows, cols):
+            kinds.append(0)
+        elif (i.rows, i.cols) == (rows, 1):
+            kinds.append(1)
+        elif (i.rows, i.cols) == (1, cols):
+            kinds.append(2)
+        else:
+            raise native.NativeError(native.E_DIM, "fusedCellwise: operand %dx%d does not broadcast to %dx%d" % (i.rows, i.cols, rows, cols))
+    tokens = expr.tokens if isinstance(expr, Expr) else list(expr)
+    a = FUSED_AGG[agg] if not isinstance(agg, int) else agg
+    orow, ocol = {0: (rows, cols), 1: (1, 1), 2: (rows, 1), 3: (1, cols)}[a]
+    out = GPUObject.allocate_dense(gCtx, orow, ocol)
+    n = len(inputs)
+    ptrs = (C.c_void_p * max(n, 1))(*[i.ptr for i in inputs])
+    kd = (C.c_int * max(n, 1))(*kinds)
+    cs = (C.c_double * max(len(consts), 1))(*[float(c) for c in consts])
+    pg = (C.c_int32 * len(tokens))(*tokens)
+    gCtx.call("sysml_b200_fused_cellwise", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, a, _p(out.ptr))
+    if a == 1:
+        v = float(out.to_host().reshape(-1)[0])
+        out.free()
+        return v
+    return out
+
+
 def transpose(gCtx, instName, in1):
     out = GPUObject.allocate_dense(gCtx, in1.cols, in1.rows)
     gCtx.call("sysml_b200_transpose", _p(in1.ptr), _p(out.ptr), in1.rows, in1.cols)

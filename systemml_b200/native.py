@@ -57,6 +57,7 @@ SIGNATURES = {
     "sysml_b200_unary": (ci, [vp, vp, vp, i64, ci]),
     "sysml_b200_cg_vector_update": (ci, [vp, vp, vp, vp, vp, vp, i64, dbl]),
     "sysml_b200_fill": (ci, [vp, vp, i64, dbl]),
+    "sysml_b200_fused_cellwise": (ci, [vp, vp, vp, ci, vp, ci, vp, ci, i64, i64, ci, vp]),
     "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),
     "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),
     "sysml_b200_dense_to_csr": (ci, [vp, vp, i64, i64, vp, vp, vp, pi64]),

@@ -152,6 +152,56 @@ def main():
         for x in (X, o_n, o_m, o_1):
             x.free()
 
+    # ---------------- fused cellwise chains vs the same chain one launch per operator ----------------
+    if want("fused"):
+        from systemml_b200.lib_matrix import Expr as E
+        n = int(50_000_000 * S)  # C3's row count: the n-vectors of the L2SVM inner loop
+        Y, Xw, Xd = g.rand(n, 1, seed=2), g.rand(n, 1, seed=3), g.rand(n, 1, seed=4)
+        t1, t2, t3 = g.empty(n, 1), g.empty(n, 1), g.empty(n, 1)
+        o1 = g.empty(1, 1)
+        e_out = E.const(0) - E.input(0) * E.input(1)
+        e_sv = e_out.binary(E.const(1), ">")
+        gexpr = e_out * e_sv * E.input(0) * E.input(2)  # sum(out * sv * Y * Xd), l2-svm.dml
+
+        def fused_fn(objs, kinds, expr, consts, rows, cols, agg, outobj):
+            ptrs = (C.c_void_p * len(objs))(*[o.ptr for o in objs])
+            kd = (C.c_int * len(objs))(*kinds)
+            cs = (C.c_double * max(len(consts), 1))(*consts)
+            pg = (C.c_int32 * len(expr.tokens))(*expr.tokens)
+            return lambda: g.call("sysml_b200_fused_cellwise", ptrs, kd, len(objs), cs, len(consts), pg, len(expr.tokens), rows, cols, agg, p_(outobj))
+        fused = fused_fn([Y, Xw, Xd], [0, 0, 0], gexpr, (1.0, 0.0), n, 1, 1, o1)
+
+        def unfused():
+            g.call("sysml_b200_binary_mm", p_(Y), p_(Xw), p_(t1), n, 1, 0, 15)      # 1 - Y*Xw
+            g.call("sysml_b200_binary_ms", p_(t1), 0.0, p_(t2), n, 7, 0)             # out > 0
+            g.call("sysml_b200_binary_mm", p_(t1), p_(t2), p_(t3), n, 1, 0, 2)       # out * sv
+            g.call("sysml_b200_binary_mm", p_(t3), p_(Y), p_(t3), n, 1, 0, 2)        # * Y
+            g.call("sysml_b200_binary_mm", p_(t3), p_(Xd), p_(t3), n, 1, 0, 2)       # * Xd
+            g.call("sysml_b200_agg_unary_dense", p_(t3), n, 1, 0, 0, p_(o1))         # sum
+        b, a = timeit(g, fused, args.reps)
+        report("fused_l2svm_sum_chain", [n, 1], b, a, nbytes=24.0 * n)
+        b, a = timeit(g, unfused, args.reps)
+        report("unfused_l2svm_sum_chain_6_launches", [n, 1], b, a, nbytes=24.0 * n)
+        for x in (Y, Xw, Xd, t1, t2, t3, o1):
+            x.free()
+        # Kmeans: P = ((-2 * XC + rowvec) <= colvec), 10M x 50
+        n, m = int(10_000_000 * S), 50
+        XC, Z, T = g.rand(n, m, seed=5), g.empty(n, m), g.empty(n, m)
+        rv, cv = g.rand(1, m, seed=6), g.rand(n, 1, seed=7)
+        kexpr = (E.const(0) * E.input(0) + E.input(1)).binary(E.input(2), "<=")
+        fused = fused_fn([XC, rv, cv], [0, 2, 1], kexpr, (-2.0,), n, m, 0, Z)
+
+        def unfused2():
+            g.call("sysml_b200_binary_ms", p_(XC), -2.0, p_(T), n * m, 2, 1)
+            g.call("sysml_b200_binary_mm", p_(T), p_(rv), p_(T), n, m, 2, 0)
+            g.call("sysml_b200_binary_mm", p_(T), p_(cv), p_(Z), n, m, 1, 6)
+        b, a = timeit(g, fused, args.reps)
+        report("fused_kmeans_assign_chain", [n, m], b, a, nbytes=16.0 * n * m + 8 * n + 8 * m)
+        b, a = timeit(g, unfused2, args.reps)
+        report("unfused_kmeans_assign_chain_3_launches", [n, m], b, a, nbytes=16.0 * n * m + 8 * n + 8 * m)
+        for x in (XC, Z, T, rv, cv):
+            x.free()
+
     # ---------------- CSR (C3 scaled: 20M x 10k, ~Poisson(10) nnz/row) ----------------
     if want("csr"):
         rows, cols, per = int(20_000_000 * S), 10_000, 10
