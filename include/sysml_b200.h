@@ -286,6 +286,8 @@ int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, doubl
 #define SYSML_FUSED_CONST 1  /* push consts[arg] */
 #define SYSML_FUSED_BINARY 2 /* pop y, pop x, push x <SYSML_OP_arg> y */
 #define SYSML_FUSED_UNARY 3  /* pop x, push SYSML_UN_arg(x) */
+#define SYSML_FUSED_PICK 4   /* push a copy of the value arg places below the top (0 = duplicate the top): shared subexpressions */
+#define SYSML_FUSED_NIP 5    /* drop the value just below the top (ends the scope of a shared subexpression) */
 #define SYSML_FUSED_TOKEN(kind, arg) (((kind) << 24) | (arg))
 #define SYSML_FUSED_AGG_NONE 0
 #define SYSML_FUSED_AGG_SUM 1

@@ -248,6 +248,10 @@ def fused_cellwise(inputs, consts, tokens, rows, cols, agg=0):
             elif kind == 3:
                 x = stack.pop()
                 stack.append(_UNARY_NP[arg](np.asarray(x, dtype=np.float64)) if not np.isscalar(x) else float(_UNARY_NP[arg](np.float64(x))))
+            elif kind == 4:
+                stack.append(stack[-1 - arg])
+            elif kind == 5:
+                del stack[-2]
             else:
                 raise ValueError("bad token")
     assert len(stack) == 1

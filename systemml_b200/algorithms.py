@@ -123,3 +123,102 @@ def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1
     for o in (beta, eta, mu, resid, grad, d, r, p, q, nr2_d):
         o.free()
     return out, inner_counts
+
+
+def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
+    """scripts/algorithms/l2-svm.dml:103-154 (intercept = 0, labels already -1/+1): non-linear CG on the squared-hinge
+    primal with an exact Newton line search.  X: GPUObject n x m, dense or CSR (BASELINE config C3 is CSR 50M x 10k);
+    Y: GPUObject n x 1.  Per outer iteration the O(nnz) work is X %*% s and t(X) %*% (out * Y); everything else is
+    chains over n-vectors, each evaluated in one pass by fusedCellwise (fused=True) or operator by operator
+    (fused=False, the reference's plan).  Returns (w ndarray, iterations, final objective)."""
+    n, m = X.rows, X.cols
+    E = L.Expr
+    alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    sparse = X.csr is not None
+
+    def x_times(v, out):        # out = X %*% v
+        if sparse:
+            g.call("sysml_b200_matmult_csr_dense", C.c_void_p(X.csr.rowPtr), C.c_void_p(X.csr.colInd), C.c_void_p(X.csr.val),
+                   _p(v), _p(out), n, m, m, 1, 0)
+        else:
+            g.call("sysml_b200_matmult_dense", _p(X), _p(v), _p(out), n, m, m, 1, 0, 0)
+
+    def xt_times(yv, out):      # out = t(X) %*% yv
+        if sparse:
+            g.call("sysml_b200_matmult_csr_dense", C.c_void_p(X.csr.rowPtr), C.c_void_p(X.csr.colInd), C.c_void_p(X.csr.val),
+                   _p(yv), _p(out), n, m, n, 1, 1)
+        else:
+            g.call("sysml_b200_matmult_dense", _p(X), _p(yv), _p(out), n, m, n, 1, 1, 0)
+
+    def fsum(inputs, expr, consts=()):
+        return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum")
+
+    def dot(a, b):
+        return fsum([a, b], E.input(0) * E.input(1))
+
+    w, Xw, Xd, s, g_old, g_new = alloc(m, 1), alloc(n, 1), alloc(n, 1), alloc(m, 1), alloc(m, 1), alloc(m, 1)
+    t1, t2, t3 = alloc(n, 1), alloc(n, 1), alloc(n, 1)
+    g.call("sysml_b200_fill", _p(w), m, 0.0)
+    g.call("sysml_b200_fill", _p(Xw), n, 0.0)
+    xt_times(Y, g_old)
+    g.call("sysml_b200_d2d", _p(s), _p(g_old), 8 * m)
+    # inputs of the n-vector chains: 0 = Y, 1 = Xw, 2 = Xd; constants: 0 = 1.0, 1 = 0.0, 2 = step_sz
+    out_e = E.const(0) - E.input(0) * (E.input(1) + E.const(2) * E.input(2))          # 1 - Y * (Xw + step_sz*Xd)
+    g_e = E.let(out_e, lambda o: o * o.binary(E.const(1), ">") * E.input(0) * E.input(2))   # (out*sv) * Y * Xd
+    h_e = E.input(2) * out_e.binary(E.const(1), ">") * E.input(2)                     # Xd * sv * Xd
+    it, cont, obj = 0, True, 0.0
+    while cont and it < maxiter:
+        step = 0.0
+        x_times(s, Xd)
+        wd = reg * dot(w, s)
+        dd = reg * dot(s, s)
+        while True:
+            if fused:
+                gsum = fsum([Y, Xw, Xd], g_e, (1.0, 0.0, step))
+                hsum = fsum([Y, Xw, Xd], h_e, (1.0, 0.0, step))
+            else:
+                g.call("sysml_b200_axpy", _p(Xw), _p(Xd), step, _p(t1), n, 1, 0)                       # tmp_Xw
+                g.call("sysml_b200_binary_mm", _p(Y), _p(t1), _p(t1), n, 1, 0, L.BINARY_OPS["1-*"])    # out = 1 - Y*tmp_Xw
+                g.call("sysml_b200_binary_ms", _p(t1), 0.0, _p(t2), n, L.BINARY_OPS[">"], 0)           # sv
+                g.call("sysml_b200_binary_mm", _p(t1), _p(t2), _p(t1), n, 1, 0, L.BINARY_OPS["*"])     # out * sv
+                g.call("sysml_b200_binary_mm", _p(t1), _p(Y), _p(t1), n, 1, 0, L.BINARY_OPS["*"])
+                g.call("sysml_b200_binary_mm", _p(t1), _p(Xd), _p(t1), n, 1, 0, L.BINARY_OPS["*"])
+                gsum = L.unaryAggregate(g, "uak+", t1, "uak+")
+                g.call("sysml_b200_binary_mm", _p(Xd), _p(t2), _p(t3), n, 1, 0, L.BINARY_OPS["*"])
+                g.call("sysml_b200_binary_mm", _p(t3), _p(Xd), _p(t3), n, 1, 0, L.BINARY_OPS["*"])
+                hsum = L.unaryAggregate(g, "uak+", t3, "uak+")
+            gg = wd + step * dd - gsum
+            hh = dd + hsum
+            step = step - gg / hh
+            if not (gg * gg / hh >= 1e-10):
+                break
+        g.call("sysml_b200_axpy", _p(w), _p(s), step, _p(w), m, 1, 0)          # w += step_sz * s
+        g.call("sysml_b200_axpy", _p(Xw), _p(Xd), step, _p(Xw), n, 1, 0)       # Xw += step_sz * Xd
+        # out = sv * (1 - Y*Xw); obj = 0.5*sum(out*out) + reg/2*sum(w*w); t1 = out * Y
+        hinge = E.let(E.const(0) - E.input(0) * E.input(1), lambda o: o.binary(E.const(1), ">") * o)
+        if fused:
+            osum = fsum([Y, Xw], E.let(hinge, lambda o: o * o), (1.0, 0.0))
+            oy = L.fusedCellwise(g, "spoof", [Y, Xw], hinge * E.input(0), (1.0, 0.0))
+        else:
+            g.call("sysml_b200_binary_mm", _p(Y), _p(Xw), _p(t1), n, 1, 0, L.BINARY_OPS["1-*"])
+            g.call("sysml_b200_binary_ms", _p(t1), 0.0, _p(t2), n, L.BINARY_OPS[">"], 0)
+            g.call("sysml_b200_binary_mm", _p(t2), _p(t1), _p(t1), n, 1, 0, L.BINARY_OPS["*"])
+            osum = L.unaryAggregate(g, "uasqk+", t1, "uasqk+")
+            oy = alloc(n, 1)
+            g.call("sysml_b200_binary_mm", _p(t1), _p(Y), _p(oy), n, 1, 0, L.BINARY_OPS["*"])
+        obj = 0.5 * osum + reg / 2.0 * dot(w, w)
+        xt_times(oy, g_new)
+        oy.free()
+        g.call("sysml_b200_axpy", _p(g_new), _p(w), -float(reg), _p(g_new), m, 1, 0)     # g_new = t(X)(out*Y) - reg*w
+        tmp = dot(s, g_old)
+        be = dot(g_new, g_new) / dot(g_old, g_old)
+        g.call("sysml_b200_axpy", _p(g_new), _p(s), be, _p(s), m, 1, 0)                  # s = be*s + g_new
+        g.call("sysml_b200_d2d", _p(g_old), _p(g_new), 8 * m)
+        cont = (step * tmp >= tol * obj) and dot(s, s) != 0.0
+        it += 1
+        if log is not None:
+            log.append((it, obj))
+    res = w.to_host().reshape(-1)
+    for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3):
+        o.free()
+    return res, it, obj

@@ -382,6 +382,14 @@ std::string gen_eval(const int32_t* prog, int n_tokens, int n_inputs, int n_cons
         stack.push_back(nt++);
         break;
       }
+      case SYSML_FUSED_PICK:
+        if ((size_t)arg >= stack.size()) { err = "pick reaches below the stack"; return ""; }
+        stack.push_back(stack[stack.size() - 1 - (size_t)arg]);
+        break;
+      case SYSML_FUSED_NIP:
+        if (stack.size() < 2) { err = "stack underflow at nip"; return ""; }
+        stack.erase(stack.end() - 2);
+        break;
       default:
         err = "unknown token kind";
         return "";

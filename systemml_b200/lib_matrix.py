@@ -202,27 +202,34 @@ FUSED_AGG = {None: 0, "none": 0, "sum": 1, "rowSums": 2, "colSums": 3}
 
 
 class Expr:
-    """Tiny expression builder for fusedCellwise: Expr.input(0) * Expr.const(0) ... -> postfix tokens of
-    include/sysml_b200.h (SYSML_FUSED_TOKEN)."""
+    """Expression builder for fusedCellwise:  (Expr.const(0) - Expr.input(0) * Expr.input(1)).binary(Expr.const(1), ">")
+    -> postfix tokens of include/sysml_b200.h (SYSML_FUSED_TOKEN).  Expr.let(value, lambda v: body(v)) evaluates
+    `value` once and lets `body` use it several times (PICK / NIP tokens)."""
 
-    def __init__(self, tokens):
-        self.tokens = list(tokens)
+    def __init__(self, node):
+        # a raw token list is accepted as-is (tests of malformed programs)
+        self.node = ("raw", list(node)) if isinstance(node, (list, tuple)) and (not node or isinstance(node[0], int)) else node
 
     @staticmethod
     def input(i):
-        return Expr([(0 << 24) | i])
+        return Expr(("in", i))
 
     @staticmethod
     def const(i):
-        return Expr([(1 << 24) | i])
+        return Expr(("const", i))
+
+    @staticmethod
+    def let(value, body):
+        ref = Expr(("ref", object()))
+        return Expr(("let", ref.node[1], value, body(ref)))
 
     def binary(self, other, op):
         opc = BINARY_OPS[op] if isinstance(op, str) else int(op)
-        return Expr(self.tokens + other.tokens + [(2 << 24) | opc])
+        return Expr(("bin", opc, self, other))
 
     def unary(self, op):
         opc = UNARY_OPS[op] if isinstance(op, str) else int(op)
-        return Expr(self.tokens + [(3 << 24) | opc])
+        return Expr(("un", opc, self))
 
     def __add__(self, o):
         return self.binary(o, "+")
@@ -235,6 +242,35 @@ class Expr:
 
     def __truediv__(self, o):
         return self.binary(o, "/")
+
+    def _lin(self, depth, env, out):
+        n = self.node
+        k = n[0]
+        if k == "raw":
+            out.extend(n[1])
+        elif k == "in":
+            out.append((0 << 24) | n[1])
+        elif k == "const":
+            out.append((1 << 24) | n[1])
+        elif k == "bin":
+            n[2]._lin(depth, env, out)
+            n[3]._lin(depth + 1, env, out)
+            out.append((2 << 24) | n[1])
+        elif k == "un":
+            n[2]._lin(depth, env, out)
+            out.append((3 << 24) | n[1])
+        elif k == "ref":
+            out.append((4 << 24) | (depth - 1 - env[n[1]]))
+        elif k == "let":
+            n[2]._lin(depth, env, out)                      # the shared value sits at stack index `depth`
+            n[3]._lin(depth + 1, {**env, n[1]: depth}, out)
+            out.append(5 << 24)                             # drop it from under the result
+
+    @property
+    def tokens(self):
+        out = []
+        self._lin(0, {}, out)
+        return out
 
 
 def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None):

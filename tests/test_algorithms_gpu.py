@@ -94,3 +94,63 @@ def test_glm_poisson_log_end_to_end(gctx):
     assert np.max(np.abs(got - btrue)) < 0.05
     dX.free()
     dy.free()
+
+
+def cpu_l2svm(Xd_, Y, reg, tol, maxiter):
+    """scripts/algorithms/l2-svm.dml:103-154 in numpy (intercept 0), dense X."""
+    n, m = Xd_.shape
+    w, Xw = np.zeros(m), np.zeros(n)
+    g_old = Xd_.T @ Y
+    s = g_old.copy()
+    it, cont, obj = 0, True, 0.0
+    while cont and it < maxiter:
+        step = 0.0
+        Xd = Xd_ @ s
+        wd, dd = reg * np.sum(w * s), reg * np.sum(s * s)
+        while True:
+            out = 1 - Y * (Xw + step * Xd)
+            sv = (out > 0).astype(np.float64)
+            out = out * sv
+            g = wd + step * dd - np.sum(out * Y * Xd)
+            h = dd + np.sum(Xd * sv * Xd)
+            step = step - g / h
+            if not (g * g / h >= 1e-10):
+                break
+        w = w + step * s
+        Xw = Xw + step * Xd
+        out = 1 - Y * Xw
+        out = (out > 0) * out
+        obj = 0.5 * np.sum(out * out) + reg / 2 * np.sum(w * w)
+        g_new = Xd_.T @ (out * Y) - reg * w
+        tmp = np.sum(s * g_old)
+        be = np.sum(g_new * g_new) / np.sum(g_old * g_old)
+        s = be * s + g_new
+        g_old = g_new
+        cont = (step * tmp >= tol * obj) and np.sum(s * s) != 0
+        it += 1
+    return w, it, obj
+
+
+@pytest.mark.parametrize("sparse", [True, False])
+def test_l2svm_end_to_end(gctx, sparse):
+    """BASELINE config C3's workload (L2SVM on a CSR matrix) at test size: SpMV / t(X)%*%y on the CSR kernels,
+    every n-vector chain of the line search as ONE fused launch; same iterations and weights as the script run in
+    numpy, and as the operator-by-operator plan."""
+    from systemml_b200.algorithms import l2svm
+    n, m = 30_000, 300
+    X = O.java_test_matrix(n, m, -1, 1, 0.05 if sparse else 1.0, 7)
+    wtrue = O.rand_uniform(m, seed=3)
+    Y = np.where(X @ wtrue + 0.05 * O.rand_uniform(n, seed=4) > 0, 1.0, -1.0)
+    exp_w, exp_it, exp_obj = cpu_l2svm(X, Y, 1.0, 0.001, 20)
+    if sparse:
+        rp, ci, va = O.dense_to_csr(X)
+        dX = gctx.csr(rp, ci, va, X.shape)
+    else:
+        dX = gctx.dense(X)
+    dY = gctx.dense(Y.reshape(n, 1))
+    for fused in (True, False):
+        w, it, obj = l2svm(gctx, dX, dY, reg=1.0, tol=0.001, maxiter=20, fused=fused)
+        assert it == exp_it, (fused, it, exp_it)
+        assert abs(obj - exp_obj) <= 1e-9 * abs(exp_obj)
+        assert_equal_matrices(exp_w, w, rel=1e-7, what="l2svm weights (fused=%s)" % fused)
+    assert np.mean(np.sign(X @ w) == Y) > 0.9  # and it separates the classes
