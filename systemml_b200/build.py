@@ -64,7 +64,7 @@ def build(force=False, verbose=False):
         spills = []
         for l in out.splitlines():
             mm = _re.search(r"(\d+) bytes spill stores", l)
-            if mm and int(mm.group(1)) > 64:  # a handful of bytes is harmless; kilobytes mean ptxas gave up
+            if mm and int(mm.group(1)) > 256:  # tens of bytes outside the inner loops are harmless; kilobytes mean ptxas gave up
                 spills.append(l)
         if rc == 0 and spills:
             out += "\nERROR: register spills in %s:\n%s\n" % (src, "\n".join(spills[:5]))

@@ -38,6 +38,9 @@ struct GemmArgs {
   int tiles_m, tiles_n;
   int sym;      // only tiles tj >= ti
   int vecA, vecB;
+  int diag_last;  // ws kernel, sym: 1-D grid, the (cheaper) diagonal tiles come last (see dgemm_ws_kernel)
+  int nsplits;
+  int edge_diag;  // 1 when the last diagonal tile hangs over the edge of the matrix
 };
 
 __device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes) {
@@ -54,7 +57,6 @@ __device__ __forceinline__ void cp_async_wait() {
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
-
 // Copies a logical [R][Ccols] tile whose rows are contiguous in global memory (row r at src + r*ld)
 // into shared memory with leading dimension LD; rows >= rvalid and columns >= cvalid are zero-filled.
 template <int R, int CCOLS, int LD, int NT>
@@ -285,8 +287,78 @@ __device__ __forceinline__ void cp_async_mbar_arrive(uint64_t* bar) {
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// ---- strip mapping of one diagonal 128x128 tile (see dgemm_ws_kernel): warp w owns fragment rows w and 15-w ----
+template <bool TA, bool TB, class Cfg, int BKT, int NST>
+struct StripCtx {
+  const double* As;
+  const double* Bs;
+  uint64_t* full;
+  uint64_t* empty;
+  double* outp;
+  i64 M, N, i0, j0;
+  int nkb, lane, warp;
+};
+
+// LO0 / LO1: first fragment column of the two fragment rows.  Consumes nkb stages of the ring, then writes the
+// fragments (the tile lies inside the matrix).
+template <int LO0, int LO1, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __forceinline__ void strip_tile(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  constexpr int LDA = Cfg::LDA, LDB = Cfg::LDB;
+  constexpr int A_K4 = TA ? 4 * LDA : 4;
+  constexpr int B_NT = TB ? 8 * LDB : 8;
+  constexpr int B_K4 = TB ? 4 : 4 * LDB;
+  const int gid = c.lane >> 2, tig = c.lane & 3;
+  const int a_off0 = TA ? (tig * LDA + LO0 * 8 + gid) : ((LO0 * 8 + gid) * LDA + tig);
+  const int a_off1 = TA ? (tig * LDA + LO1 * 8 + gid) : ((LO1 * 8 + gid) * LDA + tig);
+  const int b_off = TB ? (gid * LDB + tig) : (tig * LDB + gid);
+  double acc0[16][2], acc1[16][2];  // entries below LO0 / LO1 are never touched and cost no registers
+#pragma unroll
+  for (int b = 0; b < 16; b++) acc0[b][0] = acc0[b][1] = acc1[b][0] = acc1[b][1] = 0.0;
+  for (int kb = 0; kb < c.nkb; kb++, it++) {
+    const int s = it % NST;
+    const uint32_t ph = (it / NST) & 1u;
+    mbar_wait(&c.full[s], ph);
+    const double* as = c.As + s * Cfg::A_ELEMS;
+    const double* bs = c.Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+    for (int k4 = 0; k4 < BKT / 4; k4++) {
+      const double a0 = as[k4 * A_K4 + a_off0], a1 = as[k4 * A_K4 + a_off1];
+      double bf[16];
+#pragma unroll
+      for (int b = LO0; b < 16; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+      for (int b = LO0; b < 16; b++) {
+        dmma884(acc0[b][0], acc0[b][1], a0, bf[b]);
+        if (b >= LO1) dmma884(acc1[b][0], acc1[b][1], a1, bf[b]);
+      }
+    }
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(&c.empty[s]);
+  }
+  const i64 r0 = c.i0 + LO0 * 8 + gid, r1 = c.i0 + LO1 * 8 + gid;
+#pragma unroll
+  for (int b = LO0; b < 16; b++) {
+    const i64 j = c.j0 + b * 8 + 2 * tig;
+    *reinterpret_cast<double2*>(c.outp + r0 * c.N + j) = make_double2(acc0[b][0], acc0[b][1]);
+    if (b >= LO1) *reinterpret_cast<double2*>(c.outp + r1 * c.N + j) = make_double2(acc1[b][0], acc1[b][1]);
+  }
+}
+
 __device__ __forceinline__ void tile_coords(const GemmArgs& g, int t, int& ti, int& tj) {
-  if (g.sym) {  // upper-triangular tile list, row by row
+  if (g.sym && g.diag_last) {  // strictly upper tiles row by row, then the diagonal (its ragged last tile first)
+    const int T = g.tiles_n, noff = T * (T - 1) / 2;
+    if (t >= noff) {
+      const int d = t - noff;
+      ti = tj = g.edge_diag ? (d == 0 ? T - 1 : d - 1) : d;
+      return;
+    }
+    ti = 0;
+    while (t >= T - 1 - ti) {
+      t -= T - 1 - ti;
+      ti++;
+    }
+    tj = ti + 1 + t;
+  } else if (g.sym) {  // upper-triangular tile list, row by row
     ti = 0;
     while (t >= g.tiles_n - ti) {
       t -= g.tiles_n - ti;
@@ -299,8 +371,12 @@ __device__ __forceinline__ void tile_coords(const GemmArgs& g, int t, int& ti, i
   }
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST, int NPW>
-__global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kernel(const GemmArgs g) {
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT, int NST, int NPW, bool STRIP>
+__global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
+                                   // an explicit minimum: without one ptxas has at times settled on 32 registers and
+                                   // kilobytes of spills for this kernel.  Two CTAs per SM where the stages leave room.
+                                   (2 * (GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>::SMEM + 1152) <= 228 * 1024) ? 2 : 1)
+    dgemm_ws_kernel(const GemmArgs g) {
   using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST>;
   constexpr int NCW = WARPS_M * WARPS_N;  // consumer warps
   constexpr int MT = Cfg::MT, NTL = Cfg::NTL, LDA = Cfg::LDA, LDB = Cfg::LDB;
@@ -316,7 +392,25 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   // output tiles are walked with a grid stride: with gridDim.x == ntiles this is one tile per CTA; the direct
   // (no split-K) launches use one CTA per SM slot so that the copy pipeline never drains between tiles
   const int ntiles = g.sym ? g.tiles_n * (g.tiles_n + 1) / 2 : g.tiles_m * g.tiles_n;
-  const i64 kbeg = (i64)blockIdx.y * g.k_per_split;
+  // diag_last launches are one-dimensional: first every (split, off-diagonal tile) with the tile index fastest --
+  // concurrent CTAs then read the same k range and share its panels through L2 -- and only then the cheaper
+  // (split, diagonal tile) CTAs, so that the short jobs fill the tail of the schedule
+  int split = blockIdx.y, tile0 = blockIdx.x, tstep = gridDim.x;
+  if (g.diag_last) {
+    // expensive tiles: the strictly upper ones and a ragged last diagonal tile (it takes the generic path)
+    const int T = g.tiles_n, n1 = T * (T - 1) / 2 + g.edge_diag, n2 = T - g.edge_diag, nsplit = g.nsplits;
+    int lin = blockIdx.x;
+    if (lin < n1 * nsplit) {
+      split = lin / n1;
+      tile0 = lin - split * n1;
+    } else {
+      lin -= n1 * nsplit;
+      split = lin / n2;
+      tile0 = n1 + (lin - split * n2);
+    }
+    tstep = ntiles;  // one tile per CTA
+  }
+  const i64 kbeg = (i64)split * g.k_per_split;
   const i64 kend = (kbeg + g.k_per_split < g.K) ? kbeg + g.k_per_split : g.K;
   const int nkb = (int)((kend - kbeg + BKT - 1) / BKT);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -337,7 +431,7 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
     // ===================== producer warps (warp NCW does the bulk copies; all NPW share the cp.async rows) =====================
     const int pw = warp - NCW;
     uint32_t it = 0;  // k blocks issued so far, over all tiles of this CTA
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int tile = tile0; tile < ntiles; tile += tstep) {
     int ti, tj;
     tile_coords(g, tile, ti, tj);
     const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
@@ -392,10 +486,33 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
   constexpr int B_K4 = TB ? 4 : 4 * LDB;
 
   uint32_t it = 0;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  for (int tile = tile0; tile < ntiles; tile += tstep) {
   int ti, tj;
   tile_coords(g, tile, ti, tj);
   const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
+  if constexpr (STRIP) {
+    // Diagonal tiles of a symmetric product: only fragments on or right of the diagonal are needed.  The tile is
+    // 16 x 16 fragments of 8x8; warp w takes fragment rows w and 15-w, which need 16-w and w+1 fragment columns:
+    // 17 DMMAs per k-step for every warp instead of 32.  The column ranges are compile-time (one instantiation
+    // per warp index): a predicated-off DMMA still occupies the tensor pipe (measured), and ptxas if-converts
+    // short branches, so the skipped fragments must not exist in the code at all.
+    static_assert(!STRIP || (BM == 128 && BN == 128 && WARPS_M * WARPS_N == 8), "strip mapping is written for 128x128 tiles and 8 warps");
+    if (g.sym && ti == tj && i0 + BM <= g.M) {
+      double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
+      const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
+      switch (warp) {
+        case 0: strip_tile<0, 15>(sc, it); break;
+        case 1: strip_tile<1, 14>(sc, it); break;
+        case 2: strip_tile<2, 13>(sc, it); break;
+        case 3: strip_tile<3, 12>(sc, it); break;
+        case 4: strip_tile<4, 11>(sc, it); break;
+        case 5: strip_tile<5, 10>(sc, it); break;
+        case 6: strip_tile<6, 9>(sc, it); break;
+        default: strip_tile<7, 8>(sc, it); break;
+      }
+      continue;
+    }
+  }
   double acc[MT][NTL][2];
 #pragma unroll
   for (int a = 0; a < MT; a++)
@@ -423,7 +540,7 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32) dgemm_ws_kerne
     if (lane == 0) mbar_arrive(&empty[s]);
   }
 
-  double* outp = g.out + (size_t)blockIdx.y * (size_t)g.M * (size_t)g.N;
+  double* outp = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
 #pragma unroll
   for (int a = 0; a < MT; a++) {
     const i64 i = i0 + wm0 + a * 8 + gid;
@@ -495,9 +612,13 @@ inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, 
   p.tiles_n = (int)((N + BN - 1) / BN);
   p.ntiles = sym ? p.tiles_n * (p.tiles_n + 1) / 2 : p.tiles_m * p.tiles_n;
   const i64 kblocks = (K + bk - 1) / bk;
-  // aim at ~6 waves of CTAs (1 CTA per SM) but keep >= 32 k-blocks (512 contraction steps) per CTA
-  i64 want = ((i64)ctx->sm_count * 6 + p.ntiles - 1) / p.ntiles;
+  // Aim at ~24 waves of CTAs (1 CTA per SM): the last, partly filled wave costs up to one CTA duration, 1/6 of
+  // the run at 6 waves (measured on 1M x 5000: 820 whole-K CTAs = 5.5 waves ran as 6).  Keep >= 32 k-blocks (512
+  // contraction steps) per CTA and at most 1 GiB of partial outputs (written and read once: < 0.5 ms).
+  i64 want = ((i64)ctx->sm_count * 24 + p.ntiles - 1) / p.ntiles;
   i64 maxs = kblocks * bk / 512;
+  const i64 by_bytes = ((i64)1 << 30) / (M * N * 8 > 0 ? M * N * 8 : 1);
+  if (maxs > by_bytes) maxs = by_bytes;
   if (maxs < 1) maxs = 1;
   if (want > maxs) want = maxs;
   if (want < 1) want = 1;
@@ -515,7 +636,7 @@ inline Plan make_plan(sysml_b200_ctx* ctx, i64 M, i64 N, i64 K, int BM, int BN, 
   return p;
 }
 
-template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES, int NPW = 1>
+template <bool TA, bool TB, int BM, int BN, int WARPS_M, int WARPS_N, int BKT = BK, int NST = STAGES, int NPW = 1, bool STRIP = false>
 int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
              int64_t* h_nnz) {
   using Cfg = GemmCfg<TA, TB, BM, BN, WARPS_M, WARPS_N>;           // legacy cp.async kernel (BK = 16, 4 stages)
@@ -545,7 +666,7 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
   const bool ws_ok = g.vecA && g.vecB && (M % 2 == 0) && (N % 2 == 0) &&
                      ((reinterpret_cast<uintptr_t>(g.out) & 15) == 0) && getenv("SYSML_B200_GEMM_NO_WS") == nullptr;
   if (ws_ok) {
-    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST, NPW>;
+    auto kws = dgemm_ws_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N, BKT, NST, NPW, STRIP>;
     const size_t smem_ws = WsCfg::SMEM + 128;
     SYSML_CUDA(ctx, cudaFuncSetAttribute(kws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_ws));
     int gx = p.ntiles;
@@ -555,7 +676,14 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
       if (per_sm < 1) per_sm = 1;
       if (gx > per_sm * ctx->sm_count) gx = per_sm * ctx->sm_count;
     }
-    kws<<<dim3((unsigned)gx, (unsigned)p.splits), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
+    if (sym && STRIP && (i64)p.ntiles * p.splits < (1ll << 31)) {
+      g.diag_last = 1;
+      g.nsplits = p.splits;
+      g.edge_diag = (M % BM != 0) ? 1 : 0;
+      kws<<<dim3((unsigned)(p.ntiles * p.splits)), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
+    } else {
+      kws<<<dim3((unsigned)gx, (unsigned)p.splits), WsCfg::NT + 32 * NPW, smem_ws, ctx->stream>>>(g);
+    }
     SYSML_LAUNCH_CHECK(ctx, "dgemm_ws_kernel");
   } else {
     dgemm_kernel<TA, TB, BM, BN, WARPS_M, WARPS_N><<<dim3((unsigned)p.ntiles, (unsigned)p.splits), Cfg::NT, Cfg::SMEM, ctx->stream>>>(g);
@@ -588,7 +716,8 @@ template <bool TA, bool TB>
 int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
                   int64_t* h_nnz) {
   if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (sym || N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, sym, h_nnz);
+  if (sym) return run_gemm<TA, TB, 128, 128, 2, 4, BK, STAGES, 1, true>(ctx, A, lda, B, ldb, C, M, N, K, true, h_nnz);
+  if (N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, h_nnz);
   if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   // K-contiguous A (no bulk copies possible): one producer warp cannot keep enough cp.async in flight
   // (measured ~28 KB per SM), so four producer warps share the rows of every stage
