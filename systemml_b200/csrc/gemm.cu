@@ -722,9 +722,12 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
   // K-contiguous A (no bulk copies possible): one producer warp cannot keep enough cp.async in flight
   // (measured ~28 KB per SM), so four producer warps share the rows of every stage
   constexpr int NP = TA ? 1 : 4;
-  if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  // t(X) %*% P with a narrow P: three stages instead of four let two CTAs share an SM (16 consumer warps keep the
+  // tensor pipe busier while both it and HBM are near their limits)
+  constexpr int SKST = TA ? 3 : STAGES;
+  if (N <= 8) return run_gemm<TA, TB, 256, 8, 8, 1, BK, SKST, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 16) return run_gemm<TA, TB, 256, 16, 8, 1, BK, SKST, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (N <= 24) return run_gemm<TA, TB, 256, 24, 8, 1, BK, SKST, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 32) return run_gemm<TA, TB, 256, 32, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 40) return run_gemm<TA, TB, 256, 40, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (N <= 48) return run_gemm<TA, TB, 256, 48, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
