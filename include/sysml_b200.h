@@ -330,8 +330,15 @@ int sysml_b200_comm_create(sysml_b200_ctx* ctx, int rank, int world, int64_t max
                            sysml_b200_comm** out, void* handle_out64);
 int sysml_b200_comm_connect(sysml_b200_comm* comm, const void* all_handles);
 int sysml_b200_comm_destroy(sysml_b200_comm* comm);
-/* buf[0..len) <- sum over ranks, in place, identical bits on every rank (len <= max_values). */
+/* buf[0..len) <- sum over ranks, in place, identical bits on every rank (buffers longer than max_values go
+ * through the mailbox in pieces). */
 int sysml_b200_allreduce_sum(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len);
+/* Same exchange with sum, max or min as the combiner (colMaxs / colMins / max / min of row-sharded
+ * operands; Math.max/min semantics, so the result is exact and identical on every rank). */
+#define SYSML_REDUCE_SUM 0
+#define SYSML_REDUCE_MAX 1
+#define SYSML_REDUCE_MIN 2
+int sysml_b200_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len, int op);
 /* mmchain on the local row shard fused with the sum over ranks (m <= 4096). */
 int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X,
                                        const double* v, const double* w, double* out, int64_t n,

@@ -16,6 +16,7 @@
 // The mailbox of a rank is one cudaMalloc block exported with cudaIpcGetMemHandle and opened by the
 // peers (one process per GPU, as torchrun launches them).
 #include "common.cuh"
+#include "cellwise_ops.cuh"
 
 struct sysml_b200_comm {
   sysml_b200_ctx* ctx;
@@ -57,6 +58,7 @@ __device__ __forceinline__ double ld_relaxed_sys(const double* p) {
 // partial: [P][m] local per-CTA partial rows (or, with P == 1, the local vector itself).
 // Every rank launches this kernel with the same m and grid; CTA c of every rank exchanges columns
 // [32c, 32c+32).
+template <int ROP>  // 0 sum, 1 max, 2 min (Math.max/min semantics) over the ranks; the local P partial rows are always summed
 __global__ void __launch_bounds__(256) colpartial_allreduce_kernel(const double* __restrict__ partial, int P, int m,
                                                                    double* __restrict__ out, const PeerArgs pa) {
   __shared__ double sh_hi[8][33], sh_lo[8][33];
@@ -93,7 +95,7 @@ __global__ void __launch_bounds__(256) colpartial_allreduce_kernel(const double*
       t.lo = sh_lo[q][c];
       a0.add(t);
     }
-    local = a0.value();
+    local = (P == 1) ? __ldcg(partial + j) : a0.value();  // a single row passes through untouched (keeps -0.0 for max/min)
   }
   const size_t slot = (size_t)(pa.parity * pa.world + pa.rank);
   // 2. push this rank's 32 values into every mailbox (own one included)
@@ -113,8 +115,11 @@ __global__ void __launch_bounds__(256) colpartial_allreduce_kernel(const double*
   __syncwarp();
   if (j < m) {
     const double* mine = pa.data[pa.rank];
-    double s = 0.0;
-    for (int src = 0; src < pa.world; src++) s = __dadd_rn(s, ld_relaxed_sys(mine + (size_t)(pa.parity * pa.world + src) * pa.m_pad + j));
+    double s = ld_relaxed_sys(mine + (size_t)(pa.parity * pa.world) * pa.m_pad + j);
+    for (int src = 1; src < pa.world; src++) {
+      const double x = ld_relaxed_sys(mine + (size_t)(pa.parity * pa.world + src) * pa.m_pad + j);
+      s = (ROP == 0) ? __dadd_rn(s, x) : (ROP == 1) ? sysml_ops::jmax(s, x) : sysml_ops::jmin(s, x);
+    }
     out[j] = s;
   }
 }
@@ -122,7 +127,7 @@ __global__ void __launch_bounds__(256) colpartial_allreduce_kernel(const double*
 }  // namespace
 
 // used by mmchain.cu (fused finish) and by sysml_b200_allreduce_sum below
-int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out) {
+int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out, int rop) {
   if (!comm) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce: null communicator");
   if (comm->ctx != ctx) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce: communicator belongs to another context");
   if (m > comm->m_pad) return sysml_set_error(ctx, SYSML_E_LIMIT, "allreduce: %d values exceed the communicator's capacity of %d", m, comm->m_pad);
@@ -142,7 +147,9 @@ int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, co
     pa.data[p] = (double*)comm->peer_base[p];
     pa.flags[p] = (unsigned int*)((char*)comm->peer_base[p] + data_bytes);
   }
-  colpartial_allreduce_kernel<<<ncta, 256, 0, ctx->stream>>>(partial, P, m, out, pa);
+  if (rop == SYSML_REDUCE_MAX) colpartial_allreduce_kernel<1><<<ncta, 256, 0, ctx->stream>>>(partial, P, m, out, pa);
+  else if (rop == SYSML_REDUCE_MIN) colpartial_allreduce_kernel<2><<<ncta, 256, 0, ctx->stream>>>(partial, P, m, out, pa);
+  else colpartial_allreduce_kernel<0><<<ncta, 256, 0, ctx->stream>>>(partial, P, m, out, pa);
   SYSML_LAUNCH_CHECK(ctx, "colpartial_allreduce_kernel");
   return SYSML_OK;
 }
@@ -213,12 +220,22 @@ int sysml_b200_comm_destroy(sysml_b200_comm* comm) {
   return SYSML_OK;
 }
 
-int sysml_b200_allreduce_sum(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len) {
+int sysml_b200_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len, int op) {
   SYSML_ENTER(ctx);
-  if (len < 0 || (len > 0 && !buf)) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce_sum: bad arguments");
-  if (len == 0) return SYSML_OK;
-  if (len > 0x7fffffffLL) return sysml_set_error(ctx, SYSML_E_LIMIT, "allreduce_sum: too many values");
-  return sysml_launch_allreduce_finish(ctx, comm, buf, 1, (int)len, buf);
+  if (len < 0 || (len > 0 && !buf)) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce: bad arguments");
+  if (op != SYSML_REDUCE_SUM && op != SYSML_REDUCE_MAX && op != SYSML_REDUCE_MIN) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce: unknown op %d", op);
+  if (!comm) return sysml_set_error(ctx, SYSML_E_INVALID, "allreduce: null communicator");
+  // longer buffers go through the mailbox in capacity-sized pieces (tsmm results: m*m values)
+  for (int64_t off = 0; off < len; off += comm->m_pad) {
+    const int64_t n = (len - off < comm->m_pad) ? len - off : comm->m_pad;
+    int rc = sysml_launch_allreduce_finish(ctx, comm, buf + off, 1, (int)n, buf + off, op);
+    if (rc) return rc;
+  }
+  return SYSML_OK;
+}
+
+int sysml_b200_allreduce_sum(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len) {
+  return sysml_b200_allreduce(ctx, comm, buf, len, SYSML_REDUCE_SUM);
 }
 
 }  // extern "C"

@@ -22,7 +22,7 @@
 #include "common.cuh"
 
 struct sysml_b200_comm;
-int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out);
+int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out, int rop);
 
 namespace {
 
@@ -279,7 +279,7 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
   SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel");
   if (MODE != MODE_MV) {
-    if (a.comm) return sysml_launch_allreduce_finish(ctx, a.comm, a.partial, (int)(grid * G), a.m, a.out);
+    if (a.comm) return sysml_launch_allreduce_finish(ctx, a.comm, a.partial, (int)(grid * G), a.m, a.out, SYSML_REDUCE_SUM);
     colpartial_reduce_kernel<<<(unsigned)((a.m + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)(grid * G), a.m, a.out);
     SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel");
   }
@@ -483,7 +483,7 @@ extern "C" int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b20
   if (m > 4096) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_allreduce: more than 4096 columns; run mmchain_dense then allreduce_sum");
   if (n == 0) {  // an empty shard still has to take part in the exchange
     SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
-    return sysml_launch_allreduce_finish(ctx, comm, out, 1, (int)m, out);
+    return sysml_launch_allreduce_finish(ctx, comm, out, 1, (int)m, out, SYSML_REDUCE_SUM);
   }
   StreamArgs a{};
   a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type; a.comm = comm;

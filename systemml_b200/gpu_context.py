@@ -240,6 +240,10 @@ class Communicator:
     def allreduce_sum(self, ptr, length):
         self.gctx.call("sysml_b200_allreduce_sum", self.handle, C.c_void_p(ptr), int(length))
 
+    def allreduce(self, ptr, length, op="sum"):
+        """op: 'sum' | 'max' | 'min' -- in place, identical bits on every rank."""
+        self.gctx.call("sysml_b200_allreduce", self.handle, C.c_void_p(ptr), int(length), {"sum": 0, "max": 1, "min": 2}[op])
+
     def destroy(self):
         if self.handle:
             self.gctx._lib.sysml_b200_comm_destroy(self.handle)

@@ -67,6 +67,7 @@ SIGNATURES = {
     "sysml_b200_comm_connect": (ci, [vp, vp]),
     "sysml_b200_comm_destroy": (ci, [vp]),
     "sysml_b200_allreduce_sum": (ci, [vp, vp, vp, i64]),
+    "sysml_b200_allreduce": (ci, [vp, vp, vp, i64, ci]),
     "sysml_b200_mmchain_dense_allreduce": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci]),
     # ---- include/sysml_b200_host.h ----
     "sysml_b200_ec_create": (ci, [ci, dbl, ci, i64, pvp]),

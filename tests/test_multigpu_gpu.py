@@ -1,5 +1,6 @@
 """Two real GPUs: row-sharded mmchain with the sum exchange fused into the finishing kernel (NVLink peer
-memory, csrc/comm.cu) against the single-device result and the CPU oracle.  Skipped on a one-GPU box."""
+memory, csrc/comm.cu) against the single-device result and the CPU oracle, plus the other sharded plans of
+SURVEY 8e (tsmm, t(P)%*%X, colSums, colMaxs/colMins, sum) as local op + one exchange.  Skipped on a one-GPU box."""
 import os
 import socket
 
@@ -50,6 +51,30 @@ def _worker(rank, world, port, n, m, out_dir):
     cs = L.unaryAggregate(g, "uack+", X, "uack+")
     comm.allreduce_sum(cs.ptr, m)
     res["cs"] = cs.to_host().reshape(-1)
+    # the other sharded plans of SURVEY 8e -- each: local op on the row shard, then ONE exchange
+    comm2 = Communicator(g, rank, world, 1 << 16, torch_exchange())
+    Xs = g.rand(r1 - r0, 160, seed=21, offset=r0 * 160)                 # narrower operand for tsmm / t(P)%*%X
+    t, _ = L.matmultTSMM(g, "tsmm", Xs, True, with_nnz=True)            # tsmm LEFT: sum of the shards' m x m
+    comm2.allreduce(t.ptr, 160 * 160, "sum")
+    res["tsmm"] = t.to_host()
+    Pm = g.rand(r1 - r0, 24, seed=22, offset=r0 * 24)                   # t(P) %*% X (Kmeans centroid update)
+    tpx = L.matmult(g, "ba+*", Pm, Xs, isLeftTransposed=True)
+    comm2.allreduce(tpx.ptr, 24 * 160, "sum")
+    res["tpx"] = tpx.to_host()
+    for opc, rop in (("uacmax", "max"), ("uacmin", "min")):           # colMaxs / colMins: exact
+        o = L.unaryAggregate(g, opc, Xs, opc)
+        comm2.allreduce(o.ptr, 160, rop)
+        res[opc] = o.to_host().reshape(-1)
+    sm = g.empty(1, 1)                                                  # sum(X): all-reduce of one value
+    g.call("sysml_b200_agg_unary_dense", C.c_void_p(Xs.ptr), r1 - r0, 160, 0, 0, C.c_void_p(sm.ptr))
+    comm2.allreduce(sm.ptr, 1, "sum")
+    res["sum"] = sm.to_host().reshape(-1)
+    big = g.rand(200_000, 1, seed=30 + rank)                            # longer than the mailbox: goes in pieces
+    comm2.allreduce(big.ptr, 200_000, "sum")
+    res["big"] = big.to_host().reshape(-1)
+    g.sync()
+    dist.barrier()
+    comm2.destroy()
     np.savez(os.path.join(out_dir, "rank%d.npz" % rank), **res)
     g.sync()
     dist.barrier()
@@ -73,6 +98,17 @@ def test_fused_allreduce_mmchain_two_gpus(tmp_path):
         a, b = r[0]["q%d" % it], r[1]["q%d" % it]
         assert np.array_equal(a, b), "all ranks must hold bit-identical results"
         assert np.max(np.abs((a - exp) / exp)) < 1e-9
+    Xs = O.rand_uniform(n * 160, seed=21).reshape(n, 160)
+    Pm = O.rand_uniform(n * 24, seed=22).reshape(n, 24)
+    for key in ("tsmm", "tpx", "uacmax", "uacmin", "sum", "big"):
+        assert np.array_equal(r[0][key], r[1][key]), key
+    exp_t, _ = O.tsmm_dense(Xs, True, O.num_threads())
+    assert np.max(np.abs(r[0]["tsmm"] - exp_t)) < 1e-9 * np.max(np.abs(exp_t))
+    exp_tpx = (Pm.astype(np.longdouble).T @ Xs.astype(np.longdouble)).astype(np.float64)
+    assert np.max(np.abs(r[0]["tpx"] - exp_tpx)) < 1e-9 * np.max(np.abs(exp_tpx))
+    assert np.array_equal(r[0]["uacmax"], Xs.max(axis=0)) and np.array_equal(r[0]["uacmin"], Xs.min(axis=0))
+    assert abs(r[0]["sum"][0] - float(np.sum(Xs.astype(np.longdouble)))) < 1e-9 * n
+    assert np.array_equal(r[0]["big"], O.rand_uniform(200_000, seed=30) + O.rand_uniform(200_000, seed=31))
     exp_cs = O.agg_unary_dense(X, O.SUM, O.COL, 4)
     assert np.array_equal(r[0]["cs"], r[1]["cs"])
     assert np.max(np.abs(r[0]["cs"] - exp_cs)) < 1e-9 * np.max(np.abs(exp_cs)) + 1e-9
