@@ -59,6 +59,8 @@ inline unsigned rows_grid(sysml_b200_ctx* ctx, i64 rows, int L, int threads) {
 // MODE 0: out[r] = A[r,:] . v                      (SpMV)
 // MODE 1: c[col] += (w-adjusted A[r,:].v) * A[r,col] (sparse mmchain), ct as in SYSML_CHAIN_*
 // MODE 2: c[col] += y[r] * A[r,col]                 (t(A) %*% y)
+// MODE 3 (streamed kernel only): out[r] = sum / sum of squares / max / min of row r (ct = SYSML_AGG_*, implicit zeros
+//         join max/min when the row has fewer than out_len = cols entries); colind is never read
 template <int L, int MODE>
 __global__ void __launch_bounds__(256, 8) csr_row_kernel(const int* __restrict__ rp, const int* __restrict__ ci,
                                                       const double* __restrict__ va, const double* __restrict__ v,
@@ -165,7 +167,9 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
       nk0 = __ldg(a.rp + r0);
       nk1 = __ldg(a.rp + r1);
     }
-    for (uint32_t it = 0; tile < a.ntiles; tile += gridDim.x, it++) {
+    int s = 0;
+    uint32_t ph = 0;  // stage index and phase advance incrementally (no division by the runtime stage count)
+    for (; tile < a.ntiles; tile += gridDim.x, s = (s + 1 == nst) ? 0 : s + 1, ph ^= (s == 0) ? 1u : 0u) {
       const int k0 = nk0, k1 = nk1;
       const int nt = tile + gridDim.x;
       if (nt < a.ntiles) {  // boundaries of the next tile: in flight while this one waits for its stage
@@ -174,8 +178,6 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
         nk0 = __ldg(a.rp + q0);
         nk1 = __ldg(a.rp + q1);
       }
-      const int s = it % nst;
-      const uint32_t ph = (it / nst) & 1u;
       mbar_wait(&empty[s], ph ^ 1u);
       const i64 r0 = (i64)tile * TR;
       const int ka = k0 & ~3, kb = (k1 + 3) & ~3;
@@ -184,12 +186,12 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
       if (fast) {
         unsigned char* st = stages + (size_t)s * stage_bytes;
         const uint32_t nk = (uint32_t)(kb - ka);
-        mbar_expect_tx(&full[s], RPB + (have_w ? TR * 8 : 0) + nk * 12u);
+        mbar_expect_tx(&full[s], RPB + (have_w ? TR * 8 : 0) + nk * (MODE == 3 ? 8u : 12u));
         bulk_g2s(st, a.rp + r0, RPB, &full[s], pol);
         if (have_w) bulk_g2s(st + RPB, a.w + r0, TR * 8, &full[s], pol);
         if (nk) {
           bulk_g2s(st + RPB + TR * 8, a.va + ka, nk * 8u, &full[s], pol);
-          bulk_g2s(st + RPB + TR * 8 + (size_t)cap * 8, a.ci + ka, nk * 4u, &full[s], pol);
+          if (MODE != 3) bulk_g2s(st + RPB + TR * 8 + (size_t)cap * 8, a.ci + ka, nk * 4u, &full[s], pol);
         }
       } else {
         mbar_arrive(&full[s]);
@@ -218,10 +220,9 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
   if ((MODE != 2 && a.v_smem > 0) || (MODE != 0 && a.out_smem > 0)) named_bar_sync(1, NC);
   const int sub = lane & (L - 1);
   const int row = tid / L;  // this thread's row of every tile
-  uint32_t it = 0;
-  for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, it++) {
-    const int s = it % nst;
-    const uint32_t ph = (it / nst) & 1u;
+  int s = 0;
+  uint32_t ph = 0, it = 0;
+  for (int tile = blockIdx.x; tile < a.ntiles; tile += gridDim.x, it++, s = (s + 1 == nst) ? 0 : s + 1, ph ^= (s == 0) ? 1u : 0u) {
     mbar_wait(&full[s], ph);
     const int4 mt = meta[s];
     const i64 r0 = (i64)tile * TR;
@@ -232,6 +233,37 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
       const double* va_s = reinterpret_cast<const double*>(st + RPB + TR * 8);
       const int* ci_s = reinterpret_cast<const int*>(st + RPB + TR * 8 + (size_t)cap * 8);
       const int lo = rp_s[row] - mt.x, hi = rp_s[row + 1] - mt.x;
+      if (MODE == 3) {
+        if (a.ct <= SYSML_AGG_SUMSQ) {
+          CompSum cs;
+          for (int k = lo + sub; k < hi; k += L) {
+            const double x = va_s[k];
+            cs.add(a.ct == SYSML_AGG_SUMSQ ? __dmul_rn(x, x) : x);
+          }
+#pragma unroll
+          for (int o = L >> 1; o > 0; o >>= 1) {
+            CompSum t;
+            t.hi = __shfl_xor_sync(0xffffffffu, cs.hi, o);
+            t.lo = __shfl_xor_sync(0xffffffffu, cs.lo, o);
+            cs.add(t);
+          }
+          if (sub == 0) a.out[r0 + row] = (isinf(cs.hi) || cs.lo != cs.lo) ? cs.hi : cs.value();
+        } else {
+          const bool ismax = a.ct == SYSML_AGG_MAX;
+          double t = ismax ? -CUDART_INF : CUDART_INF;
+          for (int k = lo + sub; k < hi; k += L) t = ismax ? jmax(t, va_s[k]) : jmin(t, va_s[k]);
+#pragma unroll
+          for (int o = L >> 1; o > 0; o >>= 1) {
+            const double u = __shfl_xor_sync(0xffffffffu, t, o);
+            t = ismax ? jmax(t, u) : jmin(t, u);
+          }
+          if ((i64)(hi - lo) < a.out_len) t = ismax ? jmax(t, 0.0) : jmin(t, 0.0);
+          if (sub == 0) a.out[r0 + row] = t;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+        continue;
+      }
       double p = 0.0;
       if (MODE != 2) {
         if (a.v_smem > 0) {  // shared-memory gathers: short latency, a plain loop is cheapest
@@ -278,6 +310,35 @@ __global__ void __launch_bounds__(NC + 32, 1) csr_stream_kernel(const CsrStreamA
       const i64 rend = (r0 + TR < a.rows) ? r0 + TR : a.rows;
       for (i64 r = r0 + warp; r < rend; r += NC / 32) {
         const int lo = __ldg(a.rp + r), hi = __ldg(a.rp + r + 1);
+        if (MODE == 3) {
+          if (a.ct <= SYSML_AGG_SUMSQ) {
+            CompSum cs;
+            for (int k = lo + lane; k < hi; k += 32) {
+              const double x = ldg_stream(a.va + k);
+              cs.add(a.ct == SYSML_AGG_SUMSQ ? __dmul_rn(x, x) : x);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              CompSum t;
+              t.hi = __shfl_xor_sync(0xffffffffu, cs.hi, o);
+              t.lo = __shfl_xor_sync(0xffffffffu, cs.lo, o);
+              cs.add(t);
+            }
+            if (lane == 0) a.out[r] = (isinf(cs.hi) || cs.lo != cs.lo) ? cs.hi : cs.value();
+          } else {
+            const bool ismax = a.ct == SYSML_AGG_MAX;
+            double t = ismax ? -CUDART_INF : CUDART_INF;
+            for (int k = lo + lane; k < hi; k += 32) t = ismax ? jmax(t, ldg_stream(a.va + k)) : jmin(t, ldg_stream(a.va + k));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              const double u = __shfl_xor_sync(0xffffffffu, t, o);
+              t = ismax ? jmax(t, u) : jmin(t, u);
+            }
+            if ((i64)(hi - lo) < a.out_len) t = ismax ? jmax(t, 0.0) : jmin(t, 0.0);
+            if (lane == 0) a.out[r] = t;
+          }
+          continue;
+        }
         double p = 0.0;
         if (MODE != 2) {
           for (int k = lo + lane; k < hi; k += 32) p = fma(ldg_stream(a.va + k), vsrc[__ldg(a.ci + k)], p);
@@ -732,6 +793,8 @@ inline int sysml_reduce_partial_rows_fwd(sysml_b200_ctx* ctx, const double* part
   return ::sysml_reduce_partial_rows(ctx, partial, P, m, out);
 }
 
+constexpr int SYSML_NOT_STREAMED = 12345;  // internal: launch_csr_row<3> found the matrix not eligible for the streamed kernel
+
 template <int MODE>
 int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const double* va, const double* v, const double* w,
                    double* out, i64 rows, i64 nnz, int ct, i64 out_len, i64 vlen) {
@@ -760,7 +823,7 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
       // Streaming pays only with v (modes 0/1) and the scatter target (modes 1/2) resident in shared memory
       // (measured: without them the row-at-a-time kernel, which has the whole L1 for v, is faster): one CTA per
       // SM with 896 consumers, or 512 when only the smaller tiles leave room for three stages.
-      const size_t need = (MODE != 2 ? (size_t)vlen * 8 : 0) + (MODE != 0 ? (size_t)out_len * 8 : 0);
+      const size_t need = ((MODE == 0 || MODE == 1) ? (size_t)vlen * 8 : 0) + ((MODE == 1 || MODE == 2) ? (size_t)out_len * 8 : 0);
       const size_t fixed = 256 + need;
       int cap = 0, nst = 0;
       size_t stage = stage_of(896, &cap);
@@ -771,8 +834,8 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
       }
       if (fixed + 3 * stage <= all) {
         nst = (int)((all - fixed) / stage);
-        if (MODE != 2) sa.v_smem = (int)vlen;
-        if (MODE != 0) sa.out_smem = (int)out_len;
+        if (MODE == 0 || MODE == 1) sa.v_smem = (int)vlen;
+        if (MODE == 1 || MODE == 2) sa.out_smem = (int)out_len;
       }
       if (nst > 6) nst = 6;
       if (nst >= 2) {
@@ -788,6 +851,7 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
   }
   int replicas = 1;
   double* target = out;
+  if (MODE == 3 && !stream) return SYSML_NOT_STREAMED;
   if (stream && MODE != 0 && sa.out_smem > 0) {
     // one partial row per CTA (every cell written by the kernel) + 32 zeroed rows for the L2-reduction share
     sa.red_replicas = 32;
@@ -800,7 +864,7 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
     target = (double*)ws;
     sa.red_out = target + (size_t)g * out_len;
     SYSML_CUDA(ctx, cudaMemsetAsync(sa.red_out, 0, (size_t)sa.red_replicas * out_len * sizeof(double), ctx->stream));
-  } else if (MODE != 0 && out_len <= (1 << 20) && nnz > 64 * out_len) {
+  } else if ((MODE == 1 || MODE == 2) && out_len <= (1 << 20) && nnz > 64 * out_len) {
     replicas = 32;
     while (replicas > 1 && (i64)replicas * out_len * 8 > (64ll << 20)) replicas >>= 1;
     if ((unsigned)replicas > g) replicas = (int)g;
@@ -838,6 +902,7 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
     if (replicas > 1) return sysml_reduce_partial_rows_fwd(ctx, target, replicas, (int)out_len, out);
     return SYSML_OK;
   }
+  if constexpr (MODE != 3) {
   switch (L) {
     case 2: csr_row_kernel<2, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
     case 4: csr_row_kernel<4, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
@@ -845,9 +910,18 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
     case 16: csr_row_kernel<16, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
     default: csr_row_kernel<32, MODE><<<g, 256, 0, ctx->stream>>>(rp, ci, va, v, w, target, rows, ct, replicas, out_len); break;
   }
+  }
   SYSML_LAUNCH_CHECK(ctx, "csr_row_kernel");
   if (replicas > 1) return sysml_reduce_partial_rows_fwd(ctx, target, replicas, (int)out_len, out);
   return SYSML_OK;
+}
+
+// row sums / sums of squares / max / min of a CSR matrix on the streamed kernel; *done = false when it does not apply
+int launch_csr_row_agg_streamed(sysml_b200_ctx* ctx, const int* rp, const int* ci, const double* va, double* out, i64 rows, i64 cols,
+                                i64 nnz, int op, bool* done) {
+  const int rc = launch_csr_row<3>(ctx, rp, ci, va, nullptr, nullptr, out, rows, nnz, op, cols, 0);
+  *done = (rc == SYSML_OK);
+  return rc == SYSML_NOT_STREAMED ? SYSML_OK : rc;
 }
 
 int fetch_nnz(sysml_b200_ctx* ctx, const int32_t* rowptr, i64 rows, i64* nnz) {
@@ -1028,6 +1102,11 @@ extern "C" int sysml_b200_agg_unary_csr(sysml_b200_ctx* ctx, const int32_t* rowp
   if (!is_sum && !is_mm && !is_idx) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "agg_unary_csr: opcode %d on CSR input", op);
   if (is_idx && dir != SYSML_DIR_ROW) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowIndexMax/Min exist only per row");
   if (dir == SYSML_DIR_ROW) {
+    if (!is_idx && nnz > 0) {  // big matrices with short rows: streamed (falls through when not eligible)
+      bool done = false;
+      rc = launch_csr_row_agg_streamed(ctx, rowptr, colind, val, out, rows, cols, nnz, op, &done);
+      if (rc || done) return rc;
+    }
     const int L = pick_lanes(nnz, rows);
     const unsigned g = rows_grid(ctx, rows, L, 256);
     switch (L) {

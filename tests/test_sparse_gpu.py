@@ -167,6 +167,14 @@ def test_csr_streamed_rows(gctx, rows, cols, mean, full_rows, empty_every, monke
         e = O.mmchain_csr(rp, ci, va, shape, v, y if ct else None, ct, 4)
         g = L.mmchain(gctx, "mmchain", dX, gctx.dense(v), gctx.dense(y) if ct else None, ct).to_host().reshape(-1)
         assert np.max(np.abs(e - g)) <= 1e-9 * max(np.max(np.abs(e)), 1e-300), ct
+    # row aggregates on the streamed kernel (colind is not even read): sums to a few ulp, max / min exact
+    for opc, op, exact in (("uark+", O.SUM, False), ("uarsqk+", O.SUMSQ, False), ("uarmax", O.MAX, True), ("uarmin", O.MIN, True)):
+        e = O.agg_unary_csr(rp, ci, va, shape, op, O.ROW, 1)
+        gr = L.unaryAggregate(gctx, opc, dX, opc).to_host().reshape(-1)
+        if exact:
+            assert np.array_equal(e, gr), opc
+        else:
+            assert np.max(np.abs(e - gr)) <= 1e-12 * max(1.0, np.max(np.abs(e))), opc
     # t(X) %*% y: exact column sums in extended precision
     e2 = np.zeros(cols, dtype=np.longdouble)
     np.add.at(e2, ci, va.astype(np.longdouble) * np.repeat(y.reshape(-1), np.diff(rp)).astype(np.longdouble))
