@@ -230,6 +230,29 @@ int sysml_b200_matmult_csr_csr(sysml_b200_ctx* ctx, const int32_t* a_rowptr, con
                                const double* a_val, const int32_t* b_rowptr, const int32_t* b_colind,
                                const double* b_val, double* C, int64_t a_rows, int64_t a_cols,
                                int64_t b_rows, int64_t b_cols);
+/* Operations whose RESULT is CSR.  No explicit zeros are stored (as the CPU's sparse rows: SparseRow.append skips
+ * them), so *c_nnz equals MatrixBlock.recomputeNonZeros of the dense result.
+ *   csr_transpose           : CSRPointer.transpose (csr2csc, CSRPointer.java:463-481); nnz is unchanged, the caller
+ *                             allocates t_rowptr[cols+1], t_colind[nnz], t_val[nnz].
+ *   csr_add                 : C = alpha*A + beta*B, the sparse branch of LibMatrixCUDA.dgeam (cusparseDcsrgeam,
+ *                             LibMatrixCUDA.java:1593-1701; CSRPointer.allocateForDgeam :227-299).
+ *   matmult_csr_csr_sparse  : LibMatrixCuMatMult.sparseSparseMatMult (cusparseDcsrgemm, LibMatrixCuMatMult.java:150-195;
+ *                             CSRPointer.allocateForMatrixMultiply :301-399); per output cell the products are added
+ *                             in ascending k like LibMatrixMult.matrixMultSparseSparse (:1397-1500): bit-identical.
+ * For the last two the caller passes c_rowptr[rows+1]; the library sizes the result in a symbolic pass, allocates
+ * *c_colind / *c_val itself (release them with sysml_b200_free) and returns the count in *c_nnz.
+ * matmult_csr_csr_sparse refuses more than 2^28 intermediate products with SYSML_E_LIMIT. */
+int sysml_b200_csr_transpose(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                             int64_t rows, int64_t cols, int32_t* t_rowptr, int32_t* t_colind, double* t_val);
+int sysml_b200_csr_add(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind, const double* a_val,
+                       double alpha, const int32_t* b_rowptr, const int32_t* b_colind, const double* b_val,
+                       double beta, int64_t rows, int64_t cols, int32_t* c_rowptr, int32_t** c_colind,
+                       double** c_val, int64_t* c_nnz);
+int sysml_b200_matmult_csr_csr_sparse(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind,
+                                      const double* a_val, const int32_t* b_rowptr, const int32_t* b_colind,
+                                      const double* b_val, int64_t a_rows, int64_t a_cols, int64_t b_rows,
+                                      int64_t b_cols, int32_t* c_rowptr, int32_t** c_colind, double** c_val,
+                                      int64_t* c_nnz);
 /* X %*% t(X) for CSR X (LibMatrixMult.prepMatrixMultTransposeSelfInput :3679-3685 + the RIGHT kernel). */
 int sysml_b200_tsmm_csr_right(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
                               const double* val, double* out, int64_t rows, int64_t cols,

@@ -120,6 +120,14 @@ class CSRPointer:
         self.rowPtr = gctx.allocate((self.rows + 1) * 4)
         self.colInd = gctx.allocate(max(self.nnz, 1) * 4)
 
+    @staticmethod
+    def adopt(gctx, rows, rowPtr, colInd, val, nnz):
+        """Takes ownership of arrays the library allocated (results of csr_add / matmult_csr_csr_sparse)."""
+        c = CSRPointer.__new__(CSRPointer)
+        c.gctx, c.nnz, c.rows = gctx, int(nnz), int(rows)
+        c.rowPtr, c.colInd, c.val = rowPtr, colInd or 0, val or 0
+        return c
+
     def deallocate(self):
         for p in (self.val, self.rowPtr, self.colInd):
             self.gctx.cudaFreeHelper(p)

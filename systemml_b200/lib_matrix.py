@@ -315,6 +315,46 @@ def transpose(gCtx, instName, in1):
     return out
 
 
+def _adopt_csr(gCtx, rows, cols, rp, pci, pva, nnz):
+    from .gpu_context import CSRPointer
+    out = GPUObject(gCtx, rows, cols)
+    out.csr = CSRPointer.adopt(gCtx, rows, rp, pci.value, pva.value, nnz.value)
+    return out
+
+
+def sparseTranspose(gCtx, instName, in1):
+    """t(X) of a CSR operand, CSR result (CSRPointer.transpose / csr2csc, CSRPointer.java:463-481)."""
+    from .gpu_context import CSRPointer
+    out = GPUObject(gCtx, in1.cols, in1.rows)
+    out.csr = CSRPointer(gCtx, in1.csr.nnz, in1.cols)
+    gCtx.call("sysml_b200_csr_transpose", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val), in1.rows, in1.cols,
+              _p(out.csr.rowPtr), _p(out.csr.colInd), _p(out.csr.val))
+    return out
+
+
+def sparseSparseAdd(gCtx, instName, in1, in2, alpha=1.0, beta=1.0):
+    """alpha*A + beta*B for two CSR operands, CSR result (LibMatrixCUDA.dgeam's sparse branch, LibMatrixCUDA.java:1593-1701)."""
+    if (in1.rows, in1.cols) != (in2.rows, in2.cols):
+        _dim_error("sparse + sparse: %dx%d vs %dx%d" % (in1.rows, in1.cols, in2.rows, in2.cols))
+    rp = gCtx.allocate((in1.rows + 1) * 4)
+    pci, pva, nnz = C.c_void_p(), C.c_void_p(), C.c_int64()
+    gCtx.call("sysml_b200_csr_add", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val), float(alpha), _p(in2.csr.rowPtr),
+              _p(in2.csr.colInd), _p(in2.csr.val), float(beta), in1.rows, in1.cols, _p(rp), C.byref(pci), C.byref(pva), C.byref(nnz))
+    return _adopt_csr(gCtx, in1.rows, in1.cols, rp, pci, pva, nnz)
+
+
+def sparseSparseMatmult(gCtx, instName, in1, in2):
+    """CSR %*% CSR with a CSR result (LibMatrixCuMatMult.sparseSparseMatMult, LibMatrixCuMatMult.java:150-195)."""
+    if in1.cols != in2.rows:
+        _dim_error("sparse %%*%% sparse: inner dimensions %d vs %d" % (in1.cols, in2.rows))
+    rp = gCtx.allocate((in1.rows + 1) * 4)
+    pci, pva, nnz = C.c_void_p(), C.c_void_p(), C.c_int64()
+    gCtx.call("sysml_b200_matmult_csr_csr_sparse", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val), _p(in2.csr.rowPtr),
+              _p(in2.csr.colInd), _p(in2.csr.val), in1.rows, in1.cols, in2.rows, in2.cols, _p(rp), C.byref(pci), C.byref(pva),
+              C.byref(nnz))
+    return _adopt_csr(gCtx, in1.rows, in2.cols, rp, pci, pva, nnz)
+
+
 def denseToSparse(gCtx, in1):
     """GPUObject.denseToSparse (GPUObject.java:199-245): two-phase nnz count + fill."""
     from .gpu_context import CSRPointer

@@ -57,6 +57,9 @@ SIGNATURES = {
     "sysml_b200_unary": (ci, [vp, vp, vp, i64, ci]),
     "sysml_b200_cg_vector_update": (ci, [vp, vp, vp, vp, vp, vp, i64, dbl]),
     "sysml_b200_fill": (ci, [vp, vp, i64, dbl]),
+    "sysml_b200_csr_transpose": (ci, [vp, vp, vp, vp, i64, i64, vp, vp, vp]),
+    "sysml_b200_csr_add": (ci, [vp, vp, vp, vp, dbl, vp, vp, vp, dbl, i64, i64, vp, vp, vp, pi64]),
+    "sysml_b200_matmult_csr_csr_sparse": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_fused_cellwise": (ci, [vp, vp, vp, ci, vp, ci, vp, ci, i64, i64, ci, vp]),
     "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),
     "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),

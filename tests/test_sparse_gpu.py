@@ -180,3 +180,80 @@ def test_csr_streamed_rows(gctx, rows, cols, mean, full_rows, empty_every, monke
     np.add.at(e2, ci, va.astype(np.longdouble) * np.repeat(y.reshape(-1), np.diff(rp)).astype(np.longdouble))
     g2 = L.matmult(gctx, "ba+*", dX, gctx.dense(y), isLeftTransposed=True).to_host().reshape(-1)
     assert np.max(np.abs(e2.astype(np.float64) - g2)) <= 1e-9 * max(float(np.max(np.abs(e2))), 1e-300)
+
+
+def _csr_to_dense(rp, ci, va, shape):
+    D = np.zeros(shape)
+    for r in range(shape[0]):
+        D[r, ci[rp[r]:rp[r + 1]]] = va[rp[r]:rp[r + 1]]
+    return D
+
+
+def _check_csr(got, exp_dense, exact=True):
+    """CSR invariants (sorted distinct columns, no explicit zeros, nnz = count of non-zeros) + values."""
+    rp, ci, va = got.to_host()
+    rows, cols = exp_dense.shape
+    assert rp[0] == 0 and rp[-1] == len(ci) == len(va) == got.csr.nnz
+    assert np.all(np.diff(rp) >= 0)
+    for r in range(rows):
+        seg = ci[rp[r]:rp[r + 1]]
+        assert np.all(np.diff(seg) > 0) and (len(seg) == 0 or (seg[0] >= 0 and seg[-1] < cols))
+    assert np.all(va != 0.0)
+    assert got.csr.nnz == int(np.count_nonzero(exp_dense))
+    D = _csr_to_dense(rp, ci, va, exp_dense.shape)
+    if exact:
+        assert np.array_equal(D, exp_dense)
+    else:
+        assert_equal_matrices(exp_dense, D, rel=1e-12, what="sparse result")
+
+
+@pytest.mark.parametrize("rows,cols,sp", [(300, 200, 0.1), (1, 500, 0.3), (700, 3, 0.5), (64, 64, 0.0), (2049, 1300, 0.01)])
+def test_sparse_transpose_and_add(gctx, rows, cols, sp):
+    """CSR results: t(X) (csr2csc) and alpha*A + beta*B (csrgeam), incl. cancellation to exact zeros."""
+    from systemml_b200 import LibMatrixB200 as L
+    A = O.java_test_matrix(rows, cols, -1, 1, sp, 21)
+    B = O.java_test_matrix(rows, cols, -1, 1, sp, 22)
+    if sp > 0:
+        B[::3] = A[::3]  # A - B cancels exactly on these rows
+    dA, _ = _csr(gctx, A)
+    dB, _ = _csr(gctx, B)
+    _check_csr(L.sparseTranspose(gctx, "r'", dA), np.ascontiguousarray(A.T))
+    _check_csr(L.sparseSparseAdd(gctx, "+", dA, dB), A + B)
+    _check_csr(L.sparseSparseAdd(gctx, "-", dA, dB, 1.0, -1.0), A - B)
+    _check_csr(L.sparseSparseAdd(gctx, "+*", dA, dB, 1.0, 0.37), A + 0.37 * B)
+
+
+def _ref_sparse_sparse(A, B):
+    """LibMatrixMult.matrixMultSparseSparse (LibMatrixMult.java:1397-1500): per row of A, for k ascending,
+    c[i, cols(B[k,:])] += a * vals(B[k,:]) -- products and sums separately rounded."""
+    m, n = A.shape[0], B.shape[1]
+    Cm = np.zeros((m, n))
+    bnz = [np.nonzero(B[k])[0] for k in range(B.shape[0])]
+    for i in range(m):
+        for k in np.nonzero(A[i])[0]:
+            j = bnz[k]
+            if len(j):
+                Cm[i, j] += A[i, k] * B[k, j]
+    return Cm
+
+
+@pytest.mark.parametrize("m,k,n,spa,spb", [(300, 500, 200, 0.1, 0.05), (1, 400, 300, 1.0, 0.1), (700, 50, 1200, 0.02, 0.3),
+                                           (64, 64, 64, 0.5, 0.0), (1500, 900, 700, 0.004, 0.004)])
+def test_sparse_sparse_matmult_sparse_output(gctx, m, k, n, spa, spb):
+    from systemml_b200 import LibMatrixB200 as L
+    A = O.java_test_matrix(m, k, -1, 1, spa, 11)
+    B = O.java_test_matrix(k, n, -1, 1, spb, 12)
+    dA, _ = _csr(gctx, A)
+    dB, _ = _csr(gctx, B)
+    got = L.sparseSparseMatmult(gctx, "ba+*", dA, dB)
+    _check_csr(got, _ref_sparse_sparse(A, B))  # bit-exact: same products, same summation order
+    # and it agrees with the dense-output entry point
+    dense = L.matmult(gctx, "ba+*", dA, dB).to_host()
+    rp, ci, va = got.to_host()
+    assert np.max(np.abs(dense - _csr_to_dense(rp, ci, va, (m, n)))) <= 1e-12 * max(np.max(np.abs(dense)), 1e-300)  # other summation order
+    # integer-valued operands: products that cancel exactly leave no entry behind
+    Ai = np.round(O.java_test_matrix(40, 30, -2, 2, 0.5, 5))
+    Bi = np.round(O.java_test_matrix(30, 50, -2, 2, 0.5, 6))
+    dAi, _ = _csr(gctx, Ai)
+    dBi, _ = _csr(gctx, Bi)
+    _check_csr(L.sparseSparseMatmult(gctx, "ba+*", dAi, dBi), Ai @ Bi)
