@@ -19,6 +19,8 @@
 // a fixed order, so the result is deterministic run to run.
 //
 // Algorithmic bytes per launch: 8*n*m (X once) + 8*m (v) + 8*m (out) [+ 8*n (w)];  flops 4*n*m.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 struct sysml_b200_comm;
@@ -39,6 +41,7 @@ struct StreamArgs {
   int ct;
   i64 total_tiles;
   int use_tma;
+  int w_smem;  // w rides the stage ring too (R doubles per stage after the row tiles) instead of being read by the consumers
   sysml_b200_comm* comm;  // host side only: non-null -> the finishing kernel also does the cross-GPU sum
 };
 
@@ -81,16 +84,20 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
       const i64 r0 = tile * R;
       const i64 rows = (n - r0 < R) ? (n - r0) : R;
       double* dst = tiles + (size_t)s * stage_elems;
+      double* wdst = tiles + (size_t)STAGES * stage_elems + (size_t)s * R;
       const double* src = a.X + r0 * (i64)m;
       if (a.use_tma && rows == R) {
         if (lane == 0) {
           const uint32_t bytes = (uint32_t)(stage_elems * sizeof(double));
-          mbar_expect_tx(&full[s], bytes);
+          mbar_expect_tx(&full[s], bytes + (a.w_smem ? R * 8u : 0u));
           bulk_g2s(dst, src, bytes, &full[s], pol);
+          if (a.w_smem) bulk_g2s(wdst, a.w + r0, R * 8u, &full[s], pol);
         }
       } else {
         // ragged last tile / unaligned base: warp copy with zero padding of rows >= n
         const i64 valid = rows * (i64)m;
+        if (a.w_smem)
+          for (int i = lane; i < R; i += 32) wdst[i] = (i < rows) ? a.w[r0 + i] : 0.0;
         for (i64 i = lane; i < (i64)stage_elems; i += 32) dst[i] = (i < valid) ? ldg_stream(src + i) : 0.0;
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
@@ -121,7 +128,8 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
     const i64 r0 = tile * R + (i64)g * RG;
 
     double wv[RG];
-    if (MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv)) {
+    const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv);
+    if (need_w && !a.w_smem) {
 #pragma unroll
       for (int rr = 0; rr < RG; rr++) wv[rr] = (r0 + rr < n) ? __ldg(a.w + r0 + rr) : 0.0;
     } else {
@@ -131,6 +139,12 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
 
     mbar_wait(&full[s], ph);
     const double* T = tiles + (size_t)s * stage_elems + (size_t)g * RG * m;
+    if (need_w && a.w_smem) {
+      // w arrived with the tile: a global load here sits on the critical path of every (short) tile
+      const double* ws = tiles + (size_t)STAGES * stage_elems + (size_t)s * R + g * RG;
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) wv[rr] = ws[rr];
+    }
 
     double x[RG][CPT];
 #pragma unroll
@@ -261,12 +275,19 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   constexpr int R = G * RG;
   constexpr int NWG = TC / 32;
   auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES>;
-  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8;
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8;
   if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowstream: smem %zu too large", smem);
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   a.total_tiles = (a.n + R - 1) / R;
   const size_t stage_bytes = (size_t)R * a.m * 8;
   a.use_tma = ((reinterpret_cast<uintptr_t>(a.X) & 15) == 0) && (stage_bytes % 16 == 0) && (stage_bytes < (1u << 20));
+  const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv);
+  // narrow rows only: there a tile is consumed in a few hundred cycles and a global load of w sits on its critical
+  // path (10M x 100 XtwXv: 1.73 -> 1.18 ms); with 8 KB rows the consumers' own loads are hidden and the extra
+  // 32-byte copy per tile costs more than it saves (10M x 1000: 11.2 -> 11.8 ms)
+  bool w_ring = a.m <= 256;
+  if (const char* e = getenv("SYSML_B200_MMCHAIN_W_RING")) w_ring = atoi(e) != 0;  // A/B switch for measurements
+  a.w_smem = (need_w && a.w && w_ring && (reinterpret_cast<uintptr_t>(a.w) & 15) == 0 && (R % 2 == 0)) ? 1 : 0;
   i64 grid = (i64)ctx->sm_count * ctas_per_sm;
   if (grid > a.total_tiles) grid = a.total_tiles;
   if (grid < 1) grid = 1;
