@@ -150,8 +150,10 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
         else:
             g.call("sysml_b200_matmult_dense", _p(X), _p(yv), _p(out), n, m, n, 1, 1, 0)
 
+    fs = alloc(1, 1)
+
     def fsum(inputs, expr, consts=()):
-        return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum")
+        return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs)
 
     def dot(a, b):
         return fsum([a, b], E.input(0) * E.input(1))
@@ -219,6 +221,199 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
         if log is not None:
             log.append((it, obj))
     res = w.to_host().reshape(-1)
-    for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3):
+    for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3, fs):
         o.free()
     return res, it, obj
+
+
+def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
+    """One run of the Lloyd iterations of scripts/algorithms/Kmeans.dml:130-176 from given initial centroids
+    (BASELINE config C5: X 10M x 100, k = 50).  X: GPUObject n x m dense, C0: GPUObject k x m.
+    Per iteration: D = -2*(X %*% t(C)) + t(rowSums(C^2)); minD = rowMins(D); P = (D <= minD) / rowSums(D <= minD);
+    C_new = (t(P) %*% X) / t(colSums(P)).  Returns (C ndarray, iterations, wcss, termination code 1/2/3)."""
+    n, m, k = X.rows, X.cols, C0.rows
+    E = L.Expr
+    alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    Cc, Cn, XC, D, P = alloc(k, m), alloc(k, m), alloc(n, k), alloc(n, k), alloc(n, k)
+    c2, minD, rs, den, s1 = alloc(k, 1), alloc(n, 1), alloc(n, 1), alloc(k, 1), alloc(1, 1)
+    g.call("sysml_b200_d2d", _p(Cc), _p(C0), 8 * k * m)
+    g.call("sysml_b200_agg_unary_dense", _p(X), n, m, L.AGG_SUMSQ, L.DIR_ALL, _p(s1))
+    sumXsq = _scalar(g, s1)
+    c2_row = GPUObject.wrap(g, c2.ptr, 1, k)      # t(rowSums(C^2)): the same k doubles seen as a row vector
+    den_col = den                                  # t(colSums(P)) as a k x 1 column
+    wcss, it, term = float("inf"), 0, 0
+    while term == 0:
+        g.call("sysml_b200_matmult_dense", _p(X), _p(Cc), _p(XC), n, m, k, m, 0, 1)                 # X %*% t(C)
+        g.call("sysml_b200_agg_unary_dense", _p(Cc), k, m, L.AGG_SUMSQ, L.DIR_ROW, _p(c2))           # rowSums(C^2)
+        if fused:
+            L.fusedCellwise(g, "spoof", [XC, c2_row], E.const(0) * E.input(0) + E.input(1), (-2.0,), out=D)
+        else:
+            g.call("sysml_b200_binary_ms", _p(XC), -2.0, _p(D), n * k, L.BINARY_OPS["*"], 1)
+            g.call("sysml_b200_binary_mm", _p(D), _p(c2), _p(D), n, k, L.BCAST_ROW, L.BINARY_OPS["+"])
+        g.call("sysml_b200_agg_unary_dense", _p(D), n, k, L.AGG_MIN, L.DIR_ROW, _p(minD))            # rowMins(D)
+        g.call("sysml_b200_agg_unary_dense", _p(minD), n, 1, L.AGG_SUM, L.DIR_ALL, _p(s1))
+        wcss_old, wcss = wcss, sumXsq + _scalar(g, s1)
+        if fused:
+            le = E.input(0).binary(E.input(1), "<=")
+            L.fusedCellwise(g, "spoof", [D, minD], le, (), "rowSums", out=rs)
+            L.fusedCellwise(g, "spoof", [D, minD, rs], le / E.input(2), out=P)
+        else:
+            g.call("sysml_b200_binary_mm", _p(D), _p(minD), _p(P), n, k, L.BCAST_COL, L.BINARY_OPS["<="])
+            g.call("sysml_b200_agg_unary_dense", _p(P), n, k, L.AGG_SUM, L.DIR_ROW, _p(rs))
+            g.call("sysml_b200_binary_mm", _p(P), _p(rs), _p(P), n, k, L.BCAST_COL, L.BINARY_OPS["/"])
+        g.call("sysml_b200_agg_unary_dense", _p(P), n, k, L.AGG_SUM, L.DIR_COL, _p(den))             # colSums(P)
+        g.call("sysml_b200_matmult_dense", _p(P), _p(X), _p(Cn), n, k, n, m, 1, 0)                   # t(P) %*% X
+        g.call("sysml_b200_binary_mm", _p(Cn), _p(den_col), _p(Cn), k, m, L.BCAST_COL, L.BINARY_OPS["/"])
+        it += 1
+        if log is not None:
+            log.append((it, wcss))
+        if wcss_old - wcss < eps * wcss:
+            term = 1
+        elif it >= max_iter:
+            term = 2
+        elif float(np.sum(den.to_host() <= 0)) > 0:
+            term = 3
+        else:
+            Cc, Cn = Cn, Cc
+    out = Cc.to_host()
+    for o in (Cc, Cn, XC, D, P, c2, minD, rs, den, s1):
+        o.free()
+    return out, it, wcss, term
+
+
+def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0, log=None):
+    """scripts/algorithms/MultiLogReg.dml:150-340 with icpt = 0 (BASELINE config C4: X 1M x 5000, K = 20):
+    trust-region Newton with a conjugate-gradient inner solver.  X: GPUObject N x D; Y: GPUObject N x K, the one-hot
+    labels of the K non-baseline classes; y_last: GPUObject N x 1, the indicator of the baseline class (the script's
+    Y[, K+1]).  The script carries N x (K+1) matrices whose last column of LT is identically zero; here that column
+    is implicit: rowMaxs(LT) = max(rowMaxs(X B), 0), rowSums(exp_LT) = rowSums(exp(X B - mx)) + exp(-mx), which are
+    the same operations on the same values.  The O(N D K) work per inner iteration is X %*% V and t(X) %*% (N x K).
+    Returns (B ndarray D x K, outer iterations, objective)."""
+    N, Dm, K = X.rows, X.cols, Y.cols
+    E = L.Expr
+    alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    eta0, eta1, eta2, sigma1, sigma2, sigma3, psi = 1e-4, 0.25, 0.75, 0.25, 0.5, 4.0, 0.1
+
+    fs = alloc(1, 1)
+
+    def fsum(inputs, expr, consts=()):
+        return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs)
+
+    def dotm(a, b):
+        return fsum([a, b], E.input(0) * E.input(1))
+
+    def xt_times(M_, out):     # out (D x K) = t(X) %*% M_ (N x K)
+        g.call("sysml_b200_matmult_dense", _p(X), _p(M_), _p(out), N, Dm, N, K, 1, 0)
+
+    def x_times(V_, out):      # out (N x K) = X %*% V_ (D x K)
+        g.call("sysml_b200_matmult_dense", _p(X), _p(V_), _p(out), N, Dm, Dm, K, 0, 0)
+
+    def axpy(a, b, alpha, out):  # out = a + alpha*b
+        g.call("sysml_b200_axpy", _p(a), _p(b), float(alpha), _p(out), a.rows, a.cols, 0)
+
+    rsx = alloc(N, 1)
+    g.call("sysml_b200_agg_unary_dense", _p(X), N, Dm, L.AGG_SUMSQ, L.DIR_ROW, _p(rsx))
+    mxs = L.unaryAggregate(g, "uamax", rsx, "uamax")
+    rsx.free()
+    delta = 0.5 * np.sqrt(Dm) / np.sqrt(mxs)
+    lam = float(reg)
+    B, Bn, S, Sn, R, V, HV, Grad = (alloc(Dm, K) for _ in range(8))
+    P, Pn, Q, LT, T1 = (alloc(N, K) for _ in range(5))
+    mx, rs, rs2b = alloc(N, 1), alloc(N, 1), alloc(N, 1)
+    g.call("sysml_b200_fill", _p(B), Dm * K, 0.0)
+    g.call("sysml_b200_fill", _p(P), N * K, 1.0 / (K + 1))
+    obj = N * np.log(K + 1)
+
+    def gradient(Pm, Bm):
+        g.call("sysml_b200_binary_mm", _p(Pm), _p(Y), _p(T1), N, K, 0, L.BINARY_OPS["-"])    # P - Y
+        xt_times(T1, Grad)
+        axpy(Grad, Bm, lam, Grad)                                                              # + lambda * B
+        return np.sqrt(dotm(Grad, Grad))
+
+    norm_Grad = gradient(P, B)
+    norm_Grad_initial = norm_Grad
+    if maxinneriter == 0:
+        maxinneriter = Dm * K
+    it = 1
+    converge = (norm_Grad < tol) or (it > maxiter)
+    while not converge:
+        g.call("sysml_b200_fill", _p(S), Dm * K, 0.0)
+        g.call("sysml_b200_binary_ms", _p(Grad), -1.0, _p(R), Dm * K, L.BINARY_OPS["*"], 0)    # R = -Grad
+        g.call("sysml_b200_d2d", _p(V), _p(R), 8 * Dm * K)
+        delta2 = delta ** 2
+        inneriter = 1
+        norm_R2 = dotm(R, R)
+        innerconverge = np.sqrt(norm_R2) <= psi * norm_Grad
+        reached = 0
+        while not innerconverge:
+            x_times(V, Q)
+            # Q = P * (X V);  T1 = Q - P * rowSums(Q)
+            g.call("sysml_b200_binary_mm", _p(P), _p(Q), _p(Q), N, K, 0, L.BINARY_OPS["*"])
+            g.call("sysml_b200_agg_unary_dense", _p(Q), N, K, L.AGG_SUM, L.DIR_ROW, _p(rs))
+            L.fusedCellwise(g, "spoof", [Q, P, rs], E.input(0) - E.input(1) * E.input(2), out=T1)
+            xt_times(T1, HV)
+            axpy(HV, V, lam, HV)
+            alpha = norm_R2 / dotm(V, HV)
+            axpy(S, V, alpha, Sn)
+            norm_Snew2 = dotm(Sn, Sn)
+            if norm_Snew2 <= delta2:
+                S, Sn = Sn, S
+                axpy(R, HV, -alpha, R)
+                old = norm_R2
+                norm_R2 = dotm(R, R)
+                axpy(R, V, norm_R2 / old, V)
+                innerconverge = np.sqrt(norm_R2) <= psi * norm_Grad
+            else:
+                reached = 1
+                sv, v2, s2 = dotm(S, V), dotm(V, V), dotm(S, S)
+                rad = np.sqrt(sv ** 2 + v2 * (delta2 - s2))
+                alpha = (delta2 - s2) / (sv + rad) if sv >= 0 else (rad - sv) / v2
+                axpy(S, V, alpha, S)
+                axpy(R, HV, -alpha, R)
+                innerconverge = True
+            inneriter += 1
+            innerconverge = innerconverge or (inneriter > maxinneriter)
+        gs = dotm(S, Grad)
+        qk = -0.5 * (gs - dotm(S, R))
+        axpy(B, S, 1.0, Bn)
+        x_times(Bn, LT)
+        g.call("sysml_b200_agg_unary_dense", _p(LT), N, K, L.AGG_MAX, L.DIR_ROW, _p(mx))
+        g.call("sysml_b200_binary_ms", _p(mx), 0.0, _p(mx), N, L.BINARY_OPS["max"], 0)           # the implicit zero column
+        g.call("sysml_b200_binary_mm", _p(LT), _p(mx), _p(LT), N, K, L.BCAST_COL, L.BINARY_OPS["-"])
+        g.call("sysml_b200_unary", _p(LT), _p(Pn), N * K, L.UNARY_OPS["exp"])                    # exp_LT
+        g.call("sysml_b200_agg_unary_dense", _p(Pn), N, K, L.AGG_SUM, L.DIR_ROW, _p(rs))
+        # rs += exp(0 - mx)
+        rs2 = L.fusedCellwise(g, "spoof", [rs, mx], E.input(0) + (E.const(0) - E.input(1)).unary("exp"), (0.0,), out=rs2b)
+        g.call("sysml_b200_binary_mm", _p(Pn), _p(rs2), _p(Pn), N, K, L.BCAST_COL, L.BINARY_OPS["/"])
+        sum_y_lt = dotm(Y, LT) + fsum([y_last, mx], E.input(0) * (E.const(0) - E.input(1)), (0.0,))
+        obj_new = -sum_y_lt + fsum([rs2], E.input(0).unary("log")) + 0.5 * lam * dotm(Bn, Bn)
+        actred = obj - obj_new
+        rho = actred / qk
+        accepted = rho > eta0
+        snorm = np.sqrt(dotm(S, S))
+        if it == 1:
+            delta = min(delta, snorm)
+        alpha2 = obj_new - obj - gs
+        alpha = sigma3 if alpha2 <= 0 else max(sigma1, -0.5 * gs / alpha2)
+        if rho < eta0:
+            delta = min(max(alpha, sigma1) * snorm, sigma2 * delta)
+        elif rho < eta1:
+            delta = max(sigma1 * delta, min(alpha * snorm, sigma2 * delta))
+        elif rho < eta2:
+            delta = max(sigma1 * delta, min(alpha * snorm, sigma3 * delta))
+        else:
+            delta = max(delta, min(alpha * snorm, sigma3 * delta))
+        if accepted:
+            B, Bn = Bn, B
+            P, Pn = Pn, P
+            norm_Grad = gradient(P, B)
+            obj = obj_new
+        if log is not None:
+            log.append((it, inneriter - 1, obj, norm_Grad))
+        it += 1
+        converge = (norm_Grad < tol * norm_Grad_initial) or (it > maxiter) or \
+                   (reached == 0 and abs(actred) < (abs(obj) + abs(obj_new)) * 1e-14)
+    out = B.to_host()
+    for o in (B, Bn, S, Sn, R, V, HV, Grad, P, Pn, Q, LT, T1, mx, rs, rs2b, fs):
+        o.free()
+    return out, it - 1, obj

@@ -273,11 +273,12 @@ class Expr:
         return out
 
 
-def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None):
+def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None, out=None):
     """One-pass evaluation of a cellwise chain over `inputs` (GPUObjects: rows x cols matrices, rows x 1 column
     vectors or 1 x cols row vectors), optionally reduced by sum / rowSums / colSums -- the GPU twin of the code
     generator's cellwise template (runtime/codegen/SpoofCellwise.java).  Returns a GPUObject, or a float for
-    agg="sum" (read back like LibMatrixCUDA.unaryAggregate does for scalars, LibMatrixCUDA.java:692-693)."""
+    agg="sum" (read back like LibMatrixCUDA.unaryAggregate does for scalars, LibMatrixCUDA.java:692-693).
+    `out` reuses an existing buffer of the right size instead of allocating the result."""
     if rows is None:
         rows = max(i.rows for i in inputs)
     if cols is None:
@@ -295,7 +296,11 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     tokens = expr.tokens if isinstance(expr, Expr) else list(expr)
     a = FUSED_AGG[agg] if not isinstance(agg, int) else agg
     orow, ocol = {0: (rows, cols), 1: (1, 1), 2: (rows, 1), 3: (1, cols)}[a]
-    out = GPUObject.allocate_dense(gCtx, orow, ocol)
+    given = out is not None
+    if out is None:
+        out = GPUObject.allocate_dense(gCtx, orow, ocol)
+    elif out.rows * out.cols != orow * ocol:
+        raise native.NativeError(native.E_DIM, "fusedCellwise: out holds %dx%d, result is %dx%d" % (out.rows, out.cols, orow, ocol))
     n = len(inputs)
     ptrs = (C.c_void_p * max(n, 1))(*[i.ptr for i in inputs])
     kd = (C.c_int * max(n, 1))(*kinds)
@@ -303,8 +308,9 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     pg = (C.c_int32 * len(tokens))(*tokens)
     gCtx.call("sysml_b200_fused_cellwise", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, a, _p(out.ptr))
     if a == 1:
-        v = float(out.to_host().reshape(-1)[0])
-        out.free()
+        v = float(gCtx.d2h(out.ptr, (1,))[0])
+        if not given:
+            out.free()
         return v
     return out
 

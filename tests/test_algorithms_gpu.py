@@ -154,3 +154,144 @@ def test_l2svm_end_to_end(gctx, sparse):
         assert abs(obj - exp_obj) <= 1e-9 * abs(exp_obj)
         assert_equal_matrices(exp_w, w, rel=1e-7, what="l2svm weights (fused=%s)" % fused)
     assert np.mean(np.sign(X @ w) == Y) > 0.9  # and it separates the classes
+
+
+def cpu_kmeans_lloyd(X, C, max_iter, eps):
+    """scripts/algorithms/Kmeans.dml:130-176 in numpy."""
+    sumXsq = np.sum(X ** 2)
+    wcss, it, term = np.inf, 0, 0
+    while term == 0:
+        D = -2 * (X @ C.T) + np.sum(C ** 2, axis=1)[None, :]
+        minD = D.min(axis=1, keepdims=True)
+        wcss_old, wcss = wcss, sumXsq + np.sum(minD)
+        P = (D <= minD).astype(np.float64)
+        P = P / P.sum(axis=1, keepdims=True)
+        den = P.sum(axis=0)
+        C_new = (P.T @ X) / den[:, None]
+        it += 1
+        if wcss_old - wcss < eps * wcss:
+            term = 1
+        elif it >= max_iter:
+            term = 2
+        elif np.sum(den <= 0) > 0:
+            term = 3
+        else:
+            C = C_new
+    return C, it, wcss, term
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_kmeans_end_to_end(gctx, fused):
+    """BASELINE config C5's workload at test size: Gaussian blobs, k = 12."""
+    from systemml_b200.algorithms import kmeans_lloyd
+    rng = np.random.default_rng(4)
+    n, m, k = 60_000, 20, 12
+    centers = rng.uniform(-10, 10, (k, m))
+    X = centers[rng.integers(0, k, n)] + rng.normal(size=(n, m))
+    C0 = X[rng.choice(n, k, replace=False)].copy()
+    expC, exp_it, exp_wcss, exp_term = cpu_kmeans_lloyd(X, C0, 25, 1e-6)
+    gotC, it, wcss, term = kmeans_lloyd(gctx, gctx.dense(X), gctx.dense(C0), max_iter=25, eps=1e-6, fused=fused)
+    assert (it, term) == (exp_it, exp_term)
+    assert abs(wcss - exp_wcss) <= 1e-9 * abs(exp_wcss)
+    assert_equal_matrices(expC, gotC, rel=1e-9, what="Kmeans centroids")
+
+
+def cpu_multilogreg(X, Y, y_last, reg, tol, maxiter, maxinneriter):
+    """scripts/algorithms/MultiLogReg.dml:150-340 in numpy, icpt = 0 (the script's N x (K+1) matrices carried explicitly)."""
+    N, D = X.shape
+    K = Y.shape[1]
+    Yf = np.hstack([Y, y_last])
+    eta0, eta1, eta2, sigma1, sigma2, sigma3, psi = 1e-4, 0.25, 0.75, 0.25, 0.5, 4.0, 0.1
+    delta = 0.5 * np.sqrt(D) / np.max(np.sqrt(np.sum(X ** 2, axis=1)))
+    B = np.zeros((D, K))
+    P = np.full((N, K + 1), 1.0 / (K + 1))
+    obj = N * np.log(K + 1)
+    Grad = X.T @ (P[:, :K] - Y) + reg * B
+    norm_Grad = np.sqrt(np.sum(Grad ** 2))
+    norm_Grad_initial = norm_Grad
+    if maxinneriter == 0:
+        maxinneriter = D * K
+    it = 1
+    converge = (norm_Grad < tol) or (it > maxiter)
+    while not converge:
+        S = np.zeros((D, K))
+        R = -Grad
+        V = R.copy()
+        delta2 = delta ** 2
+        inneriter = 1
+        norm_R2 = np.sum(R ** 2)
+        innerconverge = np.sqrt(norm_R2) <= psi * norm_Grad
+        reached = 0
+        while not innerconverge:
+            Q = P[:, :K] * (X @ V)
+            HV = X.T @ (Q - P[:, :K] * Q.sum(axis=1, keepdims=True)) + reg * V
+            alpha = norm_R2 / np.sum(V * HV)
+            Snew = S + alpha * V
+            if np.sum(Snew ** 2) <= delta2:
+                S = Snew
+                R = R - alpha * HV
+                old = norm_R2
+                norm_R2 = np.sum(R ** 2)
+                V = R + (norm_R2 / old) * V
+                innerconverge = np.sqrt(norm_R2) <= psi * norm_Grad
+            else:
+                reached = 1
+                sv, v2, s2 = np.sum(S * V), np.sum(V ** 2), np.sum(S ** 2)
+                rad = np.sqrt(sv ** 2 + v2 * (delta2 - s2))
+                alpha = (delta2 - s2) / (sv + rad) if sv >= 0 else (rad - sv) / v2
+                S = S + alpha * V
+                R = R - alpha * HV
+                innerconverge = True
+            inneriter += 1
+            innerconverge = innerconverge or inneriter > maxinneriter
+        gs = np.sum(S * Grad)
+        qk = -0.5 * (gs - np.sum(S * R))
+        B_new = B + S
+        LT = np.hstack([X @ B_new, np.zeros((N, 1))])
+        LT = LT - LT.max(axis=1, keepdims=True)
+        exp_LT = np.exp(LT)
+        P_new = exp_LT / exp_LT.sum(axis=1, keepdims=True)
+        obj_new = -np.sum(Yf * LT) + np.sum(np.log(exp_LT.sum(axis=1))) + 0.5 * np.sum(reg * B_new ** 2)
+        actred = obj - obj_new
+        rho = actred / qk
+        snorm = np.sqrt(np.sum(S ** 2))
+        if it == 1:
+            delta = min(delta, snorm)
+        alpha2 = obj_new - obj - gs
+        alpha = sigma3 if alpha2 <= 0 else max(sigma1, -0.5 * gs / alpha2)
+        if rho < eta0:
+            delta = min(max(alpha, sigma1) * snorm, sigma2 * delta)
+        elif rho < eta1:
+            delta = max(sigma1 * delta, min(alpha * snorm, sigma2 * delta))
+        elif rho < eta2:
+            delta = max(sigma1 * delta, min(alpha * snorm, sigma3 * delta))
+        else:
+            delta = max(delta, min(alpha * snorm, sigma3 * delta))
+        if rho > eta0:
+            B, P = B_new, P_new
+            Grad = X.T @ (P[:, :K] - Y) + reg * B
+            norm_Grad = np.sqrt(np.sum(Grad ** 2))
+            obj = obj_new
+        it += 1
+        converge = (norm_Grad < tol * norm_Grad_initial) or (it > maxiter) or \
+                   (reached == 0 and abs(actred) < (abs(obj) + abs(obj_new)) * 1e-14)
+    return B, it - 1, obj
+
+
+def test_multilogreg_end_to_end(gctx):
+    """BASELINE config C4's workload at test size (K + 1 = 5 classes): same trust-region path, same B."""
+    from systemml_b200.algorithms import multilogreg
+    rng = np.random.default_rng(3)
+    N, D, K = 30_000, 40, 4
+    X = rng.uniform(-1, 1, (N, D))
+    Wt = rng.normal(size=(D, K + 1))
+    labels = np.argmax(X @ Wt + 0.5 * rng.gumbel(size=(N, K + 1)), axis=1)
+    Yfull = np.eye(K + 1)[labels]
+    Y, y_last = np.ascontiguousarray(Yfull[:, :K]), np.ascontiguousarray(Yfull[:, K:])
+    expB, exp_it, exp_obj = cpu_multilogreg(X, Y, y_last, 1.0, 1e-6, 12, 0)
+    gotB, it, obj = multilogreg(gctx, gctx.dense(X), gctx.dense(Y), gctx.dense(y_last), reg=1.0, tol=1e-6, maxiter=12)
+    assert it == exp_it
+    assert abs(obj - exp_obj) <= 1e-9 * abs(exp_obj)
+    assert_equal_matrices(expB, gotB, rel=1e-6, what="MultiLogReg B")
+    pred = np.argmax(np.hstack([X @ gotB, np.zeros((N, 1))]), axis=1)
+    assert np.mean(pred == labels) > 0.6
