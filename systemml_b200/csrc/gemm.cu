@@ -344,6 +344,58 @@ __device__ __forceinline__ void strip_tile(const StripCtx<TA, TB, Cfg, BKT, NST>
   }
 }
 
+// Off-diagonal tile that hangs over the right edge of the matrix: only NF of the 16 fragment columns exist
+// (m = 1000: 13; m = 5000: 1).  Same strip mapping -- warp w owns fragment rows w and 15-w -- with the column
+// count a compile-time constant, so the missing fragments cost neither DMMAs nor registers.
+template <int NF, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __forceinline__ void strip_edge_tile(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  constexpr int LDA = Cfg::LDA, LDB = Cfg::LDB;
+  constexpr int A_K4 = TA ? 4 * LDA : 4;
+  constexpr int B_NT = TB ? 8 * LDB : 8;
+  constexpr int B_K4 = TB ? 4 : 4 * LDB;
+  const int gid = c.lane >> 2, tig = c.lane & 3;
+  const int fa0 = c.warp, fa1 = 15 - c.warp;
+  const int a_off0 = TA ? (tig * LDA + fa0 * 8 + gid) : ((fa0 * 8 + gid) * LDA + tig);
+  const int a_off1 = TA ? (tig * LDA + fa1 * 8 + gid) : ((fa1 * 8 + gid) * LDA + tig);
+  const int b_off = TB ? (gid * LDB + tig) : (tig * LDB + gid);
+  double acc0[NF][2], acc1[NF][2];
+#pragma unroll
+  for (int b = 0; b < NF; b++) acc0[b][0] = acc0[b][1] = acc1[b][0] = acc1[b][1] = 0.0;
+  for (int kb = 0; kb < c.nkb; kb++, it++) {
+    const int s = it % NST;
+    const uint32_t ph = (it / NST) & 1u;
+    mbar_wait(&c.full[s], ph);
+    const double* as = c.As + s * Cfg::A_ELEMS;
+    const double* bs = c.Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+    for (int k4 = 0; k4 < BKT / 4; k4++) {
+      const double a0 = as[k4 * A_K4 + a_off0], a1 = as[k4 * A_K4 + a_off1];
+      double bf[NF];
+#pragma unroll
+      for (int b = 0; b < NF; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+      for (int b = 0; b < NF; b++) {
+        dmma884(acc0[b][0], acc0[b][1], a0, bf[b]);
+        dmma884(acc1[b][0], acc1[b][1], a1, bf[b]);
+      }
+    }
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(&c.empty[s]);
+  }
+  const i64 r0 = c.i0 + fa0 * 8 + gid, r1 = c.i0 + fa1 * 8 + gid;
+#pragma unroll
+  for (int b = 0; b < NF; b++) {
+    const i64 j = c.j0 + b * 8 + 2 * tig;
+    if (j + 1 < c.N) {
+      *reinterpret_cast<double2*>(c.outp + r0 * c.N + j) = make_double2(acc0[b][0], acc0[b][1]);
+      *reinterpret_cast<double2*>(c.outp + r1 * c.N + j) = make_double2(acc1[b][0], acc1[b][1]);
+    } else if (j < c.N) {
+      c.outp[r0 * c.N + j] = acc0[b][0];
+      c.outp[r1 * c.N + j] = acc1[b][0];
+    }
+  }
+}
+
 __device__ __forceinline__ void tile_coords(const GemmArgs& g, int t, int& ti, int& tj) {
   if (g.sym && g.diag_last) {  // strictly upper tiles row by row, then the diagonal (its ragged last tile first)
     const int T = g.tiles_n, noff = T * (T - 1) / 2;
@@ -509,6 +561,29 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
         case 5: strip_tile<5, 10>(sc, it); break;
         case 6: strip_tile<6, 9>(sc, it); break;
         default: strip_tile<7, 8>(sc, it); break;
+      }
+      continue;
+    }
+    if (g.sym && ti != tj && i0 + BM <= g.M && j0 + BN > g.N) {  // last tile column of a ragged matrix
+      double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
+      const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
+      switch ((int)((g.N - j0 + 7) / 8)) {
+        case 1: strip_edge_tile<1>(sc, it); break;
+        case 2: strip_edge_tile<2>(sc, it); break;
+        case 3: strip_edge_tile<3>(sc, it); break;
+        case 4: strip_edge_tile<4>(sc, it); break;
+        case 5: strip_edge_tile<5>(sc, it); break;
+        case 6: strip_edge_tile<6>(sc, it); break;
+        case 7: strip_edge_tile<7>(sc, it); break;
+        case 8: strip_edge_tile<8>(sc, it); break;
+        case 9: strip_edge_tile<9>(sc, it); break;
+        case 10: strip_edge_tile<10>(sc, it); break;
+        case 11: strip_edge_tile<11>(sc, it); break;
+        case 12: strip_edge_tile<12>(sc, it); break;
+        case 13: strip_edge_tile<13>(sc, it); break;
+        case 14: strip_edge_tile<14>(sc, it); break;
+        case 15: strip_edge_tile<15>(sc, it); break;
+        default: strip_edge_tile<16>(sc, it); break;
       }
       continue;
     }
