@@ -301,7 +301,8 @@ int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, doubl
  * template (runtime/codegen/SpoofCellwise.java: NO_AGG / FULL_AGG / ROW_AGG / COL_AGG).
  *   inputs[i]      device pointers; input_kinds[i] = SYSML_BCAST_NONE (rows x cols), _COL (rows x 1), _ROW (1 x cols)
  *   program        postfix tokens SYSML_FUSED_TOKEN(kind, arg); binary/unary args are SYSML_OP_* / SYSML_UN_*
- *   agg            SYSML_FUSED_AGG_*; out holds rows*cols, 1, rows or cols doubles accordingly
+ *   agg            SYSML_FUSED_AGG_* (none, or sum / min / max over all cells, per row, per column); out holds
+ *                  rows*cols, 1, rows or cols doubles accordingly
  * The chain is compiled to a kernel on first use (NVRTC, sm_100a) and cached by program; every operator has the
  * arithmetic of its unfused kernel, so without an aggregate the result is bit-identical to the unfused sequence.
  * Fails with SYSML_E_UNSUPPORTED when NVRTC or the driver library cannot be loaded (no CPU path). */
@@ -316,6 +317,12 @@ int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, doubl
 #define SYSML_FUSED_AGG_SUM 1
 #define SYSML_FUSED_AGG_ROWSUMS 2
 #define SYSML_FUSED_AGG_COLSUMS 3
+#define SYSML_FUSED_AGG_MIN 4      /* min / max endings (SpoofCellwise.AggOp MIN, MAX; sum of squares is x*x in the chain) */
+#define SYSML_FUSED_AGG_ROWMINS 5
+#define SYSML_FUSED_AGG_COLMINS 6
+#define SYSML_FUSED_AGG_MAX 7
+#define SYSML_FUSED_AGG_ROWMAXS 8
+#define SYSML_FUSED_AGG_COLMAXS 9
 #define SYSML_FUSED_MAX_INPUTS 8
 #define SYSML_FUSED_MAX_CONSTS 8
 #define SYSML_FUSED_MAX_TOKENS 64

@@ -216,7 +216,7 @@ _UNARY_NP = {
 def fused_cellwise(inputs, consts, tokens, rows, cols, agg=0):
     """The UNFUSED reference evaluation of a postfix cellwise program (tokens as SYSML_FUSED_TOKEN): one
     LibMatrixBincell op per binary token (bincellOp, LibMatrixBincell.java:87-339), numpy for the unary builtins,
-    then LibMatrixAgg sum / rowSums / colSums (agg 1/2/3).  Operands broadcast like the reference: rows x 1 and
+    then LibMatrixAgg sum / rowSums / colSums (agg 1/2/3), min (4/5/6) or max (7/8/9).  Operands broadcast like the reference: rows x 1 and
     1 x cols vectors against rows x cols."""
     stack = []
 
@@ -258,7 +258,8 @@ def fused_cellwise(inputs, consts, tokens, rows, cols, agg=0):
     res = full(stack[0])
     if agg == 0:
         return res
-    return agg_unary_dense(res, SUM, {1: ALL, 2: ROW, 3: COL}[agg], 1)
+    op = SUM if agg <= 3 else (MIN if agg <= 6 else MAX)
+    return agg_unary_dense(res, op, {1: ALL, 2: ROW, 3: COL}[(agg - 1) % 3 + 1], 1)
 
 
 def count_nnz(A):

@@ -246,7 +246,8 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
         g.call("sysml_b200_matmult_dense", _p(X), _p(Cc), _p(XC), n, m, k, m, 0, 1)                 # X %*% t(C)
         g.call("sysml_b200_agg_unary_dense", _p(Cc), k, m, L.AGG_SUMSQ, L.DIR_ROW, _p(c2))           # rowSums(C^2)
         if fused:
-            L.fusedCellwise(g, "spoof", [XC, c2_row], E.const(0) * E.input(0) + E.input(1), (-2.0,), out=D)
+            d_e = E.const(0) * E.input(0) + E.input(1)
+            L.fusedCellwise(g, "spoof", [XC, c2_row], d_e, (-2.0,), out=D)
         else:
             g.call("sysml_b200_binary_ms", _p(XC), -2.0, _p(D), n * k, L.BINARY_OPS["*"], 1)
             g.call("sysml_b200_binary_mm", _p(D), _p(c2), _p(D), n, k, L.BCAST_ROW, L.BINARY_OPS["+"])

@@ -24,7 +24,10 @@
 #include <string>
 #include <vector>
 
+#include <math_constants.h>
+
 #include "common.cuh"
+#include "cellwise_ops.cuh"
 
 namespace {
 
@@ -56,19 +59,34 @@ __device__ __forceinline__ void two_sum(double a, double b, double& s, double& e
   double bb = __dsub_rn(s, a);
   e = __dadd_rn(__dsub_rn(a, __dsub_rn(s, bb)), __dsub_rn(b, bb));
 }
-struct Comp {  // compensated sum: value = hi + lo
+// accumulator of the aggregate: FUSED_AOP 0 = compensated sum (value = hi + lo), 1 = min, 2 = max (Math.min/max
+// semantics of the unfused kernels: NaN propagates, -0.0 < +0.0; lo unused)
+#define FUSED_ACC_INIT {(FUSED_AOP == 1) ? __longlong_as_double(0x7ff0000000000000LL) : (FUSED_AOP == 2) ? __longlong_as_double(0xfff0000000000000LL) : 0.0, 0.0}
+struct Comp {
   double hi, lo;
   __device__ __forceinline__ void add(double x) {
-    double s, e;
-    two_sum(hi, x, s, e);
-    hi = s;
-    lo = __dadd_rn(lo, e);
+    if (FUSED_AOP == 0) {
+      double s, e;
+      two_sum(hi, x, s, e);
+      hi = s;
+      lo = __dadd_rn(lo, e);
+    } else {
+      hi = (FUSED_AOP == 1) ? sysml_ops::jmin(hi, x) : sysml_ops::jmax(hi, x);
+    }
   }
   __device__ __forceinline__ void merge(double ohi, double olo) {
-    double s, e;
-    two_sum(hi, ohi, s, e);
-    hi = s;
-    lo = __dadd_rn(__dadd_rn(lo, olo), e);
+    if (FUSED_AOP == 0) {
+      double s, e;
+      two_sum(hi, ohi, s, e);
+      hi = s;
+      lo = __dadd_rn(__dadd_rn(lo, olo), e);
+    } else {
+      hi = (FUSED_AOP == 1) ? sysml_ops::jmin(hi, ohi) : sysml_ops::jmax(hi, ohi);
+    }
+  }
+  __device__ __forceinline__ double result() const {
+    if (FUSED_AOP != 0) return hi;
+    return (isinf(hi) || lo != lo) ? hi : __dadd_rn(hi, lo);
   }
 };
 __device__ __forceinline__ void group_merge(Comp& a, int W) {
@@ -86,7 +104,7 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 #if FUSED_AGG == 1
-  Comp acc{0.0, 0.0}, acc2{0.0, 0.0};
+  Comp acc FUSED_ACC_INIT, acc2 FUSED_ACC_INIT;
 #endif
 #if FUSED_VEC2
   const long long n2 = len >> 1;
@@ -138,7 +156,7 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   const long long stride = (long long)gridDim.x * blockDim.x;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
 #if FUSED_AGG == 1
-  Comp acc{0.0, 0.0};
+  Comp acc FUSED_ACC_INIT;
 #endif
   if (i < len) {
     long long r = i / cols, c = i - r * cols;
@@ -187,7 +205,7 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   constexpr int RPW = 32 / FUSED_W;
   for (long long base = gw * RPW; base < rows; base += nw * RPW) {
     const long long r = base + lane / FUSED_W;
-    Comp acc{0.0, 0.0};
+    Comp acc FUSED_ACC_INIT;
     if (r < rows) {
       const long long off = r * cols;
       for (long long c = sub; c < cols; c += FUSED_W) {
@@ -197,7 +215,7 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
       }
     }
     group_merge(acc, FUSED_W);
-    if (r < rows && sub == 0) a.out[r] = (isinf(acc.hi) || acc.lo != acc.lo) ? acc.hi : __dadd_rn(acc.hi, acc.lo);
+    if (r < rows && sub == 0) a.out[r] = acc.result();
   }
 }
 #else
@@ -210,7 +228,7 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   __shared__ double sh[2][256];
   for (long long c0 = 0; c0 < cols; c0 += CPB) {
     const long long c = c0 + cl;
-    Comp acc{0.0, 0.0};
+    Comp acc FUSED_ACC_INIT;
     if (rl < RPB && c < cols) {
       for (long long r = (long long)blockIdx.x * RPB + rl; r < rows; r += (long long)gridDim.x * RPB) {
         double x[FUSED_NIN + 1];
@@ -233,30 +251,53 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
 )FUSEDSRC";
 
 // ---- precompiled finishers (fixed order => run-to-run reproducible) ----
-__global__ void fused_sum_finish(const double* __restrict__ partial, int n, double* __restrict__ out) {
-  // one warp: lane-strided compensated merge, then a butterfly
-  CompSum s;
-  for (int i = threadIdx.x; i < n; i += 32) {
-    s.add(partial[2 * i]);
-    s.lo = __dadd_rn(s.lo, partial[2 * i + 1]);
+template <int AOP>
+__device__ __forceinline__ void fin_add(CompSum& s, double hi, double lo) {
+  if (AOP == 0) {
+    s.add(hi);
+    s.lo = __dadd_rn(s.lo, lo);
+  } else {
+    s.hi = (AOP == 1) ? sysml_ops::jmin(s.hi, hi) : sysml_ops::jmax(s.hi, hi);
   }
-  for (int o = 16; o > 0; o >>= 1) {
-    CompSum t;
-    t.hi = __shfl_xor_sync(0xffffffffu, s.hi, o);
-    t.lo = __shfl_xor_sync(0xffffffffu, s.lo, o);
-    s.add(t);
-  }
-  if (threadIdx.x == 0) out[0] = (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
 }
+template <int AOP>
+__device__ __forceinline__ CompSum fin_init() {
+  CompSum s;
+  if (AOP == 1) s.hi = CUDART_INF;
+  if (AOP == 2) s.hi = -CUDART_INF;
+  return s;
+}
+template <int AOP>
+__device__ __forceinline__ double fin_result(const CompSum& s) {
+  if (AOP != 0) return s.hi;
+  return (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
+}
+template <int AOP>
+__global__ void fused_all_finish(const double* __restrict__ partial, int n, double* __restrict__ out) {
+  // one warp: lane-strided merge in a fixed order, then a butterfly
+  CompSum s = fin_init<AOP>();
+  for (int i = threadIdx.x; i < n; i += 32) fin_add<AOP>(s, partial[2 * i], partial[2 * i + 1]);
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ohi = __shfl_xor_sync(0xffffffffu, s.hi, o);
+    const double olo = __shfl_xor_sync(0xffffffffu, s.lo, o);
+    if (AOP == 0) {
+      CompSum t;
+      t.hi = ohi;
+      t.lo = olo;
+      s.add(t);
+    } else {
+      fin_add<AOP>(s, ohi, olo);
+    }
+  }
+  if (threadIdx.x == 0) out[0] = fin_result<AOP>(s);
+}
+template <int AOP>
 __global__ void fused_col_finish(const double* __restrict__ partial, int P, i64 cols, double* __restrict__ out) {
   const i64 c = (i64)blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cols) return;
-  CompSum s;
-  for (int p = 0; p < P; p++) {
-    s.add(partial[((size_t)p * 2) * cols + c]);
-    s.lo = __dadd_rn(s.lo, partial[((size_t)p * 2 + 1) * cols + c]);
-  }
-  out[c] = (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
+  CompSum s = fin_init<AOP>();
+  for (int p = 0; p < P; p++) fin_add<AOP>(s, partial[((size_t)p * 2) * cols + c], partial[((size_t)p * 2 + 1) * cols + c]);
+  out[c] = fin_result<AOP>(s);
 }
 
 // ---- dynamically loaded NVRTC + driver entry points ----
@@ -417,20 +458,25 @@ std::string gen_defines() {
 
 extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
                                          const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
-                                         int64_t cols, int agg, double* out) {
+                                         int64_t cols, int agg_in, double* out) {
   SYSML_ENTER(ctx);
+  int agg = agg_in;
   if (n_inputs < 0 || n_inputs > SYSML_FUSED_MAX_INPUTS || n_consts < 0 || n_consts > SYSML_FUSED_MAX_CONSTS || n_tokens < 1 ||
       n_tokens > SYSML_FUSED_MAX_TOKENS)
     return sysml_set_error(ctx, SYSML_E_LIMIT, "fused_cellwise: at most %d inputs, %d constants, %d tokens", SYSML_FUSED_MAX_INPUTS,
                            SYSML_FUSED_MAX_CONSTS, SYSML_FUSED_MAX_TOKENS);
   if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "fused_cellwise: negative dimension");
-  if (agg < SYSML_FUSED_AGG_NONE || agg > SYSML_FUSED_AGG_COLSUMS) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: unknown aggregate %d", agg);
+  if (agg < SYSML_FUSED_AGG_NONE || agg > SYSML_FUSED_AGG_COLMAXS) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: unknown aggregate %d", agg_in);
+  // split into the accumulator (0 sum, 1 min, 2 max) and the direction, numbered like the three sum codes
+  const int aop = agg <= SYSML_FUSED_AGG_COLSUMS ? 0 : (agg <= SYSML_FUSED_AGG_COLMINS ? 1 : 2);
+  if (agg > SYSML_FUSED_AGG_COLSUMS) agg = (agg - 1) % 3 + 1;
   if (!program || (n_inputs && (!inputs || !input_kinds)) || (n_consts && !consts)) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: null pointer");
   const i64 len = rows * cols;
   const i64 out_len = agg == SYSML_FUSED_AGG_NONE ? len : agg == SYSML_FUSED_AGG_SUM ? 1 : agg == SYSML_FUSED_AGG_ROWSUMS ? rows : cols;
   if (out_len == 0) return SYSML_OK;
   if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: out is null");
   if (len == 0) {  // an empty operand: every sum is 0 (LibMatrixAgg: empty input -> zero output)
+    if (aop != 0) return sysml_set_error(ctx, SYSML_E_DIM, "fused_cellwise: min / max of an empty operand");
     SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)out_len * sizeof(double), ctx->stream));
     return SYSML_OK;
   }
@@ -462,7 +508,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
 
   // ---- find or build the kernel ----
   std::string key;
-  appendf(key, "d%d|s%d|v%d|w%d|a%d|n%d|", ctx->device, shape, vec2, W, kagg, n_inputs);
+  appendf(key, "d%d|s%d|v%d|w%d|a%d|o%d|n%d|", ctx->device, shape, vec2, W, kagg, aop, n_inputs);
   for (int i = 0; i < n_inputs; i++) {
     const int kd = input_kinds[i];
     const bool full = kd == SYSML_BCAST_NONE || (kd == SYSML_BCAST_COL && cols == 1) || (kd == SYSML_BCAST_ROW && rows == 1);
@@ -482,8 +528,8 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
       const std::string eval = gen_eval(program, n_tokens, n_inputs, n_consts, err);
       if (eval.empty()) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: %s", err.c_str());
       std::string src = gen_defines();
-      appendf(src, "#define FUSED_NIN %d\n#define FUSED_SHAPE %d\n#define FUSED_VEC2 %d\n#define FUSED_W %d\n#define FUSED_AGG %d\n", n_inputs,
-              shape, vec2, W, kagg);
+      appendf(src, "#define FUSED_NIN %d\n#define FUSED_SHAPE %d\n#define FUSED_VEC2 %d\n#define FUSED_W %d\n#define FUSED_AGG %d\n#define FUSED_AOP %d\n",
+              n_inputs, shape, vec2, W, kagg, aop);
       // per-input loads: matrices stream past L1, broadcast vectors are cached reads
       std::string flat = "#define FUSED_LOAD_FLAT(i) ", rc = "#define FUSED_LOAD_RC(i, r, c) ", l2 = "#define FUSED_LOAD2(i) ";
       for (int i = 0; i < n_inputs; i++) {
@@ -560,10 +606,15 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   }
   ctx->launches++;
   if (kagg == 1) {
-    fused_sum_finish<<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
-    SYSML_LAUNCH_CHECK(ctx, "fused_sum_finish");
+    if (aop == 0) fused_all_finish<0><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
+    else if (aop == 1) fused_all_finish<1><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
+    else fused_all_finish<2><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
+    SYSML_LAUNCH_CHECK(ctx, "fused_all_finish");
   } else if (kagg == 3) {
-    fused_col_finish<<<(unsigned)((cols + 255) / 256), 256, 0, ctx->stream>>>(fa.partial, (int)grid, cols, out);
+    const unsigned fg = (unsigned)((cols + 255) / 256);
+    if (aop == 0) fused_col_finish<0><<<fg, 256, 0, ctx->stream>>>(fa.partial, (int)grid, cols, out);
+    else if (aop == 1) fused_col_finish<1><<<fg, 256, 0, ctx->stream>>>(fa.partial, (int)grid, cols, out);
+    else fused_col_finish<2><<<fg, 256, 0, ctx->stream>>>(fa.partial, (int)grid, cols, out);
     SYSML_LAUNCH_CHECK(ctx, "fused_col_finish");
   }
   return SYSML_OK;

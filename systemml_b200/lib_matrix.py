@@ -198,7 +198,8 @@ def unaryOp(gCtx, instName, in1, op):
     return out
 
 
-FUSED_AGG = {None: 0, "none": 0, "sum": 1, "rowSums": 2, "colSums": 3}
+FUSED_AGG = {None: 0, "none": 0, "sum": 1, "rowSums": 2, "colSums": 3, "min": 4, "rowMins": 5, "colMins": 6,
+             "max": 7, "rowMaxs": 8, "colMaxs": 9}
 
 
 class Expr:
@@ -295,7 +296,7 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
             raise native.NativeError(native.E_DIM, "fusedCellwise: operand %dx%d does not broadcast to %dx%d" % (i.rows, i.cols, rows, cols))
     tokens = expr.tokens if isinstance(expr, Expr) else list(expr)
     a = FUSED_AGG[agg] if not isinstance(agg, int) else agg
-    orow, ocol = {0: (rows, cols), 1: (1, 1), 2: (rows, 1), 3: (1, cols)}[a]
+    orow, ocol = {0: (rows, cols), 1: (1, 1), 2: (rows, 1), 3: (1, cols)}[a if a <= 3 else (a - 1) % 3 + 1]
     given = out is not None
     if out is None:
         out = GPUObject.allocate_dense(gCtx, orow, ocol)
@@ -307,7 +308,7 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     cs = (C.c_double * max(len(consts), 1))(*[float(c) for c in consts])
     pg = (C.c_int32 * len(tokens))(*tokens)
     gCtx.call("sysml_b200_fused_cellwise", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, a, _p(out.ptr))
-    if a == 1:
+    if a in (1, 4, 7):
         v = float(gCtx.d2h(out.ptr, (1,))[0])
         if not given:
             out.free()

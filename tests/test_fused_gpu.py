@@ -37,7 +37,8 @@ def _close(exp, got, what):
 
 
 def _oracle(arrays, expr, consts, agg, rows, cols):
-    return O.fused_cellwise(arrays, consts, expr.tokens, rows, cols, {None: 0, "sum": 1, "rowSums": 2, "colSums": 3}[agg])
+    from systemml_b200.lib_matrix import FUSED_AGG
+    return O.fused_cellwise(arrays, consts, expr.tokens, rows, cols, FUSED_AGG[agg])
 
 
 @pytest.mark.parametrize("n", [1, 7, 4096, 100_001, 1_000_000])
@@ -144,3 +145,23 @@ def test_special_values_and_errors(gctx):
         L.fusedCellwise(gctx, "spoof", [dA, gctx.dense(np.zeros((3, 4)))], E.input(0) + E.input(1))
     # empty operand: sums are zero
     assert L.fusedCellwise(gctx, "spoof", [gctx.dense(np.zeros((0, 5)))], E.input(0), (), "sum", rows=0, cols=5) == 0.0
+
+
+@pytest.mark.parametrize("rows,cols", [(1, 1), (64, 130), (1024, 21), (777, 1025), (5, 5000), (100_000, 50), (4097, 1)])
+def test_min_max_endings(gctx, rows, cols):
+    """Chains ending in min / max (SpoofCellwise.AggOp MIN, MAX), all three directions: exact -- no rounding in a
+    min or max -- including NaN propagation and -0.0 < +0.0 (Kmeans: rowMins(-2*XC + t(c2)) without materialising D)."""
+    from systemml_b200.lib_matrix import Expr as E
+    rng = np.random.default_rng(rows + 7 * cols)
+    XC = rng.uniform(-1, 1, (rows, cols))
+    c2 = rng.uniform(0, 2, (1, cols))
+    if rows * cols > 50:
+        XC.flat[3], XC.flat[11], XC.flat[20] = np.nan, 0.0, -0.0
+    expr = E.const(0) * E.input(0) + E.input(1)
+    for agg in ("min", "rowMins", "colMins", "max", "rowMaxs", "colMaxs"):
+        exp = _oracle([XC, c2], expr, (-2.0,), agg, rows, cols).reshape(-1)
+        got = _run(gctx, [XC, c2], expr, (-2.0,), agg)
+        got = np.array([got]) if isinstance(got, float) else got.reshape(-1)
+        assert np.array_equal(np.isnan(exp), np.isnan(got)), agg
+        ok = ~np.isnan(exp)
+        assert np.array_equal(exp[ok].view(np.int64), got[ok].view(np.int64)), agg
