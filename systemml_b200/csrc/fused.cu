@@ -18,6 +18,7 @@
 // call fails with SYSML_E_UNSUPPORTED.
 #include <dlfcn.h>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <map>
 #include <mutex>
@@ -71,7 +72,13 @@ struct Comp {
       hi = s;
       lo = __dadd_rn(lo, e);
     } else {
-      hi = (FUSED_AOP == 1) ? sysml_ops::jmin(hi, x) : sysml_ops::jmax(hi, x);
+      // branch-free: plain compare-select, and two sticky flags kept as the bit pattern of lo (bit 0: a NaN was
+      // seen, bit 1: a zero of the winning sign -- -0.0 for min, +0.0 for max -- was seen); settled in result()
+      long long f = __double_as_longlong(lo);
+      f |= (x != x) ? 1ll : 0ll;
+      f |= (__double_as_longlong(x) == ((FUSED_AOP == 1) ? (long long)0x8000000000000000ull : 0ll)) ? 2ll : 0ll;
+      lo = __longlong_as_double(f);
+      hi = ((FUSED_AOP == 1) ? (x < hi) : (x > hi)) ? x : hi;
     }
   }
   __device__ __forceinline__ void merge(double ohi, double olo) {
@@ -81,11 +88,17 @@ struct Comp {
       hi = s;
       lo = __dadd_rn(__dadd_rn(lo, olo), e);
     } else {
-      hi = (FUSED_AOP == 1) ? sysml_ops::jmin(hi, ohi) : sysml_ops::jmax(hi, ohi);
+      lo = __longlong_as_double(__double_as_longlong(lo) | __double_as_longlong(olo));
+      hi = ((FUSED_AOP == 1) ? (ohi < hi) : (ohi > hi)) ? ohi : hi;
     }
   }
   __device__ __forceinline__ double result() const {
-    if (FUSED_AOP != 0) return hi;
+    if (FUSED_AOP != 0) {
+      const long long f = __double_as_longlong(lo);
+      if (f & 1) return __longlong_as_double(0x7ff8000000000000LL);
+      if (hi == 0.0 && (f & 2)) return (FUSED_AOP == 1) ? -0.0 : 0.0;
+      return hi;
+    }
     return (isinf(hi) || lo != lo) ? hi : __dadd_rn(hi, lo);
   }
 };
@@ -205,17 +218,63 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   constexpr int RPW = 32 / FUSED_W;
   for (long long base = gw * RPW; base < rows; base += nw * RPW) {
     const long long r = base + lane / FUSED_W;
-    Comp acc FUSED_ACC_INIT;
+    Comp acc FUSED_ACC_INIT, accb FUSED_ACC_INIT;  // two chains per lane: twice the loads in flight
     if (r < rows) {
       const long long off = r * cols;
-      for (long long c = sub; c < cols; c += FUSED_W) {
+      long long c = sub;
+      for (; c + FUSED_W < cols; c += 2 * FUSED_W) {
+        double x[FUSED_NIN + 1], y[FUSED_NIN + 1];
+        FUSED_LOAD_RC(off + c, r, c)
+        FUSED_LOAD_RC_Y(off + c + FUSED_W, r, c + FUSED_W)
+        acc.add(fused_eval(x, a.k));
+        accb.add(fused_eval(y, a.k));
+      }
+      if (c < cols) {
         double x[FUSED_NIN + 1];
         FUSED_LOAD_RC(off + c, r, c)
         acc.add(fused_eval(x, a.k));
       }
     }
+    acc.merge(accb.hi, accb.lo);
     group_merge(acc, FUSED_W);
     if (r < rows && sub == 0) a.out[r] = acc.result();
+  }
+}
+#elif FUSED_SHAPE == 4
+// ---- row aggregates of a NARROW matrix (specialised on the column count): a warp takes FUSED_RW adjacent rows,
+// which are contiguous in memory, evaluates the chain over them with flat, fully coalesced, fully unrolled loads
+// (dozens of independent loads per lane instead of a handful per row), parks the values in shared memory and
+// then reduces every row with 32/FUSED_RW lanes ----
+extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArgs a) {
+  constexpr int COLS = FUSED_COLS, RW = FUSED_RW, TILE = RW * COLS, LPR = 32 / RW;
+  __shared__ double sh[8][TILE];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const long long rows = a.rows;
+  const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long rb = gw * RW; rb < rows; rb += nw * RW) {
+    const int nvalid = (int)((rows - rb < RW ? rows - rb : RW) * COLS);
+#pragma unroll
+    for (int e0 = 0; e0 < TILE; e0 += 32) {
+      const int e = e0 + lane;
+      if (e < nvalid) {
+        const int rr = e / COLS, c = e - rr * COLS;
+        const long long r = rb + rr;
+        double x[FUSED_NIN + 1];
+        FUSED_LOAD_RC(rb * COLS + e, r, c)
+        sh[w][e] = fused_eval(x, a.k);
+      }
+    }
+    __syncwarp();
+    const int row = lane / LPR, sub = lane - row * LPR;
+    Comp acc FUSED_ACC_INIT;
+    if (rb + row < rows) {
+      const double* p = &sh[w][row * COLS];
+      for (int c = sub; c < COLS; c += LPR) acc.add(p[c]);
+    }
+    group_merge(acc, LPR);
+    if (rb + row < rows && sub == 0) a.out[rb + row] = acc.result();
+    __syncwarp();
   }
 }
 #else
@@ -256,8 +315,9 @@ __device__ __forceinline__ void fin_add(CompSum& s, double hi, double lo) {
   if (AOP == 0) {
     s.add(hi);
     s.lo = __dadd_rn(s.lo, lo);
-  } else {
-    s.hi = (AOP == 1) ? sysml_ops::jmin(s.hi, hi) : sysml_ops::jmax(s.hi, hi);
+  } else {  // (value, flag bits) pairs as the generated kernels write them
+    s.lo = __longlong_as_double(__double_as_longlong(s.lo) | __double_as_longlong(lo));
+    s.hi = ((AOP == 1) ? (hi < s.hi) : (hi > s.hi)) ? hi : s.hi;
   }
 }
 template <int AOP>
@@ -269,7 +329,12 @@ __device__ __forceinline__ CompSum fin_init() {
 }
 template <int AOP>
 __device__ __forceinline__ double fin_result(const CompSum& s) {
-  if (AOP != 0) return s.hi;
+  if (AOP != 0) {
+    const long long f = __double_as_longlong(s.lo);
+    if (f & 1) return CUDART_NAN;
+    if (s.hi == 0.0 && (f & 2)) return (AOP == 1) ? -0.0 : 0.0;
+    return s.hi;
+  }
   return (isinf(s.hi) || s.lo != s.lo) ? s.hi : s.value();
 }
 template <int AOP>
@@ -493,10 +558,18 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   }
   // kernel shape
   int shape, vec2 = 0, W = 32;
-  if (agg == SYSML_FUSED_AGG_ROWSUMS && cols > 1) {
+  int RW = 0;
+  if (agg == SYSML_FUSED_AGG_ROWSUMS && cols > 1 && cols <= 96 && getenv("SYSML_B200_FUSED_NO_NARROW") == nullptr) {
+    shape = 4;  // narrow: rows per warp = largest power of two with RW * cols <= 768 cells (6 KB per warp, 48 KB per CTA)
+    RW = 32;
+    while (RW > 1 && (i64)RW * cols > 768) RW >>= 1;
+  } else if (agg == SYSML_FUSED_AGG_ROWSUMS && cols > 1) {
     shape = 2;
-    W = 1;
-    while (W < 32 && 2 * W <= cols) W <<= 1;  // largest power of two <= cols
+    W = 1;  // lanes per row: ~8 cells per lane, so a warp covers several adjacent (contiguous) rows of a narrow matrix
+    if (const char* e = getenv("SYSML_B200_FUSED_ROW_LANES")) W = atoi(e);  // A/B switch for measurements
+    else
+      while (W < 32 && 8 * W < cols) W <<= 1;
+    if (W != 1 && W != 2 && W != 4 && W != 8 && W != 16 && W != 32) W = 32;
   } else if (agg == SYSML_FUSED_AGG_COLSUMS && rows > 1) {
     shape = 3;
   } else {
@@ -504,11 +577,11 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
     vec2 = (shape == 0 && aligned16 && (len % 2 == 0)) ? 1 : 0;
   }
   // row sums over one column / column sums over one row are the chain itself
-  const int kagg = (shape <= 1 && agg == SYSML_FUSED_AGG_SUM) ? 1 : (shape == 2 ? 2 : (shape == 3 ? 3 : 0));
+  const int kagg = (shape <= 1 && agg == SYSML_FUSED_AGG_SUM) ? 1 : ((shape == 2 || shape == 4) ? 2 : (shape == 3 ? 3 : 0));
 
   // ---- find or build the kernel ----
   std::string key;
-  appendf(key, "d%d|s%d|v%d|w%d|a%d|o%d|n%d|", ctx->device, shape, vec2, W, kagg, aop, n_inputs);
+  appendf(key, "d%d|s%d|v%d|w%d|a%d|o%d|n%d|c%lld|", ctx->device, shape, vec2, W, kagg, aop, n_inputs, shape == 4 ? (long long)cols : 0ll);
   for (int i = 0; i < n_inputs; i++) {
     const int kd = input_kinds[i];
     const bool full = kd == SYSML_BCAST_NONE || (kd == SYSML_BCAST_COL && cols == 1) || (kd == SYSML_BCAST_ROW && rows == 1);
@@ -530,8 +603,10 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
       std::string src = gen_defines();
       appendf(src, "#define FUSED_NIN %d\n#define FUSED_SHAPE %d\n#define FUSED_VEC2 %d\n#define FUSED_W %d\n#define FUSED_AGG %d\n#define FUSED_AOP %d\n",
               n_inputs, shape, vec2, W, kagg, aop);
+      appendf(src, "#define FUSED_COLS %d\n#define FUSED_RW %d\n", shape == 4 ? (int)cols : 1, shape == 4 ? RW : 1);
       // per-input loads: matrices stream past L1, broadcast vectors are cached reads
-      std::string flat = "#define FUSED_LOAD_FLAT(i) ", rc = "#define FUSED_LOAD_RC(i, r, c) ", l2 = "#define FUSED_LOAD2(i) ";
+      std::string flat = "#define FUSED_LOAD_FLAT(i) ", rc = "#define FUSED_LOAD_RC(i, r, c) ", rcy = "#define FUSED_LOAD_RC_Y(i, r, c) ",
+                  l2 = "#define FUSED_LOAD2(i) ";
       for (int i = 0; i < n_inputs; i++) {
         const int kd = input_kinds[i];
         const bool full = kd == SYSML_BCAST_NONE || (kd == SYSML_BCAST_COL && cols == 1) || (kd == SYSML_BCAST_ROW && rows == 1);
@@ -539,9 +614,12 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
         if (full) appendf(rc, "x[%d] = ld_stream(a.in[%d] + (i)); ", i, i);
         else if (kd == SYSML_BCAST_COL) appendf(rc, "x[%d] = __ldg(a.in[%d] + (r)); ", i, i);
         else appendf(rc, "x[%d] = __ldg(a.in[%d] + (c)); ", i, i);
+        if (full) appendf(rcy, "y[%d] = ld_stream(a.in[%d] + (i)); ", i, i);
+        else if (kd == SYSML_BCAST_COL) appendf(rcy, "y[%d] = __ldg(a.in[%d] + (r)); ", i, i);
+        else appendf(rcy, "y[%d] = __ldg(a.in[%d] + (c)); ", i, i);
         appendf(l2, "{ const double2 v_ = ld_stream2(reinterpret_cast<const double2*>(a.in[%d]) + (i)); x[%d] = v_.x; y[%d] = v_.y; } ", i, i, i);
       }
-      src += flat + "\n" + rc + "\n" + l2 + "\n";
+      src += flat + "\n" + rc + "\n" + rcy + "\n" + l2 + "\n";
       src += kOpsHeaderText;
       src += eval;
       src += kKernelTemplate;
@@ -586,6 +664,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   i64 grid;
   const i64 cap = (i64)ctx->sm_count * 8;
   if (shape == 2) grid = (rows + (256 / W) - 1) / (256 / W);
+  else if (shape == 4) grid = (rows + 8 * RW - 1) / (8 * RW);
   else if (shape == 3) grid = (rows + 7) / 8;
   else grid = ((vec2 ? len / 2 : len) + 255) / 256;
   if (grid > cap) grid = cap;

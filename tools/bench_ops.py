@@ -199,6 +199,16 @@ def main():
         report("fused_kmeans_assign_chain", [n, m], b, a, nbytes=16.0 * n * m + 8 * n + 8 * m)
         b, a = timeit(g, unfused2, args.reps)
         report("unfused_kmeans_assign_chain_3_launches", [n, m], b, a, nbytes=16.0 * n * m + 8 * n + 8 * m)
+        # row-wise endings on the same narrow matrix: rowSums(XC * Z') and rowMins(-2*XC + rv) in one pass each
+        rs = g.empty(n, 1)
+        g.call("sysml_b200_rand_uniform", p_(T), n * m, 9, 0, -1.0, 1.0)
+        f1 = fused_fn([XC, T], [0, 0], E.input(0) * E.input(1), (), n, m, 2, rs)
+        b, a = timeit(g, f1, args.reps)
+        report("fused_rowSums_of_product", [n, m], b, a, nbytes=16.0 * n * m + 8 * n)
+        f2 = fused_fn([XC, rv], [0, 2], E.const(0) * E.input(0) + E.input(1), (-2.0,), n, m, 5, rs)
+        b, a = timeit(g, f2, args.reps)
+        report("fused_rowMins_of_distance_chain", [n, m], b, a, nbytes=8.0 * n * m + 8 * n + 8 * m)
+        rs.free()
         for x in (XC, Z, T, rv, cv):
             x.free()
 
