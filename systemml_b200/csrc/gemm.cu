@@ -396,6 +396,55 @@ __device__ __forceinline__ void strip_edge_tile(const StripCtx<TA, TB, Cfg, BKT,
   }
 }
 
+// Small output (M <= 64, N <= 128: t(P) %*% X of Kmeans, 50 x 100): the whole product is one 64 x 128 tile and
+// every CTA a slice of the contraction.  Warp w owns fragment row w and the NF fragment columns that exist
+// (compile time); warps whose rows lie past M only keep the ring protocol going.  On a 50 x 100 output that is
+// 13 DMMAs per k-step and warp instead of the 16 of a 2 x 4 warp grid that cannot skip its padding.
+template <int NF, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __forceinline__ void strip_small_tile(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  constexpr int LDA = Cfg::LDA, LDB = Cfg::LDB;
+  constexpr int A_K4 = TA ? 4 * LDA : 4;
+  constexpr int B_NT = TB ? 8 * LDB : 8;
+  constexpr int B_K4 = TB ? 4 : 4 * LDB;
+  const int gid = c.lane >> 2, tig = c.lane & 3;
+  const int fa = c.warp;
+  const bool active = c.i0 + fa * 8 < c.M;
+  const int a_off = TA ? (tig * LDA + fa * 8 + gid) : ((fa * 8 + gid) * LDA + tig);
+  const int b_off = TB ? (gid * LDB + tig) : (tig * LDB + gid);
+  double acc[NF][2];
+#pragma unroll
+  for (int b = 0; b < NF; b++) acc[b][0] = acc[b][1] = 0.0;
+  for (int kb = 0; kb < c.nkb; kb++, it++) {
+    const int s = it % NST;
+    const uint32_t ph = (it / NST) & 1u;
+    mbar_wait(&c.full[s], ph);
+    if (active) {
+      const double* as = c.As + s * Cfg::A_ELEMS + a_off;
+      const double* bs = c.Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+      for (int k4 = 0; k4 < BKT / 4; k4++) {
+        const double a0 = as[k4 * A_K4];
+        double bf[NF];
+#pragma unroll
+        for (int b = 0; b < NF; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+        for (int b = 0; b < NF; b++) dmma884(acc[b][0], acc[b][1], a0, bf[b]);
+      }
+    }
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(&c.empty[s]);
+  }
+  const i64 r = c.i0 + fa * 8 + gid;
+  if (r < c.M) {
+#pragma unroll
+    for (int b = 0; b < NF; b++) {
+      const i64 j = c.j0 + b * 8 + 2 * tig;
+      if (j + 1 < c.N) *reinterpret_cast<double2*>(c.outp + r * c.N + j) = make_double2(acc[b][0], acc[b][1]);
+      else if (j < c.N) c.outp[r * c.N + j] = acc[b][0];
+    }
+  }
+}
+
 __device__ __forceinline__ void tile_coords(const GemmArgs& g, int t, int& ti, int& tj) {
   if (g.sym && g.diag_last) {  // strictly upper tiles row by row, then the diagonal (its ragged last tile first)
     const int T = g.tiles_n, noff = T * (T - 1) / 2;
@@ -542,13 +591,38 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
   int ti, tj;
   tile_coords(g, tile, ti, tj);
   const i64 i0 = (i64)ti * BM, j0 = (i64)tj * BN;
-  if constexpr (STRIP) {
+  if constexpr (STRIP && BM == 64) {
+    static_assert(!(STRIP && BM == 64) || (BN == 128 && WARPS_M * WARPS_N == 8), "small-output strip mapping: 64x128 tile, 8 warps");
+    double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
+    const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
+    const i64 ncols = (g.N - j0 < BN) ? g.N - j0 : BN;
+    switch ((int)((ncols + 7) / 8)) {
+      case 1: strip_small_tile<1>(sc, it); break;
+      case 2: strip_small_tile<2>(sc, it); break;
+      case 3: strip_small_tile<3>(sc, it); break;
+      case 4: strip_small_tile<4>(sc, it); break;
+      case 5: strip_small_tile<5>(sc, it); break;
+      case 6: strip_small_tile<6>(sc, it); break;
+      case 7: strip_small_tile<7>(sc, it); break;
+      case 8: strip_small_tile<8>(sc, it); break;
+      case 9: strip_small_tile<9>(sc, it); break;
+      case 10: strip_small_tile<10>(sc, it); break;
+      case 11: strip_small_tile<11>(sc, it); break;
+      case 12: strip_small_tile<12>(sc, it); break;
+      case 13: strip_small_tile<13>(sc, it); break;
+      case 14: strip_small_tile<14>(sc, it); break;
+      case 15: strip_small_tile<15>(sc, it); break;
+      default: strip_small_tile<16>(sc, it); break;
+    }
+    continue;
+  }
+  if constexpr (STRIP && BM == 128) {
     // Diagonal tiles of a symmetric product: only fragments on or right of the diagonal are needed.  The tile is
     // 16 x 16 fragments of 8x8; warp w takes fragment rows w and 15-w, which need 16-w and w+1 fragment columns:
     // 17 DMMAs per k-step for every warp instead of 32.  The column ranges are compile-time (one instantiation
     // per warp index): a predicated-off DMMA still occupies the tensor pipe (measured), and ptxas if-converts
     // short branches, so the skipped fragments must not exist in the code at all.
-    static_assert(!STRIP || (BM == 128 && BN == 128 && WARPS_M * WARPS_N == 8), "strip mapping is written for 128x128 tiles and 8 warps");
+    static_assert(!(STRIP && BM == 128) || (BN == 128 && WARPS_M * WARPS_N == 8), "strip mapping is written for 128x128 tiles and 8 warps");
     if (g.sym && ti == tj && i0 + BM <= g.M) {
       double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
       const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
@@ -790,7 +864,7 @@ int run_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64
 template <bool TA, bool TB>
 int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
                   int64_t* h_nnz) {
-  if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
+  if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4, BK, STAGES, TA ? 1 : 4, true>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   if (sym) return run_gemm<TA, TB, 128, 128, 2, 4, BK, STAGES, 1, true>(ctx, A, lda, B, ldb, C, M, N, K, true, h_nnz);
   if (N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, h_nnz);
   if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);

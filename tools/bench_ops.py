@@ -106,7 +106,8 @@ def main():
     # ---------------- dense matmult (C4 / C5 skinny right-hand sides) ----------------
     if want("matmult"):
         for (M, K, N, ta, tag) in ((int(1_000_000 * S), 5000, 20, 0, "C4_XV"), (int(1_000_000 * S), 5000, 20, 1, "C4_tXP"),
-                                   (int(10_000_000 * S), 100, 50, 0, "C5_XtC"), (int(10_000_000 * S), 100, 50, 1, "C5_tPX"),
+                                   (int(10_000_000 * S), 100, 50, 0, "C5_XtC"), (int(10_000_000 * S), 100, 50, 1, "C5_tXP_100x50"),
+                                   (int(10_000_000 * S), 50, 100, 1, "C5_tPX_50x100_kmeans"),
                                    (8192, 8192, 8192, 0, "square8k")):
             if ta:  # t(A) %*% B with A: M x K stored, B: M x N  -> K x N
                 A, B = g.rand(M, K, seed=1), g.rand(M, N, seed=2)
