@@ -804,14 +804,21 @@ int launch_csr_row(sysml_b200_ctx* ctx, const int* rp, const int* ci, const doub
   CsrStreamArgs sa{};
   bool stream = false;
   size_t stream_smem = 0;
-  int SL = 1;  // lanes per row in the streamed kernel: smallest power of two >= mean/4
+  int SL = 1;  // lanes per row in the streamed kernel
   int NC = 512;
   {
     const bool has_w = (MODE == 2) || (MODE == 1 && ct != SYSML_CHAIN_XtXv);
     const uintptr_t al = reinterpret_cast<uintptr_t>(rp) | reinterpret_cast<uintptr_t>(ci) | reinterpret_cast<uintptr_t>(va) |
                          (has_w ? reinterpret_cast<uintptr_t>(w) : 0);
     const double mean = (double)nnz / (double)rows;
-    while (SL < 32 && 4 * SL < mean) SL <<= 1;
+    // ~8 entries per lane for the gather / reduce modes, ~4 for the scatter modes (measured on 20M x 10k, ~10 per row:
+    // SpMV 0.55 -> 0.53 ms, rowSums 0.66 -> 0.46 ms with 2 lanes; t(X)y and mmchain are faster with 4)
+    const int per_lane = (MODE == 0 || MODE == 3) ? 8 : 4;
+    while (SL < 32 && per_lane * SL < mean) SL <<= 1;
+    if (const char* e = getenv("SYSML_B200_CSR_STREAM_LANES")) {  // A/B switch for measurements
+      const int v_ = atoi(e);
+      if (v_ == 1 || v_ == 2 || v_ == 4 || v_ == 8 || v_ == 16 || v_ == 32) SL = v_;
+    }
     if ((al & 15) == 0 && nnz >= (1 << 20) && rows >= (i64)(896 / SL) * ctx->sm_count && mean <= 256.0 &&
         getenv("SYSML_B200_CSR_NO_STREAM") == nullptr) {
       const size_t all = (size_t)ctx->max_smem_optin;
