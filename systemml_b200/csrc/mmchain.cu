@@ -47,7 +47,10 @@ struct StreamArgs {
 
 // NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
 // RG rows per thread-group per tile, STAGES-deep ring.  G = NTC/TC groups, R = G*RG rows per tile.
-template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES>
+// XSMEM (wide rows, 4096 < m <= 8192): a row no longer fits the consumers' registers next to its accumulators, so
+// the tile is read from shared memory in BOTH phases and v lives in shared memory too; the stage is released after
+// the second phase.  X is still read from HBM once.
+template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES, bool XSMEM = false>
 __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a) {
   constexpr int G = NTC / TC;
   constexpr int R = G * RG;
@@ -112,13 +115,19 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
   const int lane = tid & 31;
   const int wg = tt >> 5;
 
-  double vreg[CPT];
+  double vreg[XSMEM ? 1 : CPT];
   double c[CPT];
+  double* v_s = tiles + (size_t)STAGES * stage_elems + (size_t)STAGES * R;  // XSMEM only: v behind the w ring
 #pragma unroll
   for (int k = 0; k < CPT; k++) {
     const int j = tt + TC * k;
-    vreg[k] = (MODE != MODE_VM && j < m) ? a.v[j] : 0.0;
+    if (!XSMEM) vreg[k] = (MODE != MODE_VM && j < m) ? a.v[j] : 0.0;
     c[k] = 0.0;
+  }
+  if (XSMEM) {
+    if (MODE != MODE_VM)
+      for (int j = tid; j < m; j += NTC) v_s[j] = a.v[j];
+    named_bar_sync(1, NTC);
   }
 
   int it = 0;
@@ -146,13 +155,15 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
       for (int rr = 0; rr < RG; rr++) wv[rr] = ws[rr];
     }
 
-    double x[RG][CPT];
+    double x[XSMEM ? 1 : RG][XSMEM ? 1 : CPT];
+    if (!XSMEM) {
 #pragma unroll
-    for (int rr = 0; rr < RG; rr++) {
+      for (int rr = 0; rr < RG; rr++) {
 #pragma unroll
-      for (int k = 0; k < CPT; k++) {
-        const int j = tt + TC * k;
-        x[rr][k] = (j < m) ? T[rr * m + j] : 0.0;
+        for (int k = 0; k < CPT; k++) {
+          const int j = tt + TC * k;
+          x[rr][k] = (j < m) ? T[rr * m + j] : 0.0;
+        }
       }
     }
 
@@ -161,13 +172,21 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
 #pragma unroll
       for (int rr = 0; rr < RG; rr++) {
         double p = 0.0;
+        if (XSMEM) {
+#pragma unroll 8
+          for (int k = 0; k < CPT; k++) {
+            const int j = tt + TC * k;
+            if (j < m) p = fma(T[rr * m + j], v_s[j], p);
+          }
+        } else {
 #pragma unroll
-        for (int k = 0; k < CPT; k++) p = fma(x[rr][k], vreg[k], p);
+          for (int k = 0; k < CPT; k++) p = fma(x[rr][k], vreg[k], p);
+        }
         t[rr] = p;
       }
     }
     // every x value has been consumed (or, for VM, is ordered by the release below): free the stage
-    mbar_arrive(&empty[s]);
+    if (!XSMEM) mbar_arrive(&empty[s]);
 
     if (MODE != MODE_VM) {
 #pragma unroll
@@ -195,6 +214,7 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
         for (int rr = 0; rr < RG; rr++)
           if (r0 + rr < n) a.out[r0 + rr] = t[rr];
       }
+      if (XSMEM) mbar_arrive(&empty[s]);
       continue;
     }
     if (MODE == MODE_CHAIN) {
@@ -209,10 +229,22 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
 #pragma unroll
       for (int rr = 0; rr < RG; rr++) t[rr] = wv[rr];
     }
+    if (XSMEM) {
 #pragma unroll
-    for (int k = 0; k < CPT; k++) {
+      for (int k = 0; k < CPT; k++) {
+        const int j = tt + TC * k;
+        if (j < m) {
 #pragma unroll
-      for (int rr = 0; rr < RG; rr++) c[k] = fma(t[rr], x[rr][k], c[k]);
+          for (int rr = 0; rr < RG; rr++) c[k] = fma(t[rr], T[rr * m + j], c[k]);
+        }
+      }
+      mbar_arrive(&empty[s]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < CPT; k++) {
+#pragma unroll
+        for (int rr = 0; rr < RG; rr++) c[k] = fma(t[rr], x[rr][k], c[k]);
+      }
     }
   }
 
@@ -269,13 +301,13 @@ __global__ void __launch_bounds__(256) colpartial_reduce_kernel(const double* __
   }
 }
 
-template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES>
+template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES, bool XSMEM = false>
 int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   constexpr int G = NTC / TC;
   constexpr int R = G * RG;
   constexpr int NWG = TC / 32;
-  auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES>;
-  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8;
+  auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES, XSMEM>;
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8 + (XSMEM ? (size_t)a.m * 8 : 0);
   if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowstream: smem %zu too large", smem);
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   a.total_tiles = (a.n + R - 1) / R;
@@ -319,11 +351,16 @@ int launch_rowstream(sysml_b200_ctx* ctx, const StreamArgs& a) {
   if (m <= 1024) return launch_cfg<MODE, 128, 128, 8, 4, 3>(ctx, a, 2);
   if (m <= 2048) return launch_cfg<MODE, 256, 256, 8, 4, 3>(ctx, a, 1);
   if (m <= 4096) return launch_cfg<MODE, 256, 256, 16, 2, 3>(ctx, a, 1);
+  if constexpr (MODE == MODE_CHAIN) {
+    // wide rows: tile and v stay in shared memory, two stages of two rows (one row above 5600 columns)
+    if (m <= 5600) return launch_cfg<MODE, 256, 256, 22, 2, 2, true>(ctx, a, 1);
+    if (m <= 8192) return launch_cfg<MODE, 256, 256, 32, 1, 2, true>(ctx, a, 1);
+  }
   return SYSML_E_UNSUPPORTED;
 }
 
 // ------------------------------------------------------------------------------------------------
-// Wide-row fallbacks (m > 4096): X is read twice for mmchain (MV then VM).
+// Wide-row fallbacks (MV / VM above 4096 columns; mmchain above 8192, where X is read twice: MV then VM).
 // ------------------------------------------------------------------------------------------------
 // one warp per row, grid-stride over rows
 __global__ void mv_wide_kernel(const double* __restrict__ X, const double* __restrict__ v, double* __restrict__ out,
@@ -465,12 +502,12 @@ extern "C" int sysml_b200_mmchain_dense(sysml_b200_ctx* ctx, const double* X, co
     SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
     return SYSML_OK;
   }
-  if (m <= 4096) {
+  if (m <= 8192) {
     StreamArgs a{};
     a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type;
     return launch_rowstream<MODE_CHAIN>(ctx, a);
   }
-  // wide rows: t = X v ; t = w*t | t-w ; out = t(X) t   (X read twice)
+  // very wide rows (> 8192 columns): t = X v ; t = w*t | t-w ; out = t(X) t   (X read twice)
   void* ws = nullptr;
   const size_t tbytes = (((size_t)n * sizeof(double)) + 255) & ~(size_t)255;
   // reserve the partial area up front so the second workspace call cannot move the block
@@ -501,7 +538,7 @@ extern "C" int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b20
   if (rc) return rc;
   if (!comm) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_allreduce: null communicator");
   if (m == 0) return SYSML_OK;
-  if (m > 4096) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_allreduce: more than 4096 columns; run mmchain_dense then allreduce_sum");
+  if (m > 8192) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_allreduce: more than 8192 columns; run mmchain_dense then allreduce_sum");
   if (n == 0) {  // an empty shard still has to take part in the exchange
     SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
     return sysml_launch_allreduce_finish(ctx, comm, out, 1, (int)m, out, SYSML_REDUCE_SUM);

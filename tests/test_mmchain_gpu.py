@@ -44,7 +44,8 @@ def test_reference_mapmultchain_shapes(gctx, ct, sparsity):
 
 
 @pytest.mark.parametrize("n,m", [(1, 1), (2, 3), (7, 64), (24, 65), (25, 129), (1000, 100), (513, 257), (4099, 1000),
-                                 (300, 1025), (130, 2049), (70, 4096), (33, 5000), (64, 9001)])
+                                 (300, 1025), (130, 2049), (70, 4096), (33, 5000), (64, 9001), (3001, 4097), (2000, 5600), (1999, 5601),
+                                 (1500, 8192), (700, 8193)])
 @pytest.mark.parametrize("ct", [0, 1, 2])
 def test_ragged_shapes(gctx, n, m, ct):
     rng = np.random.default_rng(1000 * n + m + ct)
