@@ -351,16 +351,14 @@ int launch_rowstream(sysml_b200_ctx* ctx, const StreamArgs& a) {
   if (m <= 1024) return launch_cfg<MODE, 128, 128, 8, 4, 3>(ctx, a, 2);
   if (m <= 2048) return launch_cfg<MODE, 256, 256, 8, 4, 3>(ctx, a, 1);
   if (m <= 4096) return launch_cfg<MODE, 256, 256, 16, 2, 3>(ctx, a, 1);
-  if constexpr (MODE == MODE_CHAIN) {
-    // wide rows: tile and v stay in shared memory, two stages of two rows (one row above 5600 columns)
-    if (m <= 5600) return launch_cfg<MODE, 256, 256, 22, 2, 2, true>(ctx, a, 1);
-    if (m <= 8192) return launch_cfg<MODE, 256, 256, 32, 1, 2, true>(ctx, a, 1);
-  }
+  // wide rows: tile and v stay in shared memory, two stages of two rows (one row above 5600 columns)
+  if (m <= 5600) return launch_cfg<MODE, 256, 256, 22, 2, 2, true>(ctx, a, 1);
+  if (m <= 8192) return launch_cfg<MODE, 256, 256, 32, 1, 2, true>(ctx, a, 1);
   return SYSML_E_UNSUPPORTED;
 }
 
 // ------------------------------------------------------------------------------------------------
-// Wide-row fallbacks (MV / VM above 4096 columns; mmchain above 8192, where X is read twice: MV then VM).
+// Wide-row fallbacks (above 8192 columns; mmchain then reads X twice: MV then VM).
 // ------------------------------------------------------------------------------------------------
 // one warp per row, grid-stride over rows
 __global__ void mv_wide_kernel(const double* __restrict__ X, const double* __restrict__ v, double* __restrict__ out,
@@ -465,7 +463,7 @@ int sysml_reduce_partial_rows(sysml_b200_ctx* ctx, const double* partial, int P,
 
 // internal entry points used by matmult.cu as well
 int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m) {
-  if (m <= 4096) {
+  if (m <= 8192) {
     StreamArgs a{};
     a.X = X; a.v = v; a.w = nullptr; a.out = out; a.n = n; a.m = (int)m; a.ct = 0;
     return launch_rowstream<MODE_MV>(ctx, a);
@@ -474,7 +472,7 @@ int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double
 }
 
 int sysml_dense_vm(sysml_b200_ctx* ctx, const double* X, const double* y, double* out, i64 n, i64 m) {
-  if (m <= 4096) {
+  if (m <= 8192) {
     StreamArgs a{};
     a.X = X; a.v = nullptr; a.w = y; a.out = out; a.n = n; a.m = (int)m; a.ct = 0;
     return launch_rowstream<MODE_VM>(ctx, a);

@@ -143,7 +143,7 @@ def test_run_to_run_determinism(gctx):
     dX.free()
 
 
-@pytest.mark.parametrize("n,m", [(3471, 567), (1000, 1), (1, 1000), (257, 4097), (100_000, 100)])
+@pytest.mark.parametrize("n,m", [(3471, 567), (1000, 1), (1, 1000), (257, 4097), (100_000, 100), (1201, 5600), (999, 8192), (130, 8193)])
 def test_mv_and_vm(gctx, n, m):
     """X %*% v and t(X) %*% y (= t(t(y) %*% X)): matrixMultDenseDenseMVShortRHS / VM (LibMatrixMult.java:950-993)."""
     from systemml_b200 import LibMatrixB200 as L
