@@ -48,8 +48,8 @@ struct StreamArgs {
 // NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
 // RG rows per thread-group per tile, STAGES-deep ring.  G = NTC/TC groups, R = G*RG rows per tile.
 // XSMEM (wide rows, 4096 < m <= 8192): a row no longer fits the consumers' registers next to its accumulators, so
-// the tile is read from shared memory in BOTH phases and v lives in shared memory too; the stage is released after
-// the second phase.  X is still read from HBM once.
+// the tile is read from shared memory in BOTH phases (v and the accumulators stay in registers, one row per tile);
+// the stage is released after the second phase.  X is still read from HBM once.
 template <int MODE, int NTC, int TC, int CPT, int RG, int STAGES, bool XSMEM = false>
 __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a) {
   constexpr int G = NTC / TC;
@@ -115,19 +115,13 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
   const int lane = tid & 31;
   const int wg = tt >> 5;
 
-  double vreg[XSMEM ? 1 : CPT];
+  double vreg[CPT];
   double c[CPT];
-  double* v_s = tiles + (size_t)STAGES * stage_elems + (size_t)STAGES * R;  // XSMEM only: v behind the w ring
 #pragma unroll
   for (int k = 0; k < CPT; k++) {
     const int j = tt + TC * k;
-    if (!XSMEM) vreg[k] = (MODE != MODE_VM && j < m) ? a.v[j] : 0.0;
+    vreg[k] = (MODE != MODE_VM && j < m) ? a.v[j] : 0.0;
     c[k] = 0.0;
-  }
-  if (XSMEM) {
-    if (MODE != MODE_VM)
-      for (int j = tid; j < m; j += NTC) v_s[j] = a.v[j];
-    named_bar_sync(1, NTC);
   }
 
   int it = 0;
@@ -173,10 +167,10 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
       for (int rr = 0; rr < RG; rr++) {
         double p = 0.0;
         if (XSMEM) {
-#pragma unroll 8
+#pragma unroll
           for (int k = 0; k < CPT; k++) {
             const int j = tt + TC * k;
-            if (j < m) p = fma(T[rr * m + j], v_s[j], p);
+            if (j < m) p = fma(T[rr * m + j], vreg[k], p);
           }
         } else {
 #pragma unroll
@@ -307,7 +301,7 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   constexpr int R = G * RG;
   constexpr int NWG = TC / 32;
   auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES, XSMEM>;
-  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8 + (XSMEM ? (size_t)a.m * 8 : 0);
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8;
   if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowstream: smem %zu too large", smem);
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   a.total_tiles = (a.n + R - 1) / R;
@@ -351,9 +345,9 @@ int launch_rowstream(sysml_b200_ctx* ctx, const StreamArgs& a) {
   if (m <= 1024) return launch_cfg<MODE, 128, 128, 8, 4, 3>(ctx, a, 2);
   if (m <= 2048) return launch_cfg<MODE, 256, 256, 8, 4, 3>(ctx, a, 1);
   if (m <= 4096) return launch_cfg<MODE, 256, 256, 16, 2, 3>(ctx, a, 1);
-  // wide rows: tile and v stay in shared memory, two stages of two rows (one row above 5600 columns)
-  if (m <= 5600) return launch_cfg<MODE, 256, 256, 22, 2, 2, true>(ctx, a, 1);
-  if (m <= 8192) return launch_cfg<MODE, 256, 256, 32, 1, 2, true>(ctx, a, 1);
+  // wide rows: the tile stays in shared memory for both phases, one row per tile, 4 / 3 stages
+  if (m <= 5600) return launch_cfg<MODE, 256, 256, 22, 1, 4, true>(ctx, a, 1);
+  if (m <= 8192) return launch_cfg<MODE, 256, 256, 32, 1, 3, true>(ctx, a, 1);
   return SYSML_E_UNSUPPORTED;
 }
 
