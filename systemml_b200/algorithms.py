@@ -246,18 +246,22 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
         g.call("sysml_b200_matmult_dense", _p(X), _p(Cc), _p(XC), n, m, k, m, 0, 1)                 # X %*% t(C)
         g.call("sysml_b200_agg_unary_dense", _p(Cc), k, m, L.AGG_SUMSQ, L.DIR_ROW, _p(c2))           # rowSums(C^2)
         if fused:
+            # D is never written: every consumer re-evaluates -2*XC + t(c2) from XC on the fly
             d_e = E.const(0) * E.input(0) + E.input(1)
-            L.fusedCellwise(g, "spoof", [XC, c2_row], d_e, (-2.0,), out=D)
+            L.fusedCellwise(g, "spoof", [XC, c2_row], d_e, (-2.0,), "rowMins", out=minD)              # rowMins(D)
         else:
             g.call("sysml_b200_binary_ms", _p(XC), -2.0, _p(D), n * k, L.BINARY_OPS["*"], 1)
             g.call("sysml_b200_binary_mm", _p(D), _p(c2), _p(D), n, k, L.BCAST_ROW, L.BINARY_OPS["+"])
-        g.call("sysml_b200_agg_unary_dense", _p(D), n, k, L.AGG_MIN, L.DIR_ROW, _p(minD))            # rowMins(D)
+            g.call("sysml_b200_agg_unary_dense", _p(D), n, k, L.AGG_MIN, L.DIR_ROW, _p(minD))        # rowMins(D)
         g.call("sysml_b200_agg_unary_dense", _p(minD), n, 1, L.AGG_SUM, L.DIR_ALL, _p(s1))
         wcss_old, wcss = wcss, sumXsq + _scalar(g, s1)
         if fused:
-            le = E.input(0).binary(E.input(1), "<=")
-            L.fusedCellwise(g, "spoof", [D, minD], le, (), "rowSums", out=rs)
-            L.fusedCellwise(g, "spoof", [D, minD, rs], le / E.input(2), out=P)
+            le = d_e.binary(E.input(2), "<=")                                                       # D <= minD
+            L.fusedCellwise(g, "spoof", [XC, c2_row, minD], le, (-2.0,), "rowSums", out=rs)
+            # P / rowSums(P) with P in {0, 1}: 1/rs once per row, then a product per cell -- the same bits as the
+            # script's division (0/rs = 0*(1/rs) = 0, 1/rs = 1*(1/rs)) at a fraction of its cost
+            g.call("sysml_b200_binary_ms", _p(rs), 1.0, _p(rs), n, L.BINARY_OPS["/"], 1)
+            L.fusedCellwise(g, "spoof", [XC, c2_row, minD, rs], le * E.input(3), (-2.0,), out=P)
         else:
             g.call("sysml_b200_binary_mm", _p(D), _p(minD), _p(P), n, k, L.BCAST_COL, L.BINARY_OPS["<="])
             g.call("sysml_b200_agg_unary_dense", _p(P), n, k, L.AGG_SUM, L.DIR_ROW, _p(rs))
