@@ -18,6 +18,8 @@
 // Algorithmic flops: tsmm n*m*(m+1); matmult 2*M*N*K.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 int sysml_dense_mv(sysml_b200_ctx* ctx, const double* X, const double* v, double* out, i64 n, i64 m);
@@ -667,14 +669,15 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
   for (int a = 0; a < MT; a++)
 #pragma unroll
     for (int b = 0; b < NTL; b++) acc[a][b][0] = acc[a][b][1] = 0.0;
-  for (int kb = 0; kb < nkb; kb++, it++) {
+  // one k block: wait for its stage, run n4 k4-steps (all BKT/4 of them unrolled, or only those of a ragged last
+  // block that hold data -- K = 100: 1 of 4 -- the rest of the stage is zeros), release the stage
+  auto k_block = [&](auto full_block, int n4) {
     const int s = it % NST;
     const uint32_t ph = (it / NST) & 1u;
     mbar_wait(&full[s], ph);
     const double* as = As + s * Cfg::A_ELEMS + a_off;
     const double* bs = Bs + s * Cfg::B_ELEMS + b_off;
-#pragma unroll
-    for (int k4 = 0; k4 < BKT / 4; k4++) {
+    auto k4_step = [&](int k4) {
       double af[MT], bf[NTL];
 #pragma unroll
       for (int a = 0; a < MT; a++) af[a] = as[k4 * A_K4 + a * A_MT];
@@ -684,9 +687,46 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
       for (int a = 0; a < MT; a++)
 #pragma unroll
         for (int b = 0; b < NTL; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+    };
+    if constexpr (decltype(full_block)::value) {
+#pragma unroll
+      for (int k4 = 0; k4 < BKT / 4; k4++) k4_step(k4);
+    } else {
+#pragma unroll 1
+      for (int k4 = 0; k4 < n4; k4++) k4_step(k4);
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&empty[s]);
+    it++;
+  };
+  const int nfull = (int)((kend - kbeg) / BKT);
+  if (nfull == nkb) {
+    // the common case keeps the plain loop (measured: routing it through the helper above costs tsmm 0.4 % and
+    // t(X)%*%P 4 %)
+    for (int kb = 0; kb < nkb; kb++, it++) {
+      const int s = it % NST;
+      const uint32_t ph = (it / NST) & 1u;
+      mbar_wait(&full[s], ph);
+      const double* as = As + s * Cfg::A_ELEMS + a_off;
+      const double* bs = Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+      for (int k4 = 0; k4 < BKT / 4; k4++) {
+        double af[MT], bf[NTL];
+#pragma unroll
+        for (int a = 0; a < MT; a++) af[a] = as[k4 * A_K4 + a * A_MT];
+#pragma unroll
+        for (int b = 0; b < NTL; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+        for (int a = 0; a < MT; a++)
+#pragma unroll
+          for (int b = 0; b < NTL; b++) dmma884(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+    }
+  } else {
+    for (int kb = 0; kb < nfull; kb++) k_block(std::true_type{}, 0);
+    k_block(std::false_type{}, (int)((kend - kbeg - (i64)nfull * BKT + 3) / 4));
   }
 
   double* outp = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
