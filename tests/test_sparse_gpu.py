@@ -257,3 +257,27 @@ def test_sparse_sparse_matmult_sparse_output(gctx, m, k, n, spa, spb):
     dAi, _ = _csr(gctx, Ai)
     dBi, _ = _csr(gctx, Bi)
     _check_csr(L.sparseSparseMatmult(gctx, "ba+*", dAi, dBi), Ai @ Bi)
+
+
+def test_sparse_output_edge_cases(gctx):
+    """Empty operands, empty results and the product-count limit of the CSR-result operations."""
+    from systemml_b200 import LibMatrixB200 as L, native
+    Z = np.zeros((40, 30))
+    A = O.java_test_matrix(40, 30, -1, 1, 0.2, 3)
+    dZ, _ = _csr(gctx, Z)
+    dA, _ = _csr(gctx, A)
+    _check_csr(L.sparseTranspose(gctx, "r'", dZ), Z.T.copy())
+    _check_csr(L.sparseSparseAdd(gctx, "+", dZ, dZ), Z)
+    _check_csr(L.sparseSparseAdd(gctx, "+", dA, dZ), A)
+    _check_csr(L.sparseSparseAdd(gctx, "-", dA, dA, 1.0, -1.0), Z)          # everything cancels: nnz 0, no arrays
+    dAt = L.sparseTranspose(gctx, "r'", dA)
+    _check_csr(L.sparseSparseMatmult(gctx, "ba+*", dZ, dAt), np.zeros((40, 40)))
+    _check_csr(L.sparseSparseMatmult(gctx, "ba+*", dA, dAt), _ref_sparse_sparse(A, np.ascontiguousarray(A.T)))
+    with pytest.raises(native.NativeError):                                     # inner dimensions
+        L.sparseSparseMatmult(gctx, "ba+*", dA, dA)
+    with pytest.raises(native.NativeError):
+        L.sparseSparseAdd(gctx, "+", dA, dAt)
+    # t(t(A)) == A exactly
+    rp, ci, va = L.sparseTranspose(gctx, "r'", dAt).to_host()
+    rp0, ci0, va0 = dA.to_host()
+    assert np.array_equal(rp, rp0) and np.array_equal(ci, ci0) and np.array_equal(va, va0)
