@@ -234,7 +234,8 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
     n, m, k = X.rows, X.cols, C0.rows
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
-    Cc, Cn, XC, D, P = alloc(k, m), alloc(k, m), alloc(n, k), alloc(n, k), alloc(n, k)
+    Cc, Cn, XC, P = alloc(k, m), alloc(k, m), alloc(n, k), alloc(n, k)
+    D = None if fused else alloc(n, k)   # the fused plan never materialises D
     c2, minD, rs, den, s1 = alloc(k, 1), alloc(n, 1), alloc(n, 1), alloc(k, 1), alloc(1, 1)
     g.call("sysml_b200_d2d", _p(Cc), _p(C0), 8 * k * m)
     g.call("sysml_b200_agg_unary_dense", _p(X), n, m, L.AGG_SUMSQ, L.DIR_ALL, _p(s1))
@@ -282,7 +283,8 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
             Cc, Cn = Cn, Cc
     out = Cc.to_host()
     for o in (Cc, Cn, XC, D, P, c2, minD, rs, den, s1):
-        o.free()
+        if o is not None:
+            o.free()
     return out, it, wcss, term
 
 
