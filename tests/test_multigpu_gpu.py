@@ -69,6 +69,23 @@ def _worker(rank, world, port, n, m, out_dir):
     g.call("sysml_b200_agg_unary_dense", C.c_void_p(Xs.ptr), r1 - r0, 160, 0, 0, C.c_void_p(sm.ptr))
     comm2.allreduce(sm.ptr, 1, "sum")
     res["sum"] = sm.to_host().reshape(-1)
+    # the workloads themselves, row-sharded: LinearRegCG and GLM Poisson/log (north_star: end to end on 1-8 GPUs)
+    from systemml_b200.algorithms import glm_poisson_log, linreg_cg
+    na, ma = 60_000, 200
+    a0, a1 = row_shard(na, world, rank)
+    Xa = g.rand(a1 - a0, ma, seed=40, offset=a0 * ma)
+    wt = g.rand(ma, 1, seed=41)
+    ya = g.empty(a1 - a0, 1)
+    g.call("sysml_b200_matmult_dense", C.c_void_p(Xa.ptr), C.c_void_p(wt.ptr), C.c_void_p(ya.ptr), a1 - a0, ma, ma, 1, 0, 0)
+    nz = g.rand(a1 - a0, 1, seed=42, offset=a0)
+    g.call("sysml_b200_axpy", C.c_void_p(ya.ptr), C.c_void_p(nz.ptr), 0.1, C.c_void_p(ya.ptr), a1 - a0, 1, 0)
+    beta, its = linreg_cg(g, Xa, ya, reg=0.01, tol=1e-4, comm=comm)
+    res["linreg_beta"], res["linreg_its"] = beta, np.array([its])
+    bt = g.rand(ma, 1, seed=43, lo=-0.05, hi=0.05)
+    g.call("sysml_b200_matmult_dense", C.c_void_p(Xa.ptr), C.c_void_p(bt.ptr), C.c_void_p(ya.ptr), a1 - a0, ma, ma, 1, 0, 0)
+    g.call("sysml_b200_unary", C.c_void_p(ya.ptr), C.c_void_p(ya.ptr), a1 - a0, 0)      # y = exp(X b): noiseless Poisson means
+    gb, inner = glm_poisson_log(g, Xa, ya, reg=0.0, outer_iters=4, inner_iters=20, inner_tol=1e-8, comm=comm)
+    res["glm_beta"], res["glm_inner"] = gb, np.array(inner)
     big = g.rand(200_000, 1, seed=30 + rank)                            # longer than the mailbox: goes in pieces
     comm2.allreduce(big.ptr, 200_000, "sum")
     res["big"] = big.to_host().reshape(-1)
@@ -109,6 +126,19 @@ def test_fused_allreduce_mmchain_two_gpus(tmp_path):
     assert np.array_equal(r[0]["uacmax"], Xs.max(axis=0)) and np.array_equal(r[0]["uacmin"], Xs.min(axis=0))
     assert abs(r[0]["sum"][0] - float(np.sum(Xs.astype(np.longdouble)))) < 1e-9 * n
     assert np.array_equal(r[0]["big"], O.rand_uniform(200_000, seed=30) + O.rand_uniform(200_000, seed=31))
+    # sharded workloads: identical on both ranks, equal to the single-process CPU twins (oracle kernels)
+    from tests.test_algorithms_gpu import cpu_glm_poisson_log, cpu_linreg_cg
+    na, ma = 60_000, 200
+    Xa = O.rand_uniform(na * ma, seed=40).reshape(na, ma)
+    ya = Xa @ O.rand_uniform(ma, seed=41) + 0.1 * O.rand_uniform(na, seed=42)
+    eb, eits = cpu_linreg_cg(Xa, ya, 0.01, 1e-4, 0, O.num_threads())
+    assert np.array_equal(r[0]["linreg_beta"], r[1]["linreg_beta"]) and int(r[0]["linreg_its"][0]) == eits
+    assert_close = lambda e, a, rel: np.max(np.abs(e - a)) <= rel * np.max(np.abs(e))
+    assert assert_close(eb, r[0]["linreg_beta"], 1e-9)
+    yg = np.exp(Xa @ O.rand_uniform(ma, seed=43, lo=-0.05, hi=0.05))
+    egb = cpu_glm_poisson_log(Xa, yg, 0.0, 4, 20, 1e-8, O.num_threads())
+    assert np.array_equal(r[0]["glm_beta"], r[1]["glm_beta"]) and np.array_equal(r[0]["glm_inner"], r[1]["glm_inner"])
+    assert assert_close(egb, r[0]["glm_beta"], 1e-8)
     exp_cs = O.agg_unary_dense(X, O.SUM, O.COL, 4)
     assert np.array_equal(r[0]["cs"], r[1]["cs"])
     assert np.max(np.abs(r[0]["cs"] - exp_cs)) < 1e-9 * np.max(np.abs(exp_cs)) + 1e-9
