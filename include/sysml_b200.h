@@ -369,7 +369,7 @@ int sysml_b200_allreduce_sum(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double*
 #define SYSML_REDUCE_MAX 1
 #define SYSML_REDUCE_MIN 2
 int sysml_b200_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf, int64_t len, int op);
-/* mmchain on the local row shard fused with the sum over ranks (m <= 4096). */
+/* mmchain on the local row shard fused with the sum over ranks (m <= 8192). */
 int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X,
                                        const double* v, const double* w, double* out, int64_t n,
                                        int64_t m, int chain_type);
