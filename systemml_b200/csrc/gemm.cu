@@ -346,6 +346,89 @@ __device__ __forceinline__ void strip_tile(const StripCtx<TA, TB, Cfg, BKT, NST>
   }
 }
 
+// Ragged DIAGONAL tile of a symmetric product (the last one of m = 1000, or the only one of m <= 128): NF x NF
+// fragments exist and only those on or right of the diagonal are needed.  Fragment rows are paired (w, NF-1-w):
+// NF+1 fragments per pair, a middle row alone when NF is odd, warps beyond the pairs only keep the ring going.
+// R0 / R1 / NF are compile-time (R1 < 0: single row, R0 < 0: idle warp).
+template <int R0, int R1, int NF, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __noinline__ void strip_tri_tile(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  constexpr int LDA = Cfg::LDA, LDB = Cfg::LDB;
+  constexpr int A_K4 = TA ? 4 * LDA : 4;
+  constexpr int B_NT = TB ? 8 * LDB : 8;
+  constexpr int B_K4 = TB ? 4 : 4 * LDB;
+  constexpr int LO = R0 < 0 ? 0 : R0, L1 = R1 < 0 ? 0 : R1;
+  const int gid = c.lane >> 2, tig = c.lane & 3;
+  const int a_off0 = TA ? (tig * LDA + LO * 8 + gid) : ((LO * 8 + gid) * LDA + tig);
+  const int a_off1 = TA ? (tig * LDA + L1 * 8 + gid) : ((L1 * 8 + gid) * LDA + tig);
+  const int b_off = TB ? (gid * LDB + tig) : (tig * LDB + gid);
+  double acc0[16][2], acc1[16][2];
+#pragma unroll
+  for (int b = 0; b < 16; b++) acc0[b][0] = acc0[b][1] = acc1[b][0] = acc1[b][1] = 0.0;
+  for (int kb = 0; kb < c.nkb; kb++, it++) {
+    const int s = it % NST;
+    const uint32_t ph = (it / NST) & 1u;
+    mbar_wait(&c.full[s], ph);
+    if constexpr (R0 >= 0) {
+      const double* as = c.As + s * Cfg::A_ELEMS;
+      const double* bs = c.Bs + s * Cfg::B_ELEMS + b_off;
+#pragma unroll
+      for (int k4 = 0; k4 < BKT / 4; k4++) {
+        const double a0 = as[k4 * A_K4 + a_off0];
+        double a1 = 0.0;
+        if constexpr (R1 >= 0) a1 = as[k4 * A_K4 + a_off1];
+        double bf[16];
+#pragma unroll
+        for (int b = R0; b < NF; b++) bf[b] = bs[k4 * B_K4 + b * B_NT];
+#pragma unroll
+        for (int b = R0; b < NF; b++) {
+          dmma884(acc0[b][0], acc0[b][1], a0, bf[b]);
+          if constexpr (R1 >= 0)
+            if (b >= R1) dmma884(acc1[b][0], acc1[b][1], a1, bf[b]);
+        }
+      }
+    }
+    __syncwarp();
+    if (c.lane == 0) mbar_arrive(&c.empty[s]);
+  }
+  if constexpr (R0 >= 0) {
+    const i64 r0 = c.i0 + R0 * 8 + gid, r1 = c.i0 + L1 * 8 + gid;
+#pragma unroll
+    for (int b = R0; b < NF; b++) {
+      const i64 j = c.j0 + b * 8 + 2 * tig;
+      if (r0 < c.M) {
+        if (j + 1 < c.N) *reinterpret_cast<double2*>(c.outp + r0 * c.N + j) = make_double2(acc0[b][0], acc0[b][1]);
+        else if (j < c.N) c.outp[r0 * c.N + j] = acc0[b][0];
+      }
+      if constexpr (R1 >= 0) {
+        if (b >= R1 && r1 < c.M) {
+          if (j + 1 < c.N) *reinterpret_cast<double2*>(c.outp + r1 * c.N + j) = make_double2(acc1[b][0], acc1[b][1]);
+          else if (j < c.N) c.outp[r1 * c.N + j] = acc1[b][0];
+        }
+      }
+    }
+  }
+}
+template <int W, int NF, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __forceinline__ void strip_tri_warp(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  constexpr int P = NF - 1 - W;  // partner row
+  if constexpr (W < P) strip_tri_tile<W, P, NF>(c, it);
+  else if constexpr (W == P) strip_tri_tile<W, -1, NF>(c, it);
+  else strip_tri_tile<-1, -1, NF>(c, it);
+}
+template <int NF, bool TA, bool TB, class Cfg, int BKT, int NST>
+__device__ __forceinline__ void strip_tri_dispatch(const StripCtx<TA, TB, Cfg, BKT, NST>& c, uint32_t& it) {
+  switch (c.warp) {
+    case 0: strip_tri_warp<0, NF>(c, it); break;
+    case 1: strip_tri_warp<1, NF>(c, it); break;
+    case 2: strip_tri_warp<2, NF>(c, it); break;
+    case 3: strip_tri_warp<3, NF>(c, it); break;
+    case 4: strip_tri_warp<4, NF>(c, it); break;
+    case 5: strip_tri_warp<5, NF>(c, it); break;
+    case 6: strip_tri_warp<6, NF>(c, it); break;
+    default: strip_tri_warp<7, NF>(c, it); break;
+  }
+}
+
 // Off-diagonal tile that hangs over the right edge of the matrix: only NF of the 16 fragment columns exist
 // (m = 1000: 13; m = 5000: 1).  Same strip mapping -- warp w owns fragment rows w and 15-w -- with the column
 // count a compile-time constant, so the missing fragments cost neither DMMAs nor registers.
@@ -640,6 +723,28 @@ __global__ void __launch_bounds__((WARPS_M * WARPS_N + NPW) * 32,
       }
       continue;
     }
+    if (g.sym && ti == tj && i0 + BM > g.M) {  // ragged diagonal tile
+      double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
+      const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
+      switch ((int)((g.N - j0 + 7) / 8)) {
+        case 1: strip_tri_dispatch<1>(sc, it); break;
+        case 2: strip_tri_dispatch<2>(sc, it); break;
+        case 3: strip_tri_dispatch<3>(sc, it); break;
+        case 4: strip_tri_dispatch<4>(sc, it); break;
+        case 5: strip_tri_dispatch<5>(sc, it); break;
+        case 6: strip_tri_dispatch<6>(sc, it); break;
+        case 7: strip_tri_dispatch<7>(sc, it); break;
+        case 8: strip_tri_dispatch<8>(sc, it); break;
+        case 9: strip_tri_dispatch<9>(sc, it); break;
+        case 10: strip_tri_dispatch<10>(sc, it); break;
+        case 11: strip_tri_dispatch<11>(sc, it); break;
+        case 12: strip_tri_dispatch<12>(sc, it); break;
+        case 13: strip_tri_dispatch<13>(sc, it); break;
+        case 14: strip_tri_dispatch<14>(sc, it); break;
+        default: strip_tri_dispatch<15>(sc, it); break;
+      }
+      continue;
+    }
     if (g.sym && ti != tj && i0 + BM <= g.M && j0 + BN > g.N) {  // last tile column of a ragged matrix
       double* outd = g.out + (size_t)split * (size_t)g.M * (size_t)g.N;
       const StripCtx<TA, TB, Cfg, BKT, NST> sc{As, Bs, full, empty, outd, g.M, g.N, i0, j0, nkb, lane, warp};
@@ -905,7 +1010,12 @@ template <bool TA, bool TB>
 int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B, i64 ldb, double* C, i64 M, i64 N, i64 K, bool sym,
                   int64_t* h_nnz) {
   if (!sym && N > 64 && M <= 64) return run_gemm<TA, TB, 64, 128, 2, 4, BK, STAGES, TA ? 1 : 4, true>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
-  if (sym) return run_gemm<TA, TB, 128, 128, 2, 4, BK, STAGES, 1, true>(ctx, A, lda, B, ldb, C, M, N, K, true, h_nnz);
+  if (sym) {
+    // tsmm is t(X)%*%X (TA, !TB) or X%*%t(X) (!TA, TB): only those two get the strip-mapped kernel (its per-warp,
+    // per-fragment-count instantiations are the bulk of this file's compile time)
+    if constexpr (TA != TB) return run_gemm<TA, TB, 128, 128, 2, 4, BK, STAGES, 1, true>(ctx, A, lda, B, ldb, C, M, N, K, true, h_nnz);
+    else return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, true, h_nnz);
+  }
   if (N > 64) return run_gemm<TA, TB, 128, 128, 2, 4>(ctx, A, lda, B, ldb, C, M, N, K, false, h_nnz);
   if (M <= 128 && N > 32) return run_gemm<TA, TB, 128, 64, 4, 2>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
   // K-contiguous A (no bulk copies possible): one producer warp cannot keep enough cp.async in flight
