@@ -76,6 +76,63 @@ def alg_bytes_mmchain(n, m, weighted=True):
     return 8.0 * n * m + 16.0 * m + (8.0 * n if weighted else 0.0)
 
 
+def host_memory_bytes():
+    """(MemTotal, MemAvailable) of the host, clamped by the cgroup limit when there is one."""
+    tot = avail = None
+    try:
+        for l in open("/proc/meminfo"):
+            if l.startswith("MemTotal:"):
+                tot = int(l.split()[1]) * 1024
+            elif l.startswith("MemAvailable:"):
+                avail = int(l.split()[1]) * 1024
+    except OSError:
+        pass
+    for f in ("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory/memory.limit_in_bytes"):
+        try:
+            v = open(f).read().strip()
+            if v.isdigit() and int(v) < (1 << 60):
+                tot = min(tot, int(v)) if tot else int(v)
+                avail = min(avail, int(v)) if avail else int(v)
+        except OSError:
+            pass
+    return tot or (8 << 30), avail or (4 << 30)
+
+
+def reference_arm_rows(n, m):
+    """Rows of X the CPU arm (--impl reference) holds in host memory: the whole matrix when it fits in 60 % of the
+    host's RAM, else the largest whole number of million-row blocks that does (never more than half of what is
+    available right now).  Both arms compute it the same way and print it in `config`."""
+    tot, avail = host_memory_bytes()
+    budget = min(0.6 * tot, 0.5 * avail if 8.0 * n * m > 0.6 * tot else 0.9 * avail)
+    rows = int(budget // (8 * m))
+    if rows >= n:
+        return n
+    if rows >= 1_000_000:
+        rows -= rows % 1_000_000
+    return max(min(rows, n), 1)
+
+
+def make_config(args, world):
+    """The `config` object: identical in the b200 and reference arms for the same command-line arguments."""
+    n, m = args.rows, args.cols
+    # rows of rank 0's shard (systemml_b200.sharding.row_shard; restated so the reference arm imports nothing of the product)
+    nblocks = (n + 999) // 1000
+    r0, r1 = 0, min((nblocks // world + (1 if nblocks % world else 0)) * 1000, n)
+    ref_rows = reference_arm_rows(n, m)
+    coll = "none" if world == 1 else ("fused into the mmchain finishing kernel over NVLink peer memory" if args.collective == "fused" else "NCCL")
+    return {
+        "workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1]), row-sharded %d x %d rows/GPU"
+                    % (n, m, world, r1 - r0),
+        "rows": n, "cols": m,
+        "parallelism": "row-shard x%d + all-reduce(m doubles) [%s]" % (world, coll),
+        "l2": "inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush needed" % (8.0 * (r1 - r0) * m / 1e9),
+        "x_distribution": "U(-1,1) counter-based generator, seed 1",
+        "reference_arm": "CPU restatement of LibMatrixMult.matrixMultChain (oracle/) on every host CPU of this process's affinity mask; the JVM reference cannot run in this image",
+        "reference_arm_sample_rows": ref_rows,
+        "reference_arm_extrapolated": ref_rows < n,
+    }
+
+
 # --------------------------------------------------------------------------------------------------
 # clocks / throttle sampling during the timed region (pynvml, falls back to nvidia-smi)
 # --------------------------------------------------------------------------------------------------
@@ -108,7 +165,7 @@ class ClockSampler:
                 for bit, nm in names.items():
                     if r & bit:
                         self.reasons.add(nm)
-                time.sleep(0.02)
+                time.sleep(0.004)
         except Exception:
             try:
                 out = subprocess.check_output(["nvidia-smi", "-i", str(self.index), "--query-gpu=clocks.sm,clocks.max.sm",
@@ -135,13 +192,14 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the oracle's mmchain (restatement of LibMatrixMult.matrixMultChain) on a bounded sample
 # --------------------------------------------------------------------------------------------------
-def cpu_cg_iterations(n_total, m, target_seconds=12.0, max_rows=2_000_000, steps=None):
-    """Times CG iterations (mmchain XtwXv + m-vector algebra) on the host cores on the first `rows` rows of the
-    same synthetic X; returns (iters/s scaled to n_total rows, cores, sample description, seconds per sample iter)."""
+def cpu_cg_iterations(n_total, m, rows, steps=None, warmup=1, target_seconds=12.0):
+    """Times CG iterations (mmchain XtwXv + m-vector algebra) with the oracle on every host CPU this process may use, on
+    the first `rows` rows of the same synthetic X.  Returns a dict: iters/s scaled to n_total rows, threads, physical
+    cores, sample description, median seconds per sample iteration."""
     import numpy as np
     from oracle import oracle as O
-    k = O.num_threads()
-    rows = min(max_rows, n_total)
+    k = O.use_all_host_threads()   # not OMP_NUM_THREADS: torchrun exports 1 to every rank
+    logical, physical = O.host_cpus()
     X = O.rand_uniform(rows * m, seed=1).reshape(rows, m)
     w = O.rand_uniform(rows, seed=4, lo=0.0, hi=1.0)
     p = O.rand_uniform(m, seed=2)
@@ -149,8 +207,10 @@ def cpu_cg_iterations(n_total, m, target_seconds=12.0, max_rows=2_000_000, steps
     beta = np.zeros(m)
     nr2 = float(r @ r)
     t0 = time.perf_counter()
-    O.mmchain_dense(X, p, w, O.XtwXv, k)  # warm-up (page faults, thread pool)
+    O.mmchain_dense(X, p, w, O.XtwXv, k)  # first touch (page faults, thread pool)
     warm = time.perf_counter() - t0
+    for _ in range(max(warmup - 1, 0)):
+        O.mmchain_dense(X, p, w, O.XtwXv, k)
     reps = steps if steps else max(3, min(50, int(target_seconds / max(warm, 1e-3))))
     times = []
     for _ in range(reps):
@@ -168,11 +228,23 @@ def cpu_cg_iterations(n_total, m, target_seconds=12.0, max_rows=2_000_000, steps
             p = O.rand_uniform(m, seed=2)
             r = -p.copy()
             nr2 = float(r @ r)
+    mean = sum(times) / len(times)
     times.sort()
     med = times[len(times) // 2]
-    scaled = (rows / float(n_total)) / med
-    sample = "first %d of %d rows x %d cols, %d timed iterations, median; scaled to the full row count" % (rows, n_total, m, reps)
-    return scaled, k, sample, med, rows
+    if rows == n_total:
+        sample = "all %d rows x %d cols, %d timed iterations (mean)" % (rows, m, reps)
+        per_iter = mean
+    else:
+        sample = "first %d of %d rows x %d cols, %d timed iterations (median), scaled to the full row count" % (rows, n_total, m, reps)
+        per_iter = med * (n_total / float(rows))
+    return {"value": 1.0 / per_iter, "threads": k, "physical_cores": physical, "sample": sample, "sample_rows": rows,
+            "seconds_per_sample_iteration": med, "sample_gbs": alg_bytes_mmchain(rows, m) / med / 1e9}
+
+
+def cpu_baseline_block(c):
+    return {"value": c["value"], "unit": UNIT, "cores": c["threads"], "physical_cores": c["physical_cores"],
+            "threads_are": "logical CPUs in the affinity mask (SMT siblings included when physical_cores < cores)",
+            "kind": "port", "sample": c["sample"], "sample_rows": c["sample_rows"], "sample_gbs": c["sample_gbs"]}
 
 
 def run_reference_arm(args):
@@ -180,15 +252,16 @@ def run_reference_arm(args):
     if rank != 0:
         return 0
     t_start = time.perf_counter()
-    val, cores, sample, med, rows = cpu_cg_iterations(args.rows, args.cols, steps=max(args.steps, 1) + 0, max_rows=1_000_000)
+    cfg = make_config(args, max(args.gpus, 1))
+    rows = cfg["reference_arm_sample_rows"]
+    c = cpu_cg_iterations(args.rows, args.cols, rows, steps=max(args.steps, 1), warmup=max(args.warmup, 1))
+    val = c["value"]
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1000.0 / val if val > 0 else None, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1])" % (args.rows, args.cols),
-                   "arm": "CPU restatement of LibMatrixMult.matrixMultChain (oracle/, k = all host threads); the JVM reference cannot run here"},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                         "sample_gbs": alg_bytes_mmchain(rows, args.cols) / med / 1e9},
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+        "extrapolated": rows < args.rows, "ms_per_step_on_sample": 1000.0 * c["seconds_per_sample_iteration"],
+        "cpu_baseline": cpu_baseline_block(c),
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.perf_counter() - t_start,
     }
@@ -322,6 +395,45 @@ def main():
     value = 1000.0 / ms_per_step
     finite = bool(torch.isfinite(vecs["beta"]).all().item())
 
+    # ---------------- parity, outside every timed region ----------------
+    # (a) the fused exchange against the plain plan "local mmchain, then NCCL all-reduce" on the same p: the sum the
+    #     reference trusts is RDDAggregateUtils.sumStable (J/runtime/instructions/spark/utils/RDDAggregateUtils.java:58-70);
+    # (b) every rank must hold the same bits (the sharded algorithms branch on these values);
+    # (c) rank 0: the sub-result of the first 100k rows of its shard against the CPU oracle, element-wise relative
+    #     (GPUTests.assertEqualMatrices, src/test/java/org/apache/sysml/test/gpu/GPUTests.java:254-302).
+    parity = {"tolerance_rel": 1e-9}
+    g.call("sysml_b200_rand_uniform", p_(P), m, 77, 0, -1.0, 1.0)
+    if world > 1:
+        g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+        q_nccl = vecs["q"].clone()
+        dist.all_reduce(q_nccl)
+        if comm is not None:
+            g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
+            q_fused = vecs["q"].clone()
+            parity["fused_vs_nccl_max_rel"] = float(((q_fused - q_nccl).abs() / q_nccl.abs()).max().item())
+        else:
+            q_fused = q_nccl
+            parity["fused_vs_nccl_max_rel"] = None
+        gathered = [torch.empty_like(q_fused) for _ in range(world)]
+        dist.all_gather(gathered, q_fused)
+        parity["ranks_bit_identical"] = all(torch.equal(t.view(torch.int64), gathered[0].view(torch.int64)) for t in gathered)
+    if rank == 0 and not args.no_cpu:
+        from oracle import oracle as O   # the checker, never the thing measured
+        rows_o = min(nloc, 100_000)
+        g.call("sysml_b200_mmchain_dense", p_(X), p_(P), p_(w), p_(Q), rows_o, m, L.XtwXv)
+        got = vecs["q"].cpu().numpy()
+        Xh = O.rand_uniform(rows_o * m, seed=1).reshape(rows_o, m)
+        exp = O.mmchain_dense(Xh, O.rand_uniform(m, seed=77), O.rand_uniform(rows_o, seed=4, lo=0.0, hi=1.0), O.XtwXv, O.use_all_host_threads())
+        parity["oracle_max_rel"] = float(np.max(np.abs((got - exp) / exp)))
+        parity["oracle_rows"] = rows_o
+        del Xh
+    ok = [parity.get("oracle_max_rel", 0.0) < 1e-9]
+    if world > 1:
+        ok.append(bool(parity["ranks_bit_identical"]))
+        if parity["fused_vs_nccl_max_rel"] is not None:
+            ok.append(parity["fused_vs_nccl_max_rel"] < 1e-12)
+    parity["ok"] = all(ok)
+
     # ---------------- host-driven run: `e2e` ----------------
     e2e = None
     if not args.no_e2e:
@@ -427,22 +539,26 @@ def main():
         tout = tensor(m * m)
         g.call("sysml_b200_tsmm_dense", p_(X), C.c_void_p(tout.data_ptr()), nloc, m, 1, None)  # warm-up (+ workspace growth)
         torch.cuda.synchronize()
-        reps = 3
+        reps = 5
+        ts_sampler = ClockSampler(local_rank)
+        ts_sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(reps):
             g.call("sysml_b200_tsmm_dense", p_(X), C.c_void_p(tout.data_ptr()), nloc, m, 1, None)
         e1.record(stream)
         torch.cuda.synchronize()
+        ts_clocks = ts_sampler.stop()
         ms = e0.elapsed_time(e1) / reps
         flops = float(nloc) * m * (m + 1)
         tsmm = {"shape": [nloc, m], "ms": ms, "tflops_symmetric": flops / ms / 1e9, "tflops_gemm_equivalent": 2.0 * nloc * m * m / ms / 1e9,
-                "flops_counted": "n*m*(m+1) (upper triangle incl. diagonal, as the reference computes)"}
+                "flops_counted": "n*m*(m+1) (upper triangle incl. diagonal, as the reference computes)", "reps": reps, "clocks": ts_clocks}
         peaks = os.path.join(ROOT, "profiles", "fp64_peak.json")
         if os.path.exists(peaks):
             try:
                 pk = json.load(open(peaks))
                 tsmm["fp64_dmma_peak_tflops"] = pk["dmma_peak_tflops"]
+                tsmm["fp64_dmma_peak_source"] = "profiles/fp64_peak.json: this repo's own DMMA issue-rate probe (tools/probe_peaks.cu), round 1; NOT measured in this run and not a MEASURED_PEAKS.json figure"
                 tsmm["frac_of_measured_dmma_peak"] = tsmm["tflops_symmetric"] / pk["dmma_peak_tflops"]
             except Exception:
                 pass
@@ -452,32 +568,28 @@ def main():
     peak, peak_src = measured_peak()
     bytes_launch = alg_bytes_mmchain(nloc, m)
     achieved = bytes_launch / (kern_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     tp = os.path.join(ROOT, "profiles", "mmchain_traffic.json")
     if os.path.exists(tp):
         try:
             tj = json.load(open(tp))
             if tj.get("rows") == nloc and tj.get("cols") == m:
                 traffic = tj.get("dram_bytes_per_launch")
+                traffic_src = "profiles/mmchain_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this shape (%s); NOT measured in this run" % tj.get("source", "committed capture")
         except Exception:
             pass
     roofline = {"bound": "hbm", "kernel": "rowstream_kernel<CHAIN> (mmchain XtwXv)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
+                "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_per_step}
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
-            val, cores, sample, med, rows = cpu_cg_iterations(n, m)
-            cpu = {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
-                   "sample_gbs": alg_bytes_mmchain(rows, m) / med / 1e9}
+            # bounded sample (about 12 s of host time); the --impl reference arm holds reference_arm_sample_rows rows
+            cpu = cpu_baseline_block(cpu_cg_iterations(n, m, min(n, 2_000_000)))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic",
-            "config": {"workload": "GLM/LinearRegCG CG iteration, mmchain XtwXv, dense FP64 %d x %d (BASELINE configs[1]), row-sharded %d x %d rows/GPU"
-                       % (n, m, world, nloc), "parallelism": "row-shard x%d + all-reduce(m doubles) [%s]" % (world, ("fused into the mmchain finishing kernel over NVLink peer memory" if comm is not None else "NCCL") if world > 1 else "none"),
-                       "l2": "inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush needed" % (8.0 * nloc * m / 1e9),
-                       "x_distribution": "U(-1,1) counter-based generator, seed 1"},
+            "data": "synthetic", "config": make_config(args, world), "parity": parity,
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "mmchain_gbs_aggregate": achieved * world, "result_finite": finite,
         }
@@ -486,10 +598,16 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.cuda.synchronize()
+        flag = torch.tensor([0 if parity["ok"] else 1], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        parity["ok"] = int(flag.item()) == 0
         dist.barrier()
         if comm is not None:
             comm.destroy()
         dist.destroy_process_group()
+    if not parity["ok"]:
+        sys.stderr.write("bench.py: PARITY FAILED: %s\n" % json.dumps(parity))
+        return 3
     return 0
 
 

@@ -40,6 +40,7 @@ def lib():
             build()
         L = C.CDLL(_SO)
         L.orc_num_threads.restype = C.c_int
+        L.orc_set_num_threads.argtypes = [C.c_int]
         L.orc_java_test_matrix.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, i64, dp]
         L.orc_java_next_doubles.argtypes = [i64, C.c_int, dp]
         L.orc_balanced_blocks.argtypes = [C.c_int, C.c_int, C.c_int, ip]
@@ -72,6 +73,27 @@ def lib():
 
 def num_threads():
     return lib().orc_num_threads()
+
+
+def host_cpus():
+    """(logical CPUs this process may run on, distinct physical cores among them).  Independent of
+    OMP_NUM_THREADS, which torchrun sets to 1 for every rank."""
+    cpus = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
+    cores = set()
+    for c in cpus:
+        try:
+            base = "/sys/devices/system/cpu/cpu%d/topology/" % c
+            cores.add((open(base + "physical_package_id").read().strip(), open(base + "core_id").read().strip()))
+        except OSError:
+            cores.add(("?", str(c)))
+    return len(cpus), len(cores)
+
+
+def use_all_host_threads():
+    """Sets the OpenMP team size to every CPU in this process's affinity mask and returns it."""
+    k, _ = host_cpus()
+    lib().orc_set_num_threads(k)
+    return k
 
 
 def _vp(a):

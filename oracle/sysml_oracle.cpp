@@ -602,6 +602,17 @@ int orc_num_threads() {
 #endif
 }
 
+// Launchers such as torchrun export OMP_NUM_THREADS=1 to every rank; the CPU arm of bench.py asks for the
+// cores this process may run on (sched_getaffinity) instead, as the reference's k = #vcores rule does
+// (InfrastructureAnalyzer.getLocalParallelism -> LibMatrixMult.matrixMultChain(.., k), LibMatrixMult.java:284).
+void orc_set_num_threads(int k) {
+#ifdef _OPENMP
+  if (k >= 1) omp_set_num_threads(k);
+#else
+  (void)k;
+#endif
+}
+
 // TestUtils.generateTestMatrix(rows, cols, min, max, sparsity, seed) -> row-major out (pre-zeroed here)
 void orc_java_test_matrix(int rows, int cols, double min, double max, double sparsity, i64 seed, double* out) {
   JavaRandom rnd(seed);
