@@ -6,14 +6,17 @@ X of 10,000,000 x 1000 (80 GB), row-sharded over the N GPUs of one box (strong s
 fixed; per-GPU rows = 10M / N in whole 1000-row blocks).  One "step" = one CG iteration:
 
     q = t(X) %*% (w * (X %*% p))            <- mmchain XtwXv, ONE pass over the shard (the hot kernel)
-    [N > 1]  all-reduce(q) over NCCL / NVLink (m = 1000 doubles)
+    [N > 1]  all-reduce(q) over NVLink (m = 1000 doubles)
     pq = t(p) %*% q ; a = nr2 / pq ; beta += a*p ; r += a*q ; nr2' = t(r) %*% r ; p = -r + (nr2'/nr2)*p
-        (one fused kernel, sysml_b200_cg_vector_update; --unfused-tail runs it as the ~11 separate
-        m-sized instructions the reference's compiler would emit)
 
-all on the device through the C ABI of include/sysml_b200.h (no host synchronisation inside a step).
-For N > 1 the all-reduce is fused into the mmchain finishing kernel over NVLink peer memory
-(sysml_b200_mmchain_dense_allreduce); --collective nccl uses a separate NCCL all-reduce instead.
+all on the device through the C ABI of include/sysml_b200.h (no host synchronisation inside a step), as ONE call,
+sysml_b200_cg_step_dense = two launches: the streaming kernel and a finishing kernel that folds the per-CTA
+partials, exchanges them with the peers over NVLink peer memory and applies the m-vector tail in its last CTA.
+--three-launch runs the round-1 step (mmchain+exchange, then sysml_b200_cg_vector_update), --unfused-tail the ~11
+separate m-sized instructions the reference's compiler would emit, --collective nccl a separate NCCL all-reduce.
+For N > 1 a `parity` block (outside the timed regions) compares the fused exchange with local mmchain + NCCL
+all-reduce, checks that all ranks hold identical bits and compares a 100k-row sub-result with the CPU oracle; the
+process exits non-zero when it fails.
 
   value   : CG iterations per second, whole job, inputs resident in HBM (CUDA events, max over ranks)
   e2e     : the same iteration driven from HOST buffers through the reference-facing call shape: every
@@ -56,6 +59,7 @@ def parse():
     ap.add_argument("--no-tsmm", action="store_true", help="skip the auxiliary tsmm measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--three-launch", action="store_true", help="round-1 step: mmchain(+exchange), then the fused m-vector kernel as a third launch")
     ap.add_argument("--unfused-tail", action="store_true", help="run the m-vector CG algebra as ~11 separate instructions instead of the fused kernel")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: 'fused' = sum exchange inside the mmchain finishing kernel over NVLink peer memory; 'nccl' = separate all-reduce")
@@ -334,10 +338,21 @@ def main():
 
     ev_pairs = []
 
+    two_launch = not (args.unfused_tail or args.three_launch or (world > 1 and comm is None))
+
     def cg_step(record):
         if record:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
+        if two_launch:
+            # the whole iteration in two launches: streaming kernel, then the kernel that folds the per-CTA partials,
+            # exchanges them with the peers and applies the m-vector tail (programmatic dependent launches)
+            g.call("sysml_b200_cg_step_dense", comm.handle if comm is not None else None, p_(X), p_(w), p_(P), p_(Q), p_(R), p_(BETA),
+                   p_(NR2), nloc, m, L.XtwXv, 0.0)
+            if record:
+                e1.record(stream)
+                ev_pairs.append((e0, e1))
+            return
         if comm is not None:
             g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, p_(X), p_(P), p_(w), p_(Q), nloc, m, L.XtwXv)
         else:
@@ -380,18 +395,29 @@ def main():
     t_evt0, t_evt1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_evt0.record(stream)
     for _ in range(args.steps):
-        cg_step(True)
+        cg_step(False)     # no events between the launches of the timed region: they would serialise the dependent launches
     t_evt1.record(stream)
     barrier()
     clocks = sampler.stop()
     launches = g.launch_count() - launches0
     total_ms = t_evt0.elapsed_time(t_evt1)
+    # second timed region, same K steps, CUDA events around every hot-path call: the kernel time behind `roofline`
+    reset_state()
+    barrier()
+    k_evt0, k_evt1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k_evt0.record(stream)
+    for _ in range(args.steps):
+        cg_step(True)
+    k_evt1.record(stream)
+    barrier()
+    instr_total_ms = k_evt0.elapsed_time(k_evt1)
     kern_ms = sum(a.elapsed_time(b) for a, b in ev_pairs) / max(len(ev_pairs), 1)
     if world > 1:
-        t = torch.tensor([total_ms, kern_ms], dtype=torch.float64, device=dev)
+        t = torch.tensor([total_ms, kern_ms, instr_total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, kern_ms = float(t[0]), float(t[1])
+        total_ms, kern_ms, instr_total_ms = float(t[0]), float(t[1]), float(t[2])
     ms_per_step = total_ms / args.steps
+    instr_ms_per_step = instr_total_ms / args.steps
     value = 1000.0 / ms_per_step
     finite = bool(torch.isfinite(vecs["beta"]).all().item())
 
@@ -578,9 +604,11 @@ def main():
                 traffic_src = "profiles/mmchain_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this shape (%s); NOT measured in this run" % tj.get("source", "committed capture")
         except Exception:
             pass
-    roofline = {"bound": "hbm", "kernel": "rowstream_kernel<CHAIN> (mmchain XtwXv)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    roofline = {"bound": "hbm", "kernel": "rowstream_kernel<CHAIN> (mmchain XtwXv)" + (" + finish_exchange_kernel (fold of per-CTA partials, exchange, CG tail; a few microseconds)" if two_launch else ""),
+                "timed_how": "CUDA events around every hot-path call in a second timed region of the same K steps (events inside the first one would serialise its programmatic dependent launches); kernel_share_of_step is taken within that second region",
+                "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
-                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / ms_per_step}
+                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / instr_ms_per_step, "instrumented_ms_per_step": instr_ms_per_step}
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
@@ -592,6 +620,7 @@ def main():
             "data": "synthetic", "config": make_config(args, world), "parity": parity,
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "mmchain_gbs_aggregate": achieved * world, "result_finite": finite,
+            "launches_per_step": 2 if two_launch else None,
         }
         if tsmm:
             line["tsmm"] = tsmm

@@ -353,12 +353,28 @@ int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
  *   comm_create : allocates this rank's mailbox (capacity max_values doubles per message) and returns its
  *                 64-byte cudaIpcMemHandle in handle_out64; exchange the handles of all ranks by any means
  *                 (the bench uses torch.distributed.all_gather) and pass them, in rank order, to comm_connect.
- *   Every rank must issue the same sequence of collective calls with the same sizes.
+ *                 handle_out64 may be NULL when the ranks will be connected with comm_connect_local.
+ *   comm_connect_local : ranks that are contexts of ONE process -- the way the reference itself drives several
+ *                 GPUs: every parfor worker thread of one JVM owns a GPUContext and binds its device with
+ *                 cudaSetDevice (GPUContext.initializeThread, GPUContext.java:181-184; ParForProgramBlock.java:833).
+ *                 No IPC: peer access is enabled between the devices and every rank gets the peers' mailbox
+ *                 pointers.  comms[r] must be rank r of n.  Several ranks may share one device (tests).  Each rank
+ *                 still issues its own calls on its own context (from its own thread, or one thread issuing the
+ *                 asynchronous calls of all ranks in turn before synchronising any of them).
+ *   Every rank must issue the same sequence of collective calls with the same sizes.  This is checked: a flag
+ *   carries (count, combiner, kind) of the call next to its epoch, and every wait has a time budget (60 s unless
+ *   comm_set_timeout_ms changes it).  When a peer issues a different call, or does not arrive in time (it died,
+ *   skipped a call, failed validation), the kernel ends without hanging, and the NEXT call on the communicator
+ *   -- or comm_check, which first synchronises the context's stream -- returns SYSML_E_CUDA naming the peer
+ *   and the epoch.  A communicator that failed stays failed (epochs no longer agree): destroy it.
  * ---------------------------------------------------------------------------------------------- */
 typedef struct sysml_b200_comm sysml_b200_comm;
 int sysml_b200_comm_create(sysml_b200_ctx* ctx, int rank, int world, int64_t max_values,
                            sysml_b200_comm** out, void* handle_out64);
 int sysml_b200_comm_connect(sysml_b200_comm* comm, const void* all_handles);
+int sysml_b200_comm_connect_local(sysml_b200_comm** comms, int n);
+int sysml_b200_comm_set_timeout_ms(sysml_b200_comm* comm, int64_t ms);
+int sysml_b200_comm_check(sysml_b200_comm* comm);
 int sysml_b200_comm_destroy(sysml_b200_comm* comm);
 /* buf[0..len) <- sum over ranks, in place, identical bits on every rank (buffers longer than max_values go
  * through the mailbox in pieces). */
@@ -373,6 +389,17 @@ int sysml_b200_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf
 int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X,
                                        const double* v, const double* w, double* out, int64_t n,
                                        int64_t m, int chain_type);
+/* One whole conjugate-gradient iteration of LinearRegCG / GLM (scripts/algorithms/LinearRegCG.dml:176-195; inner CG of
+ * GLM.dml:1011-1030) on this rank's row shard, in two launches:
+ *   q = t(X) %*% (w * (X %*% p))  [chain_type as for mmchain; summed over the ranks of comm unless comm is NULL]
+ *   then sysml_b200_cg_vector_update(p, q, r, beta, nr2, m, lambda) -- same arithmetic, same bits --
+ *   applied by the last CTA of the finishing kernel instead of a third launch.
+ * The reference runs this as MMChainCPInstruction (MMChainCPInstruction.java:69-83) + ~10 m-sized CP instructions.
+ * Both kernels are programmatic dependent launches (their set-up overlaps the previous kernel's tail; they touch no
+ * global memory before that kernel has completed).  m <= 8192.  Every rank must make the call. */
+int sysml_b200_cg_step_dense(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X, const double* w,
+                             double* p, double* q, double* r, double* beta, double* nr2, int64_t n,
+                             int64_t m, int chain_type, double lambda);
 
 /* ------------------------------------------------------------------------------------------------
  * Synthetic data (scripts/datagen/genRandData4LinearRegression.dml uses Rand(min,max,pdf=uniform,seed)).

@@ -55,6 +55,15 @@ def linreg_cg(g, X, y, reg=1e-6, tol=1e-6, maxi=0, comm=None, fused_tail=True, l
     target = nr2_init * tol ** 2
     i = 0
     while i < maxi and nr2 > target:
+        if fused_tail and m <= 8192:
+            # the whole iteration in two launches: q = t(X) %*% (X %*% p) [summed over ranks], then the m-vector tail
+            g.call("sysml_b200_cg_step_dense", comm.handle if comm is not None else None, _p(X), None, _p(p), _p(q), _p(r), _p(beta),
+                   _p(nr2_d), n, m, L.XtXv, float(reg))
+            nr2 = _scalar(g, nr2_d)
+            i += 1
+            if log is not None:
+                log.append((i, (nr2 / nr2_init) ** 0.5))
+            continue
         # q = t(X) %*% (X %*% p)
         if comm is not None:
             g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, _p(X), _p(p), None, _p(q), n, m, L.XtXv)
@@ -110,11 +119,16 @@ def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1
         target = nr2 * inner_tol ** 2
         it = 0
         while it < inner_iters and nr2 > target and nr2 > 0.0:
-            if comm is not None:
-                g.call("sysml_b200_mmchain_dense_allreduce", comm.handle, _p(X), _p(p), _p(mu), _p(q), n, m, L.XtwXv)
+            if m <= 8192:
+                g.call("sysml_b200_cg_step_dense", comm.handle if comm is not None else None, _p(X), _p(mu), _p(p), _p(q), _p(r), _p(d),
+                       _p(nr2_d), n, m, L.XtwXv, float(reg))
             else:
-                g.call("sysml_b200_mmchain_dense", _p(X), _p(p), _p(mu), _p(q), n, m, L.XtwXv)
-            g.call("sysml_b200_cg_vector_update", _p(p), _p(q), _p(r), _p(d), _p(nr2_d), m, float(reg))
+                if comm is not None:
+                    g.call("sysml_b200_mmchain_dense", _p(X), _p(p), _p(mu), _p(q), n, m, L.XtwXv)
+                    comm.allreduce_sum(q.ptr, m)
+                else:
+                    g.call("sysml_b200_mmchain_dense", _p(X), _p(p), _p(mu), _p(q), n, m, L.XtwXv)
+                g.call("sysml_b200_cg_vector_update", _p(p), _p(q), _p(r), _p(d), _p(nr2_d), m, float(reg))
             nr2 = _scalar(g, nr2_d)
             it += 1
         inner_counts.append(it)

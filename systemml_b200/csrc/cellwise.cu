@@ -10,6 +10,7 @@
 // Algorithmic bytes: 8*(size(A) + size(B) + rows*cols) for binary, 16*len for scalar/unary.
 #include "common.cuh"
 #include "cellwise_ops.cuh"
+#include "cg_tail.cuh"
 
 namespace {
 
@@ -160,60 +161,10 @@ __global__ void transpose_kernel(const double* __restrict__ A, double* __restric
 // scalar ops on the host).  On a B200 each of them is launch latency, nothing else: one CTA does them
 // all, with compensated block reductions, and leaves nr2 on the device so no host round trip is needed.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ double block_sum_1024(double v, double* sh) {
-  CompSum s;
-  s.add(v);
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    CompSum t;
-    t.hi = __shfl_xor_sync(0xffffffffu, s.hi, o);
-    t.lo = __shfl_xor_sync(0xffffffffu, s.lo, o);
-    s.add(t);
-  }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) {
-    sh[warp] = s.hi;
-    sh[32 + warp] = s.lo;
-  }
-  __syncthreads();
-  CompSum t;
-  const int nw = blockDim.x >> 5;
-  for (int q = 0; q < nw; q++) {  // every thread adds the warp sums in the same order: identical result
-    CompSum u;
-    u.hi = sh[q];
-    u.lo = sh[32 + q];
-    t.add(u);
-  }
-  return t.value();
-}
-
 __global__ void __launch_bounds__(1024) cg_vector_update_kernel(double* __restrict__ p, double* __restrict__ q, double* __restrict__ r,
                                                                 double* __restrict__ beta, double* __restrict__ nr2, i64 m, double lambda) {
   __shared__ double sh[64];
-  const double nr2_old = *nr2;
-  double part = 0.0;
-  for (i64 j = threadIdx.x; j < m; j += blockDim.x) {
-    const double pj = p[j];
-    const double qj = __dadd_rn(q[j], __dmul_rn(lambda, pj));
-    q[j] = qj;
-    part = fma(pj, qj, part);
-  }
-  const double pq = block_sum_1024(part, sh);
-  const double a = __ddiv_rn(nr2_old, pq);
-  part = 0.0;
-  for (i64 j = threadIdx.x; j < m; j += blockDim.x) {
-    const double pj = p[j];
-    beta[j] = __dadd_rn(beta[j], __dmul_rn(a, pj));
-    const double rj = __dadd_rn(r[j], __dmul_rn(a, q[j]));
-    r[j] = rj;
-    part = fma(rj, rj, part);
-  }
-  const double nr2_new = block_sum_1024(part, sh);
-  const double b = __ddiv_rn(nr2_new, nr2_old);
-  for (i64 j = threadIdx.x; j < m; j += blockDim.x) p[j] = __dadd_rn(-r[j], __dmul_rn(b, p[j]));
-  __syncthreads();
-  if (threadIdx.x == 0) *nr2 = nr2_new;
+  cg_vector_update_body(p, q, r, beta, nr2, m, lambda, sh);
 }
 
 inline unsigned grid_for(sysml_b200_ctx* ctx, i64 work_items, int threads, int per_sm) {

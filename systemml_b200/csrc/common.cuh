@@ -126,6 +126,14 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// ---- programmatic dependent launch (PTX griddepcontrol).  Both are no-ops in a kernel that was launched without the
+// programmatic-stream-serialization attribute.  launch_dependents: the next kernel of the stream may start its CTAs
+// as soon as every CTA of this grid has executed it (or exited); wait: blocks until the PREVIOUS kernel of the stream
+// has completed and its memory is visible -- nothing that kernel wrote may be read, and nothing it reads may be
+// overwritten, before this returns. ----
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---- streaming loads that do not pollute L1 ----
 __device__ __forceinline__ double ldg_stream(const double* p) {
   double v;

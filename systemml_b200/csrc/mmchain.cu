@@ -24,7 +24,8 @@
 #include "common.cuh"
 
 struct sysml_b200_comm;
-int sysml_launch_allreduce_finish(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out, int rop);
+int sysml_launch_finish_exchange(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out, int rop,
+                                 bool pdl, double* cg_p, double* cg_r, double* cg_beta, double* cg_nr2, double cg_lambda);
 
 namespace {
 
@@ -42,7 +43,11 @@ struct StreamArgs {
   i64 total_tiles;
   int use_tma;
   int w_smem;  // w rides the stage ring too (R doubles per stage after the row tiles) instead of being read by the consumers
-  sysml_b200_comm* comm;  // host side only: non-null -> the finishing kernel also does the cross-GPU sum
+  // host side only:
+  sysml_b200_comm* comm;  // non-null -> the finishing kernel also does the cross-GPU sum
+  int pdl;                // launch this kernel and its finishing kernel as programmatic dependents of their predecessors
+  double *cg_r, *cg_beta, *cg_nr2;  // non-null -> the finishing kernel also applies the CG m-vector tail (v is p, out is q)
+  double cg_lambda;
 };
 
 // NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
@@ -73,7 +78,12 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
     }
     mbar_fence_init();
   }
+  // launched as a programmatic dependent (CG step): the set-up above overlaps the previous kernel's tail; nothing in
+  // global memory is touched before that kernel has completed.  Its own dependent (the finishing kernel) may be
+  // made resident as soon as an SM has room; it waits for this grid to complete before it reads the partials.
+  griddep_launch_dependents();
   __syncthreads();
+  griddep_wait();
 
   if (tid >= NTC) {
     // ===================== producer warp =====================
@@ -323,10 +333,24 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
     if (rc) return rc;
     a.partial = (double*)ws;
   }
-  kern<<<(unsigned)grid, NTC + 32, smem, ctx->stream>>>(a);
-  SYSML_LAUNCH_CHECK(ctx, "rowstream_kernel");
+  {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(NTC + 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = a.pdl ? 1 : 0;
+    SYSML_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, a));
+    ctx->launches++;
+  }
   if (MODE != MODE_MV) {
-    if (a.comm) return sysml_launch_allreduce_finish(ctx, a.comm, a.partial, (int)(grid * G), a.m, a.out, SYSML_REDUCE_SUM);
+    if (a.comm || a.cg_r)
+      return sysml_launch_finish_exchange(ctx, a.comm, a.partial, (int)(grid * G), a.m, a.out, SYSML_REDUCE_SUM, a.pdl != 0,
+                                          a.cg_r ? const_cast<double*>(a.v) : nullptr, a.cg_r, a.cg_beta, a.cg_nr2, a.cg_lambda);
     colpartial_reduce_kernel<<<(unsigned)((a.m + 31) / 32), 256, 0, ctx->stream>>>(a.partial, (int)(grid * G), a.m, a.out);
     SYSML_LAUNCH_CHECK(ctx, "colpartial_reduce_kernel");
   }
@@ -533,10 +557,36 @@ extern "C" int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b20
   if (m > 8192) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_allreduce: more than 8192 columns; run mmchain_dense then allreduce_sum");
   if (n == 0) {  // an empty shard still has to take part in the exchange
     SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
-    return sysml_launch_allreduce_finish(ctx, comm, out, 1, (int)m, out, SYSML_REDUCE_SUM);
+    return sysml_launch_finish_exchange(ctx, comm, out, 1, (int)m, out, SYSML_REDUCE_SUM, false, nullptr, nullptr, nullptr, nullptr, 0.0);
   }
   StreamArgs a{};
   a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type; a.comm = comm;
+  a.pdl = 1;
+  return launch_rowstream<MODE_CHAIN>(ctx, a);
+}
+
+// One conjugate-gradient iteration of LinearRegCG / GLM on this rank's row shard in TWO launches:
+//   q = t(X) %*% (w * (X %*% p))   [summed over the ranks of comm when it is not null]
+//   q += lambda*p ; a = nr2/sum(p*q) ; beta += a*p ; r += a*q ; nr2' = sum(r^2) ; p = -r + (nr2'/nr2)*p ; nr2 = nr2'
+// The streaming kernel is followed by one finishing kernel that folds the per-CTA partials, exchanges them with the
+// peers and, in its last CTA, applies the m-vector tail (cg_tail.cuh; same arithmetic as sysml_b200_cg_vector_update).
+// Both kernels are programmatic dependent launches: their set-up overlaps the tail of the kernel before them.
+extern "C" int sysml_b200_cg_step_dense(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X, const double* w, double* p,
+                                        double* q, double* r, double* beta, double* nr2, int64_t n, int64_t m, int chain_type,
+                                        double lambda) {
+  SYSML_ENTER(ctx);
+  int rc = validate_chain(ctx, X, p, w, q, n, m, chain_type);
+  if (rc) return rc;
+  if (m <= 0 || !p || !q || !r || !beta || !nr2) return sysml_set_error(ctx, SYSML_E_INVALID, "cg_step: bad arguments");
+  if (m > 8192) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "cg_step: more than 8192 columns; run mmchain_dense (+ allreduce_sum) and cg_vector_update");
+  if (n == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(q, 0, (size_t)m * sizeof(double), ctx->stream));
+    return sysml_launch_finish_exchange(ctx, comm, q, 1, (int)m, q, SYSML_REDUCE_SUM, false, p, r, beta, nr2, lambda);
+  }
+  StreamArgs a{};
+  a.X = X; a.v = p; a.w = w; a.out = q; a.n = n; a.m = (int)m; a.ct = chain_type; a.comm = comm;
+  a.pdl = 1;
+  a.cg_r = r; a.cg_beta = beta; a.cg_nr2 = nr2; a.cg_lambda = lambda;
   return launch_rowstream<MODE_CHAIN>(ctx, a);
 }
 

@@ -239,11 +239,30 @@ class Communicator:
         handle = (C.c_ubyte * 64)()
         native.check(gctx.handle, lib.sysml_b200_comm_create(gctx.handle, rank, world, int(max_values), C.byref(h), handle))
         self.handle = h
+        if exchange is None:   # connected later by Communicator.connect_local
+            return
         blobs = exchange(bytes(handle))
         assert len(blobs) == world and all(len(b) == 64 for b in blobs)
         joined = b"".join(blobs)
         buf = (C.c_ubyte * len(joined)).from_buffer_copy(joined)
         native.check(gctx.handle, lib.sysml_b200_comm_connect(self.handle, buf))
+
+    @staticmethod
+    def connect_local(gctxs, max_values):
+        """Ranks that are contexts of ONE process (GPUContext.initializeThread, GPUContext.java:181-184): rank r
+        lives on gctxs[r]; no IPC handles, peer access between the devices."""
+        world = len(gctxs)
+        comms = [Communicator(g, r, world, max_values, None) for r, g in enumerate(gctxs)]
+        arr = (C.c_void_p * world)(*[c.handle for c in comms])
+        native.check(gctxs[0].handle, gctxs[0]._lib.sysml_b200_comm_connect_local(arr, world))
+        return comms
+
+    def set_timeout_ms(self, ms):
+        native.check(self.gctx.handle, self.gctx._lib.sysml_b200_comm_set_timeout_ms(self.handle, int(ms)))
+
+    def check(self):
+        """Synchronises the context's stream and raises if an exchange failed (peer missing / different call)."""
+        native.check(self.gctx.handle, self.gctx._lib.sysml_b200_comm_check(self.handle))
 
     def allreduce_sum(self, ptr, length):
         self.gctx.call("sysml_b200_allreduce_sum", self.handle, C.c_void_p(ptr), int(length))

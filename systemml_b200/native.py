@@ -68,7 +68,11 @@ SIGNATURES = {
     "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),
     "sysml_b200_comm_create": (ci, [vp, ci, ci, i64, pvp, vp]),
     "sysml_b200_comm_connect": (ci, [vp, vp]),
+    "sysml_b200_comm_connect_local": (ci, [vp, ci]),
+    "sysml_b200_comm_set_timeout_ms": (ci, [vp, i64]),
+    "sysml_b200_comm_check": (ci, [vp]),
     "sysml_b200_comm_destroy": (ci, [vp]),
+    "sysml_b200_cg_step_dense": (ci, [vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, ci, dbl]),
     "sysml_b200_allreduce_sum": (ci, [vp, vp, vp, i64]),
     "sysml_b200_allreduce": (ci, [vp, vp, vp, i64, ci]),
     "sysml_b200_mmchain_dense_allreduce": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci]),
