@@ -74,6 +74,20 @@ int sysml_b200_ec_get_matrix_dims(sysml_b200_ec* ec, const char* name, int64_t* 
 int sysml_b200_ec_get_matrix_dense(sysml_b200_ec* ec, const char* name, double* h_out);
 int sysml_b200_ec_get_scalar(sysml_b200_ec* ec, const char* name, double* value);
 
+/* sysml.gpu.eviction.policy (DMLScript.EvictionPolicy, api/DMLScript.java:110,175,679): "lru" (default), "lfu",
+ * "min_evict" or "mru".  Decides which unlocked matrices leave the device first when an allocation does not fit
+ * (GPUMemoryManager.java:229-246 with GPUComparator :531-571; timestamps follow GPUObject.updateReleaseLocks,
+ * GPUObject.java:650-667). */
+int sysml_b200_ec_set_eviction_policy(sysml_b200_ec* ec, const char* policy);
+/* MatrixBlock.evalSparseFormatInMemory(rows, cols, nnz) (MatrixBlock.java:1001-1015): 1 when a block with that many
+ * non-zeros is kept in sparse format, 0 when dense.  Pure host arithmetic, no context needed. */
+int sysml_b200_eval_sparse_format_in_memory(int64_t rows, int64_t cols, int64_t nnz);
+/* MatrixBlock.examSparsity on the host copy of a variable (fetched from the device first when that copy is the
+ * valid one), as LibMatrixMult applies it to every matmult result (LibMatrixMult.java:113,149,168,225): the block
+ * is rewritten as CSR when evalSparseFormatInMemory says so.  *is_sparse receives the resulting format; the exact
+ * nnz is what sysml_b200_ec_get_matrix_dims returns afterwards. */
+int sysml_b200_ec_exam_sparsity(sysml_b200_ec* ec, const char* name, int* is_sparse);
+
 /* GPUStatistics counters (J/utils/GPUStatistics.java:40-62), in this order:
  * [0] executed GPU instructions, [1] H2D copies, [2] D2H copies, [3] cudaMalloc calls, [4] free-list reuses,
  * [5] cudaFree calls, [6] evictions, [7] bytes currently allocated, [8] bytes in the free list. */

@@ -6,6 +6,7 @@
 //   GPUMemoryManager                                           J/runtime/instructions/gpu/context/GPUMemoryManager.java
 //
 // Host logic only: every numeric operation is a call into the kernels of include/sysml_b200.h.
+#include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
@@ -41,12 +42,17 @@ struct DMLRuntimeException : std::runtime_error {
 struct GPUObject;
 
 // ------------------------------------------------------------------------------------------------
-// GPUMemoryManager: size-keyed free list of "rmvar-ed" pointers, eviction of unlocked matrices in LRU
-// order when the budget is exhausted (GPUMemoryManager.java:157-262; policy "lru", GPUObject.java:650-667).
+// GPUMemoryManager: size-keyed free list of "rmvar-ed" pointers, eviction of unlocked matrices when the budget is
+// exhausted (GPUMemoryManager.java:157-262) in the order the configured policy gives: LRU / LFU / MRU through the
+// timestamp every release updates (GPUObject.updateReleaseLocks, GPUObject.java:650-667), MIN_EVICT by size
+// against the request (GPUComparator, GPUMemoryManager.java:531-571).
 // Deviation: no cudaMemset after malloc (every kernel writes all of its output cells).
 // ------------------------------------------------------------------------------------------------
+enum EvictionPolicy { LRU = 0, LFU = 1, MIN_EVICT = 2, MRU = 3 };  // DMLScript.EvictionPolicy (api/DMLScript.java:110)
+
 struct GPUMemoryManager {
   sysml_b200_ctx* ctx = nullptr;
+  EvictionPolicy policy = LRU;
   double util_factor = 0.9;
   bool eager_free = false;
   i64 memory_limit = 0;
@@ -125,6 +131,20 @@ struct GPUMemoryManager {
   }
 };
 
+// MatrixBlock.evalSparseFormatInMemory (MatrixBlock.java:1001-1015) with the MCSR estimate it uses
+// (DEFAULT_SPARSEBLOCK, MatrixBlock.java:107; SparseBlockMCSR.estimateMemory, SparseBlockMCSR.java:101-116;
+// SparseRowVector.initialCapacity = 4) and estimateSizeDenseInMemory (:2339-2349).
+bool evalSparseFormatInMemory(i64 nrows, i64 ncols, i64 nnz) {
+  if (nrows <= 0 || ncols <= 0) return false;
+  const double lsparsity = (double)nnz / (double)nrows / (double)ncols;
+  const bool lsparse = lsparsity < 0.4;  // SPARSITY_TURN_POINT
+  const double cnnz = std::max(4.0, ceil(lsparsity * (double)ncols));
+  const double rlen = std::min((double)nrows, ceil(lsparsity * (double)nrows * (double)ncols));
+  const double sizeSparse = 44.0 + 16.0 + 24.0 + (double)nrows * 8.0 + rlen * (76.0 + cnnz * 12.0);
+  const double sizeDense = 44.0 + 8.0 * (double)nrows * (double)ncols;
+  return lsparse && sizeSparse < sizeDense;
+}
+
 // MatrixObject + its host block (dense row-major or CSR) -- the part of CacheableData this layer needs.
 struct MatrixObject {
   std::string name;
@@ -134,6 +154,42 @@ struct MatrixObject {
   std::vector<int32_t> h_rowptr, h_colind;
   std::vector<double> h_val;
   std::unique_ptr<GPUObject> gpu;
+
+  // MatrixBlock.recomputeNonZeros + examSparsity (MatrixBlock.java:963-990) on the host block, what LibMatrixMult does
+  // to every matmult result (LibMatrixMult.java:113,149,168,225): a dense block whose exact nnz says "sparse in memory"
+  // is rewritten as CSR (denseToSparse keeps row order and drops zeros; -0.0 counts as a zero).
+  void recomputeNonZeros() {
+    if (!host_valid) return;
+    i64 c = 0;
+    if (host_sparse) {
+      for (double v : h_val) c += (v != 0.0);
+    } else {
+      for (double v : h_dense) c += (v != 0.0);
+    }
+    nnz = c;
+  }
+  void examSparsity() {
+    if (!host_valid || host_sparse) return;
+    recomputeNonZeros();
+    if (!evalSparseFormatInMemory(rows, cols, nnz)) return;
+    h_rowptr.assign(rows + 1, 0);
+    h_colind.clear();
+    h_val.clear();
+    h_colind.reserve(nnz);
+    h_val.reserve(nnz);
+    for (i64 r = 0; r < rows; r++) {
+      for (i64 j = 0; j < cols; j++) {
+        const double v = h_dense[r * cols + j];
+        if (v != 0.0) {
+          h_colind.push_back((int32_t)j);
+          h_val.push_back(v);
+        }
+      }
+      h_rowptr[r + 1] = (int32_t)h_val.size();
+    }
+    std::vector<double>().swap(h_dense);
+    host_sparse = true;
+  }
 };
 
 // GPUObject: device state of one matrix (GPUObject.java:52-99): dense pointer or CSR triple, dirty bit,
@@ -149,27 +205,63 @@ struct GPUObject {
   bool borrowed = false;  // device block owned by the caller: never freed, never evicted
   int readLocks = 0;
   bool writeLock = false;
+  bool uploading = false;  // its device arrays are being allocated right now: not an eviction candidate
   i64 timestamp = 0;
   i64* h2d_counter;
   i64* d2h_counter;
+  i64* clock;
 
   bool isAllocated() const { return dense != nullptr || rowptr != nullptr; }
   bool isSparse() const { return rowptr != nullptr; }
-  bool isLocked() const { return writeLock || readLocks > 0; }
+  bool isLocked() const { return writeLock || readLocks > 0 || uploading; }
+  i64 getSizeOnDevice() const {  // GPUObject.getSizeOnDevice (GPUObject.java:741-753)
+    if (isSparse()) return (mat->rows + 1) * 4 + std::max<i64>(csr_nnz, 1) * 12;
+    return dense ? std::max<i64>(mat->rows * mat->cols, 1) * 8 : 0;
+  }
+  void updateReleaseLocks() {  // GPUObject.java:650-667
+    switch (mm->policy) {
+      case LRU: timestamp = ++*clock; break;
+      case LFU: timestamp += 1; break;
+      case MIN_EVICT: break;
+      case MRU: timestamp = -(++*clock); break;
+    }
+  }
 
   void copyFromHostToDevice(const char* opcode) {  // GPUObject.java:755-870
     if (!mat->host_valid) fail(SYSML_E_INVALID, "GPU : no host copy of variable %s to upload", mat->name.c_str());
     if (mat->host_sparse) {
+      // The three arrays are allocated into locals and published together (CSRPointer.allocateEmpty finishes before
+      // GPUObject sees the pointer, CSRPointer.java:271-287): a later malloc of this very upload may have to evict,
+      // and a half-built object must not be its victim.
       const i64 nnz = mat->h_rowptr.empty() ? 0 : mat->h_rowptr.back();
-      rowptr = (int32_t*)mm->malloc(opcode, (mat->rows + 1) * 4);
-      colind = (int32_t*)mm->malloc(opcode, std::max<i64>(nnz, 1) * 4);
-      val = (double*)mm->malloc(opcode, std::max<i64>(nnz, 1) * 8);
-      mm->check(sysml_b200_h2d(mm->ctx, rowptr, mat->h_rowptr.data(), (mat->rows + 1) * 4));
+      struct Guard {
+        GPUObject* o;
+        GPUMemoryManager* mm;
+        void* p[3] = {nullptr, nullptr, nullptr};
+        bool done = false;
+        ~Guard() {
+          o->uploading = false;
+          if (!done)
+            for (void* q : p)
+              if (q) {
+                try { mm->free(q, true); } catch (...) {}
+              }
+        }
+      } gd{this, mm};
+      uploading = true;
+      gd.p[0] = mm->malloc(opcode, (mat->rows + 1) * 4);
+      gd.p[1] = mm->malloc(opcode, std::max<i64>(nnz, 1) * 4);
+      gd.p[2] = mm->malloc(opcode, std::max<i64>(nnz, 1) * 8);
+      mm->check(sysml_b200_h2d(mm->ctx, gd.p[0], mat->h_rowptr.data(), (mat->rows + 1) * 4));
       if (nnz) {
-        mm->check(sysml_b200_h2d(mm->ctx, colind, mat->h_colind.data(), nnz * 4));
-        mm->check(sysml_b200_h2d(mm->ctx, val, mat->h_val.data(), nnz * 8));
+        mm->check(sysml_b200_h2d(mm->ctx, gd.p[1], mat->h_colind.data(), nnz * 4));
+        mm->check(sysml_b200_h2d(mm->ctx, gd.p[2], mat->h_val.data(), nnz * 8));
       }
+      rowptr = (int32_t*)gd.p[0];
+      colind = (int32_t*)gd.p[1];
+      val = (double*)gd.p[2];
       csr_nnz = nnz;
+      gd.done = true;
     } else {
       const i64 cells = mat->rows * mat->cols;
       dense = (double*)mm->malloc(opcode, std::max<i64>(cells, 1) * 8);
@@ -193,31 +285,64 @@ struct GPUObject {
       mat->h_dense.resize(mat->rows * mat->cols);
       if (mat->rows * mat->cols) mm->check(sysml_b200_d2h(mm->ctx, mat->h_dense.data(), dense, mat->rows * mat->cols * 8));
       mat->host_sparse = false;
+      mat->host_valid = true;
+      mat->recomputeNonZeros();  // tmp.recomputeNonZeros() (GPUObject.java:896); the host block stays dense
     }
     mat->host_valid = true;
     (*d2h_counter)++;
     dirty = false;
   }
-  void acquireDeviceRead(const char* opcode, i64 clock) {  // GPUObject.java:528-545
+  void acquireDeviceRead(const char* opcode) {  // GPUObject.java:528-545
     if (!isAllocated()) copyFromHostToDevice(opcode);
     readLocks++;
-    timestamp = clock;
   }
-  void acquireDeviceModifyDense(const char* opcode, i64 clock) {  // GPUObject.java:547-565
-    if (!isAllocated()) dense = (double*)mm->malloc(opcode, std::max<i64>(mat->rows * mat->cols, 1) * 8);
+  void acquireDeviceModifyDense(const char* opcode) {  // GPUObject.java:547-565
+    if (!isAllocated()) {
+      uploading = true;  // registered but without a block yet: the malloc below must not pick it
+      struct Reset { bool& f; ~Reset() { f = false; } } rs{uploading};
+      dense = (double*)mm->malloc(opcode, std::max<i64>(mat->rows * mat->cols, 1) * 8);
+    }
     if (isSparse()) fail(SYSML_E_INVALID, "GPU : output %s is held in sparse format", mat->name.c_str());
     dirty = true;
     writeLock = true;
-    timestamp = clock;
   }
   void releaseInput() {  // GPUObject.java:609-624
     if (readLocks <= 0) fail(SYSML_E_INVALID, "GPU : releaseInput of %s without a read lock", mat->name.c_str());
     readLocks--;
+    updateReleaseLocks();
   }
   void releaseOutput() {  // GPUObject.java:626-645
     if (!writeLock) fail(SYSML_E_INVALID, "GPU : releaseOutput of %s without a write lock", mat->name.c_str());
     writeLock = false;
+    updateReleaseLocks();
     if (!isAllocated()) fail(SYSML_E_INVALID, "GPU : attempting to release an output that was not allocated");
+  }
+  // GPUObject.sparseToDense (GPUObject.java:356-404): the CSR arrays are replaced by a dense block, for operators that
+  // have no sparse form (LibMatrixCUDA.getDensePointer, LibMatrixCUDA.java:655-664, 1382-1383)
+  void sparseToDense(const char* opcode) {
+    if (!isSparse()) return;
+    const bool was = uploading;
+    uploading = true;
+    double* d = nullptr;
+    try {
+      d = (double*)mm->malloc(opcode, std::max<i64>(mat->rows * mat->cols, 1) * 8);
+    } catch (...) {
+      uploading = was;
+      throw;
+    }
+    uploading = was;
+    int rc = sysml_b200_csr_to_dense(mm->ctx, rowptr, colind, val, mat->rows, mat->cols, d);
+    if (rc) {
+      mm->free(d, true);
+      mm->check(rc);
+    }
+    mm->free(rowptr, mm->eager_free);
+    mm->free(colind, mm->eager_free);
+    mm->free(val, mm->eager_free);
+    rowptr = colind = nullptr;
+    val = nullptr;
+    csr_nnz = 0;
+    dense = d;
   }
   void acquireHostRead() {  // GPUObject.java:593-607
     if (isAllocated() && dirty) copyFromDeviceToHost();
@@ -269,12 +394,25 @@ void* GPUMemoryManager::malloc(const char* opcode, i64 size) {
     for (void* p : toFree) guardedCudaFree(p);
     if (size <= getAvailableMemory()) A = cudaMallocWarnIfFails(size);
   }
-  // Step 5: evict unlocked matrices, least recently used first; dirty ones go back to the host first
+  // Step 5: evict unlocked matrices in the order of the policy; dirty ones go back to the host first.
+  // The reference sorts allocatedGPUObjects with GPUComparator(size) and evicts from the END of the list
+  // (GPUMemoryManager.java:229-246): descending timestamp, i.e. smallest timestamp first (LRU: oldest release; LFU:
+  // fewest releases; MRU: the negated clock makes the latest release the smallest); MIN_EVICT: the smallest block
+  // that is at least as large as the request first, then larger ones, then the too-small ones from the largest down.
   if (!A) {
     std::vector<GPUObject*> cand;
     for (GPUObject* o : objects)
       if (o->isAllocated() && !o->isLocked() && !o->borrowed) cand.push_back(o);
-    std::sort(cand.begin(), cand.end(), [](GPUObject* a, GPUObject* b) { return a->timestamp < b->timestamp; });
+    if (policy == MIN_EVICT) {
+      std::stable_sort(cand.begin(), cand.end(), [size](GPUObject* a, GPUObject* b) {
+        const i64 da = a->getSizeOnDevice() - size, db = b->getSizeOnDevice() - size;
+        if (da >= 0 && db >= 0) return da < db;
+        if (da >= 0 || db >= 0) return da >= 0;  // blocks that are large enough go before those that are not
+        return da > db;
+      });
+    } else {
+      std::stable_sort(cand.begin(), cand.end(), [](GPUObject* a, GPUObject* b) { return a->timestamp < b->timestamp; });
+    }
     for (GPUObject* o : cand) {
       if (size <= getAvailableMemory()) break;
       if (o->dirty) o->copyFromDeviceToHost();
@@ -460,6 +598,7 @@ struct sysml_b200_ec {
       mo->gpu->mat = mo;
       mo->gpu->h2d_counter = &n_h2d;
       mo->gpu->d2h_counter = &n_d2h;
+      mo->gpu->clock = &clock;
       mm.objects.push_back(mo->gpu.get());
     }
     return mo->gpu.get();
@@ -467,7 +606,7 @@ struct sysml_b200_ec {
   // ExecutionContext.getMatrixInputForGPUInstruction (:367-380)
   MatrixObject* getMatrixInputForGPUInstruction(const std::string& name, const char* opcode) {
     MatrixObject* mo = getMatrixObject(name);
-    gpuObject(mo)->acquireDeviceRead(opcode, ++clock);
+    gpuObject(mo)->acquireDeviceRead(opcode);
     return mo;
   }
   // ExecutionContext.getDenseMatrixOutputForGPUInstruction (:304-364): (re)creates the variable with the
@@ -483,7 +622,7 @@ struct sysml_b200_ec {
     mo->cols = cols;
     MatrixObject* p = mo.get();
     matrices[name] = std::move(mo);
-    gpuObject(p)->acquireDeviceModifyDense(opcode, ++clock);
+    gpuObject(p)->acquireDeviceModifyDense(opcode);
     return p;
   }
   void releaseMatrixInputForGPUInstruction(const std::string& name) { getMatrixObject(name)->gpu->releaseInput(); }
@@ -590,27 +729,90 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
     }
     ~Locks() { releaseAll(); }
   } L{this, {}, {}};
+  // device temporaries of this instruction, taken from and returned to the memory manager like the reference's
+  // (gCtx.allocate / gCtx.cudaFreeHelper inside the operator, LibMatrixCUDA.java:711,732,926,947)
+  struct Temps {
+    sysml_b200_ec* ec;
+    std::vector<void*> ptrs;
+    void* get(i64 bytes, const char* opcode) {
+      void* p = ec->mm.malloc(opcode, bytes);
+      ptrs.push_back(p);
+      return p;
+    }
+    ~Temps() {
+      if (ptrs.empty()) return;
+      sysml_b200_sync(ec->ctx);  // the kernels that read them may still be queued
+      for (void* p : ptrs) {
+        try { ec->mm.free(p, ec->mm.eager_free); } catch (...) {}
+      }
+    }
+  } T{this, {}};
+  // operators without a sparse form convert the input in place, as LibMatrixCUDA.getDensePointer does
+  // (LibMatrixCUDA.java:655-664, 1382-1383 -> GPUObject.sparseToDense)
+  auto densify = [&](MatrixObject* mo) {
+    if (mo->gpu->isSparse()) mo->gpu->sparseToDense(opc);
+  };
   switch (pi.type) {
-    case AggregateBinary: {  // AggregateBinaryGPUInstruction.processInstruction (:73-89)
+    case AggregateBinary: {  // AggregateBinaryGPUInstruction.processInstruction (:73-89) -> LibMatrixCuMatMult.matmult (:139-229)
       MatrixObject* m1 = L.in(pi.ops[0].name, opc);
       MatrixObject* m2 = L.in(pi.ops[1].name, opc);
-      const bool lt = pi.extras[0] == "true", rt = pi.extras[1] == "true";
+      bool lt = pi.extras[0] == "true", rt = pi.extras[1] == "true";
       const i64 rlen = lt ? m1->cols : m1->rows, clen = rt ? m2->rows : m2->cols;
+      if ((lt ? m1->rows : m1->cols) != (rt ? m2->cols : m2->rows))
+        fail(SYSML_E_DIM, "GPU : incompatible dimensions for ba+*: %lldx%lld%s and %lldx%lld%s", m1->rows, m1->cols, lt ? "'" : "", m2->rows, m2->cols, rt ? "'" : "");
       GPUObject *g1 = m1->gpu.get(), *g2 = m2->gpu.get();
-      if ((g2->isSparse() && (rt || (g1->isSparse() && lt))) || (g1->isSparse() && !g2->isSparse() && rt))
-        fail(SYSML_E_UNSUPPORTED, "GPU : ba+* with a transposed sparse operand in this combination is not implemented yet");
+      // Operand views as the kernels take them.  The reference passes the transpose flags on to cuSPARSE / cuBLAS for
+      // every sparsity pair (LibMatrixCuMatMult.java:139-229); here a flag the kernel of that pair has no form for is
+      // resolved by materialising the transposed operand in a temporary (freed when the instruction ends).
+      struct View {
+        bool sparse;
+        const double* dense;
+        const int32_t *rp, *ci;
+        const double* va;
+        i64 rows, cols;
+      };
+      View A{g1->isSparse(), g1->dense, g1->rowptr, g1->colind, g1->val, m1->rows, m1->cols};
+      View B{g2->isSparse(), g2->dense, g2->rowptr, g2->colind, g2->val, m2->rows, m2->cols};
+      auto transposeCsr = [&](View& V, i64 nnz) {
+        int32_t* rp = (int32_t*)T.get((V.cols + 1) * 4, opc);
+        int32_t* ci = (int32_t*)T.get(std::max<i64>(nnz, 1) * 4, opc);
+        double* va = (double*)T.get(std::max<i64>(nnz, 1) * 8, opc);
+        check(sysml_b200_csr_transpose(ctx, V.rp, V.ci, V.va, V.rows, V.cols, rp, ci, va));
+        V = View{true, nullptr, rp, ci, va, V.cols, V.rows};
+      };
+      auto transposeDense = [&](View& V) {
+        double* d = (double*)T.get(std::max<i64>(V.rows * V.cols, 1) * 8, opc);
+        check(sysml_b200_transpose(ctx, V.dense, d, V.rows, V.cols));
+        V = View{false, d, nullptr, nullptr, nullptr, V.cols, V.rows};
+      };
+      if (B.sparse && rt) {  // no kernel takes t(B) of a CSR right operand
+        transposeCsr(B, g2->csr_nnz);
+        rt = false;
+      }
+      if (A.sparse && B.sparse && lt) {  // sparse x sparse has no flags at all
+        transposeCsr(A, g1->csr_nnz);
+        lt = false;
+      }
+      if (A.sparse && !B.sparse && rt) {  // CSR x dense takes the left flag only
+        transposeDense(B);
+        rt = false;
+      }
       MatrixObject* out = L.out(pi.ops[2].name, rlen, clen, opc);
       int rc;
-      if (g2->isSparse() && g1->isSparse()) {
-        rc = sysml_b200_matmult_csr_csr(ctx, g1->rowptr, g1->colind, g1->val, g2->rowptr, g2->colind, g2->val, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols);
-      } else if (g2->isSparse()) {
-        rc = sysml_b200_matmult_dense_csr(ctx, g1->dense, g2->rowptr, g2->colind, g2->val, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt);
-      } else if (g1->isSparse()) {
-        rc = sysml_b200_matmult_csr_dense(ctx, g1->rowptr, g1->colind, g1->val, g2->dense, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt);
+      if (A.sparse && B.sparse) {
+        rc = sysml_b200_matmult_csr_csr(ctx, A.rp, A.ci, A.va, B.rp, B.ci, B.va, out->gpu->dense, A.rows, A.cols, B.rows, B.cols);
+      } else if (B.sparse) {
+        rc = sysml_b200_matmult_dense_csr(ctx, A.dense, B.rp, B.ci, B.va, out->gpu->dense, A.rows, A.cols, B.rows, B.cols, lt);
+      } else if (A.sparse) {
+        rc = sysml_b200_matmult_csr_dense(ctx, A.rp, A.ci, A.va, B.dense, out->gpu->dense, A.rows, A.cols, B.rows, B.cols, lt);
       } else {
-        rc = sysml_b200_matmult_dense(ctx, g1->dense, g2->dense, out->gpu->dense, m1->rows, m1->cols, m2->rows, m2->cols, lt, rt);
+        rc = sysml_b200_matmult_dense(ctx, A.dense, B.dense, out->gpu->dense, A.rows, A.cols, B.rows, B.cols, lt, rt);
       }
       check(rc);
+      // ret.recomputeNonZeros() after every matrixMult (LibMatrixMult.java:112,148,167,224): exact count on the device
+      int64_t nnz = 0;
+      check(sysml_b200_count_nnz(ctx, out->gpu->dense, rlen * clen, &nnz));
+      out->nnz = nnz;
       break;
     }
     case MMTSJ: {  // MMTSJGPUInstruction.processInstruction (:78-89)
@@ -641,7 +843,8 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
       std::string msg;
       if (v->rows * v->cols != X->cols) { rc = SYSML_E_DIM; msg = "mmchain: v must have ncol(X) cells"; }
       if (hasW && w->rows * w->cols != X->rows) { rc = SYSML_E_DIM; msg = "mmchain: w must have nrow(X) cells"; }
-      if (v->gpu->isSparse() || (w && w->gpu->isSparse())) { rc = SYSML_E_UNSUPPORTED; msg = "mmchain: v and w must be dense"; }
+      densify(v);
+      if (w) densify(w);
       MatrixObject* out = L.out(outName, X->cols, 1, opc);
       if (!rc) {
         if (X->gpu->isSparse())
@@ -681,9 +884,7 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
     case BuiltinUnary:
     case Reorg: {
       MatrixObject* in1 = L.in(pi.ops[0].name, opc);
-      if (in1->gpu->isSparse()) {
-        fail(SYSML_E_UNSUPPORTED, "GPU : %s on a sparse input is not implemented yet", opc);
-      }
+      densify(in1);
       const bool tr = pi.type == Reorg;
       MatrixObject* out = L.out(pi.ops[1].name, tr ? in1->cols : in1->rows, tr ? in1->rows : in1->cols, opc);
       int rc = tr ? sysml_b200_transpose(ctx, in1->gpu->dense, out->gpu->dense, in1->rows, in1->cols)
@@ -702,11 +903,10 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
         if (in1->rows == in2->rows && in1->cols == in2->cols) bcast = SYSML_BCAST_NONE;
         else if (in1->rows == in2->rows && in2->cols == 1) bcast = SYSML_BCAST_COL;
         else if (in2->rows == 1 && in1->cols == in2->cols) bcast = SYSML_BCAST_ROW;
-        if (bcast < 0 || in1->gpu->isSparse() || in2->gpu->isSparse()) {
-          if (bcast < 0)
-            fail(SYSML_E_DIM, "Incorrect dimensions of inputs in GPU axpy operation. input1:%lld X %lld and input2:%lld X %lld", in1->rows, in1->cols, in2->rows, in2->cols);
-          fail(SYSML_E_UNSUPPORTED, "GPU : axpy on sparse inputs is not implemented yet");
-        }
+        if (bcast < 0)
+          fail(SYSML_E_DIM, "Incorrect dimensions of inputs in GPU axpy operation. input1:%lld X %lld and input2:%lld X %lld", in1->rows, in1->cols, in2->rows, in2->cols);
+        densify(in1);
+        densify(in2);
         MatrixObject* out = L.out(pi.ops[3].name, in1->rows, in1->cols, opc);
         int rc = sysml_b200_axpy(ctx, in1->gpu->dense, in2->gpu->dense, scalar, out->gpu->dense, in1->rows, in1->cols, bcast);
         check(rc);
@@ -720,10 +920,9 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
         if (in1->rows == in2->rows && in1->cols == in2->cols) bcast = SYSML_BCAST_NONE;
         else if (in1->rows == in2->rows && in2->cols == 1) bcast = SYSML_BCAST_COL;
         else if (in2->rows == 1 && in1->cols == in2->cols) bcast = SYSML_BCAST_ROW;
-        if (bcast < 0 || in1->gpu->isSparse() || in2->gpu->isSparse()) {
-          if (bcast < 0) fail(SYSML_E_DIM, "GPU : incompatible dimensions %lldx%lld vs %lldx%lld for %s", in1->rows, in1->cols, in2->rows, in2->cols, opc);
-          fail(SYSML_E_UNSUPPORTED, "GPU : cellwise %s on sparse inputs is not implemented yet", opc);
-        }
+        if (bcast < 0) fail(SYSML_E_DIM, "GPU : incompatible dimensions %lldx%lld vs %lldx%lld for %s", in1->rows, in1->cols, in2->rows, in2->cols, opc);
+        densify(in1);
+        densify(in2);
         MatrixObject* out = L.out(o3.name, in1->rows, in1->cols, opc);
         int rc = sysml_b200_binary_mm(ctx, in1->gpu->dense, in2->gpu->dense, out->gpu->dense, in1->rows, in1->cols, bcast, binaryOpcode(pi.opcode));
         check(rc);
@@ -733,9 +932,7 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
         const CPOperand& mo = scalarLeft ? o2 : o1;
         const double scalar = getScalarInput(scalarLeft ? o1 : o2);
         MatrixObject* in = L.in(mo.name, opc);
-        if (in->gpu->isSparse()) {
-          fail(SYSML_E_UNSUPPORTED, "GPU : scalar %s on a sparse input is not implemented yet", opc);
-        }
+        densify(in);
         MatrixObject* out = L.out(o3.name, in->rows, in->cols, opc);
         double s = scalar;
         int code = binaryOpcode(pi.opcode);
@@ -927,6 +1124,34 @@ int sysml_b200_ec_get_scalar(sysml_b200_ec* ec, const char* name, double* value)
   }
   *value = it->second;
   return SYSML_OK;
+}
+
+int sysml_b200_ec_set_eviction_policy(sysml_b200_ec* ec, const char* policy) {
+  if (!ec || !policy) return SYSML_E_INVALID;
+  EC_TRY(ec, {
+    std::string p = policy;
+    for (auto& c : p) c = (char)tolower((unsigned char)c);
+    if (p == "lru") ec->mm.policy = LRU;
+    else if (p == "lfu") ec->mm.policy = LFU;
+    else if (p == "min_evict") ec->mm.policy = MIN_EVICT;
+    else if (p == "mru") ec->mm.policy = MRU;
+    else fail(SYSML_E_INVALID, "The eviction policy is not supported:%s", policy);
+  })
+}
+
+int sysml_b200_eval_sparse_format_in_memory(int64_t rows, int64_t cols, int64_t nnz) {
+  return evalSparseFormatInMemory(rows, cols, nnz) ? 1 : 0;
+}
+
+int sysml_b200_ec_exam_sparsity(sysml_b200_ec* ec, const char* name, int* is_sparse) {
+  if (!ec || !name) return SYSML_E_INVALID;
+  EC_TRY(ec, {
+    MatrixObject* mo = ec->getMatrixObject(name);
+    if (mo->gpu) mo->gpu->acquireHostRead();
+    if (!mo->host_valid) fail(SYSML_E_INVALID, "variable %s has no valid copy", name);
+    mo->examSparsity();
+    if (is_sparse) *is_sparse = mo->host_sparse ? 1 : 0;
+  })
 }
 
 int sysml_b200_ec_stats(sysml_b200_ec* ec, int64_t* out9) {

@@ -102,10 +102,25 @@ class ExecutionContext:
     def execute(self, instruction):
         self._check(self._lib.sysml_b200_ec_execute(self.handle, instruction.encode("utf-8")))
 
+    def setEvictionPolicy(self, policy):
+        """sysml.gpu.eviction.policy: 'lru' | 'lfu' | 'min_evict' | 'mru' (DMLScript.EvictionPolicy)."""
+        self._check(self._lib.sysml_b200_ec_set_eviction_policy(self.handle, policy.encode()))
+
+    def examSparsity(self, name):
+        """MatrixBlock.examSparsity on the host block of `name`; returns True when it is now held as CSR."""
+        f = C.c_int()
+        self._check(self._lib.sysml_b200_ec_exam_sparsity(self.handle, name.encode(), C.byref(f)))
+        return bool(f.value)
+
     def stats(self):
         out = (C.c_int64 * 9)()
         self._check(self._lib.sysml_b200_ec_stats(self.handle, out))
         return dict(zip(self.STAT_NAMES, list(out)))
+
+
+def eval_sparse_format_in_memory(rows, cols, nnz):
+    """MatrixBlock.evalSparseFormatInMemory (MatrixBlock.java:1001-1015)."""
+    return bool(native.load().sysml_b200_eval_sparse_format_in_memory(int(rows), int(cols), int(nnz)))
 
 
 def parse_instruction(instruction):

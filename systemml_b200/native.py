@@ -91,6 +91,9 @@ SIGNATURES = {
     "sysml_b200_ec_get_matrix_dense": (ci, [vp, C.c_char_p, vp]),
     "sysml_b200_ec_get_scalar": (ci, [vp, C.c_char_p, pdbl]),
     "sysml_b200_ec_stats": (ci, [vp, pi64]),
+    "sysml_b200_ec_set_eviction_policy": (ci, [vp, C.c_char_p]),
+    "sysml_b200_eval_sparse_format_in_memory": (ci, [i64, i64, i64]),
+    "sysml_b200_ec_exam_sparsity": (ci, [vp, C.c_char_p, pint]),
 }
 
 

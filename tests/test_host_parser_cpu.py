@@ -44,3 +44,17 @@ def test_parse_errors(ins, code, frag):
     with pytest.raises(native.NativeError) as ei:
         parse_instruction(ins)
     assert ei.value.code == code and frag in str(ei.value)
+
+
+def test_eval_sparse_format_in_memory_known_answers():
+    """MatrixBlock.evalSparseFormatInMemory (MatrixBlock.java:1001-1015) by hand:
+    sparse iff nnz/rows/cols < 0.4 AND the MCSR estimate 84 + 8*rows + rlen*(76 + 12*cnnz) is below 44 + 8*rows*cols,
+    with cnnz = max(4, ceil(sp*cols)), rlen = min(rows, ceil(sp*rows*cols)) (SparseBlockMCSR.java:101-116)."""
+    from systemml_b200.execution_context import eval_sparse_format_in_memory as ev
+    assert ev(1000, 1000, 1000) is True          # sp 0.001: 84 + 8000 + 1000*(76+48) = 132084 < 8000044
+    assert ev(1000, 1000, 399_999) is True       # sp just under 0.4: 84 + 8000 + 1000*(76+4800) = 4884084 < 8000044
+    assert ev(1000, 1000, 400_000) is False      # sp == 0.4 is not below the turn point
+    assert ev(1000, 1, 100) is False             # column vector: 84 + 8000 + 100*(76+48) = 20484 > 8044
+    assert ev(100, 4, 40) is False               # sp 0.1: 84 + 800 + 40*124 = 5844 > 3244
+    assert ev(10, 1000, 100) is True             # sp 0.01: cnnz 10, rlen 10: 84 + 80 + 10*196 = 2124 < 80044
+    assert ev(0, 10, 0) is False

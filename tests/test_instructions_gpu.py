@@ -201,3 +201,128 @@ def test_borrowed_device_matrix(gctx, ec):
     assert np.array_equal(X.to_host(), Xh)
     assert ec.stats()["h2d"] == 1               # only v was uploaded
     X.free()
+
+
+def test_matmult_all_transpose_flags_for_every_sparsity_pair(ec):
+    """LibMatrixCuMatMult.matmult handles the four (leftT, rightT) combinations for dense/sparse operands alike
+    (LibMatrixCuMatMult.java:139-229); so must ba+*.  Also: the output carries its exact nnz (LibMatrixMult.java:112)."""
+    rng = {"A": O.java_test_matrix(120, 90, -1, 1, 0.08, 11), "At": O.java_test_matrix(90, 120, -1, 1, 0.08, 12),
+           "B": O.java_test_matrix(90, 70, -1, 1, 0.1, 13), "Bt": O.java_test_matrix(70, 90, -1, 1, 0.1, 14)}
+    for a_sparse in (False, True):
+        for b_sparse in (False, True):
+            for lt in (False, True):
+                for rt in (False, True):
+                    A, B = rng["At" if lt else "A"], rng["Bt" if rt else "B"]
+                    for nm, M, sp in (("A", A, a_sparse), ("B", B, b_sparse)):
+                        if sp:
+                            ec.setMatrixCSR(nm, *O.dense_to_csr(M), M.shape)
+                        else:
+                            ec.setMatrix(nm, M)
+                    ec.execute(inst("ba+*", mat("A"), mat("B"), mat("C"), str(lt).lower(), str(rt).lower()))
+                    exp = (A.T if lt else A).astype(np.longdouble) @ (B.T if rt else B).astype(np.longdouble)
+                    got = ec.getMatrix("C")
+                    what = "ba+* sparse=(%s,%s) lt=%s rt=%s" % (a_sparse, b_sparse, lt, rt)
+                    assert got.shape == (120, 70), what
+                    assert np.max(np.abs(got - exp.astype(np.float64))) < 1e-13, what
+                    assert ec.getMatrixDims("C")[2] == int(np.count_nonzero(got)), what
+
+
+def test_sparse_operands_of_cellwise_unary_axpy_scalar_are_densified(ec):
+    """LibMatrixCUDA.getDensePointer converts a CSR operand with sparseToDense and proceeds
+    (LibMatrixCUDA.java:655-664, 1382-1383); the results equal the dense-input results bit for bit."""
+    X = O.java_test_matrix(300, 40, -1, 1, 0.1, 21)
+    Y = O.java_test_matrix(300, 40, -1, 1, 0.2, 22)
+    csr = lambda M: O.dense_to_csr(M) + (M.shape,)
+
+    def fresh():
+        ec.setMatrixCSR("X", *csr(X))
+        ec.setMatrixCSR("Y", *csr(Y))
+    fresh()
+    ec.execute(inst("+", mat("X"), mat("Y"), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), X + Y)
+    fresh()
+    ec.execute(inst("*", mat("X"), literal(3.0), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), X * 3.0)
+    fresh()
+    ec.execute(inst("+*", mat("X"), literal(0.5), mat("Y"), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), O.axpy(X, Y, 0.5))
+    fresh()
+    ec.execute(inst("abs", mat("X"), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), np.abs(X))
+    fresh()
+    ec.execute(inst("r'", mat("X"), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), X.T)
+    assert np.array_equal(ec.getMatrix("X"), X), "the converted input still holds the same values"
+    # mmchain with sparse v / w
+    v = O.java_test_matrix(40, 1, 0, 1, 0.5, 23)
+    w = O.java_test_matrix(300, 1, 0, 1, 0.5, 24)
+    ec.setMatrix("Xd", X)
+    ec.setMatrixCSR("v", *csr(v))
+    ec.setMatrixCSR("w", *csr(w))
+    ec.execute(inst("mmchain", mat("Xd"), mat("v"), mat("w"), mat("q"), "XtwXv"))
+    assert_equal_matrices(O.mmchain_dense(X, v, w, 1, 1), ec.getMatrix("q"))
+
+
+def test_exam_sparsity_of_a_matmult_result(ec):
+    """MatrixBlock.examSparsity after matrixMult (LibMatrixMult.java:113): a result with few non-zeros becomes CSR."""
+    A = np.zeros((200, 300))
+    A[5, 7], A[17, 3], A[199, 299] = 2.0, -1.5, 4.0
+    B = np.eye(300)
+    ec.setMatrix("A", A)
+    ec.setMatrix("B", B)
+    ec.execute(inst("ba+*", mat("A"), mat("B"), mat("C"), "false", "false"))
+    assert ec.getMatrixDims("C") == (200, 300, 3)
+    assert ec.examSparsity("C") is True
+    assert np.array_equal(ec.getMatrix("C"), A)
+    D = O.rand_uniform(200 * 300, seed=5).reshape(200, 300)
+    ec.setMatrix("D", D)
+    ec.execute(inst("ba+*", mat("D"), mat("B"), mat("E"), "false", "false"))
+    assert ec.examSparsity("E") is False and ec.getMatrixDims("E")[2] == 60000
+
+
+@pytest.mark.parametrize("policy,order,victim", [("lru", "ABS", "A"), ("mru", "ASB", "B"), ("lfu", "AASSB", "B"), ("min_evict", "ABS", "S")])
+def test_eviction_policies(policy, order, victim):
+    """sysml.gpu.eviction.policy (DMLScript.EvictionPolicy; GPUComparator, GPUMemoryManager.java:531-571; timestamps per
+    GPUObject.updateReleaseLocks, GPUObject.java:650-667): which unlocked matrix leaves the device when the next one does
+    not fit.  A, B: 8 MB, S: 4 MB, budget 22 MB, request 4 MB.  LRU: the oldest release; MRU: the latest; LFU: the fewest
+    releases; MIN_EVICT: the smallest block that is at least as large as the request."""
+    big, small = (1000, 1000), (500, 1000)
+    with ExecutionContext(0, memory_limit=22 << 20) as ec:
+        ec.setEvictionPolicy(policy)
+        ec.setMatrix("A", np.full(big, 1.0))
+        ec.setMatrix("B", np.full(big, 2.0))
+        ec.setMatrix("S", np.full(small, 3.0))
+        ec.setMatrix("N", np.full(small, 4.0))
+        for nm in order:
+            ec.execute(inst("uak+", mat(nm), scalar_var("s")))
+        assert ec.stats()["evictions"] == 0
+        ec.execute(inst("uak+", mat("N"), scalar_var("s")))   # needs 4 MB: exactly one eviction
+        assert ec.stats()["evictions"] == 1
+        for nm in [x for x in "ABS" if x != victim]:          # the survivors are still resident: no upload
+            h0 = ec.stats()["h2d"]
+            ec.execute(inst("uamax", mat(nm), scalar_var("t")))
+            assert ec.stats()["h2d"] == h0, "%s should still be resident under %s" % (nm, policy)
+        h0 = ec.stats()["h2d"]
+        ec.execute(inst("uamax", mat(victim), scalar_var("t")))
+        assert ec.stats()["h2d"] == h0 + 1, "%s should have been evicted under %s" % (victim, policy)
+        assert ec.getScalar("t") == {"A": 1.0, "B": 2.0, "S": 3.0}[victim]
+    with ExecutionContext(0) as e3:
+        with pytest.raises(native.NativeError):
+            e3.setEvictionPolicy("random")
+
+
+def test_csr_upload_under_memory_pressure_does_not_evict_itself():
+    """A CSR upload takes three allocations; under pressure the second or third one evicts, and the half-built matrix
+    must not be the victim (the reference publishes the CSRPointer only when complete, CSRPointer.java:271-287)."""
+    X = O.java_test_matrix(4000, 500, -1, 1, 0.25, 31)     # nnz ~ 500k: val 4 MB, colind 2 MB, rowptr 16 KB
+    rp, ci, va = O.dense_to_csr(X)
+    v = O.rand_uniform(500, seed=2).reshape(500, 1)
+    with ExecutionContext(0, memory_limit=11 << 20) as ec:
+        ec.setMatrix("F", np.ones((1000, 1000)))           # 8 MB resident and unlocked
+        ec.execute(inst("uak+", mat("F"), scalar_var("s")))
+        ec.setMatrixCSR("X", rp, ci, va, X.shape)
+        ec.setMatrix("v", v)
+        ec.execute(inst("ba+*", mat("X"), mat("v"), mat("Xv"), "false", "false"))
+        assert ec.stats()["evictions"] >= 1
+        assert_equal_matrices(O.matmult_csr_dense(rp, ci, va, X.shape, v, 1)[0], ec.getMatrix("Xv"))
+        assert np.array_equal(ec.getMatrix("X"), X)
