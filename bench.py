@@ -59,6 +59,7 @@ def parse():
     ap.add_argument("--no-tsmm", action="store_true", help="skip the auxiliary tsmm measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C3 / C4 / C5 block (N = 1 only)")
     ap.add_argument("--three-launch", action="store_true", help="round-1 step: mmchain(+exchange), then the fused m-vector kernel as a third launch")
     ap.add_argument("--unfused-tail", action="store_true", help="run the m-vector CG algebra as ~11 separate instructions instead of the fused kernel")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
@@ -609,6 +610,19 @@ def main():
                 "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_launch,
                 "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms / instr_ms_per_step, "instrumented_ms_per_step": instr_ms_per_step}
+    # ---------------- BASELINE configs C3, C4, C5 at their actual sizes (N = 1): per-op rooflines + end-to-end runs ----------------
+    configs = None
+    if world == 1 and not args.no_configs:
+        del tX, tw
+        torch.cuda.empty_cache()     # the library allocates with cudaMalloc: torch must give the 80 GB back first
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_configs
+        dmma_peak = 37.0
+        try:
+            dmma_peak = float(json.load(open(os.path.join(ROOT, "profiles", "fp64_peak.json")))["dmma_peak_tflops"])
+        except Exception:
+            pass
+        configs = bench_configs.run_configs(g, peak, dmma_peak, cpu=not args.no_cpu)
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu:
@@ -624,6 +638,8 @@ def main():
         }
         if tsmm:
             line["tsmm"] = tsmm
+        if configs:
+            line["configs"] = configs
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.cuda.synchronize()

@@ -409,6 +409,14 @@ int sysml_b200_cg_step_dense(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const d
  * ---------------------------------------------------------------------------------------------- */
 int sysml_b200_rand_uniform(sysml_b200_ctx* ctx, double* out, int64_t len, uint64_t seed, int64_t offset,
                             double lo, double hi);
+/* Synthetic CSR in the shape of BASELINE config C3 (every cell non-zero with a small probability, i.e. ~Poisson(mean)
+ * entries per row; the CPU analogue is Rand(..., sparsity=p), LibMatrixDatagen.java).  Rows [row_offset, row_offset+rows)
+ * of the global matrix: a row depends on (seed, global row index) only, so shards compose.  Columns are sorted and
+ * distinct within a row, values are U(-1,1) and never zero.  Two calls, like dense_to_csr: with colind == NULL the
+ * row pointers (rows+1 entries) and *h_nnz are produced; the second call fills colind / val of that size.
+ * No reference GPU counterpart; used by bench.py and the tests (bit-identical CPU twin in oracle/). */
+int sysml_b200_rand_csr(sysml_b200_ctx* ctx, int64_t rows, int64_t cols, double mean_per_row, uint64_t seed,
+                        int64_t row_offset, int32_t* rowptr, int32_t* colind, double* val, int64_t* h_nnz);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

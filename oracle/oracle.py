@@ -67,6 +67,8 @@ def lib():
         L.orc_dense_to_csr.argtypes = [dp, i64, i64, lp, C.c_void_p, C.c_void_p]
         L.orc_dense_to_csr.restype = i64
         L.orc_rand_uniform.argtypes = [dp, i64, C.c_uint64, i64, C.c_double, C.c_double]
+        L.orc_rand_csr.argtypes = [i64, i64, C.c_double, C.c_uint64, i64, lp, C.c_void_p, C.c_void_p]
+        L.orc_rand_csr.restype = i64
         _lib = L
     return _lib
 
@@ -123,6 +125,16 @@ def rand_uniform(length, seed, offset=0, lo=-1.0, hi=1.0):
     out = np.empty(length, dtype=np.float64)
     lib().orc_rand_uniform(out, length, seed, offset, lo, hi)
     return out
+
+
+def rand_csr(rows, cols, mean, seed, row_offset=0):
+    """CPU twin of sysml_b200_rand_csr: (rowptr int64, colind int32, val float64), bit-identical to the device generator."""
+    rp = np.zeros(rows + 1, dtype=np.int64)
+    nnz = lib().orc_rand_csr(rows, cols, float(mean), seed, row_offset, rp, None, None)
+    ci = np.empty(max(nnz, 1), dtype=np.int32)
+    va = np.empty(max(nnz, 1), dtype=np.float64)
+    lib().orc_rand_csr(rows, cols, float(mean), seed, row_offset, rp, ci.ctypes.data_as(C.c_void_p), va.ctypes.data_as(C.c_void_p))
+    return rp, ci[:nnz], va[:nnz]
 
 
 def mmchain_dense(X, v, w, ct, k=1):

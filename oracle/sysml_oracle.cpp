@@ -786,6 +786,7 @@ i64 orc_matmult_csr_dense(const i64* rp, const int* ci, const double* va, const 
 // out: values only (the Kahan correction cells the reference keeps beside them go to `corr` when
 //      non-null, same length as out).  MAXINDEX/MININDEX: out = 1-based index, corr = the value.
 // ---------------------------------------------------------------------------------------------
+
 }  // extern "C"
 
 static void agg_dense_range(const double* a, i64 n, int op, int dir, double* out, double* corr, i64 rl, i64 ru) {
@@ -1187,6 +1188,46 @@ void orc_rand_uniform(double* out, i64 len, uint64_t seed, i64 offset, double lo
     double u = (double)(h >> 11) * 0x1.0p-53;  // [0,1)
     out[i] = lo + (hi - lo) * u;
   }
+}
+
+
+// CPU twin of sysml_b200_rand_csr (systemml_b200/csrc/rand.cu): same hashes, same separately rounded recurrences.
+static inline int orc_csr_row_count(uint64_t hr, double mean, double p0, i64 cols) {
+  const uint64_t h = splitmix64(hr);
+  const double u0 = (double)(h >> 11) * 0x1.0p-53;
+  double pk = p0, cdf = p0;
+  int k = 0;
+  const int cap = (int)(cols < 4096 ? cols : 4096);
+  while (cdf <= u0 && k < cap) {
+    k++;
+    pk = (pk * mean) / (double)k;
+    cdf = cdf + pk;
+    if (pk < 1e-300) break;
+  }
+  return k;
+}
+// rp: rows+1 int64 (filled here); returns nnz.  Call with ci == NULL first to size the arrays.
+i64 orc_rand_csr(i64 rows, i64 cols, double mean, uint64_t seed, i64 row_offset, i64* rp, int* ci, double* va) {
+  const uint64_t s = splitmix64(seed ^ 0xC5A1ull);
+  const double p0 = std::exp(-mean);
+  rp[0] = 0;
+  for (i64 r = 0; r < rows; r++) rp[r + 1] = rp[r] + orc_csr_row_count(splitmix64(s ^ (uint64_t)(row_offset + r)), mean, p0, cols);
+  if (!ci || !va) return rp[rows];
+#pragma omp parallel for schedule(static)
+  for (i64 r = 0; r < rows; r++) {
+    const uint64_t hr = splitmix64(s ^ (uint64_t)(row_offset + r));
+    const i64 lo = rp[r];
+    const int c = (int)(rp[r + 1] - lo);
+    if (c <= 0) continue;
+    const uint64_t W = (uint64_t)(cols / c);
+    for (int j = 0; j < c; j++) {
+      const uint64_t hc = splitmix64(hr + 2ull * (uint64_t)j + 1ull), hv = splitmix64(hr + 2ull * (uint64_t)j + 2ull);
+      ci[lo + j] = (int)((uint64_t)j * W + hc % W);
+      const double u = (double)((hv >> 11) | 1ull) * 0x1.0p-53;
+      va[lo + j] = -1.0 + 2.0 * u;
+    }
+  }
+  return rp[rows];
 }
 
 }  // extern "C"

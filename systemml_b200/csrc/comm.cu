@@ -233,6 +233,26 @@ int launch_finish(sysml_b200_ctx* ctx, int ncta, bool pdl, const double* partial
   return SYSML_OK;
 }
 
+// With lazy module loading (the CUDA 12 default) the first launch of a kernel loads it, and loading may wait for work
+// already running on the device.  An exchange kernel that is spinning for a peer on the same device -- ranks that
+// share a GPU, or a peer whose first call needs a variant this rank has not used yet -- would then never see that
+// peer arrive.  So every variant is made resident when a communicator is created, before any exchange can be in flight.
+template <int ROP, int NS, bool CG>
+cudaError_t preload_one() {
+  cudaFuncAttributes fa;
+  return cudaFuncGetAttributes(&fa, finish_exchange_kernel<ROP, NS, CG>);
+}
+cudaError_t preload_exchange_kernels() {
+  cudaError_t e = preload_one<0, 32, true>();
+  if (e == cudaSuccess) e = preload_one<0, 32, false>();
+  if (e == cudaSuccess) e = preload_one<1, 32, false>();
+  if (e == cudaSuccess) e = preload_one<2, 32, false>();
+  if (e == cudaSuccess) e = preload_one<0, 1, false>();
+  if (e == cudaSuccess) e = preload_one<1, 1, false>();
+  if (e == cudaSuccess) e = preload_one<2, 1, false>();
+  return e;
+}
+
 }  // namespace
 
 // used by mmchain.cu (fused finish) and by sysml_b200_allreduce below.  comm may be null when cg is given
@@ -326,6 +346,8 @@ int sysml_b200_comm_create(sysml_b200_ctx* ctx, int rank, int world, int64_t max
   c->host_err[0] = c->host_err[1] = 0;
   e = cudaHostGetDevicePointer((void**)&c->dev_err, c->host_err, 0);
   if (e != cudaSuccess) return fail(SYSML_E_CUDA, "cudaHostGetDevicePointer", e);
+  e = preload_exchange_kernels();
+  if (e != cudaSuccess) return fail(SYSML_E_CUDA, "loading the exchange kernels", e);
   if (handle_out64) {
     cudaIpcMemHandle_t h;
     e = cudaIpcGetMemHandle(&h, c->local);

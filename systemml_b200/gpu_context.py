@@ -109,6 +109,21 @@ class GPUContext:
         return o
 
 
+def _rand_csr(gctx, rows, cols, mean, seed, row_offset=0):
+    """GPUObject holding rows [row_offset, row_offset+rows) of the synthetic CSR matrix (sysml_b200_rand_csr)."""
+    rowptr = gctx.allocate((rows + 1) * 4)
+    nnz = C.c_int64()
+    gctx.call("sysml_b200_rand_csr", rows, cols, float(mean), seed, row_offset, C.c_void_p(rowptr), None, None, C.byref(nnz))
+    o = GPUObject(gctx, rows, cols)
+    o.csr = CSRPointer.adopt(gctx, rows, rowptr, gctx.allocate(max(nnz.value, 1) * 4), gctx.allocate(max(nnz.value, 1) * 8), nnz.value)
+    gctx.call("sysml_b200_rand_csr", rows, cols, float(mean), seed, row_offset, C.c_void_p(rowptr), C.c_void_p(o.csr.colInd),
+              C.c_void_p(o.csr.val), None)
+    return o
+
+
+GPUContext.rand_csr = _rand_csr
+
+
 class CSRPointer:
     """val / rowPtr / colInd device arrays + nnz (CSRPointer.java:76-100); int32 indices, 0-based."""
 

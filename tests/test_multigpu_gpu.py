@@ -136,7 +136,7 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
         big = big + O.rand_uniform(200_000, seed=30 + k)
     assert np.array_equal(r[0]["big"], big)
     # sharded workloads: identical on both ranks, equal to the single-process CPU twins (oracle kernels)
-    from tests.test_algorithms_gpu import cpu_glm_poisson_log, cpu_linreg_cg
+    from oracle.algorithms_cpu import cpu_glm_poisson_log, cpu_linreg_cg
     na, ma = 60_000, 200
     Xa = O.rand_uniform(na * ma, seed=40).reshape(na, ma)
     ya = Xa @ O.rand_uniform(ma, seed=41) + 0.1 * O.rand_uniform(na, seed=42)

@@ -281,3 +281,19 @@ def test_sparse_output_edge_cases(gctx):
     rp, ci, va = L.sparseTranspose(gctx, "r'", dAt).to_host()
     rp0, ci0, va0 = dA.to_host()
     assert np.array_equal(rp, rp0) and np.array_equal(ci, ci0) and np.array_equal(va, va0)
+
+
+def test_device_csr_generator_matches_cpu_twin(gctx):
+    """sysml_b200_rand_csr (BASELINE config C3's shape: ~Poisson(mean) entries per row) against its CPU twin, bit for bit
+    -- structure (int32, exact) and values -- including a row shard taken with row_offset."""
+    for rows, cols, mean, seed, off in ((20_000, 10_000, 10, 2, 0), (5_000, 10_000, 10, 2, 7_000), (3_000, 64, 3.5, 9, 0), (100, 5, 40, 1, 0)):
+        o = gctx.rand_csr(rows, cols, mean, seed, row_offset=off)
+        rp, ci, va = o.to_host()
+        erp, eci, eva = O.rand_csr(rows, cols, mean, seed, row_offset=off)
+        assert np.array_equal(rp.astype(np.int64), erp), (rows, cols, mean)
+        assert np.array_equal(ci, eci) and np.array_equal(va, eva)
+        assert o.csr.nnz == int(erp[-1])
+        for r in range(0, rows, max(rows // 50, 1)):        # sorted, distinct, in range
+            c = ci[rp[r]:rp[r + 1]]
+            assert np.all(np.diff(c) > 0) and (c.size == 0 or (c[0] >= 0 and c[-1] < cols))
+        o.free()
