@@ -344,6 +344,35 @@ int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
                             const double* val, int64_t rows, int64_t cols, double* X);
 
 /* ------------------------------------------------------------------------------------------------
+ * Column-ordered copy of a constant CSR matrix ("panel CSC") for t(X) %*% y and the second half of sparse mmchain.
+ * Replaces the scatter of LibMatrixMult.matrixMultChainSparse (LibMatrixMult.java:1655-1684) and of the VM form of
+ * matrixMultSparseDense (:1262-1286) -- and, on the reference GPU path, cusparseDcsrmv with the transpose flag
+ * (LibMatrixCuMatMult.java:313-341) -- by a gather without atomics whose result is bit-identical run to run.
+ * The copy costs 12 bytes per non-zero (like CSR) and is worth building when X is used more than once, as the
+ * iterative algorithms do; the CSR entry points above remain the path for one-shot operands.
+ * Layout: rows in panels of panel_rows (<= 65536; 8192 is a good value), entries of a panel sorted by (column, row):
+ *   p_val[nnz] f64, p_lrow[nnz] u16 (row inside the panel), p_col[nnz] u16 (column, so cols <= 65536),
+ *   slice_ptr[sysml_b200_pcsc_slice_entries(rows, panel_rows)] i32 (32 column slices per panel + 1).
+ * All arrays are allocated by the caller.  cols + panel_rows doubles must fit in shared memory (SYSML_E_LIMIT).
+ *   csr_to_pcsc        : builds the copy (one stable radix sort; scratch from the context's workspace).
+ *   matmult_pcsc_vm    : out[cols] = t(X) %*% (y [* w | - w]);  w_op 0 none, 1 multiply, 2 subtract.
+ *   mmchain_csr_pcsc   : out = t(X) %*% (w * (X %*% v)) etc.; X %*% v runs on the CSR copy into tmp_n (rows doubles,
+ *                        caller-owned), the weights are applied while a panel of it is parked in shared memory.
+ * ---------------------------------------------------------------------------------------------- */
+int64_t sysml_b200_pcsc_slice_entries(int64_t rows, int panel_rows);
+int sysml_b200_csr_to_pcsc(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                           int64_t rows, int64_t cols, int64_t nnz, int panel_rows, double* p_val,
+                           uint16_t* p_lrow, uint16_t* p_col, int32_t* slice_ptr);
+int sysml_b200_matmult_pcsc_vm(sysml_b200_ctx* ctx, const double* p_val, const uint16_t* p_lrow,
+                               const uint16_t* p_col, const int32_t* slice_ptr, int64_t rows, int64_t cols,
+                               int panel_rows, const double* y, const double* w, int w_op, double* out);
+int sysml_b200_mmchain_csr_pcsc(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
+                                const double* val, const double* p_val, const uint16_t* p_lrow,
+                                const uint16_t* p_col, const int32_t* slice_ptr, int panel_rows, const double* v,
+                                const double* w, double* tmp_n, double* out, int64_t n, int64_t m,
+                                int chain_type);
+
+/* ------------------------------------------------------------------------------------------------
  * Multi-GPU sum exchange over NVLink peer memory (one process per GPU on one box, world <= 8).
  * Replaces the aggregation step of SystemML's distributed tsmm / mmchain plan, RDDAggregateUtils.sumStable
  * (J/runtime/instructions/spark/utils/RDDAggregateUtils.java:58-70, used by MapmmChainSPInstruction and

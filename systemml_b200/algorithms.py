@@ -158,7 +158,10 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
             g.call("sysml_b200_matmult_dense", _p(X), _p(v), _p(out), n, m, m, 1, 0, 0)
 
     def xt_times(yv, out):      # out = t(X) %*% yv
-        if sparse:
+        pc = X.columnOrderedCopy() if sparse else None
+        if pc is not None:          # X is constant across the iterations: gather over its column-ordered copy
+            g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, _p(yv), None, 0, _p(out))
+        elif sparse:
             g.call("sysml_b200_matmult_csr_dense", C.c_void_p(X.csr.rowPtr), C.c_void_p(X.csr.colInd), C.c_void_p(X.csr.val),
                    _p(yv), _p(out), n, m, n, 1, 1)
         else:

@@ -40,7 +40,7 @@ def test_glm_poisson_log_end_to_end(gctx):
     exp = cpu_glm_poisson_log(X, y, 0.0, 6, 15, 1e-10, O.num_threads())
     dX, dy = gctx.dense(X), gctx.dense(y.reshape(n, 1))
     got, inner = glm_poisson_log(gctx, dX, dy, reg=0.0, outer_iters=6, inner_iters=15, inner_tol=1e-10)
-    assert_equal_matrices(exp, got, rel=1e-8, what="GLM beta")
+    assert_equal_matrices(exp, got, rel=1e-9, what="GLM beta")
     assert np.max(np.abs(got - btrue)) < 0.05
     dX.free()
     dy.free()
@@ -67,7 +67,7 @@ def test_l2svm_end_to_end(gctx, sparse):
         w, it, obj = l2svm(gctx, dX, dY, reg=1.0, tol=0.001, maxiter=20, fused=fused)
         assert it == exp_it, (fused, it, exp_it)
         assert abs(obj - exp_obj) <= 1e-9 * abs(exp_obj)
-        assert_equal_matrices(exp_w, w, rel=1e-7, what="l2svm weights (fused=%s)" % fused)
+        assert_equal_matrices(exp_w, w, rel=1e-9, what="l2svm weights (fused=%s)" % fused)
     assert np.mean(np.sign(X @ w) == Y) > 0.9  # and it separates the classes
 
 
@@ -101,6 +101,6 @@ def test_multilogreg_end_to_end(gctx):
     gotB, it, obj = multilogreg(gctx, gctx.dense(X), gctx.dense(Y), gctx.dense(y_last), reg=1.0, tol=1e-6, maxiter=12)
     assert it == exp_it
     assert abs(obj - exp_obj) <= 1e-9 * abs(exp_obj)
-    assert_equal_matrices(expB, gotB, rel=1e-6, what="MultiLogReg B")
+    assert_equal_matrices(expB, gotB, rel=1e-9, what="MultiLogReg B")
     pred = np.argmax(np.hstack([X @ gotB, np.zeros((N, 1))]), axis=1)
     assert np.mean(pred == labels) > 0.6

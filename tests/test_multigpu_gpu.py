@@ -146,6 +146,6 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
     assert assert_close(eb, r[0]["linreg_beta"], 1e-9)
     yg = np.exp(Xa @ O.rand_uniform(ma, seed=43, lo=-0.05, hi=0.05))
     egb = cpu_glm_poisson_log(Xa, yg, 0.0, 4, 20, 1e-8, O.num_threads())
-    assert assert_close(egb, r[0]["glm_beta"], 1e-8)
+    assert assert_close(egb, r[0]["glm_beta"], 1e-9)
     exp_cs = O.agg_unary_dense(X, O.SUM, O.COL, 4)
     assert np.max(np.abs(r[0]["cs"] - exp_cs)) < 1e-9 * np.max(np.abs(exp_cs)) + 1e-9

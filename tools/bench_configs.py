@@ -69,6 +69,20 @@ def config_c3(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     ops.append(_op("mmchain XtwXv", a, b, hbm, dmma, nbytes=spb + 8.0 * n + 8.0 * m, flops=4.0 * nnz))
     a, b = _timeit(g, lambda: g.call("sysml_b200_agg_unary_csr", *csr, n, m, 0, 1, _p(o_r)), reps)
     ops.append(_op("rowSums", a, b, hbm, dmma, nbytes=12.0 * nnz + 4.0 * (n + 1) + 8.0 * n))
+    # the same two products through the column-ordered copy (csrc/pcsc.cu): what the iterative algorithms use from the
+    # second iteration on
+    from systemml_b200.gpu_context import PCSCPointer
+    g.sync()
+    t0 = time.perf_counter()
+    pc = PCSCPointer(g, X.csr, n, m)
+    g.sync()
+    build_s = time.perf_counter() - t0
+    a, b = _timeit(g, lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, _p(y), None, 0, _p(o_c)), reps)
+    ops.append(_op("t(X)%*%y [column-ordered copy]", a, b, hbm, dmma, nbytes=12.0 * nnz + 8.0 * n + 8.0 * m, flops=2.0 * nnz))
+    a, b = _timeit(g, lambda: g.call("sysml_b200_mmchain_csr_pcsc", *csr, *pc.args(), pc.panel_rows, _p(v), _p(w), _p(o_r), _p(o_c), n, m, 1), reps)
+    ops.append(_op("mmchain XtwXv [CSR + column-ordered copy]", a, b, hbm, dmma, nbytes=spb + 8.0 * n + 8.0 * m, flops=4.0 * nnz))
+    ops[-1]["note"] = "algorithmic bytes as for the one-pass form; this form reads X twice (24 bytes per non-zero) and writes/reads an n-vector"
+    pc.deallocate()
     # labels from a planted separator, then l2-svm.dml (icpt=0 reg=1 tol=0.001 maxiter=20, scripts/perftest/runL2SVM.sh style)
     g.call("sysml_b200_matmult_csr_dense", *csr, _p(v), _p(o_r), n, m, m, 1, 0)
     Y = g.empty(n, 1)
@@ -84,6 +98,7 @@ def config_c3(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     g.sync()
     dt = time.perf_counter() - t0
     res = {"shape": [n, m], "nnz": nnz, "layout": "CSR int32, ~Poisson(10) entries per row (sysml_b200_rand_csr seed 2)", "ops": ops,
+           "column_ordered_copy_build_seconds": round(build_s, 3),
            "algorithm": {"name": "L2SVM (l2-svm.dml, icpt=0 reg=1 tol=0.001 maxiter=20)", "outer_iterations": iters, "seconds": round(dt, 4),
                          "objective": obj}}
     if cpu:
@@ -160,7 +175,7 @@ def config_c4(g, hbm, dmma, scale=1.0, cpu=True, reps=3):
         Wh = O.rand_uniform(D * (K + 1), seed=7).reshape(D, K + 1)
         labh = np.argmax(Xh @ Wh, axis=1)
         Yh = (labh[:, None] == np.arange(K)[None, :]).astype(np.float64)
-        yl = (labh == K).astype(np.float64)
+        yl = (labh == K).astype(np.float64).reshape(ns, 1)
         t0 = time.perf_counter()
         _, it_c, _ = cpu_multilogreg(Xh, Yh, yl, 1.0, 1e-6, 5, 0)
         dc = time.perf_counter() - t0
@@ -188,8 +203,8 @@ def config_c5(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     g.call("sysml_b200_axpy", _p(X), _p(noise), 1.0, _p(X), n, m, 0)
     for o in (noise, asg, ids):
         o.free()
-    C0 = g.rand(k, m, seed=8)
-    g.call("sysml_b200_binary_mm", _p(C0), _p(centers), _p(C0), k, m, 0, L.BINARY_OPS["+"])
+    C0 = g.empty(k, m)      # initial centroids: the first k data points (several of them fall into the same blob)
+    g.call("sysml_b200_d2d", _p(C0), _p(X), 8 * k * m)
     D, oKM = g.empty(n, k), g.empty(k, m)
     ops = []
     a, b = _timeit(g, lambda: g.call("sysml_b200_matmult_dense", _p(X), _p(C0), _p(D), n, m, k, m, 0, 1), reps)
