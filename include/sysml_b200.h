@@ -97,6 +97,8 @@ typedef struct sysml_b200_ctx sysml_b200_ctx;
 #define SYSML_BCAST_NONE 0 /* B is rows x cols          */
 #define SYSML_BCAST_COL 1  /* B is rows x 1 (col vector) */
 #define SYSML_BCAST_ROW 2  /* B is 1 x cols (row vector) */
+#define SYSML_BCAST_OUTER 3 /* A is rows x 1, B is 1 x cols, C[i,j] = A[i] op B[j]: BinaryAccessType.OUTER_VECTOR_VECTOR
+                              (LibMatrixBincell.java:150-163; safeBinaryVVGeneric :565-589), binary_mm only */
 
 /* unary opcodes (kernels matrix_exp ... matrix_sigmoid, SystemML.cu:1541-1960;
  * LibMatrixCUDA.java:1969-2290) */
@@ -185,7 +187,11 @@ int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const double* X, const
  *    process exit); no cudaMalloc / cudaFree or other allocating routine is called;
  *  - all calls on one GPU share that array: calls that overlap on the GPU race with each other;
  *  - the first call on each device resolves the array's device address; issue it before starting any
- *    stream capture. */
+ *    stream capture;
+ *  - CUDA places device code on a GPU lazily by default, so that first call is also the one that makes the
+ *    array (and the kernels) resident: it needs about 2.4 MiB plus code of free device memory.  Make one
+ *    small warm-up call per device right after creating the context, before the card fills up, or run with
+ *    CUDA_MODULE_LOADING=EAGER.  From the second call on, free device memory is the same before and after. */
 #define SYSML_B200_NOALLOC_MAX_COLS 1024
 int sysml_b200_mmchain_dense_noalloc(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w,
                                      double* out, int64_t n, int64_t m, int chain_type);

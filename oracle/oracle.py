@@ -216,6 +216,10 @@ def binary_mm(A, B, op):
     rows, cols = A.shape
     if B.shape == A.shape:
         bc = 0
+    elif cols == 1 and B.shape[0] == 1 and B.shape[1] > 1:   # OUTER_VECTOR_VECTOR (LibMatrixBincell.java:150-163)
+        out = np.empty((rows, B.shape[1]), dtype=np.float64)
+        lib().orc_binary_mm(np.ascontiguousarray(A), np.ascontiguousarray(B), out, rows, B.shape[1], 3, op)
+        return out
     elif B.shape == (rows, 1):
         bc = 1
     elif B.shape == (1, cols):

@@ -1129,8 +1129,10 @@ void orc_binary_mm(const double* A, const double* B, double* C, i64 rows, i64 co
 #pragma omp parallel for schedule(static)
   for (i64 i = 0; i < rows; i++)
     for (i64 j = 0; j < cols; j++) {
+      // bcast 3: OUTER_VECTOR_VECTOR, A is rows x 1 and B is 1 x cols (safeBinaryVVGeneric, LibMatrixBincell.java:565-589)
       double b = bcast == 0 ? B[i * cols + j] : (bcast == 1 ? B[i] : B[j]);
-      C[i * cols + j] = orc_binary_scalar(A[i * cols + j], b, op);
+      double a = bcast == 3 ? A[i] : A[i * cols + j];
+      C[i * cols + j] = orc_binary_scalar(a, b, op);
     }
 }
 void orc_binary_ms(const double* A, double s, double* C, i64 len, int op, int scalar_left) {

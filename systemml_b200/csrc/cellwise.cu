@@ -47,7 +47,8 @@ __global__ void binary_bcast_kernel(const double* __restrict__ A, const double* 
   const i64 dr = stride / cols, dc = stride - dr * cols;
   for (; i < len; i += stride) {
     const double b = (BC == SYSML_BCAST_COL) ? __ldg(B + r) : __ldg(B + c);
-    C[i] = binop<OP>(ldg_stream(A + i), b);
+    const double a = (BC == SYSML_BCAST_OUTER) ? __ldg(A + r) : ldg_stream(A + i);  // outer: A is the column vector
+    C[i] = binop<OP>(a, b);
     r += dr;
     c += dc;
     if (c >= cols) {
@@ -184,6 +185,8 @@ int launch_binary(sysml_b200_ctx* ctx, const double* A, const double* B, double*
     binary_flat_kernel<OP><<<grid_for(ctx, vec2 ? len / 2 + 1 : len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, len, vec2);
   } else if (bcast == SYSML_BCAST_COL) {
     binary_bcast_kernel<OP, SYSML_BCAST_COL><<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, rows, cols);
+  } else if (bcast == SYSML_BCAST_OUTER) {
+    binary_bcast_kernel<OP, SYSML_BCAST_OUTER><<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, rows, cols);
   } else {
     binary_bcast_kernel<OP, SYSML_BCAST_ROW><<<grid_for(ctx, len, 256, 16), 256, 0, ctx->stream>>>(A, B, C, rows, cols);
   }
@@ -221,7 +224,7 @@ extern "C" int sysml_b200_binary_mm(sysml_b200_ctx* ctx, const double* A, const 
                                     int64_t cols, int bcast, int op) {
   SYSML_ENTER(ctx);
   if (rows < 0 || cols < 0) return sysml_set_error(ctx, SYSML_E_DIM, "binary_mm: negative dimension");
-  if (bcast < 0 || bcast > 2) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: bad broadcast code %d", bcast);
+  if (bcast < 0 || bcast > SYSML_BCAST_OUTER) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: bad broadcast code %d", bcast);
   if (rows * cols == 0) return SYSML_OK;
   if (!A || !B || !C) return sysml_set_error(ctx, SYSML_E_INVALID, "binary_mm: null pointer");
   switch (op) {

@@ -916,15 +916,21 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
       if (o1.isMatrix() && o2.isMatrix()) {  // MatrixMatrixArithmeticGPUInstruction.processInstruction (:38-71)
         MatrixObject* in1 = L.in(o1.name, opc);
         MatrixObject* in2 = L.in(o2.name, opc);
+        // LibMatrixBincell.getBinaryAccessType (LibMatrixBincell.java:145-163)
         int bcast = -1;
+        i64 orows = in1->rows, ocols = in1->cols;
         if (in1->rows == in2->rows && in1->cols == in2->cols) bcast = SYSML_BCAST_NONE;
-        else if (in1->rows == in2->rows && in2->cols == 1) bcast = SYSML_BCAST_COL;
-        else if (in2->rows == 1 && in1->cols == in2->cols) bcast = SYSML_BCAST_ROW;
+        else if (in1->cols > 1 && in2->cols == 1 && in1->rows == in2->rows) bcast = SYSML_BCAST_COL;
+        else if (in1->rows > 1 && in1->cols > 1 && in2->rows == 1 && in1->cols == in2->cols) bcast = SYSML_BCAST_ROW;
+        else if (in1->cols == 1 && in2->rows == 1) {  // OUTER_VECTOR_VECTOR: n x 1 op 1 x m -> n x m
+          bcast = SYSML_BCAST_OUTER;
+          ocols = in2->cols;
+        }
         if (bcast < 0) fail(SYSML_E_DIM, "GPU : incompatible dimensions %lldx%lld vs %lldx%lld for %s", in1->rows, in1->cols, in2->rows, in2->cols, opc);
         densify(in1);
         densify(in2);
-        MatrixObject* out = L.out(o3.name, in1->rows, in1->cols, opc);
-        int rc = sysml_b200_binary_mm(ctx, in1->gpu->dense, in2->gpu->dense, out->gpu->dense, in1->rows, in1->cols, bcast, binaryOpcode(pi.opcode));
+        MatrixObject* out = L.out(o3.name, orows, ocols, opc);
+        int rc = sysml_b200_binary_mm(ctx, in1->gpu->dense, in2->gpu->dense, out->gpu->dense, orows, ocols, bcast, binaryOpcode(pi.opcode));
         check(rc);
       } else if ((o1.isScalar() && o2.isMatrix()) || (o1.isMatrix() && o2.isScalar())) {
         // ScalarMatrixArithmeticGPUInstruction.processInstruction (:40-61)

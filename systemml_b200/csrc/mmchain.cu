@@ -642,9 +642,15 @@ extern "C" int sysml_b200_mmchain_dense_hostvec(sysml_b200_ctx* ctx, const doubl
 // for callers that run inside a region where the CUDA runtime must not be asked for memory at all
 // (cudaMalloc synchronises the whole device and is refused while a stream is being captured).
 //
-// For them this entry point keeps its scratch in a fixed array that is part of the loaded module: the
-// memory exists from the moment the library is loaded on a device until the process exits, whether or
-// not the function is ever called, and nothing is allocated or freed by the call itself.
+// For them this entry point keeps its scratch in a fixed array that is part of the library's device code:
+// once that code is resident on a device the memory stays until the process exits, and nothing is
+// allocated or freed by a call.  "Once resident" matters: CUDA loads device code lazily by default
+// (CUDA_MODULE_LOADING=LAZY since CUDA 12), so the array -- and the kernels -- are placed on a device by the
+// FIRST call there (the symbol lookup below triggers it).  That first call therefore does take device memory
+// (about 2.4 MiB plus code) and can fail on a card that is already full: make one small warm-up call per
+// device while memory is still plentiful (right after creating the context), or run the process with
+// CUDA_MODULE_LOADING=EAGER, in which case loading the library places everything at once.  Every later
+// call leaves the amount of free device memory exactly as it found it (tests/test_zz_no_alloc.py checks).
 //   - limit: cols <= SYSML_B200_NOALLOC_MAX_COLS (1024); larger inputs are rejected with SYSML_E_LIMIT;
 //   - footprint: NOALLOC_DOUBLES*8 + 256 bytes (about 2.4 MiB) of device memory per GPU, permanently;
 //   - the array is shared by every call on that GPU and keeps whatever the previous call left in it; a
@@ -687,6 +693,7 @@ int launch_cfg_noalloc(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm, doubl
   constexpr int NWG = TC / 32;
   auto kern = rowstream_kernel<MODE_CHAIN, NTC, TC, CPT, RG, STAGES>;
   const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8;
+  if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_noalloc: smem %zu too large", smem);
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   a.total_tiles = (a.n + R - 1) / R;
   const size_t stage_bytes = (size_t)R * a.m * 8;

@@ -17,7 +17,7 @@
 // slice_ptr[p*32 + s] is where slice s of panel p starts (slice_ptr[npanels*32] = nnz).
 //
 // Kernel.  One persistent CTA per SM, 32 warps.  Per panel: the R values of y (times / minus w for the chain types)
-// are parked in shared memory; warp s streams slice s of the panel with coalesced loads, two consecutive entries
+// are parked in shared memory; warp s streams slice s of the panel with coalesced loads, four consecutive entries
 // per lane, multiplies by the gathered y, and reduces equal-column runs with a segmented warp scan; finished runs are
 // added to the CTA's private m-vector in shared memory with plain read-modify-writes -- a column belongs to exactly
 // one slice, hence to one warp, so there is no atomic anywhere and the order of every addition is fixed.  The per-CTA
@@ -107,45 +107,104 @@ __global__ void __launch_bounds__(1024, 1) pcsc_vm_kernel(const PcscArgs a) {
     __syncthreads();
     const int* sp = a.slice_ptr + p * NSLICE + warp;
     const i64 lo = __ldg(sp), hi = __ldg(sp + 1);
-    // the warp walks its slice in steps of 64 entries, lane l holding entries 2l and 2l+1 of the step
-    for (i64 base = lo; base < hi; base += 64) {
-      const i64 e0 = base + 2 * lane, e1 = e0 + 1;
-      unsigned k0 = 0xffffffffu, k1 = 0xffffffffu;  // sentinel keys past the end: they form their own runs and are never written
-      double p0 = 0.0, p1 = 0.0;
-      if (e0 < hi) {
-        k0 = a.col[e0];
-        p0 = __dmul_rn(ldg_stream(a.val + e0), y_s[a.lrow[e0]]);
-      }
-      if (e1 < hi) {
-        k1 = a.col[e1];
-        p1 = __dmul_rn(ldg_stream(a.val + e1), y_s[a.lrow[e1]]);
-      }
-      const bool uniform = (k0 == k1);
-      // S: sum of the run that LEAVES this lane to the right (so far); a uniform lane passes an incoming run through
-      double S = uniform ? __dadd_rn(p0, p1) : p1;
-      const unsigned kl = __shfl_up_sync(0xffffffffu, k1, 1);        // key leaving the left neighbour
-      bool cont = uniform && lane > 0 && kl == k0;                    // this lane extends the neighbour's run
-      // segmented inclusive scan over the lanes (Hillis-Steele with a "reaches back d lanes" flag)
+    // The warp walks its slice in steps of 128 entries, lane l holding the four consecutive entries 4l..4l+3 of the step
+    // (two 16-byte and two 8-byte loads per lane; the walk starts at a multiple of four so that they are aligned).
+    // Entries before `lo` belong to the previous slice: they get the key of the lane's first own entry and a zero
+    // product; entries past `hi` get a sentinel key that forms its own run and is never written.  The loads of UNR steps
+    // are issued before the first of them is reduced: one step in flight per warp does not cover the HBM latency.
+    constexpr int UNR = 2;
+    constexpr unsigned SENT = 0xffffffffu;
+    for (i64 base0 = lo & ~(i64)3; base0 < hi; base0 += 128 * UNR) {
+      double pv[UNR][4];
+      unsigned kk[UNR][4], rw[UNR][4];
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const double up = __shfl_up_sync(0xffffffffu, S, d);
-        const bool upc = __shfl_up_sync(0xffffffffu, (int)cont, d) != 0;
-        if (cont && lane >= d) {
-          S = __dadd_rn(up, S);
-          cont = upc && lane >= 2 * d;  // keeps reaching back only while every lane in between passed the run through
+      for (int u = 0; u < UNR; u++) {
+        const i64 e0 = base0 + 128 * u + 4 * lane;
+        if (e0 + 3 < hi) {
+          const double2 x01 = ldg_stream2(reinterpret_cast<const double2*>(a.val + e0));
+          const double2 x23 = ldg_stream2(reinterpret_cast<const double2*>(a.val + e0 + 2));
+          const uint2 c4 = __ldg(reinterpret_cast<const uint2*>(a.col + e0));
+          const uint2 r4 = __ldg(reinterpret_cast<const uint2*>(a.lrow + e0));
+          pv[u][0] = x01.x; pv[u][1] = x01.y; pv[u][2] = x23.x; pv[u][3] = x23.y;
+          kk[u][0] = c4.x & 0xffffu; kk[u][1] = c4.x >> 16; kk[u][2] = c4.y & 0xffffu; kk[u][3] = c4.y >> 16;
+          rw[u][0] = r4.x & 0xffffu; rw[u][1] = r4.x >> 16; rw[u][2] = r4.y & 0xffffu; rw[u][3] = r4.y >> 16;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const bool in = e0 + j < hi;
+            pv[u][j] = in ? ldg_stream(a.val + e0 + j) : 0.0;
+            kk[u][j] = in ? (unsigned)a.col[e0 + j] : SENT;
+            rw[u][j] = in ? (unsigned)a.lrow[e0 + j] : 0u;
+          }
         }
       }
-      const double Sl = __shfl_up_sync(0xffffffffu, S, 1);
-      const unsigned kr = __shfl_down_sync(0xffffffffu, k0, 1);       // key entering the right neighbour
-      // (a) a non-uniform lane ends, with its first entry, whatever run came in from the left
-      if (!uniform && k0 != 0xffffffffu) {
-        const double H = (lane > 0 && kl == k0) ? __dadd_rn(Sl, p0) : p0;
-        c_s[k0] = __dadd_rn(c_s[k0], H);
+#pragma unroll
+      for (int u = 0; u < UNR; u++) {
+        const i64 e0 = base0 + 128 * u + 4 * lane;
+        if (base0 + 128 * u >= hi) break;  // warp-uniform
+        double p[4];
+        unsigned k[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          k[j] = kk[u][j];
+          p[j] = (k[j] != SENT && e0 + j >= lo) ? __dmul_rn(pv[u][j], y_s[rw[u][j]]) : 0.0;
+        }
+        if (e0 < lo) {  // only lane 0 of a slice's first step: 1..3 foreign entries, then at least one own entry
+          const unsigned own = (e0 + 1 >= lo) ? k[1] : (e0 + 2 >= lo) ? k[2] : k[3];
+#pragma unroll
+          for (int j = 0; j < 3; j++)
+            if (e0 + j < lo) k[j] = own;
+        }
+        // runs inside the lane: the head run (entries equal to k[0]), the tail run (equal to k[3]) and up to two
+        // entries in between, whose columns no other lane holds
+        const bool eq01 = k[0] == k[1], eq12 = k[1] == k[2], eq23 = k[2] == k[3];
+        const bool uniform = eq01 && eq12 && eq23;
+        double H = p[0];
+        if (eq01) H = __dadd_rn(H, p[1]);
+        if (eq01 && eq12) H = __dadd_rn(H, p[2]);
+        if (uniform) H = __dadd_rn(H, p[3]);
+        double T = (eq23 && eq12) ? p[1] : 0.0;
+        if (eq23) T = __dadd_rn(T, p[2]);
+        T = __dadd_rn(T, p[3]);
+        const bool mid1 = !eq01 && !(eq12 && eq23), mid2 = !(eq01 && eq12) && !eq23;
+        const unsigned kin = k[0], kout = k[3];
+        // S: sum of the run that LEAVES this lane to the right (so far); a uniform lane passes an incoming run through
+        double S = uniform ? H : T;
+        const unsigned kl = __shfl_up_sync(0xffffffffu, kout, 1);  // key leaving the left neighbour
+        bool cont = uniform && lane > 0 && kl == kin;               // this lane extends the neighbour's run
+        // segmented inclusive scan over the lanes (Hillis-Steele; `cont` = "the run reaches further back than the lanes
+        // folded in so far"); runs are short, so most steps are done after two or three rounds
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          if (!__any_sync(0xffffffffu, cont)) break;
+          const double up = __shfl_up_sync(0xffffffffu, S, d);
+          const bool upc = __shfl_up_sync(0xffffffffu, (int)cont, d) != 0;
+          if (cont && lane >= d) {
+            S = __dadd_rn(up, S);
+            cont = upc;
+          }
+        }
+        const double Sl = __shfl_up_sync(0xffffffffu, S, 1);
+        const unsigned kr = __shfl_down_sync(0xffffffffu, kin, 1);  // key entering the right neighbour
+        // (a) a non-uniform lane ends, with its head run, whatever run came in from the left; its in-between entries
+        //     are complete runs of their own
+        if (!uniform) {
+          if (kin != SENT) {
+            const double Hf = (lane > 0 && kl == kin) ? __dadd_rn(Sl, H) : H;
+            c_s[kin] = __dadd_rn(c_s[kin], Hf);
+          }
+          if (mid1 && mid2 && eq12) {
+            c_s[k[1]] = __dadd_rn(c_s[k[1]], __dadd_rn(p[1], p[2]));
+          } else {
+            if (mid1) c_s[k[1]] = __dadd_rn(c_s[k[1]], p[1]);
+            if (mid2) c_s[k[2]] = __dadd_rn(c_s[k[2]], p[2]);
+          }
+        }
+        __syncwarp();
+        // (b) the run leaving this lane ends here when the right neighbour does not take it on
+        if (kout != SENT && (lane == 31 || kr != kout)) c_s[kout] = __dadd_rn(c_s[kout], S);
+        __syncwarp();
       }
-      __syncwarp();
-      // (b) the run leaving this lane ends here when the right neighbour does not take it on
-      if (k1 != 0xffffffffu && (lane == 31 || kr != k1)) c_s[k1] = __dadd_rn(c_s[k1], S);
-      __syncwarp();
     }
   }
   __syncthreads();

@@ -46,7 +46,7 @@ BINARY_OPS = {
 }
 UNARY_OPS = {"exp": 0, "sqrt": 1, "round": 2, "abs": 3, "log": 4, "floor": 5, "ceil": 6, "sign": 7,
              "sigmoid": 8, "sin": 9, "cos": 10, "tan": 11, "tanh": 12}
-BCAST_NONE, BCAST_COL, BCAST_ROW = 0, 1, 2
+BCAST_NONE, BCAST_COL, BCAST_ROW, BCAST_OUTER = 0, 1, 2, 3
 
 
 def _p(x):
@@ -178,8 +178,13 @@ def _bcast(A, B):
 
 
 def matrixMatrixArithmetic(gCtx, instName, in1, in2, op):
-    """C = A op B with column/row-vector broadcast of B (also the relational ops)."""
+    """C = A op B with column/row-vector broadcast of B (also the relational ops); a column vector against a row
+    vector gives the outer form (BinaryAccessType.OUTER_VECTOR_VECTOR, LibMatrixBincell.java:150-163)."""
     opc = BINARY_OPS[op] if isinstance(op, str) else int(op)
+    if in1.cols == 1 and in2.rows == 1 and in2.cols > 1 and in1.rows > 1:
+        out = GPUObject.allocate_dense(gCtx, in1.rows, in2.cols)
+        gCtx.call("sysml_b200_binary_mm", _p(in1.ptr), _p(in2.ptr), _p(out.ptr), in1.rows, in2.cols, BCAST_OUTER, opc)
+        return out
     out = GPUObject.allocate_dense(gCtx, in1.rows, in1.cols)
     gCtx.call("sysml_b200_binary_mm", _p(in1.ptr), _p(in2.ptr), _p(out.ptr), in1.rows, in1.cols, _bcast(in1, in2), opc)
     return out

@@ -211,3 +211,25 @@ def test_variance(gctx, rows, cols):
         got = np.array([got]) if d == O.ALL else got.to_host().reshape(-1)
         assert_equal_matrices(exp, got, rel=1e-9, what=opc)
     dX.free()
+
+
+@pytest.mark.parametrize("n,m", [(1000, 37), (3, 5000), (257, 129)])
+def test_outer_vector_vector_cellwise(gctx, n, m):
+    """n x 1 op 1 x m -> n x m (BinaryAccessType.OUTER_VECTOR_VECTOR, LibMatrixBincell.java:150-163; safeBinaryVVGeneric
+    :565-589; the sorted-row-vector comparison shortcut performBinOuterOperation :814-860 gives the same cells):
+    bit-exact for the arithmetic and relational value functions."""
+    from systemml_b200 import LibMatrixB200 as L
+    a = O.java_test_matrix(n, 1, -2, 2, 0.9, 5)
+    b = np.sort(O.java_test_matrix(1, m, -2, 2, 0.9, 6), axis=1)      # sorted: the reference would take its shortcut
+    da, db = gctx.dense(a), gctx.dense(b)
+    for opn, code in (("+", 0), ("-", 1), ("*", 2), ("/", 3), ("<", 5), ("<=", 6), (">", 7), (">=", 8), ("==", 9), ("!=", 10),
+                      ("min", 11), ("max", 12), ("1-*", 15), ("%%", 17)):
+        out = L.matrixMatrixArithmetic(gctx, opn, da, db, opn)
+        got = out.to_host()
+        assert got.shape == (n, m)
+        assert np.array_equal(O.binary_mm(a, b, code), got, equal_nan=True), opn
+        out.free()
+    exp_lt = (a < b).astype(np.float64)                               # independent statement of one of them
+    assert np.array_equal(L.matrixMatrixArithmetic(gctx, "<", da, db, "<").to_host(), exp_lt)
+    for o in (da, db):
+        o.free()

@@ -326,3 +326,17 @@ def test_csr_upload_under_memory_pressure_does_not_evict_itself():
         assert ec.stats()["evictions"] >= 1
         assert_equal_matrices(O.matmult_csr_dense(rp, ci, va, X.shape, v, 1)[0], ec.getMatrix("Xv"))
         assert np.array_equal(ec.getMatrix("X"), X)
+
+
+def test_outer_vector_vector_instruction(ec):
+    """`GPU°<°cv°rv°out` with an n x 1 and a 1 x m operand produces the n x m outer comparison (Kmeans-predict / table-style
+    idioms; BinaryAccessType.OUTER_VECTOR_VECTOR, LibMatrixBincell.java:150-163)."""
+    cv = O.java_test_matrix(200, 1, -1, 1, 1.0, 1)
+    rv = O.java_test_matrix(1, 70, -1, 1, 1.0, 2)
+    ec.setMatrix("cv", cv)
+    ec.setMatrix("rv", rv)
+    ec.execute(inst("<", mat("cv"), mat("rv"), mat("Z")))
+    assert ec.getMatrixDims("Z")[:2] == (200, 70)
+    assert np.array_equal(ec.getMatrix("Z"), (cv < rv).astype(np.float64))
+    ec.execute(inst("*", mat("cv"), mat("rv"), mat("Z")))
+    assert np.array_equal(ec.getMatrix("Z"), cv * rv)

@@ -50,6 +50,31 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row(gctx):
         o.free()
 
 
+def test_noalloc_agrees_with_the_cpu_oracle_and_leaves_free_memory_alone():
+    """On a context of its own that has never made a regular call: after the first (warm-up) call has made the
+    library's device code resident, a call changes neither the free device memory nor anything else the library holds,
+    and its result is the reference's (LibMatrixMult.matrixMultChain, LibMatrixMult.java:243-329) to 1e-9 per cell."""
+    from oracle import oracle as O
+    from systemml_b200 import GPUContext
+    with GPUContext(0) as g:
+        n, m = 30_000, 567
+        Xh = O.rand_uniform(n * m, seed=81).reshape(n, m)
+        vh, wh = O.rand_uniform(m, seed=82), O.rand_uniform(n, seed=83, lo=0.0, hi=1.0)
+        X, v, w, out = g.dense(Xh), g.dense(vh.reshape(m, 1)), g.dense(wh.reshape(n, 1)), g.empty(m, 1)
+        assert _call(g, "sysml_b200_mmchain_dense_noalloc", X, v, w, out, n, m, 1) == 0    # warm-up: loads the device code
+        g.sync()
+        free0, _ = g.getAvailableMemory()
+        for ct in (1, 0, 2):
+            assert _call(g, "sysml_b200_mmchain_dense_noalloc", X, v, w if ct else None, out, n, m, ct) == 0
+            g.sync()
+            free1, _ = g.getAvailableMemory()
+            assert free1 == free0, "a call must not change the free device memory (%d -> %d)" % (free0, free1)
+            got = out.to_host().reshape(-1)
+            assert_equal_matrices(O.mmchain_dense(Xh, vh, wh if ct else None, ct, 4), got, what="noalloc vs oracle, chain type %d" % ct)
+        for o in (X, v, w, out):
+            o.free()
+
+
 def test_noalloc_rejects_sizes_beyond_its_fixed_scratch(gctx):
     from systemml_b200 import native
     m = 1025
