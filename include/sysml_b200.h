@@ -350,6 +350,21 @@ int sysml_b200_csr_to_dense(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
                             const double* val, int64_t rows, int64_t cols, double* X);
 
 /* ------------------------------------------------------------------------------------------------
+ * One Lloyd step of Kmeans (scripts/algorithms/Kmeans.dml:146-166) in ONE pass over X:
+ *   D = -2*(X %*% t(C)) + t(c2);  minD = rowMins(D);  P = (D <= minD) / rowSums(D <= minD)
+ *   sums[k x m] = t(P) %*% X;  counts[k] = colSums(P);  *sum_min_dist = sum(minD)
+ * Stands in for the run ba+* (X %*% t(C)), *, +, uarmin, uak+, <=, uark+, /, uack+, ba+* (t(P) %*% X) that the reference
+ * executes as separate instructions (AggregateBinaryGPUInstruction.java:73-89 twice, AggregateUnaryGPUInstruction.java:67-101,
+ * MatrixMatrixArithmeticGPUInstruction.java:38-71; CPU: LibMatrixMult.java:880-1103, LibMatrixAgg.java:1624-1927), each
+ * of which round-trips an n x k matrix through memory.  c2 = rowSums(C^2) (k doubles) is computed by the caller with
+ * agg_unary_dense so that its Kahan arithmetic is the reference's; the division by the counts stays with the caller too.
+ * Ties share a record equally, as in the script.  Records containing NaN are left out of the sums (the script would
+ * propagate the NaN into every centroid).  Limits: k <= 64, an even number of columns, and C, the accumulators and two
+ * 64-row tiles must fit in shared memory (SYSML_E_UNSUPPORTED otherwise: run the step operator by operator). */
+int sysml_b200_kmeans_step(sysml_b200_ctx* ctx, const double* X, const double* C, const double* c2, int64_t n,
+                           int64_t m, int64_t k, double* sums, double* counts, double* sum_min_dist);
+
+/* ------------------------------------------------------------------------------------------------
  * Column-ordered copy of a constant CSR matrix ("panel CSC") for t(X) %*% y and the second half of sparse mmchain.
  * Replaces the scatter of LibMatrixMult.matrixMultChainSparse (LibMatrixMult.java:1655-1684) and of the VM form of
  * matrixMultSparseDense (:1262-1286) -- and, on the reference GPU path, cusparseDcsrmv with the transpose flag

@@ -243,14 +243,52 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
     return res, it, obj
 
 
+def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
+    """The same iterations with the whole step in one pass over X (sysml_b200_kmeans_step, csrc/kmeans.cu): distances on the
+    FP64 tensor cores, row minimum with the script's tie rule, centroid sums, counts and sum(minD) -- D, minD and P never
+    exist in memory.  The k x m algebra around it (rowSums(C^2), the division by the counts) stays as instructions."""
+    n, m, k = X.rows, X.cols, C0.rows
+    alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    Cc, Cn, c2, den, s1 = alloc(k, m), alloc(k, m), alloc(k, 1), alloc(k, 1), alloc(1, 1)
+    g.call("sysml_b200_d2d", _p(Cc), _p(C0), 8 * k * m)
+    g.call("sysml_b200_agg_unary_dense", _p(X), n, m, L.AGG_SUMSQ, L.DIR_ALL, _p(s1))
+    sumXsq = _scalar(g, s1)
+    wcss, it, term = float("inf"), 0, 0
+    while term == 0:
+        g.call("sysml_b200_agg_unary_dense", _p(Cc), k, m, L.AGG_SUMSQ, L.DIR_ROW, _p(c2))           # rowSums(C^2)
+        g.call("sysml_b200_kmeans_step", _p(X), _p(Cc), _p(c2), n, m, k, _p(Cn), _p(den), _p(s1))   # t(P)%*%X, colSums(P), sum(minD)
+        wcss_old, wcss = wcss, sumXsq + _scalar(g, s1)
+        g.call("sysml_b200_binary_mm", _p(Cn), _p(den), _p(Cn), k, m, L.BCAST_COL, L.BINARY_OPS["/"])  # / t(P_denom)
+        it += 1
+        if log is not None:
+            log.append((it, wcss))
+        if wcss_old - wcss < eps * wcss:
+            term = 1
+        elif it >= max_iter:
+            term = 2
+        elif float(np.sum(den.to_host() <= 0)) > 0:
+            term = 3
+        else:
+            Cc, Cn = Cn, Cc
+    out = Cc.to_host()
+    for o in (Cc, Cn, c2, den, s1):
+        o.free()
+    return out, it, wcss, term
+
+
 def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
     """One run of the Lloyd iterations of scripts/algorithms/Kmeans.dml:130-176 from given initial centroids
     (BASELINE config C5: X 10M x 100, k = 50).  X: GPUObject n x m dense, C0: GPUObject k x m.
     Per iteration: D = -2*(X %*% t(C)) + t(rowSums(C^2)); minD = rowMins(D); P = (D <= minD) / rowSums(D <= minD);
-    C_new = (t(P) %*% X) / t(colSums(P)).  Returns (C ndarray, iterations, wcss, termination code 1/2/3)."""
+    C_new = (t(P) %*% X) / t(colSums(P)).  Returns (C ndarray, iterations, wcss, termination code 1/2/3).
+    fused: True = the one-pass step kernel when the shape fits it, else the fused cellwise chains; "chains" = the chains;
+    False = one launch per operator (the reference's plan); "step" = the one-pass kernel or an error."""
     n, m, k = X.rows, X.cols, C0.rows
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    if fused == "step" or (fused is True and k <= 64 and m % 2 == 0 and (m + k + 2 * 64) * (m + 12) * 8 < 200 * 1024):
+        return _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log)
+    fused = bool(fused)   # "chains" -> True
     Cc, Cn, XC, P = alloc(k, m), alloc(k, m), alloc(n, k), alloc(n, k)
     D = None if fused else alloc(n, k)   # the fused plan never materialises D
     c2, minD, rs, den, s1 = alloc(k, 1), alloc(n, 1), alloc(n, 1), alloc(k, 1), alloc(1, 1)

@@ -6,7 +6,7 @@ import pytest
 
 from oracle import oracle as O
 from oracle.algorithms_cpu import cpu_glm_poisson_log, cpu_kmeans_lloyd, cpu_l2svm, cpu_linreg_cg, cpu_multilogreg  # noqa: F401
-from tests.util import assert_equal_matrices
+from tests.util import assert_equal_matrices, assert_parity
 
 pytestmark = pytest.mark.gpu
 
@@ -71,7 +71,7 @@ def test_l2svm_end_to_end(gctx, sparse):
     assert np.mean(np.sign(X @ w) == Y) > 0.9  # and it separates the classes
 
 
-@pytest.mark.parametrize("fused", [True, False])
+@pytest.mark.parametrize("fused", ["step", "chains", False])
 def test_kmeans_end_to_end(gctx, fused):
     """BASELINE config C5's workload at test size: Gaussian blobs, k = 12."""
     from systemml_b200.algorithms import kmeans_lloyd
@@ -104,3 +104,40 @@ def test_multilogreg_end_to_end(gctx):
     assert_equal_matrices(expB, gotB, rel=1e-9, what="MultiLogReg B")
     pred = np.argmax(np.hstack([X @ gotB, np.zeros((N, 1))]), axis=1)
     assert np.mean(pred == labels) > 0.6
+
+
+@pytest.mark.parametrize("n,m,k", [(5000, 100, 50), (63, 20, 12), (4097, 22, 64), (1000, 6, 3), (20_000, 100, 50)])
+def test_kmeans_one_pass_step_kernel(gctx, n, m, k):
+    """sysml_b200_kmeans_step against the script's step in numpy (Kmeans.dml:146-166): sums = t(P) %*% X, counts =
+    colSums(P), sum(minD); duplicate centroids give exact ties, which must share their records equally; shapes cover a
+    ragged last tile, fewer rows than a tile, m not a multiple of 4 and the largest k."""
+    import ctypes as C
+    rng = np.random.default_rng(n + m + k)
+    centers = rng.uniform(-5, 5, (k, m))
+    X = centers[rng.integers(0, k, n)] + 0.5 * rng.normal(size=(n, m))
+    Cm = centers + 0.1 * rng.normal(size=(k, m))
+    if k >= 3:
+        Cm[k - 1] = Cm[0]                      # an exact tie for every record closest to centroid 0
+    c2 = np.sum(Cm ** 2, axis=1)
+    D = -2 * (X @ Cm.T) + c2[None, :]
+    minD = D.min(axis=1, keepdims=True)
+    P = (D <= minD).astype(np.float64)
+    P = P / P.sum(axis=1, keepdims=True)
+    dX, dC = gctx.dense(X), gctx.dense(Cm)
+    dc2 = gctx.empty(k, 1)
+    gctx.call("sysml_b200_agg_unary_dense", C.c_void_p(dC.ptr), k, m, 1, 1, C.c_void_p(dc2.ptr))     # rowSums(C^2)
+    sums, cnt, smin = gctx.empty(k, m), gctx.empty(k, 1), gctx.empty(1, 1)
+    runs = []
+    for _ in range(2):
+        gctx.call("sysml_b200_kmeans_step", C.c_void_p(dX.ptr), C.c_void_p(dC.ptr), C.c_void_p(dc2.ptr), n, m, k, C.c_void_p(sums.ptr),
+                  C.c_void_p(cnt.ptr), C.c_void_p(smin.ptr))
+        runs.append((sums.to_host(), cnt.to_host().reshape(-1), float(smin.to_host()[0, 0])))
+    assert np.array_equal(runs[0][0], runs[1][0]) and np.array_equal(runs[0][1], runs[1][1]) and runs[0][2] == runs[1][2], "not reproducible"
+    got_sums, got_cnt, got_smin = runs[0]
+    assert_equal_matrices(P.sum(axis=0), got_cnt, what="kmeans counts %dx%d k=%d" % (n, m, k))
+    if k >= 3:
+        assert got_cnt[0] == got_cnt[k - 1] and got_cnt[0] > 0, "tied centroids share their records"
+    assert_parity(P.T @ X, got_sums, np.abs(P).T @ np.abs(X), n, what="kmeans sums %dx%d k=%d" % (n, m, k))
+    assert abs(got_smin - float(np.sum(minD))) <= 1e-9 * abs(float(np.sum(minD)))
+    for o in (dX, dC, dc2, sums, cnt, smin):
+        o.free()

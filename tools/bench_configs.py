@@ -217,15 +217,28 @@ def config_c5(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
         ops.append(_op(name, a, b, hbm, dmma, nbytes=8.0 * n * k + 8.0 * (n if d == 1 else k)))
     for o in (H, D, oKM, oN, oK):
         o.free()
+    # the whole Lloyd step as one kernel (csrc/kmeans.cu)
+    c2d, sums, cnt, smin = g.empty(k, 1), g.empty(k, m), g.empty(k, 1), g.empty(1, 1)
+    g.call("sysml_b200_agg_unary_dense", _p(C0), k, m, 1, 1, _p(c2d))
+    a, b = _timeit(g, lambda: g.call("sysml_b200_kmeans_step", _p(X), _p(C0), _p(c2d), n, m, k, _p(sums), _p(cnt), _p(smin)), reps)
+    ops.append(_op("one-pass Lloyd step (distances + rowMins + tie rule + t(P)%*%X + colSums + sum)", a, b, hbm, dmma, nbytes=8.0 * n * m, flops=2.0 * n * m * k))
+    ops[-1]["note"] = "flops: the distance product only (2nmk); the centroid sums are n*m additions, not a second product"
+    for o in (c2d, sums, cnt, smin):
+        o.free()
     kmeans_lloyd(g, X, C0, max_iter=1)
     g.sync()
     t0 = time.perf_counter()
     Cf, iters, wcss, term = kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6)
     g.sync()
     dt = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    _, iters_c, _, _ = kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused="chains")
+    g.sync()
+    dt_chains = time.perf_counter() - t0
     res = {"shape": [n, m], "k": k, "ops": ops,
            "algorithm": {"name": "Kmeans (Kmeans.dml Lloyd iterations of one run, eps=1e-6 max_iter=20)", "iterations": iters, "termination_code": term,
-                         "seconds": round(dt, 4), "ms_per_iteration": round(1000.0 * dt / max(iters, 1), 3), "wcss": wcss}}
+                         "seconds": round(dt, 4), "ms_per_iteration": round(1000.0 * dt / max(iters, 1), 3), "wcss": wcss,
+                         "plan": "one-pass step kernel", "ms_per_iteration_as_matmults_and_fused_chains": round(1000.0 * dt_chains / max(iters_c, 1), 3)}}
     if cpu:
         from oracle.algorithms_cpu import cpu_kmeans_lloyd
         ns = min(n, 200_000)
