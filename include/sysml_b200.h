@@ -48,6 +48,7 @@ extern "C" {
 #define SYSML_E_CUDA (-4)        /* any other CUDA runtime error                     */
 #define SYSML_E_UNSUPPORTED (-5) /* valid request this build does not implement      */
 #define SYSML_E_LIMIT (-6)       /* size beyond a documented fixed limit             */
+#define SYSML_E_WORKSPACE (-7)   /* the caller-owned scratch block is too small: see sysml_b200_ctx_set_workspace */
 
 typedef struct sysml_b200_ctx sysml_b200_ctx;
 
@@ -130,6 +131,23 @@ int sysml_b200_ctx_create(int device, sysml_b200_ctx** out);
 /* Same, but all work is queued on a stream the caller owns (cudaStream_t passed as void*). */
 int sysml_b200_ctx_create_on_stream(int device, void* cuda_stream, sysml_b200_ctx** out);
 int sysml_b200_ctx_destroy(sysml_b200_ctx* ctx);
+/* Scratch.  Kernels that reduce across CTAs (mmchain, tsmm split-K, aggregates, the sorts behind the CSR conversions)
+ * take their temporary device memory from ONE block per context.  By default the library owns that block: it grows it
+ * with cudaMalloc when a larger request arrives and keeps it until the context is destroyed.  A host runtime that
+ * accounts for every byte on the card itself -- GPUMemoryManager does (GPUMemoryManager.java:64-78, 157-262) -- hands
+ * the block over instead:
+ *   ctx_set_workspace(ctx, d_ptr, bytes): from now on scratch comes from this caller-owned, 256-byte aligned block and
+ *       the library neither allocates nor frees scratch (d_ptr == NULL returns to the library-owned default).  The call
+ *       synchronises the stream first.  The block may be replaced at any time between operations.
+ *   An operation that needs more than the block holds changes nothing and returns SYSML_E_WORKSPACE;
+ *   ctx_workspace_needed(ctx) then tells how many bytes that operation asked for: allocate (evicting if need be), call
+ *   ctx_set_workspace again and repeat the operation -- every operation overwrites its outputs, so repeating is safe.
+ *   ctx_workspace_bytes(ctx) is the size of the current block, whoever owns it.
+ * (Reference: the operator-local temporaries that LibMatrixCUDA obtains with gCtx.allocate and returns with
+ * gCtx.cudaFreeHelper, LibMatrixCUDA.java:711,732,926,947.) */
+int sysml_b200_ctx_set_workspace(sysml_b200_ctx* ctx, void* d_ptr, int64_t bytes);
+int64_t sysml_b200_ctx_workspace_needed(sysml_b200_ctx* ctx);
+int64_t sysml_b200_ctx_workspace_bytes(sysml_b200_ctx* ctx);
 int sysml_b200_sync(sysml_b200_ctx* ctx);
 const char* sysml_b200_last_error(sysml_b200_ctx* ctx); /* ctx may be NULL: last error of this thread */
 void* sysml_b200_ctx_stream(sysml_b200_ctx* ctx);       /* the cudaStream_t in use */

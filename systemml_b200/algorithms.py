@@ -286,8 +286,15 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
     n, m, k = X.rows, X.cols, C0.rows
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
-    if fused == "step" or (fused is True and k <= 64 and m % 2 == 0 and (m + k + 2 * 64) * (m + 12) * 8 < 200 * 1024):
+    if fused == "step":
         return _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log)
+    if fused is True:
+        from . import native
+        try:
+            return _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log)
+        except native.NativeError as e:   # the shape does not fit the one-pass kernel: the chains do the same step
+            if e.code != native.E_UNSUPPORTED:
+                raise
     fused = bool(fused)   # "chains" -> True
     Cc, Cn, XC, P = alloc(k, m), alloc(k, m), alloc(n, k), alloc(n, k)
     D = None if fused else alloc(n, k)   # the fused plan never materialises D

@@ -22,6 +22,8 @@ struct sysml_b200_ctx {
   bool own_stream;
   void* ws;          // scratch (device)
   size_t ws_bytes;
+  bool ws_external;  // the block belongs to the caller (sysml_b200_ctx_set_workspace): never grown or freed here
+  size_t ws_needed;  // size of the last request an external block could not satisfy
   unsigned int* counters;  // 64 zero-initialised counters; every kernel that uses one resets it
   void* pinned;      // pinned host staging
   size_t pinned_bytes;
@@ -121,6 +123,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
           smem_u32(dst_smem)),
       "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
       : "memory");
+}
+// asks the memory system to bring [src, src+bytes) into L2 (no shared-memory destination, no completion to wait for);
+// src 16B aligned, bytes % 16 == 0
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src_gmem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");

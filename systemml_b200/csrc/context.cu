@@ -17,6 +17,11 @@ int sysml_set_error(sysml_b200_ctx* ctx, int code, const char* fmt, ...) {
 }
 
 int sysml_workspace(sysml_b200_ctx* ctx, size_t bytes, void** out) {
+  if (bytes > ctx->ws_bytes && ctx->ws_external) {
+    ctx->ws_needed = bytes;
+    return sysml_set_error(ctx, SYSML_E_WORKSPACE, "scratch: this operation needs %zu bytes, the caller's workspace holds %zu (sysml_b200_ctx_set_workspace)",
+                           bytes, ctx->ws_bytes);
+  }
   if (bytes > ctx->ws_bytes) {
     // grow-only; growing synchronises the stream because in-flight kernels may still use the old block
     SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -111,7 +116,7 @@ int sysml_b200_ctx_create_on_stream(int device, void* cuda_stream, sysml_b200_ct
 int sysml_b200_ctx_destroy(sysml_b200_ctx* ctx) {
   SYSML_ENTER(ctx);
   cudaStreamSynchronize(ctx->stream);
-  if (ctx->ws) cudaFree(ctx->ws);
+  if (ctx->ws && !ctx->ws_external) cudaFree(ctx->ws);
   if (ctx->counters) cudaFree(ctx->counters);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->vec_stage) cudaFree(ctx->vec_stage);
@@ -121,6 +126,22 @@ int sysml_b200_ctx_destroy(sysml_b200_ctx* ctx) {
   delete ctx;
   return SYSML_OK;
 }
+
+int sysml_b200_ctx_set_workspace(sysml_b200_ctx* ctx, void* d_ptr, int64_t bytes) {
+  SYSML_ENTER(ctx);
+  if (bytes < 0 || (bytes > 0 && !d_ptr)) return sysml_set_error(ctx, SYSML_E_INVALID, "set_workspace: bad arguments");
+  if (d_ptr && (reinterpret_cast<uintptr_t>(d_ptr) & 255)) return sysml_set_error(ctx, SYSML_E_INVALID, "set_workspace: the block must be 256-byte aligned");
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // queued kernels may still use the current block
+  if (ctx->ws && !ctx->ws_external) SYSML_CUDA(ctx, cudaFree(ctx->ws));
+  ctx->ws = d_ptr;
+  ctx->ws_bytes = d_ptr ? (size_t)bytes : 0;
+  ctx->ws_external = d_ptr != nullptr;
+  ctx->ws_needed = 0;
+  return SYSML_OK;
+}
+
+int64_t sysml_b200_ctx_workspace_needed(sysml_b200_ctx* ctx) { return ctx ? (int64_t)ctx->ws_needed : 0; }
+int64_t sysml_b200_ctx_workspace_bytes(sysml_b200_ctx* ctx) { return ctx ? (int64_t)ctx->ws_bytes : 0; }
 
 int sysml_b200_sync(sysml_b200_ctx* ctx) {
   SYSML_ENTER(ctx);

@@ -585,6 +585,27 @@ struct sysml_b200_ec {
   i64 clock = 0;
   i64 n_inst = 0, n_h2d = 0, n_d2h = 0;
   std::string err;
+  void* workspace = nullptr;  // the kernels' scratch block, allocated through (and accounted by) the memory manager
+
+  // (Re)allocates the scratch block at `bytes` through the memory manager -- evicting matrices if that is what it takes --
+  // and hands it to the kernels.  The old block goes back first, so the manager can reuse or release it.
+  void growWorkspace(i64 bytes) {
+    check(sysml_b200_ctx_set_workspace(ctx, nullptr, 0));  // (synchronises) the library owns nothing in between: it holds no block
+    if (workspace) {
+      mm.free(workspace, true);
+      workspace = nullptr;
+    }
+    const i64 want = std::max<i64>(((bytes + bytes / 4) + 255) / 256 * 256, 1 << 20);
+    void* p = nullptr;
+    try {
+      p = mm.malloc("workspace", want);
+    } catch (const DMLRuntimeException&) {
+      p = mm.malloc("workspace", (bytes + 255) / 256 * 256);  // without the head-room, then
+    }
+    workspace = p;
+    auto it = mm.allocated.find(p);
+    check(sysml_b200_ctx_set_workspace(ctx, p, it != mm.allocated.end() ? it->second : bytes));
+  }
 
   MatrixObject* getMatrixObject(const std::string& name) {
     auto it = matrices.find(name);
@@ -992,6 +1013,14 @@ int sysml_b200_ec_create(int device, double mem_util_factor, int eager_cuda_free
   ec->mm.util_factor = mem_util_factor > 0 ? mem_util_factor : 0.9;
   ec->mm.eager_free = eager_cuda_free != 0;
   ec->mm.memory_limit = memory_limit;
+  try {
+    ec->growWorkspace(1 << 20);
+  } catch (const std::exception& e) {
+    g_host_err = e.what();
+    sysml_b200_ctx_destroy(ctx);
+    delete ec;
+    return SYSML_E_OOM;
+  }
   *out = ec;
   return SYSML_OK;
 }
@@ -999,6 +1028,7 @@ int sysml_b200_ec_create(int device, double mem_util_factor, int eager_cuda_free
 int sysml_b200_ec_destroy(sysml_b200_ec* ec) {
   if (!ec) return SYSML_E_INVALID;
   try {
+    sysml_b200_ctx_set_workspace(ec->ctx, nullptr, 0);
     ec->matrices.clear();
     ec->mm.clearMemory();
   } catch (...) {
@@ -1078,7 +1108,20 @@ int sysml_b200_ec_execute(sysml_b200_ec* ec, const char* instruction) {
   if (!ec || !instruction) return SYSML_E_INVALID;
   EC_TRY(ec, {
     ParsedInstruction pi = parseSingleInstruction(instruction);
-    ec->processInstruction(pi);
+    // The kernels' scratch is a block of the memory manager, like every other device allocation of this context.  An
+    // instruction that needs more than the block holds fails without side effects (SYSML_E_WORKSPACE): the block is
+    // re-allocated at the requested size -- through the same malloc ladder, evictions included -- and the instruction
+    // runs again (it overwrites its outputs, so that is safe).
+    for (int attempt = 0;; attempt++) {
+      try {
+        ec->processInstruction(pi);
+        break;
+      } catch (const DMLRuntimeException& e) {
+        if (e.code != SYSML_E_WORKSPACE || attempt >= 3) throw;
+        ec->n_inst--;
+        ec->growWorkspace(sysml_b200_ctx_workspace_needed(ec->ctx));
+      }
+    }
   })
 }
 

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libsystemml_b200.so")
 
-OK, E_INVALID, E_DIM, E_OOM, E_CUDA, E_UNSUPPORTED, E_LIMIT = 0, -1, -2, -3, -4, -5, -6
+OK, E_INVALID, E_DIM, E_OOM, E_CUDA, E_UNSUPPORTED, E_LIMIT, E_WORKSPACE = 0, -1, -2, -3, -4, -5, -6, -7
 
 vp, i64, u64, ci, dbl = C.c_void_p, C.c_int64, C.c_uint64, C.c_int, C.c_double
 pvp, pi64, pint, pdbl = C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int), C.POINTER(C.c_double)
@@ -21,6 +21,9 @@ SIGNATURES = {
     "sysml_b200_ctx_create": (ci, [ci, pvp]),
     "sysml_b200_ctx_create_on_stream": (ci, [ci, vp, pvp]),
     "sysml_b200_ctx_destroy": (ci, [vp]),
+    "sysml_b200_ctx_set_workspace": (ci, [vp, vp, i64]),
+    "sysml_b200_ctx_workspace_needed": (i64, [vp]),
+    "sysml_b200_ctx_workspace_bytes": (i64, [vp]),
     "sysml_b200_sync": (ci, [vp]),
     "sysml_b200_last_error": (C.c_char_p, [vp]),
     "sysml_b200_ctx_stream": (vp, [vp]),

@@ -203,8 +203,8 @@ def config_c5(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     g.call("sysml_b200_axpy", _p(X), _p(noise), 1.0, _p(X), n, m, 0)
     for o in (noise, asg, ids):
         o.free()
-    C0 = g.empty(k, m)      # initial centroids: the first k data points (several of them fall into the same blob)
-    g.call("sysml_b200_d2d", _p(C0), _p(X), 8 * k * m)
+    C0 = g.rand(k, m, seed=8)                                # initial centroids: the blob centres, each displaced by U(-1,1)
+    g.call("sysml_b200_binary_mm", _p(C0), _p(centers), _p(C0), k, m, 0, L.BINARY_OPS["+"])
     D, oKM = g.empty(n, k), g.empty(k, m)
     ops = []
     a, b = _timeit(g, lambda: g.call("sysml_b200_matmult_dense", _p(X), _p(C0), _p(D), n, m, k, m, 0, 1), reps)
@@ -228,15 +228,16 @@ def config_c5(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     kmeans_lloyd(g, X, C0, max_iter=1)
     g.sync()
     t0 = time.perf_counter()
-    Cf, iters, wcss, term = kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6)
+    # eps = 0: the run does not stop at convergence, so both plans execute exactly max_iter = 10 Lloyd iterations
+    Cf, iters, wcss, term = kmeans_lloyd(g, X, C0, max_iter=10, eps=0.0)
     g.sync()
     dt = time.perf_counter() - t0
     t0 = time.perf_counter()
-    _, iters_c, _, _ = kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused="chains")
+    _, iters_c, _, _ = kmeans_lloyd(g, X, C0, max_iter=10, eps=0.0, fused="chains")
     g.sync()
     dt_chains = time.perf_counter() - t0
     res = {"shape": [n, m], "k": k, "ops": ops,
-           "algorithm": {"name": "Kmeans (Kmeans.dml Lloyd iterations of one run, eps=1e-6 max_iter=20)", "iterations": iters, "termination_code": term,
+           "algorithm": {"name": "Kmeans (Kmeans.dml Lloyd iterations of one run, eps=0 max_iter=10: exactly 10 iterations)", "iterations": iters, "termination_code": term,
                          "seconds": round(dt, 4), "ms_per_iteration": round(1000.0 * dt / max(iters, 1), 3), "wcss": wcss,
                          "plan": "one-pass step kernel", "ms_per_iteration_as_matmults_and_fused_chains": round(1000.0 * dt_chains / max(iters_c, 1), 3)}}
     if cpu:
@@ -245,7 +246,7 @@ def config_c5(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
         Xh = g.d2h(X.ptr, (ns, m))
         C0h = C0.to_host()
         t0 = time.perf_counter()
-        _, it_c, _, _ = cpu_kmeans_lloyd(Xh, C0h, 20, 1e-6)
+        _, it_c, _, _ = cpu_kmeans_lloyd(Xh, C0h, 10, 0.0)
         dc = time.perf_counter() - t0
         res["algorithm"]["cpu_twin"] = {"kind": "numpy twin of the same script (oracle/algorithms_cpu.py; BLAS matmults)", "sample_rows": ns,
                                         "iterations": it_c, "seconds_on_sample": round(dc, 3), "ms_per_iteration_scaled_to_full_rows": round(1000.0 * dc / max(it_c, 1) * n / ns, 1)}

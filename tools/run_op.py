@@ -50,6 +50,12 @@ elif op == "pcsc":
     pc = PCSCPointer(g, S.csr, rows, cols)
     y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
     fn = lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), rows, cols, pc.panel_rows, p_(y), None, 0, p_(oc))
+elif op == "kmeans":
+    n, m, k = a
+    X, Cm = g.rand(n, m, seed=1, lo=-10.0, hi=10.0), g.rand(k, m, seed=2, lo=-10.0, hi=10.0)
+    c2, sums, cnt, smin = g.empty(k, 1), g.empty(k, m), g.empty(k, 1), g.empty(1, 1)
+    g.call("sysml_b200_agg_unary_dense", p_(Cm), k, m, 1, 1, p_(c2))
+    fn = lambda: g.call("sysml_b200_kmeans_step", p_(X), p_(Cm), p_(c2), n, m, k, p_(sums), p_(cnt), p_(smin))
 elif op == "agg":
     n, m, aop, d = a
     X = g.rand(n, m, seed=1)
