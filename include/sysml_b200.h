@@ -470,6 +470,34 @@ int sysml_b200_cg_step_dense(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const d
                              int64_t m, int chain_type, double lambda);
 
 /* ------------------------------------------------------------------------------------------------
+ * SystemML "binaryblock" files (Hadoop SequenceFile, version 6, uncompressed, of MatrixIndexes -> MatrixBlock records;
+ * blocks of brlen x bclen, 1000 x 1000 by default) straight into a row-major device matrix.
+ * Replaces ReaderBinaryBlock.readBinaryBlockMatrixFromSequenceFile (J/runtime/io/ReaderBinaryBlock.java:124-207) followed
+ * by GPUObject.copyFromHostToDevice (GPUObject.java:755-870): no JVM double[] in between (which also caps a dense block
+ * array at 2^31 cells), no synchronous whole-matrix copy.  Record layouts: MatrixIndexes.write (MatrixIndexes.java:117-130),
+ * MatrixBlock.write / readFields (MatrixBlock.java:1735-2180): dense, sparse, ultra-sparse and empty blocks are all read.
+ *   binaryblock_read_dense   : rows [row_begin, row_end) of the matrix -- this rank's shard; row_begin on a block boundary --
+ *                              into d_X ((row_end-row_begin) x cols doubles).  `path` is one SequenceFile or a directory of
+ *                              part files.  Raw block bytes go pinned slot -> device, a kernel swaps the byte order and
+ *                              places the block; file reads overlap the copies.  Blocks absent from the file are zeros.
+ *   binaryblock_read_mmchain : the same, and out = t(X) %*% (w * (X %*% v)) [chain_type as for mmchain] of the shard is
+ *                              computed WHILE the matrix arrives: as soon as a group of block rows is on the device its
+ *                              partial result is added (in row order, so the result is reproducible).  The first pass of
+ *                              LinearRegCG / GLM over a matrix that is not resident yet costs the upload, not upload + pass.
+ *   binaryblock_write        : host-side writer of the same format (tests, data preparation); dense_only = 0 picks each
+ *                              block's format as MatrixBlock.write does (evalSparseFormatOnDisk, MatrixBlock.java:1017-1031,
+ *                              isUltraSparseSerialize :897-899).  Takes no context.
+ * Compressed SequenceFiles are refused (SYSML_E_UNSUPPORTED).
+ * ---------------------------------------------------------------------------------------------- */
+int sysml_b200_binaryblock_write(const char* path, const double* h_X, int64_t rows, int64_t cols, int brlen, int bclen,
+                                 int dense_only);
+int sysml_b200_binaryblock_read_dense(sysml_b200_ctx* ctx, const char* path, int64_t rows, int64_t cols, int brlen,
+                                      int bclen, int64_t row_begin, int64_t row_end, double* d_X);
+int sysml_b200_binaryblock_read_mmchain(sysml_b200_ctx* ctx, const char* path, int64_t rows, int64_t cols, int brlen,
+                                        int bclen, int64_t row_begin, int64_t row_end, double* d_X, const double* v,
+                                        const double* w, double* out, int chain_type);
+
+/* ------------------------------------------------------------------------------------------------
  * Synthetic data (scripts/datagen/genRandData4LinearRegression.dml uses Rand(min,max,pdf=uniform,seed)).
  * Counter-based: cell i of the GLOBAL array gets hash(seed, offset + i), so any row shard equals the
  * same rows of the full matrix.  No reference GPU counterpart (RandGPU does not exist); the CPU twin is

@@ -39,6 +39,7 @@ HOST_ARRAYS = {
     ("sysml_b200_csr_add", "c_nnz"): "long_out",
     ("sysml_b200_matmult_csr_csr_sparse", "c_nnz"): "long_out",
     # generic byte copies: the Java side holds double[] blocks (DenseBlockDRB) -- int[] variants are written by hand below
+    ("sysml_b200_binaryblock_write", "h_X"): "double_in",
     ("sysml_b200_h2d", "h_src"): "double_in",
     ("sysml_b200_d2h", "h_dst"): "double_out",
 }
@@ -195,7 +196,8 @@ extern "C" {
                 args.append("(%s)%s" % (base, pname))
             elif kind == "string":
                 if "const" in ctype:
-                    pre.append("  const char* %s_c = %s ? env->GetStringUTFChars(%s, nullptr) : nullptr;" % (pname, pname, pname))
+                    # a JNI call: must happen before any array is pinned (no JNI calls inside a critical region)
+                    decl.append("  const char* %s_c = %s ? env->GetStringUTFChars(%s, nullptr) : nullptr;" % (pname, pname, pname))
                     args.append("%s_c" % pname)
                     post.append("  if (%s_c) env->ReleaseStringUTFChars(%s, %s_c);" % (pname, pname, pname))
                 else:

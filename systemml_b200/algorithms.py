@@ -256,7 +256,12 @@ def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
     wcss, it, term = float("inf"), 0, 0
     while term == 0:
         g.call("sysml_b200_agg_unary_dense", _p(Cc), k, m, L.AGG_SUMSQ, L.DIR_ROW, _p(c2))           # rowSums(C^2)
-        g.call("sysml_b200_kmeans_step", _p(X), _p(Cc), _p(c2), n, m, k, _p(Cn), _p(den), _p(s1))   # t(P)%*%X, colSums(P), sum(minD)
+        try:
+            g.call("sysml_b200_kmeans_step", _p(X), _p(Cc), _p(c2), n, m, k, _p(Cn), _p(den), _p(s1))   # t(P)%*%X, colSums(P), sum(minD)
+        except Exception:
+            for o in (Cc, Cn, c2, den, s1):
+                o.free()
+            raise
         wcss_old, wcss = wcss, sumXsq + _scalar(g, s1)
         g.call("sysml_b200_binary_mm", _p(Cn), _p(den), _p(Cn), k, m, L.BCAST_COL, L.BINARY_OPS["/"])  # / t(P_denom)
         it += 1

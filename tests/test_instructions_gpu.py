@@ -340,3 +340,52 @@ def test_outer_vector_vector_instruction(ec):
     assert np.array_equal(ec.getMatrix("Z"), (cv < rv).astype(np.float64))
     ec.execute(inst("*", mat("cv"), mat("rv"), mat("Z")))
     assert np.array_equal(ec.getMatrix("Z"), cv * rv)
+
+
+def test_scratch_is_a_block_of_the_memory_manager():
+    """The kernels' scratch is allocated through GPUMemoryManager like every matrix (so `memory_limit` covers it): an
+    instruction whose scratch request exceeds the block fails without side effects (SYSML_E_WORKSPACE), the block is
+    re-allocated at the requested size and the instruction runs again."""
+    X = O.rand_uniform(30_000 * 600, seed=3).reshape(30_000, 600)
+    with ExecutionContext(0, memory_limit=400 << 20) as ec:
+        base = ec.stats()["allocated_bytes"]
+        assert base >= 1 << 20, "the initial scratch block is on the manager's books"
+        ec.setMatrix("X", X)
+        ec.execute(inst("tsmm", mat("X"), mat("T"), "LEFT"))            # split-K partials: tens of MB of scratch
+        T, nnz = O.tsmm_dense(X, True, 8)
+        assert_equal_matrices(T, ec.getMatrix("T"))
+        st = ec.stats()
+        assert st["allocated_bytes"] > base + X.nbytes, "scratch grew through the manager"
+        assert st["instructions"] == 1, "the repeated attempt is not counted twice"
+        assert st["allocated_bytes"] <= 400 << 20
+
+
+def test_caller_owned_workspace_through_the_abi(gctx):
+    """sysml_b200_ctx_set_workspace: with a caller-owned block the library never allocates scratch; a request that does not
+    fit returns SYSML_E_WORKSPACE and ctx_workspace_needed says how much the operation wanted."""
+    import ctypes as C
+    from systemml_b200 import GPUContext
+    with GPUContext(0) as g:
+        n, m = 50_000, 1000
+        X, v, out, ref = g.rand(n, m, seed=1), g.rand(m, 1, seed=2), g.empty(m, 1), g.empty(m, 1)
+        g.call("sysml_b200_mmchain_dense", C.c_void_p(X.ptr), C.c_void_p(v.ptr), None, C.c_void_p(ref.ptr), n, m, 0)
+        small = g.allocate(4096)
+        g.call("sysml_b200_ctx_set_workspace", C.c_void_p(small), 4096)
+        free0, _ = g.getAvailableMemory()
+        rc = g._lib.sysml_b200_mmchain_dense(g.handle, C.c_void_p(X.ptr), C.c_void_p(v.ptr), None, C.c_void_p(out.ptr), n, m, 0)
+        assert rc == native.E_WORKSPACE
+        need = g._lib.sysml_b200_ctx_workspace_needed(g.handle)
+        assert need > 4096
+        assert g.getAvailableMemory()[0] == free0, "nothing was allocated behind the caller's back"
+        big = g.allocate(need)
+        g.call("sysml_b200_ctx_set_workspace", C.c_void_p(big), need)
+        g.call("sysml_b200_mmchain_dense", C.c_void_p(X.ptr), C.c_void_p(v.ptr), None, C.c_void_p(out.ptr), n, m, 0)
+        assert np.array_equal(out.to_host(), ref.to_host())
+        assert g._lib.sysml_b200_ctx_workspace_bytes(g.handle) == need
+        g.call("sysml_b200_ctx_set_workspace", None, 0)                  # back to the library-owned default
+        g.call("sysml_b200_mmchain_dense", C.c_void_p(X.ptr), C.c_void_p(v.ptr), None, C.c_void_p(out.ptr), n, m, 0)
+        assert np.array_equal(out.to_host(), ref.to_host())
+        for p in (small, big):
+            g.cudaFreeHelper(p)
+        for o in (X, v, out, ref):
+            o.free()
