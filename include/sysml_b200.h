@@ -486,11 +486,13 @@ int sysml_b200_cg_step_dense(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const d
  *                              LinearRegCG / GLM over a matrix that is not resident yet costs the upload, not upload + pass.
  *   binaryblock_write        : host-side writer of the same format (tests, data preparation); dense_only = 0 picks each
  *                              block's format as MatrixBlock.write does (evalSparseFormatOnDisk, MatrixBlock.java:1017-1031,
- *                              isUltraSparseSerialize :897-899).  Takes no context.
+ *                              isUltraSparseSerialize :897-899).  first_block_row (0-based) is added to the block-row index
+ *                              of every record, so that h_X can be one part (a run of whole block rows) of a larger matrix
+ *                              written as a directory of part files.  Takes no context.
  * Compressed SequenceFiles are refused (SYSML_E_UNSUPPORTED).
  * ---------------------------------------------------------------------------------------------- */
 int sysml_b200_binaryblock_write(const char* path, const double* h_X, int64_t rows, int64_t cols, int brlen, int bclen,
-                                 int dense_only);
+                                 int dense_only, int64_t first_block_row);
 int sysml_b200_binaryblock_read_dense(sysml_b200_ctx* ctx, const char* path, int64_t rows, int64_t cols, int brlen,
                                       int bclen, int64_t row_begin, int64_t row_end, double* d_X);
 int sysml_b200_binaryblock_read_mmchain(sysml_b200_ctx* ctx, const char* path, int64_t rows, int64_t cols, int brlen,

@@ -29,15 +29,16 @@
 #include <sys/stat.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
 
 extern "C" int sysml_b200_mmchain_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w, double* out, int64_t n,
                                         int64_t m, int chain_type);
-extern "C" int sysml_b200_axpy(sysml_b200_ctx* ctx, const double* A, const double* B, double alpha, double* C, int64_t rows, int64_t cols,
-                               int bcast);
+int sysml_reduce_partial_rows(sysml_b200_ctx* ctx, const double* partial, int P, int m, double* out);
 
 namespace {
 
@@ -168,16 +169,23 @@ struct Slot {
   bool used = false;
 };
 
+// what the reader threads share: per block row of the range, the blocks still to arrive; the callback runs under the lock
+// (the context is not thread-safe, and the stripes must be handed over one at a time)
+struct Progress {
+  std::mutex mu;
+  std::vector<int> blocks_left;
+};
+
 struct Loader {
   sysml_b200_ctx* ctx;
   i64 rows, cols, row_begin, row_end;
   int brlen, bclen;
   double* dX;
+  Progress* prog = nullptr;
   std::vector<Slot> slots;
   size_t slot_bytes = 0;
   int next = 0;
   cudaStream_t copy_stream = nullptr;
-  std::vector<int> blocks_left;  // per block row of the range: blocks still to arrive
   i64 nblocks_seen = 0;
   std::string err;
 
@@ -190,9 +198,6 @@ struct Loader {
       if (cudaMalloc((void**)&s.dev, slot_bytes) != cudaSuccess) return SYSML_E_OOM;
       if (cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming) != cudaSuccess) return SYSML_E_CUDA;
     }
-    const i64 br0 = row_begin / brlen, br1 = (row_end + brlen - 1) / brlen;
-    const int per_row = (int)((cols + bclen - 1) / bclen);
-    blocks_left.assign((size_t)std::max<i64>(br1 - br0, 0), per_row);
     return SYSML_OK;
   }
   void destroy() {
@@ -224,13 +229,14 @@ struct Loader {
     bb_place_kernel<<<(unsigned)blocks, 256, 0, copy_stream>>>((const unsigned long long*)s->dev, dX + (lo - row_begin) * cols + col0, rlen, clen, cols,
                                                                (int)(lo - row0), (int)(hi - row0), swap);
     if (cudaGetLastError() != cudaSuccess) return SYSML_E_CUDA;
-    ctx->launches++;
+    __sync_fetch_and_add(&ctx->launches, 1);  // reader threads share the context's counter
     if (cudaEventRecord(s->done, copy_stream) != cudaSuccess) return SYSML_E_CUDA;
     return SYSML_OK;
   }
 };
 
-typedef int (*stripe_cb)(void* user, i64 first_row, i64 n_rows, cudaStream_t ready_on);
+// complete: the last block of that block row; otherwise only an ordering point (make the compute stream wait on ready_on)
+typedef int (*stripe_cb)(void* user, i64 first_row, i64 n_rows, cudaStream_t ready_on, bool complete);
 
 // reads one SequenceFile; every block that intersects the row range is placed on the device
 int read_file(Loader& L, const std::string& path, stripe_cb cb, void* user) {
@@ -353,12 +359,18 @@ int read_file(Loader& L, const std::string& path, stripe_cb cb, void* user) {
     int rc = L.submit(s, bi, bj, rlen, clen, swap);
     if (rc) return rc;
     L.nblocks_seen++;
-    // a whole block row of the range has been queued: hand it to the caller (the work it queues waits on the copy stream)
+    // a whole block row of the range has been queued: hand it to the caller (the work it queues waits on the copy stream).
+    // Blocks of one block row may come from different reader threads: each thread's stream is waited for as its last
+    // block of the row is counted, so by the time the count reaches zero every contributor has been ordered.
     const i64 idx = bi - L.row_begin / L.brlen;
-    if (idx >= 0 && idx < (i64)L.blocks_left.size() && --L.blocks_left[(size_t)idx] == 0 && cb) {
-      const i64 lo = std::max(row0, L.row_begin), hi = std::min(row0 + rlen, L.row_end);
-      rc = cb(user, lo - L.row_begin, hi - lo, L.copy_stream);
-      if (rc) return rc;
+    if (idx >= 0 && idx < (i64)L.prog->blocks_left.size()) {
+      std::lock_guard<std::mutex> lock(L.prog->mu);
+      const int left = --L.prog->blocks_left[(size_t)idx];
+      if (cb) {
+        const i64 lo = std::max(row0, L.row_begin), hi = std::min(row0 + rlen, L.row_end);
+        rc = cb(user, lo - L.row_begin, hi - lo, L.copy_stream, left == 0);
+        if (rc) return rc;
+      }
     }
   }
   return SYSML_OK;
@@ -394,83 +406,105 @@ int load(sysml_b200_ctx* ctx, const char* path, i64 rows, i64 cols, int brlen, i
   if (row_begin % brlen != 0) return sysml_set_error(ctx, SYSML_E_INVALID, "binaryblock: the row range must start at a block boundary");
   if (row_end > row_begin && cols > 0 && !dX) return sysml_set_error(ctx, SYSML_E_INVALID, "binaryblock: null destination");
   if (row_end == row_begin || cols == 0) return SYSML_OK;
-  Loader L{ctx, rows, cols, row_begin, row_end, brlen, bclen, dX};
-  int rc = L.init(4);
-  if (rc) {
-    L.destroy();
-    return sysml_set_error(ctx, rc, "binaryblock: cannot set up the staging ring (%zu bytes per slot)", L.slot_bytes);
-  }
-  // blocks that never appear in the file are empty blocks (writers may skip them): the destination starts at zero
-  cudaMemsetAsync(dX, 0, (size_t)(row_end - row_begin) * cols * sizeof(double), L.copy_stream);
   std::vector<std::string> parts;
   std::string err;
-  rc = list_parts(path, &parts, &err);
-  for (size_t i = 0; !rc && i < parts.size(); i++) rc = read_file(L, parts[i], cb, user);
-  cudaError_t e = cudaStreamSynchronize(L.copy_stream);
-  if (!rc && e != cudaSuccess) {
-    rc = SYSML_E_CUDA;
-    L.err = cudaGetErrorString(e);
+  int rc = list_parts(path, &parts, &err);
+  if (rc) return sysml_set_error(ctx, rc, "binaryblock: %s", err.c_str());
+  Progress prog;
+  {
+    const i64 br0 = row_begin / brlen, br1 = (row_end + brlen - 1) / brlen;
+    prog.blocks_left.assign((size_t)std::max<i64>(br1 - br0, 0), (int)((cols + bclen - 1) / bclen));
   }
+  // blocks that never appear in the file are empty blocks (writers may skip them): the destination starts at zero
+  SYSML_CUDA(ctx, cudaMemsetAsync(dX, 0, (size_t)(row_end - row_begin) * cols * sizeof(double), ctx->stream));
+  SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  // part files are read in parallel (ReaderBinaryBlockParallel reads them with one task each), every reader with its own
+  // staging ring and copy stream
+  const int nthreads = (int)std::min<size_t>(parts.size(), 8);
+  std::vector<int> trc((size_t)nthreads, SYSML_OK);
+  std::vector<std::string> terr((size_t)nthreads);
+  auto work = [&](int t) {
+    cudaSetDevice(ctx->device);
+    Loader L{ctx, rows, cols, row_begin, row_end, brlen, bclen, dX};
+    L.prog = &prog;
+    int r = L.init(4);
+    if (r) L.err = "cannot set up the staging ring";
+    for (size_t i = (size_t)t; !r && i < parts.size(); i += (size_t)nthreads) r = read_file(L, parts[i], cb, user);
+    if (L.copy_stream) {
+      cudaError_t e = cudaStreamSynchronize(L.copy_stream);
+      if (!r && e != cudaSuccess) {
+        r = SYSML_E_CUDA;
+        L.err = cudaGetErrorString(e);
+      }
+    }
+    trc[(size_t)t] = r;
+    terr[(size_t)t] = L.err;
+    L.destroy();
+  };
+  if (nthreads <= 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; t++) th.emplace_back(work, t);
+    for (auto& x : th) x.join();
+  }
+  sysml_set_device(ctx);
+  for (int t = 0; t < nthreads; t++)
+    if (trc[(size_t)t]) return sysml_set_error(ctx, trc[(size_t)t], "binaryblock: %s", terr[(size_t)t].empty() ? "read failed" : terr[(size_t)t].c_str());
   // block rows with skipped (empty) blocks never reached zero above: report them now, in order
-  if (!rc && cb) {
+  if (cb) {
     const i64 br0 = row_begin / brlen;
-    for (size_t i = 0; !rc && i < L.blocks_left.size(); i++)
-      if (L.blocks_left[i] > 0) {
+    for (size_t i = 0; i < prog.blocks_left.size(); i++)
+      if (prog.blocks_left[i] > 0) {
         const i64 lo = std::max((br0 + (i64)i) * brlen, row_begin), hi = std::min((br0 + (i64)i + 1) * brlen, row_end);
-        rc = cb(user, lo - row_begin, hi - lo, L.copy_stream);
+        rc = cb(user, lo - row_begin, hi - lo, ctx->stream, true);
+        if (rc) return rc;
       }
   }
-  if (rc && L.err.empty() && !err.empty()) L.err = err;
-  const std::string msg = L.err;
-  L.destroy();
-  if (rc) return sysml_set_error(ctx, rc, "binaryblock: %s", msg.empty() ? "read failed" : msg.c_str());
   // later work on the context's stream sees the matrix
   SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SYSML_OK;
 }
 
+// The first pass overlapped with the upload: block rows are grouped into fixed row ranges of ~64 MB; when the last block row
+// of a group has arrived, mmchain runs on the group and writes ITS partial result into the group's own slot.  The slots
+// are added in group order at the end (fixed-order compensated reduction), so the result does not depend on which reader
+// thread was faster.
 struct ChainState {
   sysml_b200_ctx* ctx;
   const double* dX;
   const double* v;
   const double* w;
-  double* out;
-  double* tmp;
-  i64 cols;
-  int ct;
+  double* partials;  // [ngroups][cols]
+  i64 cols, nrows;
+  int ct, brlen;
+  i64 group_rows;    // multiple of brlen
+  std::vector<int> stripes_left;
   cudaEvent_t ev;
-  i64 pending_first, pending_rows, group_rows;
 };
 
-int flush_group(ChainState* st) {
-  if (st->pending_rows == 0) return SYSML_OK;
-  int rc = sysml_b200_mmchain_dense(st->ctx, st->dX + st->pending_first * st->cols, st->v, st->w ? st->w + st->pending_first : nullptr, st->tmp,
-                                    st->pending_rows, st->cols, st->ct);
-  if (rc) return rc;
-  rc = sysml_b200_axpy(st->ctx, st->out, st->tmp, 1.0, st->out, st->cols, 1, SYSML_BCAST_NONE);  // out += partial, in arrival (= row) order
-  st->pending_rows = 0;
-  return rc;
-}
-
-int chain_cb(void* user, i64 first_row, i64 n_rows, cudaStream_t ready_on) {
+int chain_cb(void* user, i64 first_row, i64 n_rows, cudaStream_t ready_on, bool complete) {
   ChainState* st = (ChainState*)user;
-  // the stripe's copies and placements are queued on the copy stream: make the compute stream wait for them
-  if (cudaEventRecord(st->ev, ready_on) != cudaSuccess || cudaStreamWaitEvent(st->ctx->stream, st->ev, 0) != cudaSuccess) return SYSML_E_CUDA;
-  if (st->pending_rows > 0 && first_row != st->pending_first + st->pending_rows) {
-    int rc = flush_group(st);  // out-of-order stripe (several part files): start a new group
-    if (rc) return rc;
+  // this reader's copies and placements of the stripe are queued on its stream: the compute stream waits for them
+  if (ready_on != st->ctx->stream) {
+    if (cudaEventRecord(st->ev, ready_on) != cudaSuccess || cudaStreamWaitEvent(st->ctx->stream, st->ev, 0) != cudaSuccess) return SYSML_E_CUDA;
   }
-  if (st->pending_rows == 0) st->pending_first = first_row;
-  st->pending_rows += n_rows;
-  return st->pending_rows >= st->group_rows ? flush_group(st) : SYSML_OK;
+  if (!complete) return SYSML_OK;
+  const i64 g = first_row / st->group_rows;
+  if (--st->stripes_left[(size_t)g] > 0) return SYSML_OK;
+  const i64 lo = g * st->group_rows, hi = std::min(lo + st->group_rows, st->nrows);
+  return sysml_b200_mmchain_dense(st->ctx, st->dX + lo * st->cols, st->v, st->w ? st->w + lo : nullptr, st->partials + (size_t)g * st->cols, hi - lo,
+                                  st->cols, st->ct);
 }
 
 }  // namespace
 
 extern "C" {
 
-int sysml_b200_binaryblock_write(const char* path, const double* h_X, int64_t rows, int64_t cols, int brlen, int bclen, int dense_only) {
-  if (!path || rows < 0 || cols < 0 || brlen < 1 || bclen < 1 || (rows * cols > 0 && !h_X)) return sysml_set_error(nullptr, SYSML_E_INVALID, "binaryblock_write: bad arguments");
+int sysml_b200_binaryblock_write(const char* path, const double* h_X, int64_t rows, int64_t cols, int brlen, int bclen, int dense_only,
+                                 int64_t first_block_row) {
+  if (!path || rows < 0 || cols < 0 || brlen < 1 || bclen < 1 || first_block_row < 0 || (rows * cols > 0 && !h_X))
+    return sysml_set_error(nullptr, SYSML_E_INVALID, "binaryblock_write: bad arguments");
   FILE* f = fopen(path, "wb");
   if (!f) return sysml_set_error(nullptr, SYSML_E_INVALID, "binaryblock_write: cannot create %s: %s", path, strerror(errno));
   std::vector<unsigned char> b;
@@ -496,15 +530,24 @@ int sysml_b200_binaryblock_write(const char* path, const double* h_X, int64_t ro
       int type = BT_DENSE;
       if (!dense_only) on_disk_format(rlen, clen, nnz, &type);
       b.clear();
-      put_be64(b, (uint64_t)(bi + 1));
+      put_be64(b, (uint64_t)(first_block_row + bi + 1));
       put_be64(b, (uint64_t)(bj + 1));
       put_be32(b, (uint32_t)rlen);
       put_be32(b, (uint32_t)clen);
       b.push_back((unsigned char)type);
       if (type == BT_DENSE) {
-        b.reserve(b.size() + (size_t)rlen * clen * 8);
-        for (int r = 0; r < rlen; r++)
-          for (int c = 0; c < clen; c++) put_double(b, src[(i64)r * cols + c]);
+        const size_t off = b.size();
+        b.resize(off + (size_t)rlen * clen * 8);
+        unsigned char* q = b.data() + off;
+        for (int r = 0; r < rlen; r++) {
+          const double* row = src + (i64)r * cols;
+          for (int c = 0; c < clen; c++, q += 8) {
+            uint64_t u;
+            memcpy(&u, row + c, 8);
+            u = __builtin_bswap64(u);
+            memcpy(q, &u, 8);
+          }
+        }
       } else if (type == BT_SPARSE) {
         if ((i64)rlen * clen > INT_MAX64) put_be64(b, (uint64_t)nnz);
         else put_be32(b, (uint32_t)nnz);
@@ -557,20 +600,32 @@ int sysml_b200_binaryblock_read_mmchain(sysml_b200_ctx* ctx, const char* path, i
   if (chain_type < 0 || chain_type > 2 || (chain_type != SYSML_CHAIN_XtXv && row_end > row_begin && !w))
     return sysml_set_error(ctx, SYSML_E_INVALID, "binaryblock_read_mmchain: bad chain type / missing w");
   if (cols == 0) return SYSML_OK;
-  SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)cols * sizeof(double), ctx->stream));
+  const i64 nrows = row_end - row_begin;
+  if (nrows == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)cols * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
   ChainState st{};
-  st.ctx = ctx; st.dX = d_X; st.v = v; st.w = w; st.out = out; st.cols = cols; st.ct = chain_type;
-  st.group_rows = std::max<i64>(((i64)64 << 20) / (8 * std::max<i64>(cols, 1)), brlen);  // ~64 MB of rows per launch
-  SYSML_CUDA(ctx, cudaMalloc((void**)&st.tmp, (size_t)cols * sizeof(double)));
+  st.ctx = ctx; st.dX = d_X; st.v = v; st.w = w; st.cols = cols; st.nrows = nrows; st.ct = chain_type; st.brlen = brlen;
+  const i64 want = std::max<i64>(((i64)64 << 20) / (8 * std::max<i64>(cols, 1)), 1);
+  st.group_rows = ((want + brlen - 1) / brlen) * brlen;
+  const i64 ngroups = (nrows + st.group_rows - 1) / st.group_rows;
+  if (ngroups > 0x7fffffffLL) return sysml_set_error(ctx, SYSML_E_LIMIT, "binaryblock_read_mmchain: too many row groups");
+  st.stripes_left.resize((size_t)ngroups);
+  for (i64 g = 0; g < ngroups; g++) {
+    const i64 lo = g * st.group_rows, hi = std::min(lo + st.group_rows, nrows);
+    st.stripes_left[(size_t)g] = (int)((hi - lo + brlen - 1) / brlen);
+  }
+  SYSML_CUDA(ctx, cudaMalloc((void**)&st.partials, (size_t)ngroups * cols * sizeof(double)));
   if (cudaEventCreateWithFlags(&st.ev, cudaEventDisableTiming) != cudaSuccess) {
-    cudaFree(st.tmp);
+    cudaFree(st.partials);
     return sysml_set_error(ctx, SYSML_E_CUDA, "binaryblock_read_mmchain: cannot create an event");
   }
   int rc = load(ctx, path, rows, cols, brlen, bclen, row_begin, row_end, d_X, chain_cb, &st);
-  if (!rc) rc = flush_group(&st);
+  if (!rc) rc = sysml_reduce_partial_rows(ctx, st.partials, (int)ngroups, (int)cols, out);
   cudaStreamSynchronize(ctx->stream);
   cudaEventDestroy(st.ev);
-  cudaFree(st.tmp);
+  cudaFree(st.partials);
   return rc;
 }
 

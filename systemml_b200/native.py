@@ -68,7 +68,7 @@ SIGNATURES = {
     "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),
     "sysml_b200_dense_to_csr": (ci, [vp, vp, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_csr_to_dense": (ci, [vp, vp, vp, vp, i64, i64, vp]),
-    "sysml_b200_binaryblock_write": (ci, [C.c_char_p, vp, i64, i64, ci, ci, ci]),
+    "sysml_b200_binaryblock_write": (ci, [C.c_char_p, vp, i64, i64, ci, ci, ci, i64]),
     "sysml_b200_binaryblock_read_dense": (ci, [vp, C.c_char_p, i64, i64, ci, ci, i64, i64, vp]),
     "sysml_b200_binaryblock_read_mmchain": (ci, [vp, C.c_char_p, i64, i64, ci, ci, i64, i64, vp, vp, vp, vp, ci]),
     "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),

@@ -80,7 +80,7 @@ def test_writer_produces_the_reference_layout(tmp_path):
     X[200:230, 128:170] = 0.0
     X[205, 130] = 7.5                                       # an ultra-sparse block (nnz < rows)
     p = str(tmp_path / "X.bb").encode()
-    assert lib.sysml_b200_binaryblock_write(p, X.ctypes.data_as(C.c_void_p), rows, cols, br, bc, 0) == 0
+    assert lib.sysml_b200_binaryblock_write(p, X.ctypes.data_as(C.c_void_p), rows, cols, br, bc, 0, 0) == 0
     blocks = _parse(p.decode())
     assert len(blocks) == 3 * 3
     types = {k: v[0] for k, v in blocks.items()}
@@ -90,5 +90,5 @@ def test_writer_produces_the_reference_layout(tmp_path):
         out[(bi - 1) * br:(bi - 1) * br + blk.shape[0], (bj - 1) * bc:(bj - 1) * bc + blk.shape[1]] = blk
     assert np.array_equal(out, X)
     # dense_only: every block is a DENSE_BLOCK
-    assert lib.sysml_b200_binaryblock_write(p, X.ctypes.data_as(C.c_void_p), rows, cols, br, bc, 1) == 0
+    assert lib.sysml_b200_binaryblock_write(p, X.ctypes.data_as(C.c_void_p), rows, cols, br, bc, 1, 0) == 0
     assert all(v[0] == 3 for v in _parse(p.decode()).values())

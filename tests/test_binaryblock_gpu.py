@@ -14,9 +14,11 @@ from tests.util import assert_equal_matrices
 pytestmark = pytest.mark.gpu
 
 
-def _write(path, X, br, bc, dense_only=0):
+def _write(path, X, br, bc, dense_only=0, first_block_row=0):
     from systemml_b200 import native
-    rc = native.load().sysml_b200_binaryblock_write(str(path).encode(), X.ctypes.data_as(C.c_void_p), X.shape[0], X.shape[1], br, bc, dense_only)
+    X = np.ascontiguousarray(X)
+    rc = native.load().sysml_b200_binaryblock_write(str(path).encode(), X.ctypes.data_as(C.c_void_p), X.shape[0], X.shape[1], br, bc, dense_only,
+                                                    first_block_row)
     assert rc == 0
 
 
@@ -56,17 +58,8 @@ def test_directory_of_part_files_and_missing_blocks(gctx, tmp_path):
     X[1000:2000] = 0.0                      # this block row is written to neither part: it must read as zeros
     d = tmp_path / "X.dir"
     d.mkdir()
-    top = np.zeros_like(X)
-    top[:1000] = X[:1000]
-    _write(d / "0-m-00000", X[:1000].copy(), br, 1000, 0)
-    # second part: rows 2000..2999 -- written as its own 1000-row matrix, then re-keyed by patching the block-row index
-    _write(d / "0-m-00001", X[2000:].copy(), br, 1000, 1)
-    raw = bytearray((d / "0-m-00001").read_bytes())
-    import struct
-    i = raw.find(struct.pack(">i", 16) + struct.pack(">qq", 1, 1))
-    assert i > 0
-    raw[i + 4:i + 12] = struct.pack(">q", 3)
-    (d / "0-m-00001").write_bytes(bytes(raw))
+    _write(d / "0-m-00000", X[:1000], br, 1000, 0)
+    _write(d / "0-m-00001", X[2000:], br, 1000, 1, first_block_row=2)     # second part: rows 2000..2999
     (d / "_SUCCESS").write_bytes(b"")
     dev = gctx.empty(rows, cols)
     gctx.call("sysml_b200_binaryblock_read_dense", str(d).encode(), rows, cols, br, 1000, 0, rows, C.c_void_p(dev.ptr))
@@ -107,3 +100,29 @@ def test_bad_files_are_refused(gctx, tmp_path):
         gctx.call("sysml_b200_binaryblock_read_dense", str(tmp_path / "ok").encode(), 10, 10, 1000, 1000, 0, 10, C.c_void_p(d.ptr))
     assert ei.value.code == native.E_DIM
     d.free()
+
+
+def test_parallel_part_files_give_the_same_bits_every_time(gctx, tmp_path):
+    """Eight part files are read by eight threads (as ReaderBinaryBlockParallel does); which one is faster must not show in
+    the overlapped first pass: group partials are added in group order."""
+    rows, cols, br = 40_000, 200, 1000
+    X = O.rand_uniform(rows * cols, seed=21).reshape(rows, cols)
+    v = O.rand_uniform(cols, seed=22)
+    d = tmp_path / "X.parts"
+    d.mkdir()
+    nparts = 8
+    per = rows // br // nparts                      # block rows per part
+    for p in range(nparts):
+        lo = p * per * br
+        _write(d / ("0-m-%05d" % p), X[lo:lo + per * br], br, 1000, 1, first_block_row=p * per)
+    dX, dv, out = gctx.empty(rows, cols), gctx.dense(v.reshape(-1, 1)), gctx.empty(cols, 1)
+    res = []
+    for _ in range(3):
+        gctx.call("sysml_b200_binaryblock_read_mmchain", str(d).encode(), rows, cols, br, 1000, 0, rows, C.c_void_p(dX.ptr), C.c_void_p(dv.ptr), None,
+                  C.c_void_p(out.ptr), 0)
+        res.append(out.to_host().reshape(-1))
+    assert np.array_equal(dX.to_host(), X)
+    assert np.array_equal(res[0], res[1]) and np.array_equal(res[1], res[2])
+    assert_equal_matrices(O.mmchain_dense(X, v, None, 0, 4), res[0], what="parallel parts, overlapped mmchain")
+    for o in (dX, dv, out):
+        o.free()
