@@ -139,12 +139,13 @@ def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1
     return out, inner_counts
 
 
-def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
+def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column_copy=False):
     """scripts/algorithms/l2-svm.dml:103-154 (intercept = 0, labels already -1/+1): non-linear CG on the squared-hinge
     primal with an exact Newton line search.  X: GPUObject n x m, dense or CSR (BASELINE config C3 is CSR 50M x 10k);
     Y: GPUObject n x 1.  Per outer iteration the O(nnz) work is X %*% s and t(X) %*% (out * Y); everything else is
     chains over n-vectors, each evaluated in one pass by fusedCellwise (fused=True) or operator by operator
-    (fused=False, the reference's plan).  Returns (w ndarray, iterations, final objective)."""
+    (fused=False, the reference's plan).  column_copy=True runs t(X) %*% y as a gather over the column-ordered copy of a
+    CSR X (csrc/pcsc.cu; deterministic), False as the scatter kernel.  Returns (w ndarray, iterations, final objective)."""
     n, m = X.rows, X.cols
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
@@ -157,9 +158,12 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None):
         else:
             g.call("sysml_b200_matmult_dense", _p(X), _p(v), _p(out), n, m, m, 1, 0, 0)
 
+    if sparse and column_copy:
+        X.transposed_uses = max(X.transposed_uses, 1)   # X is constant across the iterations: build the copy at the first use
+
     def xt_times(yv, out):      # out = t(X) %*% yv
-        pc = X.columnOrderedCopy() if sparse else None
-        if pc is not None:          # X is constant across the iterations: gather over its column-ordered copy
+        pc = X.columnOrderedCopy() if (sparse and column_copy) else None
+        if pc is not None:          # gather over the column-ordered copy (bit-identical run to run)
             g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, _p(yv), None, 0, _p(out))
         elif sparse:
             g.call("sysml_b200_matmult_csr_dense", C.c_void_p(X.csr.rowPtr), C.c_void_p(X.csr.colInd), C.c_void_p(X.csr.val),

@@ -8,6 +8,7 @@
 parity tests read like its own GPU tests.  Everything numeric happens in the native library.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -262,6 +263,8 @@ class GPUObject:
         operand goes through the scatter kernels (a one-shot operand never pays for the sort), the second one builds
         the copy, and every later t(X) %*% y / mmchain gathers from it."""
         if self.csr is None or self.csr.nnz == 0 or not PCSCPointer.fits(self.gctx, self.rows, self.cols):
+            return None
+        if os.environ.get("SYSML_B200_NO_PCSC"):   # A/B switch for measurements
             return None
         self.transposed_uses += 1
         if self.pcsc is None and self.transposed_uses >= 2:
