@@ -24,6 +24,7 @@ struct sysml_b200_ctx {
   size_t ws_bytes;
   bool ws_external;  // the block belongs to the caller (sysml_b200_ctx_set_workspace): never grown or freed here
   size_t ws_needed;  // size of the last request an external block could not satisfy
+  size_t ws_prefix;  // bytes at the start of the block that the current operation keeps for itself (nested requests start after them)
   unsigned int* counters;  // 64 zero-initialised counters; every kernel that uses one resets it
   void* pinned;      // pinned host staging
   size_t pinned_bytes;

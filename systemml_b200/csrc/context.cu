@@ -17,22 +17,26 @@ int sysml_set_error(sysml_b200_ctx* ctx, int code, const char* fmt, ...) {
 }
 
 int sysml_workspace(sysml_b200_ctx* ctx, size_t bytes, void** out) {
-  if (bytes > ctx->ws_bytes && ctx->ws_external) {
-    ctx->ws_needed = bytes;
+  // an operation that keeps data of its own at the start of the block (ws_prefix) sized the block for its nested
+  // requests beforehand: those are served after the prefix and must never move the block
+  const size_t need = bytes + ctx->ws_prefix;
+  if (need > ctx->ws_bytes && ctx->ws_external) {
+    ctx->ws_needed = need;
     return sysml_set_error(ctx, SYSML_E_WORKSPACE, "scratch: this operation needs %zu bytes, the caller's workspace holds %zu (sysml_b200_ctx_set_workspace)",
-                           bytes, ctx->ws_bytes);
+                           need, ctx->ws_bytes);
   }
-  if (bytes > ctx->ws_bytes) {
+  if (need > ctx->ws_bytes) {
+    if (ctx->ws_prefix) return sysml_set_error(ctx, SYSML_E_CUDA, "scratch: nested request of %zu bytes does not fit behind a %zu-byte prefix", bytes, ctx->ws_prefix);
     // grow-only; growing synchronises the stream because in-flight kernels may still use the old block
     SYSML_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (ctx->ws) SYSML_CUDA(ctx, cudaFree(ctx->ws));
     ctx->ws = nullptr;
     ctx->ws_bytes = 0;
-    size_t want = bytes < (size_t(8) << 20) ? (size_t(8) << 20) : bytes + bytes / 4;
+    size_t want = need < (size_t(8) << 20) ? (size_t(8) << 20) : need + need / 4;
     SYSML_CUDA(ctx, cudaMalloc(&ctx->ws, want));
     ctx->ws_bytes = want;
   }
-  *out = ctx->ws;
+  *out = (char*)ctx->ws + ctx->ws_prefix;
   return SYSML_OK;
 }
 

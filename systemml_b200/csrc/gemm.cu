@@ -1034,6 +1034,80 @@ int dispatch_gemm(sysml_b200_ctx* ctx, const double* A, i64 lda, const double* B
   return run_gemm<TA, TB, 256, 64, 8, 1, BK, STAGES, NP>(ctx, A, lda, B, ldb, C, M, N, K, false, nullptr);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Odd shapes.  The warp-specialised kernel moves 16-byte pieces: it wants even leading dimensions, even M and N and
+// 16-byte aligned bases.  An operand that is not like that (t(X) %*% X with 567 or 999 columns, an odd number of rows
+// of a skinny product) is copied once into a zero-padded, even-sized image in the context's scratch block -- zeros add
+// nothing to any sum -- the product runs on the images at full speed, and the m x n corner of the padded result is
+// copied out.  The copies cost one pass over the operands (2 x 8 bytes per cell) next to a contraction that reads each
+// cell many times.  Only when the images do not fit in half of the free device memory does the call fall back to the
+// 8-byte cp.async kernel.
+// ------------------------------------------------------------------------------------------------
+__global__ void pad_copy_kernel(const double* __restrict__ src, i64 rs, i64 cs, double* __restrict__ dst, i64 rd, i64 cd) {
+  const i64 total = rd * cd;
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const i64 r = i / cd, c = i - r * cd;
+    dst[i] = (r < rs && c < cs) ? ldg_stream(src + r * cs + c) : 0.0;
+  }
+}
+inline bool ws_friendly(const double* p, i64 ld) { return ((reinterpret_cast<uintptr_t>(p) & 15) == 0) && (ld % 2 == 0); }
+inline i64 even_up(i64 x) { return x + (x & 1); }
+
+template <bool TA, bool TB>
+int gemm_any_shape(sysml_b200_ctx* ctx, const double* A, i64 a_rows, i64 a_cols, const double* B, i64 b_rows, i64 b_cols, double* C, i64 M, i64 N,
+                   i64 K, bool sym, int64_t* h_nnz) {
+  const bool ok = ws_friendly(A, a_cols) && ws_friendly(B, b_cols) && (M % 2 == 0) && (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+  if (ok || getenv("SYSML_B200_GEMM_NO_PAD")) return dispatch_gemm<TA, TB>(ctx, A, a_cols, B, b_cols, C, M, N, K, sym, h_nnz);
+  // K is padded only where it is a leading dimension (the columns of a stored operand); an odd number of contraction
+  // ROWS needs nothing, so t(X) %*% X of an odd-row X is not copied
+  const bool kpad = (K & 1) && (!TA || TB);
+  const i64 Mp = even_up(M), Np = even_up(N), Kp = kpad ? K + 1 : K;
+  const i64 ar = TA ? Kp : Mp, ac = TA ? Mp : Kp;   // image of A
+  const i64 br = TB ? Np : Kp, bc = TB ? Kp : Np;   // image of B
+  const bool padA = (reinterpret_cast<uintptr_t>(A) & 15) != 0 || ar != a_rows || ac != a_cols;
+  const bool padB = !sym && ((reinterpret_cast<uintptr_t>(B) & 15) != 0 || br != b_rows || bc != b_cols);
+  const bool padC = Mp != M || Np != N || (reinterpret_cast<uintptr_t>(C) & 15) != 0;
+  auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  const size_t bytesA = padA ? al((size_t)ar * ac * 8) : 0, bytesB = padB ? al((size_t)br * bc * 8) : 0, bytesC = padC ? al((size_t)Mp * Np * 8) : 0;
+  const size_t prefix = bytesA + bytesB + bytesC;
+  const size_t nested = ((size_t)1 << 30) + ((size_t)1 << 20);  // run_gemm asks for at most 1 GiB + 256 bytes of split-K partials
+  size_t free_b = 0, total_b = 0;
+  cudaMemGetInfo(&free_b, &total_b);
+  if (ctx->ws_prefix != 0 || (prefix + nested > ctx->ws_bytes && prefix + nested > (free_b + (ctx->ws_external ? 0 : ctx->ws_bytes)) / 2))
+    return dispatch_gemm<TA, TB>(ctx, A, a_cols, B, b_cols, C, M, N, K, sym, h_nnz);  // no room for the images: the 8-byte kernel
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, prefix + nested, &ws);
+  if (rc) return rc;
+  char* base = (char*)ws;
+  const double* Ap = A;
+  const double* Bp = B;
+  double* Cp = C;
+  auto grid = [&](i64 n) {
+    i64 b = (n + 255) / 256;
+    const i64 cap = (i64)ctx->sm_count * 16;
+    return (unsigned)(b > cap ? cap : (b < 1 ? 1 : b));
+  };
+  if (padA) {
+    pad_copy_kernel<<<grid(ar * ac), 256, 0, ctx->stream>>>(A, a_rows, a_cols, (double*)base, ar, ac);
+    SYSML_LAUNCH_CHECK(ctx, "pad_copy_kernel");
+    Ap = (const double*)base;
+  }
+  if (sym) Bp = Ap;
+  if (padB) {
+    pad_copy_kernel<<<grid(br * bc), 256, 0, ctx->stream>>>(B, b_rows, b_cols, (double*)(base + bytesA), br, bc);
+    SYSML_LAUNCH_CHECK(ctx, "pad_copy_kernel");
+    Bp = (const double*)(base + bytesA);
+  }
+  if (padC) Cp = (double*)(base + bytesA + bytesB);
+  ctx->ws_prefix = prefix;
+  rc = dispatch_gemm<TA, TB>(ctx, Ap, ac, Bp, sym ? ac : bc, Cp, Mp, Np, Kp, sym, h_nnz);
+  ctx->ws_prefix = 0;
+  if (rc) return rc;
+  if (padC) SYSML_CUDA(ctx, cudaMemcpy2DAsync(C, (size_t)N * 8, Cp, (size_t)Np * 8, (size_t)N * 8, (size_t)M, cudaMemcpyDeviceToDevice, ctx->stream));
+  return SYSML_OK;
+}
+
 }  // namespace
 
 extern "C" int sysml_b200_tsmm_dense(sysml_b200_ctx* ctx, const double* X, double* out, int64_t rows, int64_t cols, int left,
@@ -1050,8 +1124,8 @@ extern "C" int sysml_b200_tsmm_dense(sysml_b200_ctx* ctx, const double* X, doubl
     return SYSML_OK;
   }
   if (!X) return sysml_set_error(ctx, SYSML_E_INVALID, "tsmm: X is null");
-  if (left) return dispatch_gemm<true, false>(ctx, X, cols, X, cols, out, dim, dim, K, true, h_nnz_out);
-  return dispatch_gemm<false, true>(ctx, X, cols, X, cols, out, dim, dim, K, true, h_nnz_out);
+  if (left) return gemm_any_shape<true, false>(ctx, X, rows, cols, X, rows, cols, out, dim, dim, K, true, h_nnz_out);
+  return gemm_any_shape<false, true>(ctx, X, rows, cols, X, rows, cols, out, dim, dim, K, true, h_nnz_out);
 }
 
 extern "C" int sysml_b200_matmult_dense(sysml_b200_ctx* ctx, const double* A, const double* B, double* C, int64_t a_rows,
@@ -1071,8 +1145,8 @@ extern "C" int sysml_b200_matmult_dense(sysml_b200_ctx* ctx, const double* A, co
   // vector shapes -> the HBM-bound row-streaming kernels of mmchain.cu (cublasDgemv / Ddot twins)
   if (N == 1) return trans_a ? sysml_dense_vm(ctx, A, B, C, K, M) : sysml_dense_mv(ctx, A, B, C, M, K);
   if (M == 1) return trans_b ? sysml_dense_mv(ctx, B, A, C, N, K) : sysml_dense_vm(ctx, B, A, C, K, N);
-  if (!trans_a && !trans_b) return dispatch_gemm<false, false>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
-  if (trans_a && !trans_b) return dispatch_gemm<true, false>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
-  if (!trans_a && trans_b) return dispatch_gemm<false, true>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
-  return dispatch_gemm<true, true>(ctx, A, a_cols, B, b_cols, C, M, N, K, false, nullptr);
+  if (!trans_a && !trans_b) return gemm_any_shape<false, false>(ctx, A, a_rows, a_cols, B, b_rows, b_cols, C, M, N, K, false, nullptr);
+  if (trans_a && !trans_b) return gemm_any_shape<true, false>(ctx, A, a_rows, a_cols, B, b_rows, b_cols, C, M, N, K, false, nullptr);
+  if (!trans_a && trans_b) return gemm_any_shape<false, true>(ctx, A, a_rows, a_cols, B, b_rows, b_cols, C, M, N, K, false, nullptr);
+  return gemm_any_shape<true, true>(ctx, A, a_rows, a_cols, B, b_rows, b_cols, C, M, N, K, false, nullptr);
 }

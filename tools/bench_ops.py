@@ -95,7 +95,9 @@ def main():
 
     # ---------------- tsmm ----------------
     if want("tsmm"):
-        for (n, m, tag) in ((int(10_000_000 * S), 1000, "C2shape"), (int(1_000_000 * S), 5000, "C4"), (int(2_000_000 * S), 1024, "pow2")):
+        for (n, m, tag) in ((int(10_000_000 * S), 1000, "C2shape"), (int(1_000_000 * S), 5000, "C4"), (int(2_000_000 * S), 1024, "pow2"),
+                            (int(2_000_000 * S), 1000, "even_2M"), (int(2_000_000 * S), 999, "odd_2Mx999"), (int(1_000_000 * S), 5001, "odd_1Mx5001"),
+                            (int(2_000_001 * S), 1000, "oddrows_2000001x1000")):
             X = g.rand(n, m, seed=1)
             o = g.empty(m, m)
             b, a = timeit(g, lambda: g.call("sysml_b200_tsmm_dense", p_(X), p_(o), n, m, 1, None), max(2, args.reps // 2))
