@@ -62,6 +62,8 @@ def lib():
         L.orc_binary_mm.argtypes = [dp, dp, dp, i64, i64, C.c_int, C.c_int]
         L.orc_binary_ms.argtypes = [dp, C.c_double, dp, i64, C.c_int, C.c_int]
         L.orc_axpy.argtypes = [dp, dp, C.c_double, dp, i64, i64, C.c_int]
+        L.orc_unary_round.argtypes = [dp, dp, i64]
+        L.orc_unary_signum.argtypes = [dp, dp, i64]
         L.orc_count_nnz.argtypes = [dp, i64]
         L.orc_count_nnz.restype = i64
         L.orc_dense_to_csr.argtypes = [dp, i64, i64, lp, C.c_void_p, C.c_void_p]
@@ -245,8 +247,25 @@ def axpy(A, B, alpha):
     return out
 
 
+def java_round(x):
+    """Builtin ROUND = Math.round(double) as a double (functionobjects/Builtin.java:314): ties towards +infinity, exact,
+    NaN -> 0, saturating at +-2^63."""
+    a = np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+    out = np.empty_like(a)
+    lib().orc_unary_round(a.reshape(-1), out.reshape(-1), a.size)
+    return out if out.ndim else float(out)
+
+
+def java_signum(x):
+    """Builtin SIGN = Math.signum (functionobjects/Builtin.java:311): zeros (either sign) and NaN pass through."""
+    a = np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+    out = np.empty_like(a)
+    lib().orc_unary_signum(a.reshape(-1), out.reshape(-1), a.size)
+    return out if out.ndim else float(out)
+
+
 _UNARY_NP = {
-    0: np.exp, 1: np.sqrt, 2: lambda x: np.floor(x + 0.5), 3: np.abs, 4: np.log, 5: np.floor, 6: np.ceil, 7: np.sign,
+    0: np.exp, 1: np.sqrt, 2: java_round, 3: np.abs, 4: np.log, 5: np.floor, 6: np.ceil, 7: java_signum,
     8: lambda x: 1.0 / (1.0 + np.exp(-x)), 9: np.sin, 10: np.cos, 11: np.tan, 12: np.tanh,
 }
 

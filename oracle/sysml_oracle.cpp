@@ -1124,6 +1124,34 @@ double orc_binary_scalar(double x, double y, int op) {
   }
   return NAN;
 }
+// Builtin ROUND is Math.round(double) converted back to double (FO/Builtin.java:314).  java.lang.Math.round, JDK 8 (a
+// dependency outside the reference tree; its specification: "the closest long to the argument, with ties rounding to
+// positive infinity"; NaN -> 0; values beyond the long range saturate).  Restated from the JDK 8 source: with the
+// unbiased shift s = 1074 - biasedExponent, for 0 <= s < 64 the result is ((+-significand >> s) + 1) >> 1, otherwise the
+// Java narrowing cast (long) a.
+double orc_java_round(double a) {
+  uint64_t bits;
+  memcpy(&bits, &a, 8);
+  const int64_t biasedExp = (int64_t)((bits & 0x7ff0000000000000ULL) >> 52);
+  const int64_t shift = (52 - 1 + 1023) - biasedExp;
+  if ((shift & -64) == 0) {
+    int64_t r = (int64_t)((bits & 0x000fffffffffffffULL) | 0x0010000000000000ULL);
+    if ((int64_t)bits < 0) r = -r;
+    return (double)(((r >> shift) + 1) >> 1);
+  }
+  if (a != a) return 0.0;                                   // (long) NaN == 0
+  if (a >= 9223372036854775807.0) return 9223372036854775807.0;   // saturation: Long.MAX_VALUE, as a double 2^63
+  if (a <= -9223372036854775808.0) return -9223372036854775808.0;
+  return (double)(int64_t)a;                                // |a| < 0.5 (-> 0) or an integer of magnitude >= 2^52 ... 2^63
+}
+// Builtin SIGN is Math.signum (FO/Builtin.java:311): zero and NaN are returned as they are (the sign of a zero survives)
+double orc_java_signum(double a) { return (a > 0.0) ? 1.0 : ((a < 0.0) ? -1.0 : a); }
+void orc_unary_round(const double* A, double* C, i64 len) {
+  for (i64 i = 0; i < len; i++) C[i] = orc_java_round(A[i]);
+}
+void orc_unary_signum(const double* A, double* C, i64 len) {
+  for (i64 i = 0; i < len; i++) C[i] = orc_java_signum(A[i]);
+}
 // bcast: 0 = B is rows x cols, 1 = B is a column vector (rows x 1), 2 = B is a row vector (1 x cols)
 void orc_binary_mm(const double* A, const double* B, double* C, i64 rows, i64 cols, int bcast, int op) {
 #pragma omp parallel for schedule(static)

@@ -64,12 +64,20 @@ __device__ __forceinline__ double unop(double x) {
   switch (OP) {
     case SYSML_UN_EXP: return exp(x);
     case SYSML_UN_SQRT: return sqrt(x);
-    case SYSML_UN_ROUND: return floor(__dadd_rn(x, 0.5));  // Java Math.round semantics: floor(x + 0.5)
+    case SYSML_UN_ROUND: {
+      // Builtin ROUND = (double) Math.round(x) (functionobjects/Builtin.java:314): the closest long, ties towards +infinity,
+      // computed exactly (floor(x + 0.5) with a ROUNDED sum is wrong for 0.49999999999999994 and for odd integers
+      // above 2^52); NaN -> 0; beyond the long range the value saturates at +-2^63; a long has no negative zero
+      if (x != x) return 0.0;
+      if (fabs(x) >= 4503599627370496.0) return (x >= 9223372036854775808.0) ? 9223372036854775808.0 : ((x <= -9223372036854775808.0) ? -9223372036854775808.0 : x);
+      const double r = floor(x);  // exact below 2^52, and so is x - r
+      return __dadd_rn((__dsub_rn(x, r) >= 0.5) ? __dadd_rn(r, 1.0) : r, 0.0);
+    }
     case SYSML_UN_ABS: return fabs(x);
     case SYSML_UN_LOG: return log(x);
     case SYSML_UN_FLOOR: return floor(x);
     case SYSML_UN_CEIL: return ceil(x);
-    case SYSML_UN_SIGN: return (x > 0.0) ? 1.0 : ((x < 0.0) ? -1.0 : ((x != x) ? x : 0.0));
+    case SYSML_UN_SIGN: return (x > 0.0) ? 1.0 : ((x < 0.0) ? -1.0 : x);  // Math.signum: zeros of either sign and NaN pass through
     case SYSML_UN_SIGMOID: return 1.0 / (1.0 + exp(-x));
     case SYSML_UN_SIN: return sin(x);
     case SYSML_UN_COS: return cos(x);

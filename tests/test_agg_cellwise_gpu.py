@@ -160,7 +160,14 @@ def test_axpy_and_unary_and_transpose(gctx):
         src, d = (A, dA) if name in ("abs", "floor", "ceil", "sign", "exp", "sin", "cos", "tanh") else (P, dP)
         assert_equal_matrices(fn(src), L.unaryOp(gctx, name, d, name).to_host(), rel=1e-14, what=name)
     assert_equal_matrices(1 / (1 + np.exp(-A)), L.unaryOp(gctx, "sigmoid", dA, "sigmoid").to_host(), rel=1e-14)
-    assert np.array_equal(np.floor(A * 10 + 0.5), L.unaryOp(gctx, "round", gctx.dense(A * 10), "round").to_host())
+    assert np.array_equal(O.java_round(A * 10), L.unaryOp(gctx, "round", gctx.dense(A * 10), "round").to_host())
+    # round = (double) Math.round(x) and sign = Math.signum(x) on the cases where a shortcut goes wrong (known answers in
+    # tests/test_known_answers_cpu.py): halves, 0.49999999999999994, odd integers above 2^52, NaN -> 0, saturation, signed zeros
+    S = np.array([[2.5, -2.5, 0.5, -0.5, 0.49999999999999994, -0.5000000000000001, -0.2, -0.0, 0.0, 4503599627370497.0, -4503599627370497.0,
+                   np.nan, np.inf, -np.inf, 1e300, -1e300, 2.4999999999999996, 3.5, -3.5, 1e15 + 0.5]])
+    for name, ref in (("round", O.java_round), ("sign", O.java_signum)):
+        got, exp = L.unaryOp(gctx, name, gctx.dense(S), name).to_host(), ref(S)
+        assert np.array_equal(got, exp, equal_nan=True) and np.array_equal(np.signbit(got), np.signbit(exp)), (name, got, exp)
 
 
 def test_nnz_and_conversions(gctx):
