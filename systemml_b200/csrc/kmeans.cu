@@ -230,7 +230,8 @@ __global__ void __launch_bounds__(KM_THREADS) kmeans_step_kernel(const KmArgs a)
 //                    stage
 //   warp 16          producer: streams 64-row tiles through a 3-stage ring (bulk copies, full / empty mbarriers)
 // (Tried and dropped: two distance groups on alternate tiles with 16 rows per warp -- 7.3 ms instead of 4.8 ms at C5; one
-// warp per SM sub-partition does not keep the tensor pipe fed across its fragment loads.)
+// warp per SM sub-partition does not keep the tensor pipe fed across its fragment loads.  A head start of warps 0..3
+// over 4..7, to stagger their epilogues, changes nothing: 4.76 ms for 0 ... 6 us.)
 // No shared-memory accumulator, no __syncthreads in the loop; each centroid's sum is built by one warp in a fixed order.
 // FP64 adds share their pipe with the tensor-core instructions, so the accumulation issues nothing it does not need.
 // ------------------------------------------------------------------------------------------------------------------
