@@ -277,6 +277,39 @@ int sysml_b200_matmult_csr_csr_sparse(sysml_b200_ctx* ctx, const int32_t* a_rowp
                                       const double* b_val, int64_t a_rows, int64_t a_cols, int64_t b_rows,
                                       int64_t b_cols, int32_t* c_rowptr, int32_t** c_colind, double** c_val,
                                       int64_t* c_nnz);
+
+/* Sparse-safe cellwise operations whose operand AND result stay CSR: the value function is evaluated at the stored
+ * cells only and results that are zero are dropped -- LibMatrixBincell.safeBinaryScalar's SPARSE <- SPARSE branch
+ * (LibMatrixBincell.java:938-995), safeBinaryMVSparse (:338-440), safeBinaryMMSparseDenseSkip (:760-790),
+ * safeBinaryMMSparseSparse + mergeForSparseBinary (:597-660, 1279-1340; inner join for Multiply, outer join with
+ * op(a,0) / op(0,b) otherwise) and the sparse-safe unary path of MatrixBlock.unaryOperations.  (The reference's GPU
+ * twin has no such path: LibMatrixCUDA converts every sparse operand of a cellwise operator to dense,
+ * LibMatrixCUDA.java:1360-1383 -- at the C3 shape that block would be 4 TB.)
+ * Whether an (operator, operand) pair is sparse-safe is the caller's decision, by the reference's rules
+ * (BinaryOperator.java:60-66, RightScalarOperator.java:42-49, LeftScalarOperator.java:41-46,
+ * LibMatrixBincell.isSparseSafeDivide :185-189); csr_scalar_op / csr_unary_op / csr_csr_op also check that the
+ * operator maps zero to zero and return SYSML_E_UNSUPPORTED otherwise.
+ * Two-call protocol (CSRPointer.allocateForDgeam's, CSRPointer.java:227-299), nothing is allocated by the library:
+ *   1. c_colind == c_val == NULL: symbolic pass, writes c_rowptr[rows+1] and *c_nnz;
+ *   2. the caller allocates c_colind[*c_nnz], c_val[*c_nnz] and calls again with the same operands and the c_rowptr
+ *      of step 1: numeric pass.
+ *   csr_scalar_op : C = A op scalar (scalar_left: scalar op A), op = SYSML_OP_*
+ *   csr_unary_op  : C = f(A), f = SYSML_UN_*
+ *   csr_dense_op  : C = A op B (dense_left: B op A) at A's stored cells; B dense rows x cols, rows x 1 or 1 x cols
+ *                   (bcast = SYSML_BCAST_NONE / _COL / _ROW)
+ *   csr_csr_op    : C = A op B, both CSR rows x cols */
+int sysml_b200_csr_scalar_op(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                             int64_t rows, int64_t cols, double scalar, int op, int scalar_left, int32_t* c_rowptr,
+                             int32_t* c_colind, double* c_val, int64_t* c_nnz);
+int sysml_b200_csr_unary_op(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                            int64_t rows, int64_t cols, int un_op, int32_t* c_rowptr, int32_t* c_colind,
+                            double* c_val, int64_t* c_nnz);
+int sysml_b200_csr_dense_op(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                            int64_t rows, int64_t cols, const double* B, int bcast, int op, int dense_left,
+                            int32_t* c_rowptr, int32_t* c_colind, double* c_val, int64_t* c_nnz);
+int sysml_b200_csr_csr_op(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind, const double* a_val,
+                          const int32_t* b_rowptr, const int32_t* b_colind, const double* b_val, int64_t rows,
+                          int64_t cols, int op, int32_t* c_rowptr, int32_t* c_colind, double* c_val, int64_t* c_nnz);
 /* X %*% t(X) for CSR X (LibMatrixMult.prepMatrixMultTransposeSelfInput :3679-3685 + the RIGHT kernel). */
 int sysml_b200_tsmm_csr_right(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
                               const double* val, double* out, int64_t rows, int64_t cols,

@@ -73,6 +73,11 @@ int sysml_b200_ec_get_matrix_dims(sysml_b200_ec* ec, const char* name, int64_t* 
  * is dirty (GPUObject.java:593-607). */
 int sysml_b200_ec_get_matrix_dense(sysml_b200_ec* ec, const char* name, double* h_out);
 int sysml_b200_ec_get_scalar(sysml_b200_ec* ec, const char* name, double* value);
+/* GPUObject.isSparse (GPUObject.java:416-418): *is_sparse = 1 when the variable's device block is CSR, 0 when it is dense,
+ * -1 when it has no device block.  Cellwise instructions keep a CSR operand CSR where the CPU back-end's rules say the
+ * operator is sparse-safe (LibMatrixBincell.java:116-119, 195-248; MatrixBlock.estimateSparsityOnBinary :2440-2485) and
+ * convert it to dense otherwise, as LibMatrixCUDA does for every cellwise operator (LibMatrixCUDA.java:1360-1383). */
+int sysml_b200_ec_is_sparse_on_device(sysml_b200_ec* ec, const char* name, int* is_sparse);
 
 /* sysml.gpu.eviction.policy (DMLScript.EvictionPolicy, api/DMLScript.java:110,175,679): "lru" (default), "lfu",
  * "min_evict" or "mru".  Decides which unlocked matrices leave the device first when an allocation does not fit

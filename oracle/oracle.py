@@ -40,6 +40,12 @@ def lib():
             build()
         L = C.CDLL(_SO)
         L.orc_num_threads.restype = C.c_int
+        L.orc_csr_scalar_op.restype = i64
+        L.orc_csr_scalar_op.argtypes = [lp, C.c_void_p, C.c_void_p, i64, C.c_double, C.c_int, C.c_int, lp, C.c_void_p, C.c_void_p]
+        L.orc_csr_dense_op.restype = i64
+        L.orc_csr_dense_op.argtypes = [lp, C.c_void_p, C.c_void_p, i64, i64, dp, C.c_int, C.c_int, lp, C.c_void_p, C.c_void_p]
+        L.orc_csr_csr_op.restype = i64
+        L.orc_csr_csr_op.argtypes = [lp, C.c_void_p, C.c_void_p, lp, C.c_void_p, C.c_void_p, i64, C.c_int, lp, C.c_void_p, C.c_void_p]
         L.orc_set_num_threads.argtypes = [C.c_int]
         L.orc_java_test_matrix.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, i64, dp]
         L.orc_java_next_doubles.argtypes = [i64, C.c_int, dp]
@@ -321,6 +327,36 @@ def fused_cellwise(inputs, consts, tokens, rows, cols, agg=0):
 
 def count_nnz(A):
     return lib().orc_count_nnz(np.ascontiguousarray(A).reshape(-1), A.size)
+
+
+def _csr_two_call(fn, rows, *args):
+    crp = np.zeros(rows + 1, dtype=np.int64)
+    nnz = fn(*args, crp, None, None)
+    ci = np.zeros(max(nnz, 1), dtype=np.int32)
+    va = np.zeros(max(nnz, 1), dtype=np.float64)
+    fn(*args, crp, _vp(ci), _vp(va))
+    return crp, ci[:nnz].copy(), va[:nnz].copy()
+
+
+def csr_scalar_op(rp, ci, va, rows, s, op, scalar_left=False):
+    """LibMatrixBincell.safeBinaryScalar SPARSE <- SPARSE (LibMatrixBincell.java:952-995)."""
+    return _csr_two_call(lib().orc_csr_scalar_op, rows, rp, _vp(ci), _vp(va), rows, float(s), op, 1 if scalar_left else 0)
+
+
+def csr_unary_op(rp, ci, va, rows, un_op):
+    """MatrixBlock.sparseUnaryOperations SPARSE <- SPARSE (MatrixBlock.java:2640-2672)."""
+    return _csr_two_call(lib().orc_csr_scalar_op, rows, rp, _vp(ci), _vp(va), rows, 0.0, un_op, 2)
+
+
+def csr_dense_op(rp, ci, va, rows, cols, B, op):
+    """safeBinaryMVSparse (LibMatrixBincell.java:338-440) for a vector B, safeBinaryMMSparseDenseSkip (:765-789) for a matrix."""
+    bc = 0 if B.shape == (rows, cols) else (1 if B.shape == (rows, 1) else 2)
+    return _csr_two_call(lib().orc_csr_dense_op, rows, rp, _vp(ci), _vp(va), rows, cols, np.ascontiguousarray(B), bc, op)
+
+
+def csr_csr_op(a, b, rows, op):
+    """safeBinaryMMSparseSparse / mergeForSparseBinary (LibMatrixBincell.java:597-660, 1279-1340). a, b = (rp, ci, va)."""
+    return _csr_two_call(lib().orc_csr_csr_op, rows, a[0], _vp(a[1]), _vp(a[2]), b[0], _vp(b[1]), _vp(b[2]), rows, op)
 
 
 def dense_to_csr(A):

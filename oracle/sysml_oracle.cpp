@@ -1260,4 +1260,138 @@ i64 orc_rand_csr(i64 rows, i64 cols, double mean, uint64_t seed, i64 row_offset,
   return rp[rows];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Sparse-safe cellwise operations with a sparse result.  Results are appended through SparseRow.append /
+// MatrixBlock.appendValue, both of which drop zeros.  Two-call use: ci == NULL sizes the result (rp is filled).
+// ---------------------------------------------------------------------------------------------
+struct CsrOut {
+  i64* rp;
+  int* ci;
+  double* va;
+  i64 k = 0;
+  void append(int col, double v) {
+    if (v == 0) return;
+    if (ci) {
+      ci[k] = col;
+      va[k] = v;
+    }
+    k++;
+  }
+};
+static double orc_unary_scalar(double x, int op) {
+  switch (op) {
+    case 1: return std::sqrt(x);
+    case 2: return orc_java_round(x);
+    case 3: return std::fabs(x);
+    case 5: return std::floor(x);
+    case 6: return std::ceil(x);
+    case 7: return orc_java_signum(x);
+    case 9: return std::sin(x);
+    case 11: return std::tan(x);
+    case 12: return std::tanh(x);
+  }
+  return NAN;  // exp, log, sigmoid, cos are not sparse-safe
+}
+// LibMatrixBincell.safeBinaryScalar, SPARSE <- SPARSE (LMB:952-995); unary = MatrixBlock.sparseUnaryOperations (MB:2640-2672)
+// mode 0: a op s, 1: s op a, 2: unary
+i64 orc_csr_scalar_op(const i64* rp, const int* ci, const double* va, i64 rows, double s, int op, int mode, i64* crp, int* cci,
+                      double* cva) {
+  CsrOut c{crp, cci, cva};
+  crp[0] = 0;
+  for (i64 r = 0; r < rows; r++) {
+    for (i64 j = rp[r]; j < rp[r + 1]; j++) {
+      const double val = mode == 2 ? orc_unary_scalar(va[j], op) : (mode == 1 ? orc_binary_scalar(s, va[j], op) : orc_binary_scalar(va[j], s, op));
+      c.append(ci[j], val);
+    }
+    crp[r + 1] = c.k;
+  }
+  return c.k;
+}
+// sparse op dense.  bcast 1: safeBinaryMVSparse MATRIX_COL_VECTOR (LMB:359-405), bcast 2: MATRIX_ROW_VECTOR (LMB:406-440),
+// bcast 0: safeBinaryMMSparseDenseSkip (LMB:765-789; Multiply / sparse-safe Divide).  The vector branches evaluate the
+// operator at the cells a row does NOT store as well ("empty left"), except where Multiply lets them skip.
+i64 orc_csr_dense_op(const i64* rp, const int* ci, const double* va, i64 rows, i64 cols, const double* B, int bcast, int op, i64* crp,
+                     int* cci, double* cva) {
+  const bool isMultiply = (op == 2), skipEmpty = isMultiply;
+  CsrOut c{crp, cci, cva};
+  crp[0] = 0;
+  for (i64 i = 0; i < rows; i++) {
+    const bool empty = rp[i] == rp[i + 1];
+    if (bcast == 0) {
+      for (i64 k = rp[i]; k < rp[i + 1]; k++) {
+        const double in2 = B[i * cols + ci[k]];
+        if (in2 == 0) continue;
+        c.append(ci[k], orc_binary_scalar(va[k], in2, op));
+      }
+    } else if (bcast == 1) {
+      const double v2 = B[i];
+      if (!((skipEmpty && (empty || v2 == 0)) || (empty && v2 == 0))) {
+        if (isMultiply && v2 == 1) {  // ROW COPY
+          for (i64 k = rp[i]; k < rp[i + 1]; k++) c.append(ci[k], va[k]);
+        } else {
+          // "empty left": every cell the row does not store gets op(0, v2) -- one value per row, so it is computed once and
+          // the gap loops are skipped when it is zero (appendValue would drop each of them)
+          const double gv = orc_binary_scalar(0, v2, op);
+          i64 lastIx = -1;
+          for (i64 j = rp[i]; j < rp[i + 1]; j++) {
+            for (i64 k = lastIx + 1; gv != 0 && k < ci[j]; k++) c.append((int)k, gv);
+            c.append(ci[j], orc_binary_scalar(va[j], v2, op));
+            lastIx = ci[j];
+          }
+          for (i64 k = lastIx + 1; gv != 0 && k < cols; k++) c.append((int)k, gv);
+        }
+      }
+    } else {
+      if (!(skipEmpty && empty)) {
+        i64 lastIx = -1;
+        for (i64 j = rp[i]; j < rp[i + 1]; j++) {
+          for (i64 k = lastIx + 1; !skipEmpty && k < ci[j]; k++) c.append((int)k, orc_binary_scalar(0, B[k], op));
+          c.append(ci[j], orc_binary_scalar(va[j], B[ci[j]], op));
+          lastIx = ci[j];
+        }
+        for (i64 k = lastIx + 1; !skipEmpty && k < cols; k++) c.append((int)k, orc_binary_scalar(0, B[k], op));
+      }
+    }
+    crp[i + 1] = c.k;
+  }
+  return c.k;
+}
+// sparse op sparse: safeBinaryMMSparseSparse (LMB:597-660) -> mergeForSparseBinary (LMB:1279-1322): inner join under
+// Multiply, otherwise outer join, then appendLeft / appendRight for the remainders (LMB:1324-1340)
+i64 orc_csr_csr_op(const i64* arp, const int* aci, const double* ava, const i64* brp, const int* bci, const double* bva, i64 rows, int op,
+                   i64* crp, int* cci, double* cva) {
+  CsrOut c{crp, cci, cva};
+  crp[0] = 0;
+  for (i64 r = 0; r < rows; r++) {
+    i64 p1 = arp[r], p2 = brp[r];
+    const i64 e1 = arp[r + 1], e2 = brp[r + 1];
+    if (p1 < e1 && p2 < e2 && op == 2) {
+      while (p1 < e1 && p2 < e2) {
+        const int c1 = aci[p1], c2 = bci[p2];
+        if (c1 == c2) c.append(c1, orc_binary_scalar(ava[p1], bva[p2], op));
+        p1 += (c1 <= c2) ? 1 : 0;
+        p2 += (c1 >= c2) ? 1 : 0;
+      }
+    } else {
+      while (p1 < e1 && p2 < e2) {
+        if (aci[p1] < bci[p2]) {
+          c.append(aci[p1], orc_binary_scalar(ava[p1], 0, op));
+          p1++;
+        } else if (aci[p1] == bci[p2]) {
+          c.append(aci[p1], orc_binary_scalar(ava[p1], bva[p2], op));
+          p1++;
+          p2++;
+        } else {
+          c.append(bci[p2], orc_binary_scalar(0, bva[p2], op));
+          p2++;
+        }
+      }
+      for (; p1 < e1; p1++) c.append(aci[p1], orc_binary_scalar(ava[p1], 0, op));
+      for (; p2 < e2; p2++) c.append(bci[p2], orc_binary_scalar(0, bva[p2], op));
+    }
+    crp[r + 1] = c.k;
+  }
+  return c.k;
+}
+
 }  // extern "C"

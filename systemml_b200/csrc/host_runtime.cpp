@@ -306,6 +306,28 @@ struct GPUObject {
     dirty = true;
     writeLock = true;
   }
+  // GPUObject.acquireDeviceModifySparse (GPUObject.java:567-585).  The row pointer comes from the operator's symbolic pass
+  // (as CSRPointer.allocateForDgeam / allocateForMatrixMultiply build it, CSRPointer.java:227-399) and is adopted; the two
+  // nnz-sized arrays are taken from the memory manager here.
+  void acquireDeviceModifySparse(const char* opcode, int32_t* adopted_rowptr, i64 nnz) {
+    if (isAllocated()) fail(SYSML_E_INVALID, "GPU : sparse output %s is already allocated", mat->name.c_str());
+    uploading = true;
+    struct Reset { bool& f; ~Reset() { f = false; } } rs{uploading};
+    int32_t* ci = (int32_t*)mm->malloc(opcode, std::max<i64>(nnz, 1) * 4);
+    double* va = nullptr;
+    try {
+      va = (double*)mm->malloc(opcode, std::max<i64>(nnz, 1) * 8);
+    } catch (...) {
+      mm->free(ci, true);
+      throw;
+    }
+    rowptr = adopted_rowptr;
+    colind = ci;
+    val = va;
+    csr_nnz = nnz;
+    dirty = true;
+    writeLock = true;
+  }
   void releaseInput() {  // GPUObject.java:609-624
     if (readLocks <= 0) fail(SYSML_E_INVALID, "GPU : releaseInput of %s without a read lock", mat->name.c_str());
     readLocks--;
@@ -646,6 +668,23 @@ struct sysml_b200_ec {
     gpuObject(p)->acquireDeviceModifyDense(opcode);
     return p;
   }
+  // ExecutionContext.getSparseMatrixOutputForGPUInstruction (:321-326): as above with a CSR device block of nnz cells
+  MatrixObject* getSparseMatrixOutputForGPUInstruction(const std::string& name, i64 rows, i64 cols, int32_t* rowptr, i64 nnz,
+                                                       const char* opcode) {
+    auto it = matrices.find(name);
+    if (it != matrices.end() && it->second->gpu && it->second->gpu->isLocked())
+      fail(SYSML_E_INVALID, "GPU : output variable %s is an input of the same instruction", name.c_str());
+    removeMatrix(name);
+    std::unique_ptr<MatrixObject> mo(new MatrixObject());
+    mo->name = name;
+    mo->rows = rows;
+    mo->cols = cols;
+    mo->nnz = nnz;
+    MatrixObject* p = mo.get();
+    matrices[name] = std::move(mo);
+    gpuObject(p)->acquireDeviceModifySparse(opcode, rowptr, nnz);
+    return p;
+  }
   void releaseMatrixInputForGPUInstruction(const std::string& name) { getMatrixObject(name)->gpu->releaseInput(); }
   void releaseMatrixOutputForGPUInstruction(const std::string& name) {
     MatrixObject* mo = getMatrixObject(name);
@@ -700,6 +739,30 @@ int unaryOpcode(const std::string& o) {
   if (it == m.end()) fail(SYSML_E_UNSUPPORTED, "Unsupported unary builtin: %s", o.c_str());
   return it->second;
 }
+// Which cellwise operators keep a sparse operand sparse (the CPU back-end's rules; the reference's GPU operators have no
+// sparse form and densify, LibMatrixCUDA.java:1360-1383):
+//  - scalar: ScalarOperator's constructor (ScalarOperator.java:53-59, isSparseSafeStatic :84-89) with the alternatives of
+//    RightScalarOperator (:42-49) and LeftScalarOperator (:41-46).  One deliberate difference: Power with a NEGATIVE constant
+//    is sparse-safe there ("Power && cst != 0") although 0^c is infinite; it takes the dense form here.
+//  - matrix-matrix: BinaryOperator.sparseSafe (BinaryOperator.java:60-66), Divide by an operand without zeros
+//    (LibMatrixBincell.isSparseSafeDivide :185-189)
+//  - unary: UnaryOperator's constructor (UnaryOperator.java:38-47)
+bool scalarSparseSafe(const std::string& o, double c, bool scalarLeft) {
+  if (o == "*" || o == "*2" || o == "^2" || o == "&&" || o == "-nz") return true;
+  if ((o == "!=" && c == 0) || (o == "==" && c != 0) || (o == "-" && c == 0) || (o == "max" && c <= 0) || (o == "min" && c >= 0)) return true;
+  if (!scalarLeft) return (o == ">" && c >= 0) || (o == ">=" && c > 0) || (o == "<" && c <= 0) || (o == "<=" && c < 0) || (o == "/" && c != 0) || (o == "^" && c > 0);
+  return (o == ">" && c <= 0) || (o == ">=" && c < 0) || (o == "<" && c >= 0) || (o == "<=" && c > 0);
+}
+bool binarySparseSafe(const std::string& o) { return o == "+" || o == "-" || o == "*" || o == "&&" || o == "||"; }
+bool unarySparseSafe(const std::string& o) { return o == "sin" || o == "tan" || o == "tanh" || o == "round" || o == "abs" || o == "sqrt" || o == "sign"; }
+// OptimizerUtils.getBinaryOpSparsity, worst case (OptimizerUtils.java:1079-1103)
+double binaryOpSparsity(const std::string& o, double sp1, double sp2) {
+  if (o == "+" || o == "-" || o == "||" || o == "<" || o == ">" || o == "!=" || o == "min" || o == "max") return std::min(1.0, sp1 + sp2);
+  if (o == "*" || o == "&&") return std::min(sp1, sp2);
+  if (o == "/") return std::min(1.0, sp1 + (1.0 - sp2));
+  if (o == "%%" || o == "^" || o == "-nz") return sp1;
+  return 1.0;
+}
 // InstructionUtils.parseBasicAggregateUnaryOperator: opcode -> (aggregate, direction)
 void aggOpcode(const std::string& o, int* op, int* dir) {
   std::string s = o;
@@ -738,6 +801,11 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
       outs.push_back(name);
       return mo;
     }
+    MatrixObject* outSparse(const std::string& name, i64 rows, i64 cols, int32_t* rowptr, i64 nnz, const char* opcode) {
+      MatrixObject* mo = ec->getSparseMatrixOutputForGPUInstruction(name, rows, cols, rowptr, nnz, opcode);
+      outs.push_back(name);
+      return mo;
+    }
     void releaseAll() {
       for (auto& n : ins) {
         try { ec->releaseMatrixInputForGPUInstruction(n); } catch (...) {}
@@ -772,6 +840,41 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
   // (LibMatrixCUDA.java:655-664, 1382-1383 -> GPUObject.sparseToDense)
   auto densify = [&](MatrixObject* mo) {
     if (mo->gpu->isSparse()) mo->gpu->sparseToDense(opc);
+  };
+  // A cellwise operator in its sparse form: the symbolic pass sizes the result into a row pointer taken from the memory
+  // manager, the output variable adopts it and allocates the nnz-sized arrays, the numeric pass fills them
+  // (sysml_b200.h, "two-call protocol").  Returns false -- with nothing changed -- when the library finds the operator not
+  // sparse-safe for these operands (SYSML_E_UNSUPPORTED): the caller then takes the dense form.
+  auto sparseCellwise = [&](const std::string& outName, i64 rows, i64 cols, auto call) -> bool {
+    int32_t* rp = (int32_t*)mm.malloc(opc, (rows + 1) * 4);
+    i64 nnz = 0;
+    int rc = call(rp, (int32_t*)nullptr, (double*)nullptr, &nnz);
+    if (rc) {
+      mm.free(rp, true);
+      if (rc == SYSML_E_UNSUPPORTED) return false;
+      check(rc);
+    }
+    MatrixObject* out = nullptr;
+    try {
+      out = L.outSparse(outName, rows, cols, rp, nnz, opc);
+    } catch (...) {
+      mm.free(rp, true);
+      throw;
+    }
+    check(call(out->gpu->rowptr, out->gpu->colind, out->gpu->val, &nnz));
+    return true;
+  };
+  // exact sparsity of an operand (MatrixBlock.getSparsity); a dense device block whose nnz is not known is counted
+  auto sparsityOf = [&](MatrixObject* mo) -> double {
+    const double cells = (double)mo->rows * (double)mo->cols;
+    if (cells == 0) return 0.0;
+    if (mo->gpu->isSparse()) return (double)mo->gpu->csr_nnz / cells;
+    if (mo->nnz < 0) {
+      int64_t c = 0;
+      check(sysml_b200_count_nnz(ctx, mo->gpu->dense, mo->rows * mo->cols, &c));
+      mo->nnz = c;
+    }
+    return (double)mo->nnz / cells;
   };
   switch (pi.type) {
     case AggregateBinary: {  // AggregateBinaryGPUInstruction.processInstruction (:73-89) -> LibMatrixCuMatMult.matmult (:139-229)
@@ -905,8 +1008,16 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
     case BuiltinUnary:
     case Reorg: {
       MatrixObject* in1 = L.in(pi.ops[0].name, opc);
-      densify(in1);
       const bool tr = pi.type == Reorg;
+      if (!tr && in1->gpu->isSparse() && unarySparseSafe(pi.opcode)) {  // MatrixBlock.unaryOperations: sp = sparse && op.sparseSafe (:2594)
+        GPUObject* g = in1->gpu.get();
+        const int code = unaryOpcode(pi.opcode);
+        if (sparseCellwise(pi.ops[1].name, in1->rows, in1->cols, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+              return sysml_b200_csr_unary_op(ctx, g->rowptr, g->colind, g->val, in1->rows, in1->cols, code, rp, ci, va, (int64_t*)nnz);
+            }))
+          break;
+      }
+      densify(in1);
       MatrixObject* out = L.out(pi.ops[1].name, tr ? in1->cols : in1->rows, tr ? in1->rows : in1->cols, opc);
       int rc = tr ? sysml_b200_transpose(ctx, in1->gpu->dense, out->gpu->dense, in1->rows, in1->cols)
                   : sysml_b200_unary(ctx, in1->gpu->dense, out->gpu->dense, in1->rows * in1->cols, unaryOpcode(pi.opcode));
@@ -948,6 +1059,37 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
           ocols = in2->cols;
         }
         if (bcast < 0) fail(SYSML_E_DIM, "GPU : incompatible dimensions %lldx%lld vs %lldx%lld for %s", in1->rows, in1->cols, in2->rows, in2->cols, opc);
+        // Sparse form (MatrixBlock.binaryOperations -> estimateSparsityOnBinary, MatrixBlock.java:2440-2485, 2741-2766): taken
+        // when the operator is sparse-safe (or Divide by an operand without zeros) and the estimated result is sparse in memory
+        const bool sp1 = in1->gpu->isSparse(), sp2 = in2->gpu->isSparse();
+        if ((sp1 || sp2) && bcast != SYSML_BCAST_OUTER) {
+          const std::string& o = pi.opcode;
+          const int code = binaryOpcode(o);
+          bool safe = binarySparseSafe(o);
+          double s1 = sparsityOf(in1), s2 = sparsityOf(in2);
+          if (!safe && o == "/" && sp1 && s2 == 1.0) safe = true;
+          // a vector operand counts once per row / column it is broadcast over (nz2 * n or nz2 * m, :2468-2471): its own sparsity
+          const i64 estnnz = (i64)std::llround(binaryOpSparsity(o, s1, s2) * (double)orows * (double)ocols);
+          if (safe && evalSparseFormatInMemory(orows, ocols, estnnz)) {
+            GPUObject *g1 = in1->gpu.get(), *g2 = in2->gpu.get();
+            bool done = false;
+            if (sp1 && sp2 && bcast == SYSML_BCAST_NONE) {
+              done = sparseCellwise(o3.name, orows, ocols, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+                return sysml_b200_csr_csr_op(ctx, g1->rowptr, g1->colind, g1->val, g2->rowptr, g2->colind, g2->val, orows, ocols, code, rp, ci, va,
+                                             (int64_t*)nnz);
+              });
+            } else if (sp1 && !sp2) {
+              done = sparseCellwise(o3.name, orows, ocols, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+                return sysml_b200_csr_dense_op(ctx, g1->rowptr, g1->colind, g1->val, orows, ocols, g2->dense, bcast, code, 0, rp, ci, va, (int64_t*)nnz);
+              });
+            } else if (!sp1 && sp2 && bcast == SYSML_BCAST_NONE && (o == "*" || o == "&&")) {
+              done = sparseCellwise(o3.name, orows, ocols, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+                return sysml_b200_csr_dense_op(ctx, g2->rowptr, g2->colind, g2->val, orows, ocols, g1->dense, bcast, code, 1, rp, ci, va, (int64_t*)nnz);
+              });
+            }
+            if (done) break;
+          }
+        }
         densify(in1);
         densify(in2);
         MatrixObject* out = L.out(o3.name, orows, ocols, opc);
@@ -959,12 +1101,21 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
         const CPOperand& mo = scalarLeft ? o2 : o1;
         const double scalar = getScalarInput(scalarLeft ? o1 : o2);
         MatrixObject* in = L.in(mo.name, opc);
-        densify(in);
-        MatrixObject* out = L.out(o3.name, in->rows, in->cols, opc);
         double s = scalar;
         int code = binaryOpcode(pi.opcode);
         if (pi.opcode == "*2") s = 2.0;      // Multiply2 / Power2 (LibMatrixCUDA.java:1563-1564)
         if (pi.opcode == "^2") s = 2.0;
+        // MatrixBlock.scalarOperations: the result is sparse iff the input is and the operator is sparse-safe for this constant
+        if (in->gpu->isSparse() && scalarSparseSafe(pi.opcode, s, scalarLeft)) {
+          GPUObject* g = in->gpu.get();
+          if (sparseCellwise(o3.name, in->rows, in->cols, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+                return sysml_b200_csr_scalar_op(ctx, g->rowptr, g->colind, g->val, in->rows, in->cols, s, code, scalarLeft ? 1 : 0, rp, ci, va,
+                                                (int64_t*)nnz);
+              }))
+            break;
+        }
+        densify(in);
+        MatrixObject* out = L.out(o3.name, in->rows, in->cols, opc);
         int rc = sysml_b200_binary_ms(ctx, in->gpu->dense, s, out->gpu->dense, in->rows * in->cols, code, scalarLeft ? 1 : 0);
         check(rc);
       } else {
@@ -1161,6 +1312,14 @@ int sysml_b200_ec_get_matrix_dense(sysml_b200_ec* ec, const char* name, double* 
     } else {
       std::copy(mo->h_dense.begin(), mo->h_dense.end(), h_out);
     }
+  })
+}
+
+int sysml_b200_ec_is_sparse_on_device(sysml_b200_ec* ec, const char* name, int* is_sparse) {
+  if (!ec || !name || !is_sparse) return SYSML_E_INVALID;
+  EC_TRY(ec, {
+    MatrixObject* mo = ec->getMatrixObject(name);
+    *is_sparse = (mo->gpu && mo->gpu->isAllocated()) ? (mo->gpu->isSparse() ? 1 : 0) : -1;
   })
 }
 

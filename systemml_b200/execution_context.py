@@ -112,6 +112,12 @@ class ExecutionContext:
         self._check(self._lib.sysml_b200_ec_exam_sparsity(self.handle, name.encode(), C.byref(f)))
         return bool(f.value)
 
+    def isSparseOnDevice(self, name):
+        """GPUObject.isSparse: True / False for a CSR / dense device block, None when the variable has none."""
+        f = C.c_int()
+        self._check(self._lib.sysml_b200_ec_is_sparse_on_device(self.handle, name.encode(), C.byref(f)))
+        return None if f.value < 0 else bool(f.value)
+
     def stats(self):
         out = (C.c_int64 * 9)()
         self._check(self._lib.sysml_b200_ec_stats(self.handle, out))

@@ -378,6 +378,61 @@ def sparseSparseMatmult(gCtx, instName, in1, in2):
     return _adopt_csr(gCtx, in1.rows, in2.cols, rp, pci, pva, nnz)
 
 
+def _two_pass_csr(gCtx, rows, cols, fn, *operands):
+    """The symbolic / numeric call pair of the CSR-result cellwise entry points (CSRPointer.allocateForDgeam's protocol,
+    CSRPointer.java:227-299): sizes from the first call, arrays from this context's allocator, values from the second."""
+    from .gpu_context import CSRPointer
+    rp = gCtx.allocate((rows + 1) * 4)
+    nnz = C.c_int64()
+    try:
+        gCtx.call(fn, *operands, _p(rp), None, None, C.byref(nnz))
+    except Exception:
+        gCtx.cudaFreeHelper(rp)
+        raise
+    out = GPUObject(gCtx, rows, cols)
+    out.csr = CSRPointer.adopt(gCtx, rows, rp, gCtx.allocate(max(nnz.value, 1) * 4), gCtx.allocate(max(nnz.value, 1) * 8), nnz.value)
+    gCtx.call(fn, *operands, _p(rp), _p(out.csr.colInd), _p(out.csr.val), C.byref(nnz))
+    return out
+
+
+def sparseScalarOp(gCtx, instName, in1, scalar, op, scalar_left=False):
+    """CSR op scalar with a CSR result, for (operator, constant) pairs that map 0 to 0 (LibMatrixBincell.safeBinaryScalar,
+    LibMatrixBincell.java:938-995); anything else raises (the dense form is the caller's fallback, as in the reference)."""
+    return _two_pass_csr(gCtx, in1.rows, in1.cols, "sysml_b200_csr_scalar_op", _p(in1.csr.rowPtr), _p(in1.csr.colInd),
+                         _p(in1.csr.val), in1.rows, in1.cols, float(scalar), int(op), 1 if scalar_left else 0)
+
+
+def sparseUnaryOp(gCtx, instName, in1, un_op):
+    """f(CSR) with a CSR result for f(0) == 0 (sqrt, abs, round, floor, ceil, sign, sin, tan, tanh)."""
+    return _two_pass_csr(gCtx, in1.rows, in1.cols, "sysml_b200_csr_unary_op", _p(in1.csr.rowPtr), _p(in1.csr.colInd),
+                         _p(in1.csr.val), in1.rows, in1.cols, int(un_op))
+
+
+def sparseDenseOp(gCtx, instName, in1, in2, op, dense_left=False):
+    """CSR op dense (matrix, column vector or row vector) evaluated at the CSR operand's stored cells, CSR result
+    (LibMatrixBincell.safeBinaryMVSparse :338-440, safeBinaryMMSparseDenseSkip :760-790). The caller vouches that the operator
+    is sparse-safe for this dense operand (Multiply, And; Divide by an operand without zeros, isSparseSafeDivide :185-189)."""
+    if (in2.rows, in2.cols) == (in1.rows, in1.cols):
+        bcast = BCAST_NONE
+    elif in2.cols == 1 and in2.rows == in1.rows:
+        bcast = BCAST_COL
+    elif in2.rows == 1 and in2.cols == in1.cols:
+        bcast = BCAST_ROW
+    else:
+        _dim_error("sparse op dense: %dx%d vs %dx%d" % (in1.rows, in1.cols, in2.rows, in2.cols))
+    return _two_pass_csr(gCtx, in1.rows, in1.cols, "sysml_b200_csr_dense_op", _p(in1.csr.rowPtr), _p(in1.csr.colInd),
+                         _p(in1.csr.val), in1.rows, in1.cols, _p(in2.ptr), bcast, int(op), 1 if dense_left else 0)
+
+
+def sparseSparseOp(gCtx, instName, in1, in2, op):
+    """CSR op CSR with a CSR result for operators with 0 op 0 == 0: inner join for Multiply, outer join otherwise
+    (LibMatrixBincell.safeBinaryMMSparseSparse / mergeForSparseBinary, LibMatrixBincell.java:597-660, 1279-1340)."""
+    if (in1.rows, in1.cols) != (in2.rows, in2.cols):
+        _dim_error("sparse op sparse: %dx%d vs %dx%d" % (in1.rows, in1.cols, in2.rows, in2.cols))
+    return _two_pass_csr(gCtx, in1.rows, in1.cols, "sysml_b200_csr_csr_op", _p(in1.csr.rowPtr), _p(in1.csr.colInd), _p(in1.csr.val),
+                         _p(in2.csr.rowPtr), _p(in2.csr.colInd), _p(in2.csr.val), in1.rows, in1.cols, int(op))
+
+
 def denseToSparse(gCtx, in1):
     """GPUObject.denseToSparse (GPUObject.java:199-245): two-phase nnz count + fill."""
     from .gpu_context import CSRPointer

@@ -63,6 +63,10 @@ SIGNATURES = {
     "sysml_b200_csr_transpose": (ci, [vp, vp, vp, vp, i64, i64, vp, vp, vp]),
     "sysml_b200_csr_add": (ci, [vp, vp, vp, vp, dbl, vp, vp, vp, dbl, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_matmult_csr_csr_sparse": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp, vp, vp, pi64]),
+    "sysml_b200_csr_scalar_op": (ci, [vp, vp, vp, vp, i64, i64, dbl, ci, ci, vp, vp, vp, pi64]),
+    "sysml_b200_csr_unary_op": (ci, [vp, vp, vp, vp, i64, i64, ci, vp, vp, vp, pi64]),
+    "sysml_b200_csr_dense_op": (ci, [vp, vp, vp, vp, i64, i64, vp, ci, ci, ci, vp, vp, vp, pi64]),
+    "sysml_b200_csr_csr_op": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, vp, pi64]),
     "sysml_b200_fused_cellwise": (ci, [vp, vp, vp, ci, vp, ci, vp, ci, i64, i64, ci, vp]),
     "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),
     "sysml_b200_count_nnz": (ci, [vp, vp, i64, pi64]),
@@ -106,6 +110,7 @@ SIGNATURES = {
     "sysml_b200_ec_set_eviction_policy": (ci, [vp, C.c_char_p]),
     "sysml_b200_eval_sparse_format_in_memory": (ci, [i64, i64, i64]),
     "sysml_b200_ec_exam_sparsity": (ci, [vp, C.c_char_p, pint]),
+    "sysml_b200_ec_is_sparse_on_device": (ci, [vp, C.c_char_p, pint]),
 }
 
 

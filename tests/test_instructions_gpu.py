@@ -389,3 +389,81 @@ def test_caller_owned_workspace_through_the_abi(gctx):
             g.cudaFreeHelper(p)
         for o in (X, v, out, ref):
             o.free()
+
+
+def test_sparse_operands_stay_sparse_under_sparse_safe_cellwise_instructions(ec):
+    """Cellwise instructions on a CSR operand: where the CPU back-end's rules call the operator sparse-safe (ScalarOperator /
+    BinaryOperator / UnaryOperator constructors, isSparseSafeDivide, estimateSparsityOnBinary) the device block stays CSR --
+    result cells, nnz and the format are checked -- and everywhere else the operand is converted to dense as
+    LibMatrixCUDA does, with the same cells as the dense operator."""
+    rows, cols = 4000, 300
+    A = O.java_test_matrix(rows, cols, -2, 2, 0.02, 61)
+    B = O.java_test_matrix(rows, cols, -2, 2, 0.03, 62)
+    cv = O.java_test_matrix(rows, 1, -1, 1, 0.6, 63)
+    rv = O.java_test_matrix(1, cols, 0.5, 1.5, 1.0, 64)
+    D = O.java_test_matrix(rows, cols, 0.5, 2, 1.0, 65)
+
+    def put():
+        for n, M in (("A", A), ("B", B)):
+            rp, ci, va = O.dense_to_csr(M)
+            ec.setMatrixCSR(n, rp, ci, va, M.shape)
+        ec.setMatrix("cv", cv)
+        ec.setMatrix("rv", rv)
+        ec.setMatrix("D", D)
+
+    put()
+    sparse_cases = [
+        (inst("*", mat("A"), literal(0.5), mat("Z")), O.binary_ms(A, 0.5, 2)),
+        (inst("*", literal(-3), mat("A"), mat("Z")), O.binary_ms(A, -3.0, 2, True)),
+        (inst("/", mat("A"), literal(4), mat("Z")), O.binary_ms(A, 4.0, 3)),
+        (inst("^2", mat("A"), literal(2), mat("Z")), O.binary_ms(A, 2.0, 4)),
+        (inst(">", mat("A"), literal(0), mat("Z")), O.binary_ms(A, 0.0, 7)),
+        (inst("!=", mat("A"), literal(0), mat("Z")), O.binary_ms(A, 0.0, 10)),
+        (inst("abs", mat("A"), mat("Z")), np.abs(A)),
+        (inst("sign", mat("A"), mat("Z")), O.java_signum(A)),
+        (inst("round", mat("A"), mat("Z")), O.java_round(A)),
+        (inst("*", mat("A"), mat("B"), mat("Z")), O.binary_mm(A, B, 2)),
+        (inst("+", mat("A"), mat("B"), mat("Z")), O.binary_mm(A, B, 0)),
+        (inst("-", mat("A"), mat("B"), mat("Z")), O.binary_mm(A, B, 1)),
+        (inst("*", mat("A"), mat("cv"), mat("Z")), O.binary_mm(A, cv, 2)),
+        (inst("*", mat("A"), mat("rv"), mat("Z")), O.binary_mm(A, rv, 2)),
+        (inst("/", mat("A"), mat("rv"), mat("Z")), O.binary_mm(A, rv, 3)),
+        (inst("*", mat("A"), mat("D"), mat("Z")), O.binary_mm(A, D, 2)),
+        (inst("*", mat("D"), mat("A"), mat("Z")), O.binary_mm(D, A, 2)),
+        (inst("/", mat("A"), mat("D"), mat("Z")), O.binary_mm(A, D, 3)),
+    ]
+    for instruction, exp in sparse_cases:
+        ec.execute(instruction)
+        assert ec.isSparseOnDevice("Z") is True, instruction
+        assert ec.isSparseOnDevice("A") is True, instruction
+        assert ec.getMatrixDims("Z") == (rows, cols, int(np.count_nonzero(exp))), instruction
+        got = ec.getMatrix("Z")
+        if instruction.split("°")[1] in ("^2",):
+            assert_equal_matrices(exp + 0.0, got, rel=1e-13)
+        else:
+            assert np.array_equal(got, exp + 0.0), instruction
+    dense_cases = [
+        (inst("+", mat("A"), literal(1), mat("Z")), O.binary_ms(A, 1.0, 0)),          # 0 + 1
+        (inst("^", mat("A"), literal(-1), mat("Z")), None),                           # 0 ^ -1 = Inf: dense here (see host_runtime.cpp)
+        (inst("<", mat("A"), literal(0.5), mat("Z")), O.binary_ms(A, 0.5, 5)),
+        (inst("exp", mat("A"), mat("Z")), None),
+        (inst("+", mat("A"), mat("cv"), mat("Z")), O.binary_mm(A, cv, 0)),
+        (inst("/", mat("A"), mat("cv"), mat("Z")), O.binary_mm(A, cv, 3)),            # cv holds zeros: 0/0
+        (inst("==", mat("A"), mat("B"), mat("Z")), O.binary_mm(A, B, 9)),
+        (inst("+", mat("A"), mat("D"), mat("Z")), O.binary_mm(A, D, 0)),              # the estimate says dense
+    ]
+    for instruction, exp in dense_cases:
+        put()
+        ec.execute(instruction)
+        assert ec.isSparseOnDevice("Z") is False, instruction
+        if exp is not None:
+            assert np.array_equal(ec.getMatrix("Z"), exp, equal_nan=True), instruction
+    # a sparse result feeds the next instruction like any other variable (CSR x dense matmult, aggregate)
+    put()
+    v = O.java_test_matrix(cols, 1, -1, 1, 1.0, 66)
+    ec.setMatrix("v", v)
+    ec.execute(inst("*", mat("A"), mat("cv"), mat("Z")))
+    ec.execute(inst("ba+*", mat("Z"), mat("v"), mat("q"), "false", "false"))
+    assert_equal_matrices(O.matmult_dense(A * cv, v, 4)[0], ec.getMatrix("q"))
+    ec.execute(inst("uak+", mat("Z"), scalar_var("s")))
+    assert abs(ec.getScalar("s") - O.agg_unary_dense(A * cv, O.SUM, O.ALL)[0]) < 1e-9

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta | spmv rows cols per [mode] | pcsc rows cols per | agg n m op dir"""
+"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta | spmv rows cols per [mode] | pcsc rows cols per | csrcell rows cols per kind | agg n m op dir"""
 import ctypes as C
 import os
 import sys
@@ -50,6 +50,29 @@ elif op == "pcsc":
     pc = PCSCPointer(g, S.csr, rows, cols)
     y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
     fn = lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), rows, cols, pc.panel_rows, p_(y), None, 0, p_(oc))
+elif op == "csrcell":  # sparse-safe cellwise with a CSR result: kind 0 X*y (column vector), 1 X*0.5, 2 X*X
+    rows, cols, per, kind = a[:4]
+    S = g.rand_csr(rows, cols, per, seed=2)
+    y = g.rand(rows, 1, seed=3)
+    csr3 = (C.c_void_p(S.csr.rowPtr), C.c_void_p(S.csr.colInd), C.c_void_p(S.csr.val))
+    rp, ci, va = g.allocate((rows + 1) * 4), g.allocate(S.csr.nnz * 4), g.allocate(S.csr.nnz * 8)
+    nnz = C.c_int64()
+    outs = lambda fill: (C.c_void_p(rp), C.c_void_p(ci) if fill else None, C.c_void_p(va) if fill else None, C.byref(nnz))
+
+    def fn():
+        for fill in (False, True):
+            g.timer_start()
+            if kind == 0:
+                g.call("sysml_b200_csr_dense_op", *csr3, rows, cols, p_(y), 1, 2, 0, *outs(fill))
+            elif kind == 1:
+                g.call("sysml_b200_csr_scalar_op", *csr3, rows, cols, 0.5, 2, 0, *outs(fill))
+            else:
+                g.call("sysml_b200_csr_csr_op", *csr3, *csr3, rows, cols, 2, *outs(fill))
+            ms = g.timer_stop_ms()
+            # symbolic: reads 12 B per cell + 4 B per row (+ 8 B per row for y); numeric: the same reads + 12 B per cell written
+            rd = S.csr.nnz * 12 * (2 if kind == 2 else 1) + rows * 4 * (2 if kind == 2 else 1) + (rows * 8 if kind == 0 else 0)
+            by = rd + (nnz.value * 12 + rows * 4 if fill else rows * 4)
+            print("csrcell kind", kind, "numeric" if fill else "symbolic", "ms", round(ms, 4), "GB/s", round(by / ms / 1e6, 1), "nnz", S.csr.nnz, "->", nnz.value)
 elif op == "kmeans":
     n, m, k = a
     X, Cm = g.rand(n, m, seed=1, lo=-10.0, hi=10.0), g.rand(k, m, seed=2, lo=-10.0, hi=10.0)
