@@ -386,6 +386,16 @@ int sysml_b200_cg_vector_update(sysml_b200_ctx* ctx, double* p, double* q, doubl
 int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
                               const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
                               int64_t cols, int agg, double* out);
+/* Several full sums over the same operands in ONE pass: the code generator's multi-aggregate template
+ * (runtime/codegen/SpoofMultiAggregate.java, hops/codegen/template/TemplateMultiAgg.java), which is what the compiler emits
+ * for e.g. l2-svm.dml's line search, sum(out*sv*Y*Xd) and sum(Xd*sv*Xd) over the same three n-vectors.
+ * The postfix program leaves n_out values on the stack (result 0 deepest); out[j] = sum over all cells of value j, with
+ * the compensated accumulation and the fixed merge order of fused_cellwise's SUM ending (bit-identical to n_out separate
+ * calls). 1 <= n_out <= SYSML_FUSED_MAX_RESULTS. */
+#define SYSML_FUSED_MAX_RESULTS 4
+int sysml_b200_fused_multi_agg(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
+                               const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
+                               int64_t cols, int n_out, double* out);
 /* C = t(A); replaces LibMatrixCUDA.transpose (java:1723-1729, cublasDgeam). */
 int sysml_b200_transpose(sysml_b200_ctx* ctx, const double* A, double* C, int64_t rows, int64_t cols);
 

@@ -171,16 +171,24 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
         else:
             g.call("sysml_b200_matmult_dense", _p(X), _p(yv), _p(out), n, m, n, 1, 1, 0)
 
-    fs = alloc(1, 1)
+    fs, fs4 = alloc(1, 1), alloc(4, 1)
 
     def fsum(inputs, expr, consts=()):
         return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs)
+
+    def fsums(inputs, exprs, consts=()):
+        # several sums over the same operands in one pass (the code generator's multi-aggregate template); with fused=False
+        # one pass per sum, as separate instructions would run
+        if fused:
+            return L.fusedMultiAggregate(g, "spoof", inputs, exprs, consts, out=fs4)
+        return [fsum(inputs, e, consts) for e in exprs]
 
     def dot(a, b):
         return fsum([a, b], E.input(0) * E.input(1))
 
     w, Xw, Xd, s, g_old, g_new = alloc(m, 1), alloc(n, 1), alloc(n, 1), alloc(m, 1), alloc(m, 1), alloc(m, 1)
     t1, t2, t3 = alloc(n, 1), alloc(n, 1), alloc(n, 1)
+    oy = alloc(n, 1)      # out * Y: one buffer for all iterations (a 400 MB cudaMalloc + cudaFree per iteration costs more than the kernel)
     g.call("sysml_b200_fill", _p(w), m, 0.0)
     g.call("sysml_b200_fill", _p(Xw), n, 0.0)
     xt_times(Y, g_old)
@@ -193,12 +201,11 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
     while cont and it < maxiter:
         step = 0.0
         x_times(s, Xd)
-        wd = reg * dot(w, s)
-        dd = reg * dot(s, s)
+        wd, dd = fsums([w, s], [E.input(0) * E.input(1), E.input(1) * E.input(1)])
+        wd, dd = reg * wd, reg * dd
         while True:
             if fused:
-                gsum = fsum([Y, Xw, Xd], g_e, (1.0, 0.0, step))
-                hsum = fsum([Y, Xw, Xd], h_e, (1.0, 0.0, step))
+                gsum, hsum = fsums([Y, Xw, Xd], [g_e, h_e], (1.0, 0.0, step))
             else:
                 g.call("sysml_b200_axpy", _p(Xw), _p(Xd), step, _p(t1), n, 1, 0)                       # tmp_Xw
                 g.call("sysml_b200_binary_mm", _p(Y), _p(t1), _p(t1), n, 1, 0, L.BINARY_OPS["1-*"])    # out = 1 - Y*tmp_Xw
@@ -221,20 +228,18 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
         hinge = E.let(E.const(0) - E.input(0) * E.input(1), lambda o: o.binary(E.const(1), ">") * o)
         if fused:
             osum = fsum([Y, Xw], E.let(hinge, lambda o: o * o), (1.0, 0.0))
-            oy = L.fusedCellwise(g, "spoof", [Y, Xw], hinge * E.input(0), (1.0, 0.0))
+            L.fusedCellwise(g, "spoof", [Y, Xw], hinge * E.input(0), (1.0, 0.0), out=oy)
         else:
             g.call("sysml_b200_binary_mm", _p(Y), _p(Xw), _p(t1), n, 1, 0, L.BINARY_OPS["1-*"])
             g.call("sysml_b200_binary_ms", _p(t1), 0.0, _p(t2), n, L.BINARY_OPS[">"], 0)
             g.call("sysml_b200_binary_mm", _p(t2), _p(t1), _p(t1), n, 1, 0, L.BINARY_OPS["*"])
             osum = L.unaryAggregate(g, "uasqk+", t1, "uasqk+")
-            oy = alloc(n, 1)
             g.call("sysml_b200_binary_mm", _p(t1), _p(Y), _p(oy), n, 1, 0, L.BINARY_OPS["*"])
         obj = 0.5 * osum + reg / 2.0 * dot(w, w)
         xt_times(oy, g_new)
-        oy.free()
         g.call("sysml_b200_axpy", _p(g_new), _p(w), -float(reg), _p(g_new), m, 1, 0)     # g_new = t(X)(out*Y) - reg*w
-        tmp = dot(s, g_old)
-        be = dot(g_new, g_new) / dot(g_old, g_old)
+        tmp, gn2, go2 = fsums([s, g_old, g_new], [E.input(0) * E.input(1), E.input(2) * E.input(2), E.input(1) * E.input(1)])
+        be = gn2 / go2
         g.call("sysml_b200_axpy", _p(g_new), _p(s), be, _p(s), m, 1, 0)                  # s = be*s + g_new
         g.call("sysml_b200_d2d", _p(g_old), _p(g_new), 8 * m)
         cont = (step * tmp >= tol * obj) and dot(s, s) != 0.0
@@ -242,7 +247,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
         if log is not None:
             log.append((it, obj))
     res = w.to_host().reshape(-1)
-    for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3, fs):
+    for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3, fs, fs4, oy):
         o.free()
     return res, it, obj
 

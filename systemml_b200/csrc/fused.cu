@@ -277,6 +277,76 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
     __syncwarp();
   }
 }
+#elif FUSED_SHAPE == 5
+// ---- several full sums over the same operands in one pass (the code generator's multi-aggregate template):
+// fused_eval_multi leaves FUSED_NOUT values per cell, each with its own compensated accumulator;
+// partial[out][block][2] ----
+extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArgs a) {
+  const long long len = a.rows * a.cols;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  Comp acc[FUSED_NOUT], acc2[FUSED_NOUT];
+#pragma unroll
+  for (int j = 0; j < FUSED_NOUT; j++) {
+    acc[j].hi = acc[j].lo = 0.0;
+    acc2[j].hi = acc2[j].lo = 0.0;
+  }
+#if FUSED_VEC2
+  const long long n2 = len >> 1;
+  for (long long i = tid; i < n2; i += stride) {
+    double x[FUSED_NIN + 1], y[FUSED_NIN + 1], u[FUSED_NOUT], w[FUSED_NOUT];
+    FUSED_LOAD2(i)
+    fused_eval_multi(x, a.k, u);
+    fused_eval_multi(y, a.k, w);
+#pragma unroll
+    for (int j = 0; j < FUSED_NOUT; j++) {
+      acc[j].add(u[j]);
+      acc2[j].add(w[j]);
+    }
+  }
+#else
+  {
+    const long long cols = a.cols;
+    long long i = tid;
+    if (i < len) {
+      long long r = i / cols, c = i - r * cols;
+      const long long dr = stride / cols, dc = stride - dr * cols;
+      for (; i < len; i += stride) {
+        double x[FUSED_NIN + 1], u[FUSED_NOUT];
+        FUSED_LOAD_RC(i, r, c)
+        fused_eval_multi(x, a.k, u);
+#pragma unroll
+        for (int j = 0; j < FUSED_NOUT; j++) acc[j].add(u[j]);
+        r += dr;
+        c += dc;
+        if (c >= cols) {
+          c -= cols;
+          r++;
+        }
+      }
+    }
+  }
+#endif
+  __shared__ double sh[FUSED_NOUT][2][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < FUSED_NOUT; j++) {
+    acc[j].merge(acc2[j].hi, acc2[j].lo);
+    group_merge(acc[j], 32);
+    if (lane == 0) {
+      sh[j][0][warp] = acc[j].hi;
+      sh[j][1][warp] = acc[j].lo;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < FUSED_NOUT) {
+    const int j = threadIdx.x;
+    Comp t{sh[j][0][0], sh[j][1][0]};
+    for (int q = 1; q < 8; q++) t.merge(sh[j][0][q], sh[j][1][q]);
+    a.partial[((size_t)j * gridDim.x + blockIdx.x) * 2] = t.hi;
+    a.partial[((size_t)j * gridDim.x + blockIdx.x) * 2 + 1] = t.lo;
+  }
+}
 #else
 // ---- column sums: a thread owns one column chunk, CTAs stride over row blocks; partial[grid][2][cols] ----
 extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArgs a) {
@@ -339,7 +409,9 @@ __device__ __forceinline__ double fin_result(const CompSum& s) {
 }
 template <int AOP>
 __global__ void fused_all_finish(const double* __restrict__ partial, int n, double* __restrict__ out) {
-  // one warp: lane-strided merge in a fixed order, then a butterfly
+  // one warp per result (blockIdx.x: the multi-aggregate form has several): lane-strided merge in a fixed order, then a butterfly
+  partial += (size_t)blockIdx.x * 2 * n;
+  out += blockIdx.x;
   CompSum s = fin_init<AOP>();
   for (int i = threadIdx.x; i < n; i += 32) fin_add<AOP>(s, partial[2 * i], partial[2 * i + 1]);
   for (int o = 16; o > 0; o >>= 1) {
@@ -454,8 +526,10 @@ void appendf(std::string& s, const char* fmt, ...) {
 }
 
 // postfix program -> "static double fused_eval(const double* x, const double* k)"; returns "" and sets err on a malformed program
-std::string gen_eval(const int32_t* prog, int n_tokens, int n_inputs, int n_consts, std::string& err) {
-  std::string src = "__device__ __forceinline__ double fused_eval(const double* x, const double* k) {\n";
+// (n_out > 0: "static void fused_eval_multi(const double* x, const double* k, double* o)", the program leaves n_out values)
+std::string gen_eval(const int32_t* prog, int n_tokens, int n_inputs, int n_consts, std::string& err, int n_out = 0) {
+  std::string src = n_out > 0 ? "__device__ __forceinline__ void fused_eval_multi(const double* x, const double* k, double* o) {\n"
+                              : "__device__ __forceinline__ double fused_eval(const double* x, const double* k) {\n";
   std::vector<int> stack;
   int nt = 0;
   for (int t = 0; t < n_tokens; t++) {
@@ -501,6 +575,12 @@ std::string gen_eval(const int32_t* prog, int n_tokens, int n_inputs, int n_cons
         return "";
     }
   }
+  if (n_out > 0) {
+    if ((int)stack.size() != n_out) { err = "program must leave exactly one value per result on the stack"; return ""; }
+    for (int j = 0; j < n_out; j++) appendf(src, "  o[%d] = t%d;\n", j, stack[(size_t)j]);
+    src += "}\n";
+    return src;
+  }
   if (stack.size() != 1) { err = "program must leave exactly one value on the stack"; return ""; }
   appendf(src, "  return t%d;\n}\n", stack.back());
   return src;
@@ -521,9 +601,9 @@ std::string gen_defines() {
 
 }  // namespace
 
-extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
-                                         const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
-                                         int64_t cols, int agg_in, double* out) {
+// n_out == 0: one chain, result per `agg_in`;  n_out > 0: the program leaves n_out values per cell, each summed over all cells
+static int fused_run(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs, const double* consts,
+                     int n_consts, const int32_t* program, int n_tokens, int64_t rows, int64_t cols, int agg_in, int n_out, double* out) {
   SYSML_ENTER(ctx);
   int agg = agg_in;
   if (n_inputs < 0 || n_inputs > SYSML_FUSED_MAX_INPUTS || n_consts < 0 || n_consts > SYSML_FUSED_MAX_CONSTS || n_tokens < 1 ||
@@ -537,7 +617,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   if (agg > SYSML_FUSED_AGG_COLSUMS) agg = (agg - 1) % 3 + 1;
   if (!program || (n_inputs && (!inputs || !input_kinds)) || (n_consts && !consts)) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: null pointer");
   const i64 len = rows * cols;
-  const i64 out_len = agg == SYSML_FUSED_AGG_NONE ? len : agg == SYSML_FUSED_AGG_SUM ? 1 : agg == SYSML_FUSED_AGG_ROWSUMS ? rows : cols;
+  const i64 out_len = n_out > 0 ? n_out : agg == SYSML_FUSED_AGG_NONE ? len : agg == SYSML_FUSED_AGG_SUM ? 1 : agg == SYSML_FUSED_AGG_ROWSUMS ? rows : cols;
   if (out_len == 0) return SYSML_OK;
   if (!out) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: out is null");
   if (len == 0) {  // an empty operand: every sum is 0 (LibMatrixAgg: empty input -> zero output)
@@ -559,7 +639,10 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   // kernel shape
   int shape, vec2 = 0, W = 32;
   int RW = 0;
-  if (agg == SYSML_FUSED_AGG_ROWSUMS && cols > 1 && cols <= 96 && getenv("SYSML_B200_FUSED_NO_NARROW") == nullptr) {
+  if (n_out > 0) {
+    shape = 5;
+    vec2 = (!any_bcast && aligned16 && (len % 2 == 0)) ? 1 : 0;
+  } else if (agg == SYSML_FUSED_AGG_ROWSUMS && cols > 1 && cols <= 96 && getenv("SYSML_B200_FUSED_NO_NARROW") == nullptr) {
     shape = 4;  // narrow: rows per warp = largest power of two with RW * cols <= 768 cells (6 KB per warp, 48 KB per CTA)
     RW = 32;
     while (RW > 1 && (i64)RW * cols > 768) RW >>= 1;
@@ -581,7 +664,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
 
   // ---- find or build the kernel ----
   std::string key;
-  appendf(key, "d%d|s%d|v%d|w%d|a%d|o%d|n%d|c%lld|", ctx->device, shape, vec2, W, kagg, aop, n_inputs, shape == 4 ? (long long)cols : 0ll);
+  appendf(key, "d%d|s%d|v%d|w%d|a%d|o%d|n%d|c%lld|m%d|", ctx->device, shape, vec2, W, kagg, aop, n_inputs, shape == 4 ? (long long)cols : 0ll, n_out);
   for (int i = 0; i < n_inputs; i++) {
     const int kd = input_kinds[i];
     const bool full = kd == SYSML_BCAST_NONE || (kd == SYSML_BCAST_COL && cols == 1) || (kd == SYSML_BCAST_ROW && rows == 1);
@@ -598,12 +681,12 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
       fn = it->second;
     } else {
       std::string err;
-      const std::string eval = gen_eval(program, n_tokens, n_inputs, n_consts, err);
+      const std::string eval = gen_eval(program, n_tokens, n_inputs, n_consts, err, n_out);
       if (eval.empty()) return sysml_set_error(ctx, SYSML_E_INVALID, "fused_cellwise: %s", err.c_str());
       std::string src = gen_defines();
       appendf(src, "#define FUSED_NIN %d\n#define FUSED_SHAPE %d\n#define FUSED_VEC2 %d\n#define FUSED_W %d\n#define FUSED_AGG %d\n#define FUSED_AOP %d\n",
               n_inputs, shape, vec2, W, kagg, aop);
-      appendf(src, "#define FUSED_COLS %d\n#define FUSED_RW %d\n", shape == 4 ? (int)cols : 1, shape == 4 ? RW : 1);
+      appendf(src, "#define FUSED_COLS %d\n#define FUSED_RW %d\n#define FUSED_NOUT %d\n", shape == 4 ? (int)cols : 1, shape == 4 ? RW : 1, n_out > 0 ? n_out : 1);
       // per-input loads: matrices stream past L1, broadcast vectors are cached reads
       std::string flat = "#define FUSED_LOAD_FLAT(i) ", rc = "#define FUSED_LOAD_RC(i, r, c) ", rcy = "#define FUSED_LOAD_RC_Y(i, r, c) ",
                   l2 = "#define FUSED_LOAD2(i) ";
@@ -672,7 +755,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   if (shape == 3 && grid > 2 * ctx->sm_count) grid = 2 * ctx->sm_count;
   if (kagg == 1 || kagg == 3) {
     void* ws = nullptr;
-    int rc = sysml_workspace(ctx, (size_t)grid * 2 * (kagg == 3 ? (size_t)cols : 1) * sizeof(double), &ws);
+    int rc = sysml_workspace(ctx, (size_t)grid * 2 * (kagg == 3 ? (size_t)cols : (n_out > 0 ? (size_t)n_out : 1)) * sizeof(double), &ws);
     if (rc) return rc;
     fa.partial = (double*)ws;
   }
@@ -685,7 +768,7 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
   }
   ctx->launches++;
   if (kagg == 1) {
-    if (aop == 0) fused_all_finish<0><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
+    if (aop == 0) fused_all_finish<0><<<n_out > 0 ? n_out : 1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
     else if (aop == 1) fused_all_finish<1><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
     else fused_all_finish<2><<<1, 32, 0, ctx->stream>>>(fa.partial, (int)grid, out);
     SYSML_LAUNCH_CHECK(ctx, "fused_all_finish");
@@ -697,4 +780,18 @@ extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* cons
     SYSML_LAUNCH_CHECK(ctx, "fused_col_finish");
   }
   return SYSML_OK;
+}
+
+extern "C" int sysml_b200_fused_cellwise(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
+                                         const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
+                                         int64_t cols, int agg_in, double* out) {
+  return fused_run(ctx, inputs, input_kinds, n_inputs, consts, n_consts, program, n_tokens, rows, cols, agg_in, 0, out);
+}
+
+extern "C" int sysml_b200_fused_multi_agg(sysml_b200_ctx* ctx, const double* const* inputs, const int* input_kinds, int n_inputs,
+                                          const double* consts, int n_consts, const int32_t* program, int n_tokens, int64_t rows,
+                                          int64_t cols, int n_out, double* out) {
+  if (ctx && (n_out < 1 || n_out > SYSML_FUSED_MAX_RESULTS))
+    return sysml_set_error(ctx, SYSML_E_LIMIT, "fused_multi_agg: between 1 and %d results", SYSML_FUSED_MAX_RESULTS);
+  return fused_run(ctx, inputs, input_kinds, n_inputs, consts, n_consts, program, n_tokens, rows, cols, SYSML_FUSED_AGG_SUM, n_out, out);
 }

@@ -96,9 +96,22 @@ __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int
     const int begin = __shfl_sync(full, s, 0);
     cursor[w][lane] = FILL ? ((r < a.rows) ? crp[r] : 0) : 0;
     __syncwarp();
+    // the next step's cell is loaded before this step's is processed: two loads per lane in flight
+    int c_next = 0;
+    double x_next = 0.0;
+    if (begin + lane < end) {
+      c_next = a.ci[begin + lane];
+      x_next = a.va[begin + lane];
+    }
     for (int k0 = begin; k0 < end; k0 += 32) {
       const int k = k0 + lane;
       const bool active = k < end;
+      const int c = c_next;
+      const double x = x_next;
+      if (k + 32 < end) {
+        c_next = a.ci[k + 32];
+        x_next = a.va[k + 32];
+      }
       // the row of cell k: the largest j with start[j] <= k (equal starts are empty rows; the last one holds the cell)
       int j = 0;
 #pragma unroll
@@ -107,11 +120,7 @@ __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int
         if (t <= k) j += step;
       }
       double v = 0.0;
-      int c = 0;
-      if (active) {
-        c = a.ci[k];
-        v = cell_value<MODE>(a, a.va[k], g * 32 + j, c);
-      }
+      if (active) v = cell_value<MODE>(a, x, g * 32 + j, c);
       const bool keep = active && (v != 0.0);  // SparseRow.append drops zeros; NaN is kept
       const unsigned peers = __match_any_sync(full, active ? j : 32);
       const unsigned mine = peers & __ballot_sync(full, keep);

@@ -332,6 +332,44 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     return out
 
 
+def fusedMultiAggregate(gCtx, instName, inputs, exprs, consts=(), rows=None, cols=None, out=None):
+    """sum(expr_j(inputs)) for every expression in ONE pass over the operands -- the code generator's multi-aggregate
+    template (runtime/codegen/SpoofMultiAggregate.java). Returns the sums as a list of floats (one read-back).
+    `out` may name a device buffer of at least len(exprs) doubles to reuse."""
+    if rows is None:
+        rows = max(i.rows for i in inputs)
+    if cols is None:
+        cols = max(i.cols for i in inputs)
+    kinds = []
+    for i in inputs:
+        if (i.rows, i.cols) == (rows, cols):
+            kinds.append(0)
+        elif (i.rows, i.cols) == (rows, 1):
+            kinds.append(1)
+        elif (i.rows, i.cols) == (1, cols):
+            kinds.append(2)
+        else:
+            raise native.NativeError(native.E_DIM, "fusedMultiAggregate: operand %dx%d does not broadcast to %dx%d" % (i.rows, i.cols, rows, cols))
+    tokens = []
+    for e in exprs:      # self-contained postfix runs: each leaves its value above the previous ones
+        tokens += e.tokens if isinstance(e, Expr) else list(e)
+    k = len(exprs)
+    given = out is not None
+    if out is None:
+        out = GPUObject.allocate_dense(gCtx, k, 1)
+    n = len(inputs)
+    ptrs = (C.c_void_p * max(n, 1))(*[i.ptr for i in inputs])
+    kd = (C.c_int * max(n, 1))(*kinds)
+    cs = (C.c_double * max(len(consts), 1))(*[float(c) for c in consts])
+    pg = (C.c_int32 * len(tokens))(*tokens)
+    try:
+        gCtx.call("sysml_b200_fused_multi_agg", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, k, _p(out.ptr))
+        return [float(v) for v in gCtx.d2h(out.ptr, (k,))]
+    finally:
+        if not given:
+            out.free()
+
+
 def transpose(gCtx, instName, in1):
     out = GPUObject.allocate_dense(gCtx, in1.cols, in1.rows)
     gCtx.call("sysml_b200_transpose", _p(in1.ptr), _p(out.ptr), in1.rows, in1.cols)

@@ -165,3 +165,43 @@ def test_min_max_endings(gctx, rows, cols):
         assert np.array_equal(np.isnan(exp), np.isnan(got)), agg
         ok = ~np.isnan(exp)
         assert np.array_equal(exp[ok].view(np.int64), got[ok].view(np.int64)), agg
+
+
+@pytest.mark.parametrize("n,cols", [(100_003, 1), (65_536, 1), (7, 1), (3001, 17)])
+def test_multi_aggregate_equals_separate_sums(gctx, n, cols):
+    """sysml_b200_fused_multi_agg (the code generator's multi-aggregate template, SpoofMultiAggregate.java): l2-svm.dml's two
+    line-search sums over the same three vectors in one pass, bit for bit what one fused sum per expression returns, and
+    within the usual bar of the unfused oracle evaluation; also with a broadcast operand and four results."""
+    from systemml_b200 import LibMatrixB200 as L, native
+    E = L.Expr
+    Y = np.where(O.rand_uniform(n * cols, seed=1) > 0, 1.0, -1.0).reshape(n, cols)
+    Xw = O.rand_uniform(n * cols, seed=2).reshape(n, cols)
+    Xd = O.rand_uniform(n * cols, seed=3).reshape(n, cols)
+    objs = [gctx.dense(a) for a in (Y, Xw, Xd)]
+    consts = (1.0, 0.0, 0.37)
+    out_e = E.const(0) - E.input(0) * (E.input(1) + E.const(2) * E.input(2))
+    g_e = E.let(out_e, lambda o: o * o.binary(E.const(1), ">") * E.input(0) * E.input(2))
+    h_e = E.input(2) * out_e.binary(E.const(1), ">") * E.input(2)
+    both = L.fusedMultiAggregate(gctx, "spoof", objs, [g_e, h_e], consts)
+    one = [L.fusedCellwise(gctx, "spoof", objs, e, consts, "sum") for e in (g_e, h_e)]
+    assert both == one, "same accumulation, same merge order"
+    out = 1 - Y * (Xw + 0.37 * Xd)
+    sv = (out > 0).astype(np.float64)
+    for got, exp in zip(both, (np.sum(out * sv * Y * Xd), np.sum(Xd * sv * Xd))):
+        assert abs(got - exp) <= 1e-9 * max(abs(exp), 1.0)
+    # a row-vector operand broadcast over the rows, four results (the limit)
+    if cols > 1:
+        rv = gctx.dense(O.rand_uniform(cols, seed=4).reshape(1, cols))
+        four = L.fusedMultiAggregate(gctx, "spoof", objs + [rv], [E.input(0) * E.input(3), E.input(1) * E.input(3), E.input(2), E.input(3)])
+        sep = [L.fusedCellwise(gctx, "spoof", objs + [rv], e, (), "sum") for e in (E.input(0) * E.input(3), E.input(1) * E.input(3), E.input(2), E.input(3))]
+        assert four == sep
+    with pytest.raises(native.NativeError):
+        L.fusedMultiAggregate(gctx, "spoof", objs, [E.input(0)] * 5)
+    # a program that leaves fewer values than results asked for is malformed
+    import ctypes as C
+    ptrs = (C.c_void_p * 3)(*[o.ptr for o in objs])
+    kd = (C.c_int * 3)(0, 0, 0)
+    pg = (C.c_int32 * 1)(0)
+    outb = gctx.empty(4, 1)
+    rc = gctx._lib.sysml_b200_fused_multi_agg(gctx.handle, ptrs, kd, 3, None, 0, pg, 1, n, cols, 2, C.c_void_p(outb.ptr))
+    assert rc == native.E_INVALID
