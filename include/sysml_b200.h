@@ -455,6 +455,36 @@ int sysml_b200_mmchain_csr_pcsc(sysml_b200_ctx* ctx, const int32_t* rowptr, cons
                                 int chain_type);
 
 /* ------------------------------------------------------------------------------------------------
+ * The same column-ordered copy in a layout whose products need no cross-lane work ("panelled sliced ELL", csrc/psell.cu):
+ * inside a (row panel, column slice) the entries of a column form a piece (cut at 64 entries), pieces are sorted by
+ * length and laid out 32 side by side as a group -- a lane owns a column run, entry j of the 32 pieces is one coalesced
+ * line -- so t(X) %*% y costs a load, a shared-memory gather, a multiply and an add per non-zero and nothing else.
+ * Same reference call sites as above.  Storage: 10 bytes per slot (f64 value + u16 row inside the panel; slots = nnz +
+ * padding, a few percent for Poisson-like column counts) + 72 bytes per group.
+ *   csr_to_psell       : builds the copy.  sgrp_ptr[sysml_b200_psell_segments(rows, panel_rows)] i32 is caller-allocated;
+ *                        the slot and group arrays are sized by the build and allocated by the library (release each with
+ *                        sysml_b200_free): *s_val f64[*n_slots], *s_lrow u16[*n_slots], *s_gcol u16[32 * *n_groups],
+ *                        *s_gdesc u64[*n_groups].  Temporaries (about 30 bytes per non-zero) are taken from and returned
+ *                        to the CUDA allocator inside the call.  cols <= 65535, panel_rows <= 8192.
+ *   matmult_psell_vm   : out[cols] = t(X) %*% (y [* w | - w]);  w_op 0 none, 1 multiply, 2 subtract.
+ *                        cols + 2 * (panel_rows + 1) doubles must fit in shared memory (SYSML_E_LIMIT).
+ *   mmchain_csr_psell  : out = t(X) %*% (w * (X %*% v)) etc. (X %*% v on the CSR copy into tmp_n, rows doubles).
+ * No atomics: results are bit-identical from run to run.
+ * ---------------------------------------------------------------------------------------------- */
+int64_t sysml_b200_psell_segments(int64_t rows, int panel_rows);
+int sysml_b200_csr_to_psell(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                            int64_t rows, int64_t cols, int64_t nnz, int panel_rows, int32_t* sgrp_ptr, double** s_val,
+                            uint16_t** s_lrow, uint16_t** s_gcol, uint64_t** s_gdesc, int64_t* n_slots,
+                            int64_t* n_groups);
+int sysml_b200_matmult_psell_vm(sysml_b200_ctx* ctx, const double* s_val, const uint16_t* s_lrow, const uint16_t* s_gcol,
+                                const uint64_t* s_gdesc, const int32_t* sgrp_ptr, int64_t rows, int64_t cols,
+                                int panel_rows, const double* y, const double* w, int w_op, double* out);
+int sysml_b200_mmchain_csr_psell(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
+                                 const double* s_val, const uint16_t* s_lrow, const uint16_t* s_gcol,
+                                 const uint64_t* s_gdesc, const int32_t* sgrp_ptr, int panel_rows, const double* v,
+                                 const double* w, double* tmp_n, double* out, int64_t n, int64_t m, int chain_type);
+
+/* ------------------------------------------------------------------------------------------------
  * Multi-GPU sum exchange over NVLink peer memory (one process per GPU on one box, world <= 8).
  * Replaces the aggregation step of SystemML's distributed tsmm / mmchain plan, RDDAggregateUtils.sumStable
  * (J/runtime/instructions/spark/utils/RDDAggregateUtils.java:58-70, used by MapmmChainSPInstruction and

@@ -178,6 +178,51 @@ class PCSCPointer:
         self.val = self.lrow = self.col = self.slice_ptr = 0
 
 
+class PSELLPointer:
+    """Column-ordered second copy of a CSR matrix as panelled sliced ELL (csrc/psell.cu): a lane owns a column run, so
+    t(X) %*% y is a gather with no cross-lane work."""
+    PANEL_ROWS = 8192
+
+    def __init__(self, gctx, csr, rows, cols, panel_rows=None):
+        self.gctx = gctx
+        self.rows, self.cols = int(rows), int(cols)
+        self.panel_rows = int(panel_rows or self.PANEL_ROWS)
+        n_seg = gctx._lib.sysml_b200_psell_segments(rows, self.panel_rows)
+        self.sgrp_ptr = gctx.allocate(n_seg * 4)
+        pv, pr, pc, pd = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        ns, ng = C.c_int64(), C.c_int64()
+        try:
+            gctx.call("sysml_b200_csr_to_psell", C.c_void_p(csr.rowPtr), C.c_void_p(csr.colInd), C.c_void_p(csr.val), rows, cols, csr.nnz,
+                      self.panel_rows, C.c_void_p(self.sgrp_ptr), C.byref(pv), C.byref(pr), C.byref(pc), C.byref(pd), C.byref(ns), C.byref(ng))
+        except Exception:
+            gctx.cudaFreeHelper(self.sgrp_ptr)
+            raise
+        self.val, self.lrow, self.gcol, self.gdesc = pv.value or 0, pr.value or 0, pc.value or 0, pd.value or 0
+        self.slots, self.groups, self.nnz = ns.value, ng.value, csr.nnz
+
+    @staticmethod
+    def fits(gctx, rows, cols, panel_rows=None):
+        return cols <= 65535 and (cols + 2 * ((panel_rows or PSELLPointer.PANEL_ROWS) + 1)) * 8 <= 226 * 1024
+
+    def args(self):
+        return (C.c_void_p(self.val), C.c_void_p(self.lrow), C.c_void_p(self.gcol), C.c_void_p(self.gdesc), C.c_void_p(self.sgrp_ptr))
+
+    def vm(self, y_ptr, out_ptr, w_ptr=None, w_op=0):
+        """out = t(X) %*% (y [* w | - w])"""
+        self.gctx.call("sysml_b200_matmult_psell_vm", *self.args(), self.rows, self.cols, self.panel_rows, C.c_void_p(y_ptr),
+                       C.c_void_p(w_ptr) if w_ptr else None, w_op, C.c_void_p(out_ptr))
+
+    def mmchain(self, csr, v_ptr, w_ptr, tmp_ptr, out_ptr, chain_type):
+        self.gctx.call("sysml_b200_mmchain_csr_psell", C.c_void_p(csr.rowPtr), C.c_void_p(csr.colInd), C.c_void_p(csr.val), *self.args(),
+                       self.panel_rows, C.c_void_p(v_ptr), C.c_void_p(w_ptr) if w_ptr else None, C.c_void_p(tmp_ptr), C.c_void_p(out_ptr),
+                       self.rows, self.cols, chain_type)
+
+    def deallocate(self):
+        for p in (self.val, self.lrow, self.gcol, self.gdesc, self.sgrp_ptr):
+            self.gctx.cudaFreeHelper(p)
+        self.val = self.lrow = self.gcol = self.gdesc = self.sgrp_ptr = 0
+
+
 class GPUObject:
     """Device state of one matrix: dense row-major double* or a CSRPointer (GPUObject.java:52-99)."""
 

@@ -79,6 +79,10 @@ SIGNATURES = {
     "sysml_b200_rand_uniform": (ci, [vp, vp, i64, u64, i64, dbl, dbl]),
     "sysml_b200_rand_csr": (ci, [vp, i64, i64, dbl, u64, i64, vp, vp, vp, pi64]),
     "sysml_b200_kmeans_step": (ci, [vp, vp, vp, vp, i64, i64, i64, vp, vp, vp]),
+    "sysml_b200_psell_segments": (i64, [i64, ci]),
+    "sysml_b200_csr_to_psell": (ci, [vp, vp, vp, vp, i64, i64, i64, ci, vp, vp, vp, vp, vp, pi64, pi64]),
+    "sysml_b200_matmult_psell_vm": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, ci, vp]),
+    "sysml_b200_mmchain_csr_psell": (ci, [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp, i64, i64, ci]),
     "sysml_b200_pcsc_slice_entries": (i64, [i64, ci]),
     "sysml_b200_csr_to_pcsc": (ci, [vp, vp, vp, vp, i64, i64, i64, ci, vp, vp, vp, vp]),
     "sysml_b200_matmult_pcsc_vm": (ci, [vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, ci, vp]),

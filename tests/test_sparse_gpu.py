@@ -343,6 +343,66 @@ def test_panel_csc_vm_and_mmchain(gctx, n, m, sp, panel):
         o.free()
 
 
+@pytest.mark.parametrize("n,m,sp,panel", [(5000, 300, 0.03, 512), (4097, 10_000, 0.001, 1024), (1000, 17, 0.4, 64), (70_000, 1000, 0.01, 8192),
+                                          (300, 2000, 0.05, 8192), (2049, 64, 1.0, 256), (100, 33, 0.0, 32), (9000, 40, 0.3, 8192)])
+def test_panelled_sliced_ell_vm_and_mmchain(gctx, n, m, sp, panel):
+    """t(X) %*% y and the three chain types through the sliced-ELL column copy (csrc/psell.cu) against the oracle's
+    matrixMultChainSparse / VM (LibMatrixMult.java:1655-1684, 1262-1286): 1e-9 element-wise, the same bits on every run.
+    Shapes cover several panels, a ragged last panel, empty slices, nnz = 0, and columns far longer than a piece (a column
+    of ones, fully dense blocks): cut columns share a group, whose adds are then serialised."""
+    import ctypes as C
+    from systemml_b200.gpu_context import PSELLPointer
+    X = O.java_test_matrix(n, m, -1, 1, sp, 77) if sp > 0 else np.zeros((n, m))
+    if sp >= 1.0:
+        X[X == 0] = 0.5
+    X[:, m // 2] = np.where(np.arange(n) % 3 == 0, 0.0, 1.5) if sp > 0 else 0.0     # one long column run
+    if sp > 0:
+        X[:, 0] = 1.0                                                                # an intercept column
+    rp, ci, va = O.dense_to_csr(X)
+    d = gctx.csr(rp, ci, va, X.shape)
+    pc = PSELLPointer(gctx, d.csr, n, m, panel)
+    assert pc.slots >= d.csr.nnz and pc.slots % 32 == 0
+    y = O.rand_uniform(n, seed=5)
+    v = O.rand_uniform(m, seed=6)
+    w = O.rand_uniform(n, seed=7, lo=0.0, hi=1.0)
+    dy, dv, dw = gctx.dense(y.reshape(n, 1)), gctx.dense(v.reshape(m, 1)), gctx.dense(w.reshape(n, 1))
+    out, tmp = gctx.empty(m, 1), gctx.empty(n, 1)
+    runs = []
+    for _ in range(2):
+        pc.vm(dy.ptr, out.ptr)
+        runs.append(out.to_host().reshape(-1))
+    assert np.array_equal(runs[0], runs[1]), "t(X) %*% y must be bit-identical run to run"
+    exp = (X.astype(np.longdouble).T @ y.astype(np.longdouble)).astype(np.float64)
+    assert_parity(exp, runs[0], np.abs(X).T @ np.abs(y), n, what="psell t(X)y %dx%d" % (n, m))
+    for wop, yy in ((1, y * w), (2, y - w)):
+        pc.vm(dy.ptr, out.ptr, dw.ptr, wop)
+        e2 = (X.astype(np.longdouble).T @ yy.astype(np.longdouble)).astype(np.float64)
+        assert_parity(e2, out.to_host().reshape(-1), np.abs(X).T @ np.abs(yy), n, what="psell t(X)(y op w) %dx%d" % (n, m))
+    for ct in (0, 1, 2):
+        pc.mmchain(d.csr, dv.ptr, dw.ptr if ct else None, tmp.ptr, out.ptr, ct)
+        got = out.to_host().reshape(-1)
+        e = O.mmchain_csr(rp, ci, va, X.shape, v, w if ct else None, ct, 1)
+        assert_parity(e, got, abs_terms_mmchain(X, v, w, ct), n + m, what="psell mmchain %dx%d ct=%d" % (n, m, ct))
+    # non-finite y in a row no column stores must not leak through the padded slots (they gather y_s[R] = 0)
+    if sp > 0 and sp < 1.0:
+        X2 = X.copy()
+        X2[n // 2, :] = 0.0
+        rp2, ci2, va2 = O.dense_to_csr(X2)
+        d2 = gctx.csr(rp2, ci2, va2, X2.shape)
+        pc2 = PSELLPointer(gctx, d2.csr, n, m, panel)
+        y2 = y.copy()
+        y2[n // 2] = np.inf
+        dy2 = gctx.dense(y2.reshape(n, 1))
+        pc2.vm(dy2.ptr, out.ptr)
+        assert np.all(np.isfinite(out.to_host()))
+        pc2.deallocate()
+        d2.free()
+        dy2.free()
+    pc.deallocate()
+    for o in (d, dy, dv, dw, out, tmp):
+        o.free()
+
+
 def test_gpuobject_builds_the_column_ordered_copy_on_second_use(gctx):
     """LibMatrixB200.matmult / mmchain: the first transposed use of a CSR operand scatters (one-shot operands never pay
     for the sort), the second builds the copy, later ones gather; all agree to 1e-9 and from then on bit for bit."""

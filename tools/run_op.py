@@ -50,6 +50,19 @@ elif op == "pcsc":
     pc = PCSCPointer(g, S.csr, rows, cols)
     y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
     fn = lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), rows, cols, pc.panel_rows, p_(y), None, 0, p_(oc))
+elif op == "psell":
+    rows, cols, per = a[:3]
+    from systemml_b200.gpu_context import PSELLPointer
+    import time
+    S = g.rand_csr(rows, cols, per, seed=2)
+    g.sync()
+    t0 = time.perf_counter()
+    pc = PSELLPointer(g, S.csr, rows, cols)
+    g.sync()
+    print("psell build s", round(time.perf_counter() - t0, 3), "nnz", S.csr.nnz, "slots", pc.slots, "groups", pc.groups, "padding",
+          round(pc.slots / max(S.csr.nnz, 1) - 1, 4))
+    y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
+    fn = lambda: pc.vm(y.ptr, oc.ptr)
 elif op == "csrcell":  # sparse-safe cellwise with a CSR result: kind 0 X*y (column vector), 1 X*0.5, 2 X*X
     rows, cols, per, kind = a[:4]
     S = g.rand_csr(rows, cols, per, seed=2)
