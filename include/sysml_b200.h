@@ -426,40 +426,17 @@ int sysml_b200_kmeans_step(sysml_b200_ctx* ctx, const double* X, const double* C
                            int64_t m, int64_t k, double* sums, double* counts, double* sum_min_dist);
 
 /* ------------------------------------------------------------------------------------------------
- * Column-ordered copy of a constant CSR matrix ("panel CSC") for t(X) %*% y and the second half of sparse mmchain.
- * Replaces the scatter of LibMatrixMult.matrixMultChainSparse (LibMatrixMult.java:1655-1684) and of the VM form of
- * matrixMultSparseDense (:1262-1286) -- and, on the reference GPU path, cusparseDcsrmv with the transpose flag
- * (LibMatrixCuMatMult.java:313-341) -- by a gather without atomics whose result is bit-identical run to run.
- * The copy costs 12 bytes per non-zero (like CSR) and is worth building when X is used more than once, as the
- * iterative algorithms do; the CSR entry points above remain the path for one-shot operands.
- * Layout: rows in panels of panel_rows (<= 65536; 8192 is a good value), entries of a panel sorted by (column, row):
- *   p_val[nnz] f64, p_lrow[nnz] u16 (row inside the panel), p_col[nnz] u16 (column, so cols <= 65536),
- *   slice_ptr[sysml_b200_pcsc_slice_entries(rows, panel_rows)] i32 (32 column slices per panel + 1).
- * All arrays are allocated by the caller.  cols + panel_rows doubles must fit in shared memory (SYSML_E_LIMIT).
- *   csr_to_pcsc        : builds the copy (one stable radix sort; scratch from the context's workspace).
- *   matmult_pcsc_vm    : out[cols] = t(X) %*% (y [* w | - w]);  w_op 0 none, 1 multiply, 2 subtract.
- *   mmchain_csr_pcsc   : out = t(X) %*% (w * (X %*% v)) etc.; X %*% v runs on the CSR copy into tmp_n (rows doubles,
- *                        caller-owned), the weights are applied while a panel of it is parked in shared memory.
- * ---------------------------------------------------------------------------------------------- */
-int64_t sysml_b200_pcsc_slice_entries(int64_t rows, int panel_rows);
-int sysml_b200_csr_to_pcsc(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind, const double* val,
-                           int64_t rows, int64_t cols, int64_t nnz, int panel_rows, double* p_val,
-                           uint16_t* p_lrow, uint16_t* p_col, int32_t* slice_ptr);
-int sysml_b200_matmult_pcsc_vm(sysml_b200_ctx* ctx, const double* p_val, const uint16_t* p_lrow,
-                               const uint16_t* p_col, const int32_t* slice_ptr, int64_t rows, int64_t cols,
-                               int panel_rows, const double* y, const double* w, int w_op, double* out);
-int sysml_b200_mmchain_csr_pcsc(sysml_b200_ctx* ctx, const int32_t* rowptr, const int32_t* colind,
-                                const double* val, const double* p_val, const uint16_t* p_lrow,
-                                const uint16_t* p_col, const int32_t* slice_ptr, int panel_rows, const double* v,
-                                const double* w, double* tmp_n, double* out, int64_t n, int64_t m,
-                                int chain_type);
-
-/* ------------------------------------------------------------------------------------------------
- * The same column-ordered copy in a layout whose products need no cross-lane work ("panelled sliced ELL", csrc/psell.cu):
- * inside a (row panel, column slice) the entries of a column form a piece (cut at 64 entries), pieces are sorted by
- * length and laid out 32 side by side as a group -- a lane owns a column run, entry j of the 32 pieces is one coalesced
- * line -- so t(X) %*% y costs a load, a shared-memory gather, a multiply and an add per non-zero and nothing else.
- * Same reference call sites as above.  Storage: 10 bytes per slot (f64 value + u16 row inside the panel; slots = nnz +
+ * Column-ordered second copy of a constant CSR matrix for t(X) %*% y and the second half of sparse mmchain
+ * ("panelled sliced ELL", csrc/psell.cu).  Replaces the scatter of LibMatrixMult.matrixMultChainSparse
+ * (LibMatrixMult.java:1655-1684) and of the VM form of matrixMultSparseDense (:1262-1286) -- and, on the reference GPU
+ * path, cusparseDcsrmv with the transpose flag (LibMatrixCuMatMult.java:313-341) -- by a gather without atomics whose
+ * result is bit-identical run to run.  Worth building when X is used more than once, as the iterative algorithms do; the
+ * CSR entry points above remain the path for one-shot operands.
+ * Layout: rows in panels of panel_rows, columns in 32 slices.  Inside a (panel, slice) the entries of a column form a
+ * piece (cut at 64 entries), pieces are sorted by length and laid out 32 side by side as a group -- a lane owns a column
+ * run, entry j of the 32 pieces is one coalesced line -- so t(X) %*% y costs a load, a shared-memory gather, a multiply
+ * and an add per non-zero and nothing else.
+ * Storage: 10 bytes per slot (f64 value + u16 row inside the panel; slots = nnz +
  * padding, a few percent for Poisson-like column counts) + 72 bytes per group.
  *   csr_to_psell       : builds the copy.  sgrp_ptr[sysml_b200_psell_segments(rows, panel_rows)] i32 is caller-allocated;
  *                        the slot and group arrays are sized by the build and allocated by the library (release each with

@@ -145,7 +145,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
     Y: GPUObject n x 1.  Per outer iteration the O(nnz) work is X %*% s and t(X) %*% (out * Y); everything else is
     chains over n-vectors, each evaluated in one pass by fusedCellwise (fused=True) or operator by operator
     (fused=False, the reference's plan).  column_copy=True runs t(X) %*% y as a gather over the column-ordered copy of a
-    CSR X (csrc/pcsc.cu; deterministic), False as the scatter kernel.  Returns (w ndarray, iterations, final objective)."""
+    CSR X (csrc/psell.cu; deterministic), False as the scatter kernel.  Returns (w ndarray, iterations, final objective)."""
     n, m = X.rows, X.cols
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
@@ -164,7 +164,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
     def xt_times(yv, out):      # out = t(X) %*% yv
         pc = X.columnOrderedCopy() if (sparse and column_copy) else None
         if pc is not None:          # gather over the column-ordered copy (bit-identical run to run)
-            g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, _p(yv), None, 0, _p(out))
+            pc.vm(yv.ptr, out.ptr)
         elif sparse:
             g.call("sysml_b200_matmult_csr_dense", C.c_void_p(X.csr.rowPtr), C.c_void_p(X.csr.colInd), C.c_void_p(X.csr.val),
                    _p(yv), _p(out), n, m, n, 1, 1)
@@ -187,7 +187,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
         return fsum([a, b], E.input(0) * E.input(1))
 
     w, Xw, Xd, s, g_old, g_new = alloc(m, 1), alloc(n, 1), alloc(n, 1), alloc(m, 1), alloc(m, 1), alloc(m, 1)
-    t1, t2, t3 = alloc(n, 1), alloc(n, 1), alloc(n, 1)
+    t1, t2, t3 = (alloc(n, 1), alloc(n, 1), alloc(n, 1)) if not fused else (None, None, None)   # temporaries of the unfused plan
     oy = alloc(n, 1)      # out * Y: one buffer for all iterations (a 400 MB cudaMalloc + cudaFree per iteration costs more than the kernel)
     g.call("sysml_b200_fill", _p(w), m, 0.0)
     g.call("sysml_b200_fill", _p(Xw), n, 0.0)
@@ -248,7 +248,8 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
             log.append((it, obj))
     res = w.to_host().reshape(-1)
     for o in (w, Xw, Xd, s, g_old, g_new, t1, t2, t3, fs, fs4, oy):
-        o.free()
+        if o is not None:
+            o.free()
     return res, it, obj
 
 

@@ -660,7 +660,7 @@ static int fused_run(sysml_b200_ctx* ctx, const double* const* inputs, const int
     vec2 = (shape == 0 && aligned16 && (len % 2 == 0)) ? 1 : 0;
   }
   // row sums over one column / column sums over one row are the chain itself
-  const int kagg = (shape <= 1 && agg == SYSML_FUSED_AGG_SUM) ? 1 : ((shape == 2 || shape == 4) ? 2 : (shape == 3 ? 3 : 0));
+  const int kagg = ((shape <= 1 && agg == SYSML_FUSED_AGG_SUM) || shape == 5) ? 1 : ((shape == 2 || shape == 4) ? 2 : (shape == 3 ? 3 : 0));
 
   // ---- find or build the kernel ----
   std::string key;

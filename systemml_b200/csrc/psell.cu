@@ -6,10 +6,16 @@
 //
 // are gathers with NO cross-lane work: no atomics, no segmented scan, a handful of instructions per non-zero.
 //
-// Why a second copy at all: see pcsc.cu (row-ordered CSR makes t(X) %*% y one fp64 atomic per non-zero).  Why this
-// layout: the (column, row)-sorted panel of pcsc.cu streams at the HBM rate's 0.62 because a warp that finds equal
-// columns in neighbouring lanes has to fold them with a segmented scan -- ~1.8 warp instructions per non-zero, and the
-// issue slots run out before the memory does (profiles/r02_ncu_pcsc_vm_summary.txt).  Here a lane OWNS a column run.
+// Why a second copy.  Row-ordered CSR makes t(X) %*% y a scatter: c[colind[k]] += y[i] * val[k].  On the GPU that is an
+// fp64 atomic per non-zero -- shared-memory fp64 atomics are compare-and-swap loops, L2 reductions are a fraction of the
+// HBM rate -- and the order of the additions, hence the low bits of the result, changes from run to run.  X is constant
+// across the iterations of L2SVM / GLM / LinearRegCG, so it pays to keep a copy in which the scatter is a gather.  A
+// plain CSC copy is not that copy: its gathers go to y, an n-vector (400 MB at C3) that no cache holds; hence panels.
+// Why this layout.  The first version of the copy kept a panel's entries sorted by (column, row) and let a warp fold
+// equal columns in neighbouring lanes with a segmented scan: ~1.8 warp instructions per non-zero, the issue slots ran
+// out before the memory did and it streamed at 0.62 of the copy rate (profiles/r02_ncu_pcsc_vm_summary.txt).  Here a
+// lane OWNS a column run; issue slots are 29 % busy and what is left is latency (profiles/r02_ncu_psell_vm_summary.txt),
+// which an L2 prefetch two groups ahead takes from 1.42 to 1.20 ms at C3 (0.82 of the copy rate).
 //
 // Layout.  Rows are cut into panels of R rows, the columns into 32 slices (one per warp).  Inside a (panel, slice) the
 // entries of one column are a "piece" (a column with more than LMAX entries in the panel is cut into several);
@@ -37,6 +43,8 @@
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 #include <cub/iterator/transform_input_iterator.cuh>
+
+#include <stdlib.h>
 
 #include <vector>
 
@@ -154,6 +162,8 @@ struct PsellArgs {
   i64 n;
   int m, R;
   i64 npanels;
+  int pf;   // L2 prefetch distance in groups (0: none)
+  int pfc;  // groups per prefetch request
 };
 
 constexpr int YPT = 8;  // y values per thread per panel held in registers (R <= 1024 * YPT)
@@ -182,6 +192,45 @@ __global__ void __launch_bounds__(1024, 1) psell_vm_kernel(const PsellArgs a) {
   if (tid == 0) y_buf[0][a.R] = y_buf[1][a.R] = 0.0;
   double yr[YPT];
   psell_fetch_y(a, blockIdx.x, tid, yr);
+  // L2 prefetch cursor: this warp's groups, over all the panels of the CTA, are one stream; the cursor runs a.pf groups
+  // ahead of the group being multiplied and asks L2 for each group's two slot ranges with one bulk prefetch each, so
+  // the loads below meet L2 latency, not DRAM latency (the kernel is latency-bound: 64 registers per thread leave room for
+  // 8 entries per lane in flight)
+  i64 pf_p = blockIdx.x;
+  int pf_g = 0, pf_end = 0;
+  bool pf_live = a.pf > 0 && pf_p < a.npanels;
+  if (pf_live) {
+    const int* q = a.sgrp_ptr + pf_p * NSLICE + warp;
+    pf_g = __ldg(q);
+    pf_end = __ldg(q + 1);
+  }
+  auto pf_step = [&]() {
+    while (pf_live && pf_g >= pf_end) {
+      pf_p += gridDim.x;
+      if (pf_p >= a.npanels) {
+        pf_live = false;
+        break;
+      }
+      const int* q = a.sgrp_ptr + pf_p * NSLICE + warp;
+      pf_g = __ldg(q);
+      pf_end = __ldg(q + 1);
+    }
+    if (!pf_live) return;
+    // a.pfc consecutive groups (contiguous slots) per request: fewer, larger prefetches
+    const int gl = (pf_g + a.pfc <= pf_end) ? pf_g + a.pfc - 1 : pf_end - 1;
+    if (lane == 0) {
+      const uint2 d0 = __ldg(a.gdesc + pf_g);
+      const uint2 d1 = __ldg(a.gdesc + gl);
+      const unsigned ln = d1.x + (d1.y & 0xffffu) - d0.x;
+      if (ln) {
+        bulk_prefetch_l2(a.val + (i64)d0.x * 32, ln * 256u);
+        bulk_prefetch_l2(a.lrow + (i64)d0.x * 32, ln * 64u);
+      }
+    }
+    pf_g = gl + 1;
+  };
+  for (int q = 0; q < a.pf; q += a.pfc) pf_step();
+  int pf_tick = 0;
   int buf = 0;
   for (i64 p = blockIdx.x; p < a.npanels; p += gridDim.x, buf ^= 1) {
     double* y_s = y_buf[buf];
@@ -196,6 +245,10 @@ __global__ void __launch_bounds__(1024, 1) psell_vm_kernel(const PsellArgs a) {
     const int g0 = __ldg(sp), g1 = __ldg(sp + 1);
     uint2 d = (g0 < g1) ? __ldg(a.gdesc + g0) : make_uint2(0u, 0u);
     for (int g = g0; g < g1; g++) {
+      if (++pf_tick == a.pfc) {
+        pf_tick = 0;
+        pf_step();
+      }
       const uint2 dn = (g + 1 < g1) ? __ldg(a.gdesc + g + 1) : make_uint2(0u, 0u);  // the next group's descriptor, ahead of need
       const unsigned col = __ldg(a.gcol + (i64)g * 32 + lane);
       const int len = (int)(d.y & 0xffffu);
@@ -343,7 +396,7 @@ int sysml_b200_csr_to_psell(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
   int* sidx = T.get<int>(np);
   int* sidx2 = T.get<int>(np);
   if (T.err != cudaSuccess) return sysml_set_error(ctx, SYSML_E_OOM, "csr_to_psell: piece index: %s", cudaGetErrorString(T.err));
-  if (2 * ((size_t)np + 1) > (size_t)nnz) {  // (cannot happen: a piece has at least one entry, so np <= nnz; two key arrays need 2 np)
+  if (2 * ((size_t)np + 1) > (size_t)nnz) {  // mostly short runs: the two key arrays do not fit in the old one
     skey = T.get<u64>(np);
     skey2 = T.get<u64>(np);
     if (T.err != cudaSuccess) return sysml_set_error(ctx, SYSML_E_OOM, "csr_to_psell: piece keys: %s", cudaGetErrorString(T.err));
@@ -424,6 +477,12 @@ int sysml_b200_matmult_psell_vm(sysml_b200_ctx* ctx, const double* s_val, const 
   a.val = s_val; a.lrow = s_lrow; a.gcol = s_gcol; a.gdesc = (const uint2*)s_gdesc; a.sgrp_ptr = sgrp_ptr; a.y = y; a.w = w; a.wop = w_op;
   a.n = rows; a.m = (int)cols; a.R = panel_rows;
   a.npanels = (rows + panel_rows - 1) / panel_rows;
+  a.pf = 2;  // measured at C3: 0 -> 1.42 ms, 1..2 -> 1.20, 3 -> 1.31, 4 -> 1.37, 8 and more -> 1.8 (the prefetched lines push each other out of L2)
+  if (const char* e = getenv("SYSML_B200_PSELL_PREFETCH")) a.pf = atoi(e);  // A/B switch for measurements
+  if (a.pf < 0 || a.pf > 64) a.pf = 0;
+  a.pfc = 1;
+  if (const char* e = getenv("SYSML_B200_PSELL_PREFETCH_CHUNK")) a.pfc = atoi(e);
+  if (a.pfc < 1 || a.pfc > 16) a.pfc = 1;
   i64 grid = ctx->sm_count;
   if (grid > a.npanels) grid = a.npanels;
   void* ws = nullptr;

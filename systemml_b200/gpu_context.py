@@ -150,37 +150,10 @@ class CSRPointer:
         self.val = self.rowPtr = self.colInd = 0
 
 
-class PCSCPointer:
-    """Column-ordered second copy of a CSR matrix (csrc/pcsc.cu): what CSRPointer.transpose / csr2csc
-    (CSRPointer.java:463-481) would give, cut into row panels so that the gathered vector fits in shared memory."""
-    PANEL_ROWS = 8192
-
-    def __init__(self, gctx, csr, rows, cols, panel_rows=None):
-        self.gctx = gctx
-        self.panel_rows = int(panel_rows or self.PANEL_ROWS)
-        n_slice = gctx._lib.sysml_b200_pcsc_slice_entries(rows, self.panel_rows)
-        nz = max(csr.nnz, 1)
-        self.val, self.lrow, self.col = gctx.allocate(nz * 8), gctx.allocate(nz * 2), gctx.allocate(nz * 2)
-        self.slice_ptr = gctx.allocate(n_slice * 4)
-        gctx.call("sysml_b200_csr_to_pcsc", C.c_void_p(csr.rowPtr), C.c_void_p(csr.colInd), C.c_void_p(csr.val), rows, cols, csr.nnz,
-                  self.panel_rows, C.c_void_p(self.val), C.c_void_p(self.lrow), C.c_void_p(self.col), C.c_void_p(self.slice_ptr))
-
-    @staticmethod
-    def fits(gctx, rows, cols, panel_rows=None):
-        return cols <= 65536 and (cols + (panel_rows or PCSCPointer.PANEL_ROWS)) * 8 <= 220 * 1024
-
-    def args(self):
-        return (C.c_void_p(self.val), C.c_void_p(self.lrow), C.c_void_p(self.col), C.c_void_p(self.slice_ptr))
-
-    def deallocate(self):
-        for p in (self.val, self.lrow, self.col, self.slice_ptr):
-            self.gctx.cudaFreeHelper(p)
-        self.val = self.lrow = self.col = self.slice_ptr = 0
-
-
 class PSELLPointer:
-    """Column-ordered second copy of a CSR matrix as panelled sliced ELL (csrc/psell.cu): a lane owns a column run, so
-    t(X) %*% y is a gather with no cross-lane work."""
+    """Column-ordered second copy of a CSR matrix as panelled sliced ELL (csrc/psell.cu) -- what CSRPointer.transpose /
+    csr2csc (CSRPointer.java:463-481) would give, cut into row panels so that the gathered vector fits in shared memory,
+    and laid out so that a lane owns a column run: t(X) %*% y is a gather with no cross-lane work and no atomics."""
     PANEL_ROWS = 8192
 
     def __init__(self, gctx, csr, rows, cols, panel_rows=None):
@@ -232,7 +205,7 @@ class GPUObject:
         self.cols = int(cols)
         self.ptr = 0          # jcudaDenseMatrixPtr
         self.csr = None       # jcudaSparseMatrixPtr
-        self.pcsc = None      # column-ordered copy of a CSR matrix, built on its second transposed use
+        self.colcopy = None   # column-ordered copy of a CSR matrix (PSELLPointer), built on its second transposed use
         self.transposed_uses = 0
         self.dirty = False
         self.owns = True
@@ -304,23 +277,23 @@ class GPUObject:
         return rp, ci, va
 
     def columnOrderedCopy(self):
-        """The panel-CSC copy of a CSR matrix, or None while it is not worth having: the first transposed use of an
+        """The column-ordered copy of a CSR matrix, or None while it is not worth having: the first transposed use of an
         operand goes through the scatter kernels (a one-shot operand never pays for the sort), the second one builds
         the copy, and every later t(X) %*% y / mmchain gathers from it."""
-        if self.csr is None or self.csr.nnz == 0 or not PCSCPointer.fits(self.gctx, self.rows, self.cols):
+        if self.csr is None or self.csr.nnz == 0 or not PSELLPointer.fits(self.gctx, self.rows, self.cols):
             return None
-        if os.environ.get("SYSML_B200_NO_PCSC"):   # A/B switch for measurements
+        if os.environ.get("SYSML_B200_NO_COLUMN_COPY"):   # A/B switch for measurements
             return None
         self.transposed_uses += 1
-        if self.pcsc is None and self.transposed_uses >= 2:
-            self.pcsc = PCSCPointer(self.gctx, self.csr, self.rows, self.cols)
-        return self.pcsc
+        if self.colcopy is None and self.transposed_uses >= 2:
+            self.colcopy = PSELLPointer(self.gctx, self.csr, self.rows, self.cols)
+        return self.colcopy
 
     def clearData(self):
         """GPUObject.clearData (GPUObject.java:948-970)."""
-        if self.pcsc is not None:
-            self.pcsc.deallocate()
-            self.pcsc = None
+        if self.colcopy is not None:
+            self.colcopy.deallocate()
+            self.colcopy = None
         if self.owns and self.ptr:
             self.gctx.cudaFreeHelper(self.ptr)
         self.ptr = 0

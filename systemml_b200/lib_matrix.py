@@ -72,8 +72,7 @@ def mmchain(gCtx, instName, X, v, w, ctype):
         pc = X.columnOrderedCopy()
         if pc is not None:
             tmp = GPUObject.allocate_dense(gCtx, n, 1)
-            gCtx.call("sysml_b200_mmchain_csr_pcsc", _p(X.csr.rowPtr), _p(X.csr.colInd), _p(X.csr.val), *pc.args(), pc.panel_rows,
-                      _p(v.ptr), _p(wp), _p(tmp.ptr), _p(out.ptr), n, m, ct)
+            pc.mmchain(X.csr, v.ptr, wp, tmp.ptr, out.ptr, ct)
             tmp.free()
         else:
             gCtx.call("sysml_b200_mmchain_csr", _p(X.csr.rowPtr), _p(X.csr.colInd), _p(X.csr.val), _p(v.ptr), _p(wp),
@@ -138,7 +137,7 @@ def matmult(gCtx, instName, left, right, isLeftTransposed=False, isRightTranspos
             raise native.NativeError(native.E_UNSUPPORTED, "CSR x t(dense)")
         pc = left.columnOrderedCopy() if (isLeftTransposed and n == 1) else None
         if pc is not None:   # t(X) %*% y as a gather over the column-ordered copy
-            gCtx.call("sysml_b200_matmult_pcsc_vm", *pc.args(), left.rows, left.cols, pc.panel_rows, _p(right.ptr), None, 0, _p(out.ptr))
+            pc.vm(right.ptr, out.ptr)
             return out
         gCtx.call("sysml_b200_matmult_csr_dense", _p(left.csr.rowPtr), _p(left.csr.colInd), _p(left.csr.val),
                   _p(right.ptr), _p(out.ptr), left.rows, left.cols, right.rows, right.cols,

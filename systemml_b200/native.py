@@ -83,10 +83,6 @@ SIGNATURES = {
     "sysml_b200_csr_to_psell": (ci, [vp, vp, vp, vp, i64, i64, i64, ci, vp, vp, vp, vp, vp, pi64, pi64]),
     "sysml_b200_matmult_psell_vm": (ci, [vp, vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, ci, vp]),
     "sysml_b200_mmchain_csr_psell": (ci, [vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp, i64, i64, ci]),
-    "sysml_b200_pcsc_slice_entries": (i64, [i64, ci]),
-    "sysml_b200_csr_to_pcsc": (ci, [vp, vp, vp, vp, i64, i64, i64, ci, vp, vp, vp, vp]),
-    "sysml_b200_matmult_pcsc_vm": (ci, [vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, ci, vp]),
-    "sysml_b200_mmchain_csr_pcsc": (ci, [vp, vp, vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp, i64, i64, ci]),
     "sysml_b200_comm_create": (ci, [vp, ci, ci, i64, pvp, vp]),
     "sysml_b200_comm_connect": (ci, [vp, vp]),
     "sysml_b200_comm_connect_local": (ci, [vp, ci]),

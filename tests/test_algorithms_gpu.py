@@ -70,7 +70,7 @@ def test_l2svm_end_to_end(gctx, sparse):
         assert_equal_matrices(exp_w, w, rel=1e-9, what="l2svm weights (fused=%s)" % fused)
     if sparse:   # t(X) %*% y as a gather over the column-ordered copy: same iterations, same weights, and the same bits twice
         runs = [l2svm(gctx, dX, dY, reg=1.0, tol=0.001, maxiter=20, column_copy=True) for _ in range(2)]
-        assert dX.pcsc is not None and runs[0][1] == exp_it
+        assert dX.colcopy is not None and runs[0][1] == exp_it
         assert_equal_matrices(exp_w, runs[0][0], rel=1e-9, what="l2svm weights (column-ordered copy)")
         assert np.array_equal(runs[0][0], runs[1][0]) and runs[0][2] == runs[1][2]
     assert np.mean(np.sign(X @ w) == Y) > 0.9  # and it separates the classes

@@ -299,50 +299,6 @@ def test_device_csr_generator_matches_cpu_twin(gctx):
         o.free()
 
 
-def _pcsc(gctx, X, panel_rows):
-    """(GPUObject of X as CSR, PCSCPointer) for a host matrix X."""
-    from systemml_b200.gpu_context import PCSCPointer
-    rp, ci, va = O.dense_to_csr(X)
-    d = gctx.csr(rp, ci, va, X.shape)
-    return d, PCSCPointer(gctx, d.csr, X.shape[0], X.shape[1], panel_rows), (rp, ci, va)
-
-
-@pytest.mark.parametrize("n,m,sp,panel", [(5000, 300, 0.03, 512), (4097, 10_000, 0.001, 1024), (1000, 17, 0.4, 64), (70_000, 1000, 0.01, 8192),
-                                          (300, 2000, 0.05, 8192), (2049, 64, 1.0, 256), (100, 33, 0.0, 32)])
-def test_panel_csc_vm_and_mmchain(gctx, n, m, sp, panel):
-    """t(X) %*% y and the three chain types through the column-ordered copy (csrc/pcsc.cu) against the oracle's
-    matrixMultChainSparse / VM (LibMatrixMult.java:1655-1684, 1262-1286): 1e-9 element-wise, and the same bits on
-    every run (no atomics).  Shapes cover several panels, a ragged last panel, empty slices, full columns, nnz = 0."""
-    import ctypes as C
-    X = O.java_test_matrix(n, m, -1, 1, sp, 77) if sp > 0 else np.zeros((n, m))
-    if sp >= 1.0:
-        X[X == 0] = 0.5
-    X[:, m // 2] = np.where(np.arange(n) % 3 == 0, 0.0, 1.5) if sp > 0 else 0.0     # one long column run
-    d, pc, (rp, ci, va) = _pcsc(gctx, X, panel)
-    y = O.rand_uniform(n, seed=5)
-    v = O.rand_uniform(m, seed=6)
-    w = O.rand_uniform(n, seed=7, lo=0.0, hi=1.0)
-    dy, dv, dw = gctx.dense(y.reshape(n, 1)), gctx.dense(v.reshape(m, 1)), gctx.dense(w.reshape(n, 1))
-    out, tmp = gctx.empty(m, 1), gctx.empty(n, 1)
-    p_ = lambda o: C.c_void_p(o.ptr)
-    runs = []
-    for _ in range(2):
-        gctx.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, p_(dy), None, 0, p_(out))
-        runs.append(out.to_host().reshape(-1))
-    assert np.array_equal(runs[0], runs[1]), "t(X) %*% y must be bit-identical run to run"
-    exp = (X.astype(np.longdouble).T @ y.astype(np.longdouble)).astype(np.float64)
-    assert_parity(exp, runs[0], np.abs(X).T @ np.abs(y), n, what="pcsc t(X)y %dx%d" % (n, m))
-    for ct in (0, 1, 2):
-        gctx.call("sysml_b200_mmchain_csr_pcsc", C.c_void_p(d.csr.rowPtr), C.c_void_p(d.csr.colInd), C.c_void_p(d.csr.val), *pc.args(),
-                  pc.panel_rows, p_(dv), p_(dw) if ct else None, p_(tmp), p_(out), n, m, ct)
-        got = out.to_host().reshape(-1)
-        e = O.mmchain_csr(rp, ci, va, X.shape, v, w if ct else None, ct, 1)
-        assert_parity(e, got, abs_terms_mmchain(X, v, w, ct), n + m, what="pcsc mmchain %dx%d ct=%d" % (n, m, ct))
-    pc.deallocate()
-    for o in (d, dy, dv, dw, out, tmp):
-        o.free()
-
-
 @pytest.mark.parametrize("n,m,sp,panel", [(5000, 300, 0.03, 512), (4097, 10_000, 0.001, 1024), (1000, 17, 0.4, 64), (70_000, 1000, 0.01, 8192),
                                           (300, 2000, 0.05, 8192), (2049, 64, 1.0, 256), (100, 33, 0.0, 32), (9000, 40, 0.3, 8192)])
 def test_panelled_sliced_ell_vm_and_mmchain(gctx, n, m, sp, panel):
@@ -416,11 +372,11 @@ def test_gpuobject_builds_the_column_ordered_copy_on_second_use(gctx):
         o = L.matmult(gctx, "ba+*", d, y, isLeftTransposed=True)
         r.append(o.to_host().reshape(-1))
         o.free()
-        assert (d.pcsc is not None) == (i >= 1)
+        assert (d.colcopy is not None) == (i >= 1)
     assert_equal_matrices(r[0], r[1], what="scatter vs gather")
     assert np.array_equal(r[1], r[2]) and np.array_equal(r[2], r[3])
     v = gctx.dense(O.rand_uniform(500, seed=10).reshape(-1, 1))
     q = L.mmchain(gctx, "mmchain", d, v, None, "XtXv")
     assert_equal_matrices(O.mmchain_csr(rp, ci, va, X.shape, O.rand_uniform(500, seed=10), None, 0, 1), q.to_host().reshape(-1))
     d.free()
-    assert d.pcsc is None
+    assert d.colcopy is None

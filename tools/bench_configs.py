@@ -69,17 +69,17 @@ def config_c3(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     ops.append(_op("mmchain XtwXv", a, b, hbm, dmma, nbytes=spb + 8.0 * n + 8.0 * m, flops=4.0 * nnz))
     a, b = _timeit(g, lambda: g.call("sysml_b200_agg_unary_csr", *csr, n, m, 0, 1, _p(o_r)), reps)
     ops.append(_op("rowSums", a, b, hbm, dmma, nbytes=12.0 * nnz + 4.0 * (n + 1) + 8.0 * n))
-    # the same two products through the column-ordered copy (csrc/pcsc.cu): what the iterative algorithms use from the
+    # the same two products through the column-ordered copy (csrc/psell.cu): what the iterative algorithms use from the
     # second iteration on
-    from systemml_b200.gpu_context import PCSCPointer
+    from systemml_b200.gpu_context import PSELLPointer
     g.sync()
     t0 = time.perf_counter()
-    pc = PCSCPointer(g, X.csr, n, m)
+    pc = PSELLPointer(g, X.csr, n, m)
     g.sync()
     build_s = time.perf_counter() - t0
-    a, b = _timeit(g, lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), n, m, pc.panel_rows, _p(y), None, 0, _p(o_c)), reps)
+    a, b = _timeit(g, lambda: pc.vm(y.ptr, o_c.ptr), reps)
     ops.append(_op("t(X)%*%y [column-ordered copy]", a, b, hbm, dmma, nbytes=12.0 * nnz + 8.0 * n + 8.0 * m, flops=2.0 * nnz))
-    a, b = _timeit(g, lambda: g.call("sysml_b200_mmchain_csr_pcsc", *csr, *pc.args(), pc.panel_rows, _p(v), _p(w), _p(o_r), _p(o_c), n, m, 1), reps)
+    a, b = _timeit(g, lambda: pc.mmchain(X.csr, v.ptr, w.ptr, o_r.ptr, o_c.ptr, 1), reps)
     ops.append(_op("mmchain XtwXv [CSR + column-ordered copy]", a, b, hbm, dmma, nbytes=spb + 8.0 * n + 8.0 * m, flops=4.0 * nnz))
     ops[-1]["note"] = "algorithmic bytes as for the one-pass form; this form reads X twice (24 bytes per non-zero) and writes/reads an n-vector"
     pc.deallocate()

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta | spmv rows cols per [mode] | pcsc rows cols per | csrcell rows cols per kind | agg n m op dir"""
+"""Runs ONE op a few times (for ncu captures): python tools/run_op.py tsmm 2000000 1000 | mmchain n m | matmult M K N ta | spmv rows cols per [mode] | psell rows cols per | csrcell rows cols per kind | agg n m op dir"""
 import ctypes as C
 import os
 import sys
@@ -43,13 +43,6 @@ elif op == "spmv":
         fn = lambda: g.call("sysml_b200_matmult_csr_dense", *csr3, p_(y), p_(oc), rows, cols, rows, 1, 1)
     else:
         fn = lambda: g.call("sysml_b200_mmchain_csr", *csr3, p_(v), p_(y), p_(oc), rows, cols, 1)
-elif op == "pcsc":
-    rows, cols, per = a[:3]
-    from systemml_b200.gpu_context import PCSCPointer
-    S = g.rand_csr(rows, cols, per, seed=2)
-    pc = PCSCPointer(g, S.csr, rows, cols)
-    y, oc = g.rand(rows, 1, seed=3), g.empty(cols, 1)
-    fn = lambda: g.call("sysml_b200_matmult_pcsc_vm", *pc.args(), rows, cols, pc.panel_rows, p_(y), None, 0, p_(oc))
 elif op == "psell":
     rows, cols, per = a[:3]
     from systemml_b200.gpu_context import PSELLPointer
