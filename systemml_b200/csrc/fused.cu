@@ -121,9 +121,13 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
 #endif
 #if FUSED_VEC2
   const long long n2 = len >> 1;
-  for (long long i = tid; i < n2; i += stride) {
-    double x[FUSED_NIN + 1], y[FUSED_NIN + 1];
+  // two strides per trip, all loads first: twice the bytes in flight per thread (a 50M-cell vector is a 0.2 ms kernel and
+  // latency-bound otherwise); the additions happen in the order of the one-stride loop, so the sums are the same bits
+  for (long long i = tid; i < n2; i += 2 * stride) {
+    double x[FUSED_NIN + 1], y[FUSED_NIN + 1], xb[FUSED_NIN + 1], yb[FUSED_NIN + 1];
+    const long long ib = i + stride;
     FUSED_LOAD2(i)
+    if (ib < n2) { FUSED_LOAD2B(ib) }
     const double u = fused_eval(x, a.k), w = fused_eval(y, a.k);
 #if FUSED_AGG == 1
     acc.add(u);
@@ -131,6 +135,15 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
 #else
     reinterpret_cast<double2*>(a.out)[i] = make_double2(u, w);
 #endif
+    if (ib < n2) {
+      const double ub = fused_eval(xb, a.k), wb = fused_eval(yb, a.k);
+#if FUSED_AGG == 1
+      acc.add(ub);
+      acc2.add(wb);
+#else
+      reinterpret_cast<double2*>(a.out)[ib] = make_double2(ub, wb);
+#endif
+    }
   }
 #else
   for (long long i = tid; i < len; i += stride) {
@@ -293,15 +306,26 @@ extern "C" __global__ void __launch_bounds__(256, 4) fused_kernel(const FusedArg
   }
 #if FUSED_VEC2
   const long long n2 = len >> 1;
-  for (long long i = tid; i < n2; i += stride) {
-    double x[FUSED_NIN + 1], y[FUSED_NIN + 1], u[FUSED_NOUT], w[FUSED_NOUT];
+  for (long long i = tid; i < n2; i += 2 * stride) {  // two strides per trip, as in the single-result kernel
+    double x[FUSED_NIN + 1], y[FUSED_NIN + 1], xb[FUSED_NIN + 1], yb[FUSED_NIN + 1], u[FUSED_NOUT], w[FUSED_NOUT];
+    const long long ib = i + stride;
     FUSED_LOAD2(i)
+    if (ib < n2) { FUSED_LOAD2B(ib) }
     fused_eval_multi(x, a.k, u);
     fused_eval_multi(y, a.k, w);
 #pragma unroll
     for (int j = 0; j < FUSED_NOUT; j++) {
       acc[j].add(u[j]);
       acc2[j].add(w[j]);
+    }
+    if (ib < n2) {
+      fused_eval_multi(xb, a.k, u);
+      fused_eval_multi(yb, a.k, w);
+#pragma unroll
+      for (int j = 0; j < FUSED_NOUT; j++) {
+        acc[j].add(u[j]);
+        acc2[j].add(w[j]);
+      }
     }
   }
 #else
@@ -689,7 +713,7 @@ static int fused_run(sysml_b200_ctx* ctx, const double* const* inputs, const int
       appendf(src, "#define FUSED_COLS %d\n#define FUSED_RW %d\n#define FUSED_NOUT %d\n", shape == 4 ? (int)cols : 1, shape == 4 ? RW : 1, n_out > 0 ? n_out : 1);
       // per-input loads: matrices stream past L1, broadcast vectors are cached reads
       std::string flat = "#define FUSED_LOAD_FLAT(i) ", rc = "#define FUSED_LOAD_RC(i, r, c) ", rcy = "#define FUSED_LOAD_RC_Y(i, r, c) ",
-                  l2 = "#define FUSED_LOAD2(i) ";
+                  l2 = "#define FUSED_LOAD2(i) ", l2b = "#define FUSED_LOAD2B(i) ";
       for (int i = 0; i < n_inputs; i++) {
         const int kd = input_kinds[i];
         const bool full = kd == SYSML_BCAST_NONE || (kd == SYSML_BCAST_COL && cols == 1) || (kd == SYSML_BCAST_ROW && rows == 1);
@@ -701,8 +725,9 @@ static int fused_run(sysml_b200_ctx* ctx, const double* const* inputs, const int
         else if (kd == SYSML_BCAST_COL) appendf(rcy, "y[%d] = __ldg(a.in[%d] + (r)); ", i, i);
         else appendf(rcy, "y[%d] = __ldg(a.in[%d] + (c)); ", i, i);
         appendf(l2, "{ const double2 v_ = ld_stream2(reinterpret_cast<const double2*>(a.in[%d]) + (i)); x[%d] = v_.x; y[%d] = v_.y; } ", i, i, i);
+        appendf(l2b, "{ const double2 v_ = ld_stream2(reinterpret_cast<const double2*>(a.in[%d]) + (i)); xb[%d] = v_.x; yb[%d] = v_.y; } ", i, i, i);
       }
-      src += flat + "\n" + rc + "\n" + rcy + "\n" + l2 + "\n";
+      src += flat + "\n" + rc + "\n" + rcy + "\n" + l2 + "\n" + l2b + "\n";
       src += kOpsHeaderText;
       src += eval;
       src += kKernelTemplate;

@@ -96,6 +96,19 @@ __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int
     const int begin = __shfl_sync(full, s, 0);
     cursor[w][lane] = FILL ? ((r < a.rows) ? crp[r] : 0) : 0;
     __syncwarp();
+    // the warp's next group of rows is asked into L2 now (one bulk prefetch per array): with ~10 cells per row a lane has
+    // only two loads in flight, and this turns their DRAM latency into L2 latency
+    if (lane == 0 && g + nwarps < groups) {
+      const i64 rn = (g + nwarps) * 32, rl = (rn + 32 < a.rows) ? rn + 32 : a.rows;
+      const i64 kb = a.rp[rn], ke = a.rp[rl];
+      if (ke > kb) {
+        // whole 16-byte pieces inside the arrays: the start rounds down, the end rounds down too (it is only a hint)
+        const i64 c0 = kb & ~(i64)3, c1 = ke & ~(i64)3;
+        const i64 v0 = kb & ~(i64)1, v1 = ke & ~(i64)1;
+        if (c1 > c0) bulk_prefetch_l2(a.ci + c0, (uint32_t)((c1 - c0) * 4));
+        if (v1 > v0) bulk_prefetch_l2(a.va + v0, (uint32_t)((v1 - v0) * 8));
+      }
+    }
     // the next step's cell is loaded before this step's is processed: two loads per lane in flight
     int c_next = 0;
     double x_next = 0.0;
