@@ -277,6 +277,15 @@ int sysml_b200_matmult_csr_csr_sparse(sysml_b200_ctx* ctx, const int32_t* a_rowp
                                       const double* b_val, int64_t a_rows, int64_t a_cols, int64_t b_rows,
                                       int64_t b_cols, int32_t* c_rowptr, int32_t** c_colind, double** c_val,
                                       int64_t* c_nnz);
+/* Ultra-sparse left operand times a dense matrix with a CSR result: LibMatrixMult.matrixMultUltraSparse, left branch
+ * (LibMatrixMult.java:1510-1566; chosen by isUltraSparseMatrixMult :3761-3777, e.g. a selection / permutation matrix times
+ * X): only the rows of A that hold cells produce anything -- one cell selects and scales a row of B, more cells add their
+ * products in ascending k -- and zero results are not stored.  Two-call protocol as for the sparse cellwise operators
+ * below (c_colind == c_val == NULL: symbolic pass). */
+int sysml_b200_matmult_ultra_sparse_left(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind,
+                                         const double* a_val, const double* B, int64_t a_rows, int64_t a_cols,
+                                         int64_t b_cols, int32_t* c_rowptr, int32_t* c_colind, double* c_val,
+                                         int64_t* c_nnz);
 
 /* Sparse-safe cellwise operations whose operand AND result stay CSR: the value function is evaluated at the stored
  * cells only and results that are zero are dropped -- LibMatrixBincell.safeBinaryScalar's SPARSE <- SPARSE branch

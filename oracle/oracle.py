@@ -44,6 +44,8 @@ def lib():
         L.orc_csr_scalar_op.argtypes = [lp, C.c_void_p, C.c_void_p, i64, C.c_double, C.c_int, C.c_int, lp, C.c_void_p, C.c_void_p]
         L.orc_csr_dense_op.restype = i64
         L.orc_csr_dense_op.argtypes = [lp, C.c_void_p, C.c_void_p, i64, i64, dp, C.c_int, C.c_int, lp, C.c_void_p, C.c_void_p]
+        L.orc_matmult_ultra_sparse_left.restype = i64
+        L.orc_matmult_ultra_sparse_left.argtypes = [lp, C.c_void_p, C.c_void_p, dp, i64, i64, lp, C.c_void_p, C.c_void_p]
         L.orc_csr_csr_op.restype = i64
         L.orc_csr_csr_op.argtypes = [lp, C.c_void_p, C.c_void_p, lp, C.c_void_p, C.c_void_p, i64, C.c_int, lp, C.c_void_p, C.c_void_p]
         L.orc_set_num_threads.argtypes = [C.c_int]
@@ -352,6 +354,12 @@ def csr_dense_op(rp, ci, va, rows, cols, B, op):
     """safeBinaryMVSparse (LibMatrixBincell.java:338-440) for a vector B, safeBinaryMMSparseDenseSkip (:765-789) for a matrix."""
     bc = 0 if B.shape == (rows, cols) else (1 if B.shape == (rows, 1) else 2)
     return _csr_two_call(lib().orc_csr_dense_op, rows, rp, _vp(ci), _vp(va), rows, cols, np.ascontiguousarray(B), bc, op)
+
+
+def matmult_ultra_sparse_left(a, B):
+    """LibMatrixMult.matrixMultUltraSparse with an ultra-sparse left operand a = (rp, ci, va) and a dense B: CSR result."""
+    rows, n = len(a[0]) - 1, B.shape[1]
+    return _csr_two_call(lib().orc_matmult_ultra_sparse_left, rows, a[0], _vp(a[1]), _vp(a[2]), np.ascontiguousarray(B), rows, n)
 
 
 def csr_csr_op(a, b, rows, op):

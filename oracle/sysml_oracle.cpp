@@ -1394,4 +1394,37 @@ i64 orc_csr_csr_op(const i64* arp, const int* aci, const double* ava, const i64*
   return c.k;
 }
 
+// LibMatrixMult.matrixMultUltraSparse, left operand ultra-sparse, right operand dense (LMM:1510-1566); the result is sparse.
+// alen == 1: row selection, values appended where b != 0 (recomputeNonZeros / c.append), then scaled in place by aval when
+// it is not 1 (vectMultiplyInPlace); general case: c(i,j) = c(i,j) + aval*b for every non-zero product, k ascending
+// (quickGetValue / quickSetValue: a value that becomes 0 is removed).
+i64 orc_matmult_ultra_sparse_left(const i64* arp, const int* aci, const double* ava, const double* B, i64 m, i64 n, i64* crp, int* cci,
+                                  double* cva) {
+  CsrOut c{crp, cci, cva};
+  crp[0] = 0;
+  std::vector<double> row((size_t)n);
+  for (i64 i = 0; i < m; i++) {
+    const i64 apos = arp[i], alen = arp[i + 1] - arp[i];
+    if (alen == 1) {
+      const double aval = ava[apos];
+      const double* b = B + (i64)aci[apos] * n;
+      for (i64 j = 0; j < n; j++)
+        if (b[j] != 0) c.append((int)j, aval != 1 ? b[j] * aval : b[j]);
+    } else if (alen > 1) {
+      std::fill(row.begin(), row.end(), 0.0);
+      for (i64 k = apos; k < apos + alen; k++) {
+        const double aval = ava[k];
+        const double* b = B + (i64)aci[k] * n;
+        for (i64 j = 0; j < n; j++) {
+          const double cvald = aval * b[j];
+          if (cvald != 0) row[j] = row[j] + cvald;
+        }
+      }
+      for (i64 j = 0; j < n; j++) c.append((int)j, row[j]);
+    }
+    crp[i + 1] = c.k;
+  }
+  return c.k;
+}
+
 }  // extern "C"

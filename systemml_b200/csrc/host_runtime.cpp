@@ -909,6 +909,28 @@ void sysml_b200_ec::processInstruction(const ParsedInstruction& pi) {
         check(sysml_b200_transpose(ctx, V.dense, d, V.rows, V.cols));
         V = View{false, d, nullptr, nullptr, nullptr, V.cols, V.rows};
       };
+      // LibMatrixMult.isUltraSparseMatrixMult (LibMatrixMult.java:3761-3777) -> matrixMultUltraSparse with a sparse result
+      // (:135, 1502-1592).  Taken here for its left branch with a dense right operand and no transpose flags (a selection
+      // or permutation matrix, a few cells, times X); the other forms go through the general kernels, which compute the
+      // same cells in the same order into a dense block.  (The reference's permutation-matrix clause, :3769-3770, needs a scan
+      // of the row lengths and is covered here only as far as the sparsity clauses reach.)
+      if (A.sparse && !B.sparse && !lt && !rt && m2->cols > 1) {
+        const double cells1 = (double)m1->rows * (double)m1->cols;
+        const double spA = cells1 > 0 ? (double)g1->csr_nnz / cells1 : 0.0;
+        const bool us1 = spA < 0.00004 && g1->csr_nnz < 40;       // MatrixBlock.isUltraSparse (MatrixBlock.java:876-885)
+        const bool us1NoNnz = spA < 0.00004;
+        const double spB = sparsityOf(m2);
+        // OptimizerUtils.getMatMultSparsity, worst case (OptimizerUtils.java:985-991)
+        const double outSp = std::min(1.0, spA * (double)m1->cols) * std::min(1.0, spB * (double)m2->rows);
+        const bool ultra = us1 || (us1NoNnz && outSp < 0.0004) ||
+                           (spA < 0.0004 && g1->csr_nnz < 40 && cells1 + (double)m2->rows * (double)m2->cols < (double)m1->rows * (double)m2->cols && outSp < 0.4);
+        if (ultra) {
+          const bool done = sparseCellwise(pi.ops[2].name, rlen, clen, [&](int32_t* rp, int32_t* ci, double* va, i64* nnz) {
+            return sysml_b200_matmult_ultra_sparse_left(ctx, A.rp, A.ci, A.va, B.dense, A.rows, A.cols, B.cols, rp, ci, va, (int64_t*)nnz);
+          });
+          if (done) break;
+        }
+      }
       if (B.sparse && rt) {  // no kernel takes t(B) of a CSR right operand
         transposeCsr(B, g2->csr_nnz);
         rt = false;

@@ -177,6 +177,56 @@ __global__ void spgemm_emit_kernel(const u64* __restrict__ keys, const double* _
   }
 }
 
+// ---------------- ultra-sparse left operand x dense: CSR result ----------------
+// LibMatrixMult.matrixMultUltraSparse, left branch (LibMatrixMult.java:1510-1566): only the rows of A that hold cells produce
+// anything; a row with one cell selects (and scales) a row of B, a longer row adds its products in ascending k, skipping
+// products that are zero; results that are zero are not stored.  A thread looks at one row of A; the rows that hold cells are
+// then taken one after the other by the whole warp, lanes over the columns of B.
+template <bool FILL>
+__global__ void __launch_bounds__(256) us_left_kernel(const int* __restrict__ arp, const int* __restrict__ aci, const double* __restrict__ ava,
+                                                       const double* __restrict__ B, i64 rows, i64 n, int* __restrict__ cnt, const int* __restrict__ crp,
+                                                       int* __restrict__ cci, double* __restrict__ cva) {
+  const int lane = threadIdx.x & 31;
+  const i64 nthreads = (i64)gridDim.x * blockDim.x;
+  for (i64 base = ((i64)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < rows; base += nthreads) {
+    const i64 r = base + lane;
+    int lo = 0, hi = 0;
+    if (r < rows) {
+      lo = arp[r];
+      hi = arp[r + 1];
+      if (!FILL && hi <= lo) cnt[r] = 0;  // (rows with cells get their count from lane 0 below)
+    }
+    unsigned todo = __ballot_sync(0xffffffffu, hi > lo);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int klo = __shfl_sync(0xffffffffu, lo, src), khi = __shfl_sync(0xffffffffu, hi, src);
+      const i64 row = base + src;
+      int written = 0;
+      const int obase = FILL ? crp[row] : 0;
+      for (i64 j0 = 0; j0 < n; j0 += 32) {
+        const i64 j = j0 + lane;
+        double c = 0.0;
+        if (j < n) {
+          for (int k = klo; k < khi; k++) {
+            const double p = __dmul_rn(__ldg(ava + k), __ldg(B + (i64)__ldg(aci + k) * n + j));
+            if (p != 0.0) c = __dadd_rn(c, p);
+          }
+        }
+        const bool keep = (j < n) && (c != 0.0);
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (FILL && keep) {
+          const int pos = obase + written + __popc(m & ((1u << lane) - 1u));
+          cci[pos] = (int)j;
+          cva[pos] = c;
+        }
+        written += __popc(m);
+      }
+      if (!FILL && lane == 0) cnt[row] = written;
+    }
+  }
+}
+
 int exclusive_scan_int(sysml_b200_ctx* ctx, const int* in, int* out, i64 n, void* tmp, size_t tmp_bytes) {
   SYSML_CUDA(ctx, cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in, out, (int)n, ctx->stream));
   return SYSML_OK;
@@ -267,6 +317,48 @@ int sysml_b200_csr_add(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32
   geam_kernel<true><<<grid_for(ctx, rows, 128), 128, 0, ctx->stream>>>(a_rowptr, a_colind, a_val, b_rowptr, b_colind, b_val, alpha, beta,
                                                                        rows, c_rowptr, *c_colind, *c_val);
   SYSML_LAUNCH_CHECK(ctx, "geam_kernel<fill>");
+  return SYSML_OK;
+}
+
+int sysml_b200_matmult_ultra_sparse_left(sysml_b200_ctx* ctx, const int32_t* a_rowptr, const int32_t* a_colind, const double* a_val, const double* B,
+                                         int64_t a_rows, int64_t a_cols, int64_t b_cols, int32_t* c_rowptr, int32_t* c_colind, double* c_val,
+                                         int64_t* c_nnz) {
+  SYSML_ENTER(ctx);
+  if (a_rows < 0 || a_cols < 0 || b_cols < 0 || a_rows >= 0x7fffffffLL || b_cols > 0x7fffffffLL) return sysml_set_error(ctx, SYSML_E_DIM, "matmult_ultra_sparse_left: bad dimensions");
+  if (!c_rowptr || !c_nnz) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_ultra_sparse_left: null c_rowptr / c_nnz");
+  if ((c_colind == nullptr) != (c_val == nullptr)) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_ultra_sparse_left: c_colind and c_val must both be NULL (symbolic pass) or both be set");
+  const bool fill = c_colind != nullptr;
+  if (a_rows == 0 || b_cols == 0 || a_cols == 0) {
+    if (!fill) {
+      SYSML_CUDA(ctx, cudaMemsetAsync(c_rowptr, 0, (size_t)(a_rows + 1) * sizeof(int), ctx->stream));
+      *c_nnz = 0;
+    }
+    return SYSML_OK;
+  }
+  if (!a_rowptr || !B) return sysml_set_error(ctx, SYSML_E_INVALID, "matmult_ultra_sparse_left: null input");
+  const unsigned g = grid_for(ctx, a_rows, 256);
+  if (fill) {
+    us_left_kernel<true><<<g, 256, 0, ctx->stream>>>(a_rowptr, a_colind, a_val, B, a_rows, b_cols, nullptr, c_rowptr, c_colind, c_val);
+    SYSML_LAUNCH_CHECK(ctx, "us_left_kernel<fill>");
+    return SYSML_OK;
+  }
+  size_t scan_bytes = 0;
+  SYSML_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (const int*)nullptr, (int*)nullptr, (int)(a_rows + 1), ctx->stream));
+  void* ws = nullptr;
+  int rc = sysml_workspace(ctx, padded((size_t)(a_rows + 1) * 4) + padded(scan_bytes) + 512, &ws);
+  if (rc) return rc;
+  char* p = (char*)ws;
+  int* cnt = carve<int>(p, a_rows + 1);
+  void* tmp = p;
+  SYSML_CUDA(ctx, cudaMemsetAsync(cnt + a_rows, 0, sizeof(int), ctx->stream));
+  us_left_kernel<false><<<g, 256, 0, ctx->stream>>>(a_rowptr, a_colind, a_val, B, a_rows, b_cols, cnt, nullptr, nullptr, nullptr);
+  SYSML_LAUNCH_CHECK(ctx, "us_left_kernel<count>");
+  rc = exclusive_scan_int(ctx, cnt, c_rowptr, a_rows + 1, tmp, scan_bytes);
+  if (rc) return rc;
+  int nnz = 0;
+  rc = fetch_int(ctx, c_rowptr + a_rows, &nnz);
+  if (rc) return rc;
+  *c_nnz = nnz;
   return SYSML_OK;
 }
 

@@ -461,6 +461,15 @@ def sparseDenseOp(gCtx, instName, in1, in2, op, dense_left=False):
                          _p(in1.csr.val), in1.rows, in1.cols, _p(in2.ptr), bcast, int(op), 1 if dense_left else 0)
 
 
+def ultraSparseMatmult(gCtx, instName, in1, in2):
+    """CSR (ultra-sparse: a selection / permutation matrix, a handful of cells) %*% dense with a CSR result:
+    LibMatrixMult.matrixMultUltraSparse, left branch (LibMatrixMult.java:1510-1566)."""
+    if in1.cols != in2.rows:
+        _dim_error("ultra-sparse %%*%% dense: inner dimensions %d vs %d" % (in1.cols, in2.rows))
+    return _two_pass_csr(gCtx, in1.rows, in2.cols, "sysml_b200_matmult_ultra_sparse_left", _p(in1.csr.rowPtr), _p(in1.csr.colInd),
+                         _p(in1.csr.val), _p(in2.ptr), in1.rows, in1.cols, in2.cols)
+
+
 def sparseSparseOp(gCtx, instName, in1, in2, op):
     """CSR op CSR with a CSR result for operators with 0 op 0 == 0: inner join for Multiply, outer join otherwise
     (LibMatrixBincell.safeBinaryMMSparseSparse / mergeForSparseBinary, LibMatrixBincell.java:597-660, 1279-1340)."""

@@ -63,6 +63,7 @@ SIGNATURES = {
     "sysml_b200_csr_transpose": (ci, [vp, vp, vp, vp, i64, i64, vp, vp, vp]),
     "sysml_b200_csr_add": (ci, [vp, vp, vp, vp, dbl, vp, vp, vp, dbl, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_matmult_csr_csr_sparse": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, vp, vp, vp, pi64]),
+    "sysml_b200_matmult_ultra_sparse_left": (ci, [vp, vp, vp, vp, vp, i64, i64, i64, vp, vp, vp, pi64]),
     "sysml_b200_csr_scalar_op": (ci, [vp, vp, vp, vp, i64, i64, dbl, ci, ci, vp, vp, vp, pi64]),
     "sysml_b200_csr_unary_op": (ci, [vp, vp, vp, vp, i64, i64, ci, vp, vp, vp, pi64]),
     "sysml_b200_csr_dense_op": (ci, [vp, vp, vp, vp, i64, i64, vp, ci, ci, ci, vp, vp, vp, pi64]),

@@ -467,3 +467,27 @@ def test_sparse_operands_stay_sparse_under_sparse_safe_cellwise_instructions(ec)
     assert_equal_matrices(O.matmult_dense(A * cv, v, 4)[0], ec.getMatrix("q"))
     ec.execute(inst("uak+", mat("Z"), scalar_var("s")))
     assert abs(ec.getScalar("s") - O.agg_unary_dense(A * cv, O.SUM, O.ALL)[0]) < 1e-9
+
+
+def test_ultra_sparse_matmult_instruction_gives_a_sparse_result(ec):
+    """ba+* with an ultra-sparse left operand (LibMatrixMult.isUltraSparseMatrixMult, LibMatrixMult.java:3761-3777) keeps the
+    result sparse on the device, as matrixMultUltraSparse does on the CPU; a merely sparse left operand goes through the
+    general kernel into a dense block. Same cells either way."""
+    m, k, n = 200_000, 400, 50
+    P = np.zeros((m, k))
+    P[[5, 77_000, 150_001], [3, 399, 17]] = [1.0, 1.0, -2.5]          # three cells in 80M: a row selection
+    X = O.java_test_matrix(k, n, -1, 1, 0.9, 4)
+    rp, ci, va = O.dense_to_csr(P)
+    ec.setMatrixCSR("P", rp, ci, va, P.shape)
+    ec.setMatrix("X", X)
+    ec.execute(inst("ba+*", mat("P"), mat("X"), mat("Z"), "false", "false"))
+    assert ec.isSparseOnDevice("Z") is True
+    exp = P @ X
+    assert ec.getMatrixDims("Z") == (m, n, int(np.count_nonzero(exp)))
+    assert np.array_equal(ec.getMatrix("Z"), exp)
+    S = O.java_test_matrix(2000, k, -1, 1, 0.05, 6)
+    rp, ci, va = O.dense_to_csr(S)
+    ec.setMatrixCSR("S", rp, ci, va, S.shape)
+    ec.execute(inst("ba+*", mat("S"), mat("X"), mat("Z2"), "false", "false"))
+    assert ec.isSparseOnDevice("Z2") is False
+    assert_equal_matrices(O.matmult_dense(S, X, 4)[0], ec.getMatrix("Z2"))

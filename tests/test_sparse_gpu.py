@@ -380,3 +380,34 @@ def test_gpuobject_builds_the_column_ordered_copy_on_second_use(gctx):
     assert_equal_matrices(O.mmchain_csr(rp, ci, va, X.shape, O.rand_uniform(500, seed=10), None, 0, 1), q.to_host().reshape(-1))
     d.free()
     assert d.colcopy is None
+
+
+@pytest.mark.parametrize("m,k,n", [(5000, 700, 300), (40_000, 64, 33), (1, 50, 1000), (300, 300, 5)])
+def test_ultra_sparse_left_matmult_sparse_result(gctx, m, k, n):
+    """A selection / permutation-like left operand (a handful of cells) times a dense matrix, CSR result, against the oracle's
+    LibMatrixMult.matrixMultUltraSparse (left branch, LibMatrixMult.java:1510-1566): structure and values bit for bit --
+    single-cell rows select and scale a row of B, longer rows add their products in ascending k -- and the same cells as
+    the general CSR x dense kernel."""
+    from systemml_b200 import LibMatrixB200 as L, native
+    rng = np.random.default_rng(5)
+    A = np.zeros((m, k))
+    rows = rng.choice(m, size=min(m, 12), replace=False)
+    for i, r in enumerate(rows):
+        cols = rng.choice(k, size=1 if i % 3 else min(k, 4), replace=False)
+        A[r, cols] = np.where(i % 2, 1.0, rng.uniform(-2, 2, size=len(cols)))
+    B = O.java_test_matrix(k, n, -1, 1, 0.6, 9)
+    B[:, n // 2] = 0.0
+    a = O.dense_to_csr(A)
+    dA, dB = gctx.csr(a[0].astype(np.int32), a[1], a[2], A.shape), gctx.dense(B)
+    got = L.ultraSparseMatmult(gctx, "ba+*", dA, dB)
+    ref = O.matmult_ultra_sparse_left(a, B)
+    rp, ci, va = got.to_host()
+    assert got.csr.nnz == ref[0][-1] and np.array_equal(np.asarray(rp, dtype=np.int64), ref[0])
+    assert np.array_equal(ci[:got.csr.nnz], ref[1]) and np.array_equal(va[:got.csr.nnz], ref[2])
+    dense = L.matmult(gctx, "ba+*", dA, dB).to_host()
+    assert_equal_matrices(dense, _csr_to_dense(rp, ci, va, (m, n)), what="ultra-sparse vs general kernel")
+    # empty left operand, and a dimension error
+    dZ = gctx.csr(np.zeros(m + 1, dtype=np.int32), np.zeros(0, dtype=np.int32), np.zeros(0), A.shape)
+    assert L.ultraSparseMatmult(gctx, "ba+*", dZ, dB).csr.nnz == 0
+    with pytest.raises(native.NativeError):
+        L.ultraSparseMatmult(gctx, "ba+*", dA, gctx.dense(np.zeros((k + 1, n))))
