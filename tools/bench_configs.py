@@ -69,6 +69,19 @@ def config_c3(g, hbm, dmma, scale=1.0, cpu=True, reps=5):
     ops.append(_op("mmchain XtwXv", a, b, hbm, dmma, nbytes=spb + 8.0 * n + 8.0 * m, flops=4.0 * nnz))
     a, b = _timeit(g, lambda: g.call("sysml_b200_agg_unary_csr", *csr, n, m, 0, 1, _p(o_r)), reps)
     ops.append(_op("rowSums", a, b, hbm, dmma, nbytes=12.0 * nnz + 4.0 * (n + 1) + 8.0 * n))
+    # a sparse-safe cellwise operator that keeps X in CSR (csrc/sparse_cellwise.cu): X * y with y a column vector, both passes
+    # (symbolic: sizes; numeric: values) into preallocated arrays
+    c_rp, c_ci, c_va = g.allocate((n + 1) * 4), g.allocate(max(nnz, 1) * 4), g.allocate(max(nnz, 1) * 8)
+    c_nnz = C.c_int64()
+
+    def x_times_colvec():
+        for fill in (False, True):
+            g.call("sysml_b200_csr_dense_op", *csr, n, m, _p(y), 1, L.BINARY_OPS["*"], 0, C.c_void_p(c_rp), C.c_void_p(c_ci) if fill else None,
+                   C.c_void_p(c_va) if fill else None, C.byref(c_nnz))
+    a, b = _timeit(g, x_times_colvec, reps)
+    ops.append(_op("X * y (column vector), CSR result, symbolic + numeric pass", a, b, hbm, dmma, nbytes=2 * (12.0 * nnz + 4.0 * n + 8.0 * n) + 12.0 * nnz + 8.0 * n))
+    for q in (c_rp, c_ci, c_va):
+        g.cudaFreeHelper(q)
     # the same two products through the column-ordered copy (csrc/psell.cu): what the iterative algorithms use from the
     # second iteration on
     from systemml_b200.gpu_context import PSELLPointer
