@@ -38,6 +38,17 @@ HOST_ARRAYS = {
     ("sysml_b200_mem_info", "total_bytes"): "long_out",
     ("sysml_b200_csr_add", "c_nnz"): "long_out",
     ("sysml_b200_matmult_csr_csr_sparse", "c_nnz"): "long_out",
+    ("sysml_b200_matmult_ultra_sparse_left", "c_nnz"): "long_out",
+    ("sysml_b200_csr_scalar_op", "c_nnz"): "long_out",
+    ("sysml_b200_csr_unary_op", "c_nnz"): "long_out",
+    ("sysml_b200_csr_dense_op", "c_nnz"): "long_out",
+    ("sysml_b200_csr_csr_op", "c_nnz"): "long_out",
+    ("sysml_b200_csr_to_psell", "n_slots"): "long_out",
+    ("sysml_b200_csr_to_psell", "n_groups"): "long_out",
+    ("sysml_b200_fused_multi_agg", "inputs"): "long_in",
+    ("sysml_b200_fused_multi_agg", "input_kinds"): "int_in",
+    ("sysml_b200_fused_multi_agg", "consts"): "double_in",
+    ("sysml_b200_fused_multi_agg", "program"): "int_in",
     # generic byte copies: the Java side holds double[] blocks (DenseBlockDRB) -- int[] variants are written by hand below
     ("sysml_b200_binaryblock_write", "h_X"): "double_in",
     ("sysml_b200_h2d", "h_src"): "double_in",
