@@ -19,8 +19,8 @@
 //
 // Kernels: one warp owns 32 consecutive rows and walks their stored cells as ONE contiguous run, 32 cells per
 // step (coalesced 4- and 8-byte loads); a lane finds the row of its cell by a 5-step search over the 32 row
-// starts held one per lane (shuffles), results that survive are ranked inside their row with match_any +
-// ballot, and the per-row write cursors live in shared memory.  Two CSR operands: one thread per row merges
+// starts held one per lane (shuffles), results that survive are ranked inside their row from one ballot of the
+// run starts (rows ascend with the cell index), and the per-row write cursors live in shared memory.  Two CSR operands: one thread per row merges
 // the two sorted runs (rows are ~10 cells at the C3 shape).
 #include <cub/device/device_scan.cuh>
 
@@ -65,7 +65,8 @@ struct CellArgs {
   const double* B;
 };
 
-template <int MODE>
+// OPT: the operator when it is known at compile time (Multiply, by far the most common sparse-safe one: inlined), -1 otherwise
+template <int MODE, int OPT>
 __device__ __forceinline__ double cell_value(const CellArgs& a, double x, i64 row, int col) {
   if (MODE == M_UNARY) return unop_rt(a.op, x);
   double y;
@@ -73,6 +74,7 @@ __device__ __forceinline__ double cell_value(const CellArgs& a, double x, i64 ro
   else if (MODE == M_DENSE) y = a.B[row * a.cols + col];
   else if (MODE == M_COL) y = a.B[row];
   else y = a.B[col];
+  if (OPT == SYSML_OP_MULTIPLY) return __dmul_rn(x, y);
   const bool left = (MODE == M_SCALAR_L) || (MODE >= M_DENSE && a.left);
   return left ? binop_rt(a.op, y, x) : binop_rt(a.op, x, y);
 }
@@ -80,7 +82,7 @@ __device__ __forceinline__ double cell_value(const CellArgs& a, double x, i64 ro
 constexpr int CW_WARPS = 8;
 
 // COUNT: cnt[r] = number of non-zero results in row r.   FILL: results written at crp[r] + rank inside the row.
-template <int MODE, bool FILL>
+template <int MODE, bool FILL, int OPT>
 __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int* __restrict__ cnt, const int* __restrict__ crp,
                                                                   int* __restrict__ cci, double* __restrict__ cva) {
   __shared__ int cursor[CW_WARPS][32];
@@ -133,13 +135,18 @@ __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int
         if (t <= k) j += step;
       }
       double v = 0.0;
-      if (active) v = cell_value<MODE>(a, x, g * 32 + j, c);
+      if (active) v = cell_value<MODE, OPT>(a, x, g * 32 + j, c);
       const bool keep = active && (v != 0.0);  // SparseRow.append drops zeros; NaN is kept
-      const unsigned peers = __match_any_sync(full, active ? j : 32);
-      const unsigned mine = peers & __ballot_sync(full, keep);
+      // the lanes of one row are neighbours (rows ascend with k): a row's run starts where j changes
+      const int jp = __shfl_up_sync(full, j, 1);
+      const unsigned starts = __ballot_sync(full, lane == 0 || jp != j || !active) | 1u;
+      const int first = 31 - __clz(starts & (lt | (1u << lane)));          // first lane of this lane's run
+      const unsigned after = starts & ~(lt | (1u << lane));                // run starts to the right
+      const unsigned run = (after ? ((1u << (__ffs(after) - 1)) - 1u) : full) & ~((1u << first) - 1u);
+      const unsigned mine = run & __ballot_sync(full, keep);
       const int base = active ? cursor[w][j] : 0;
       __syncwarp();
-      if (active && (peers & lt) == 0) cursor[w][j] = base + __popc(mine);  // one leader per row
+      if (active && lane == first) cursor[w][j] = base + __popc(mine);  // one leader per row
       if (FILL && keep) {
         const int pos = base + __popc(mine & lt);
         cci[pos] = c;
@@ -240,8 +247,14 @@ int fetch(sysml_b200_ctx* ctx, void* h, const void* d, size_t bytes) {
 template <int MODE>
 int launch_cell(sysml_b200_ctx* ctx, const CellArgs& a, bool fill, int* cnt, const int* crp, int* cci, double* cva) {
   const unsigned g = grid_for(ctx, (a.rows + 31) / 32, CW_WARPS);
-  if (fill) csr_cell_kernel<MODE, true><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, nullptr, crp, cci, cva);
-  else csr_cell_kernel<MODE, false><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, cnt, nullptr, nullptr, nullptr);
+  const bool mult = MODE != M_UNARY && a.op == SYSML_OP_MULTIPLY;
+  if (fill) {
+    if (mult) csr_cell_kernel<MODE, true, SYSML_OP_MULTIPLY><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, nullptr, crp, cci, cva);
+    else csr_cell_kernel<MODE, true, -1><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, nullptr, crp, cci, cva);
+  } else {
+    if (mult) csr_cell_kernel<MODE, false, SYSML_OP_MULTIPLY><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, cnt, nullptr, nullptr, nullptr);
+    else csr_cell_kernel<MODE, false, -1><<<g, CW_WARPS * 32, 0, ctx->stream>>>(a, cnt, nullptr, nullptr, nullptr);
+  }
   SYSML_LAUNCH_CHECK(ctx, "csr_cell_kernel");
   return SYSML_OK;
 }
