@@ -19,6 +19,15 @@ elif op == "mmchain":
     n, m = a
     X, v, w, o = g.rand(n, m, seed=1), g.rand(m, 1, seed=2), g.rand(n, 1, seed=3, lo=0.0, hi=1.0), g.empty(m, 1)
     fn = lambda: g.call("sysml_b200_mmchain_dense", p_(X), p_(v), p_(w), p_(o), n, m, 1)
+elif op == "mmchain_in_big":  # the same product with X placed inside one allocation of `big_gb` GB (does the size of the ALLOCATION matter?)
+    n, m, big_gb, off_gb = a
+    from systemml_b200.gpu_context import GPUObject
+    base = g.allocate(big_gb << 30)
+    X = GPUObject(g, n, m)
+    X.ptr, X.owns = base + (off_gb << 30), False
+    g.call("sysml_b200_rand_uniform", C.c_void_p(X.ptr), n * m, 1, 0, -1.0, 1.0)
+    v, w, o = g.rand(m, 1, seed=2), g.rand(n, 1, seed=3, lo=0.0, hi=1.0), g.empty(m, 1)
+    fn = lambda: g.call("sysml_b200_mmchain_dense", p_(X), p_(v), p_(w), p_(o), n, m, 1)
 elif op == "matmult":
     M, K, N, ta = a
     if ta:
@@ -92,7 +101,7 @@ elif op == "agg":
     fn = lambda: g.call("sysml_b200_agg_unary_dense", p_(X), n, m, aop, d, p_(o))
 else:
     raise SystemExit("unknown op")
-for _ in range(3):
+for _ in range(5 if op.startswith("mmchain") else 3):
     g.timer_start()
     fn()
     print(op, a, "ms", round(g.timer_stop_ms(), 4))
