@@ -516,6 +516,18 @@ int sysml_b200_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, double* buf
 int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* X,
                                        const double* v, const double* w, double* out, int64_t n,
                                        int64_t m, int chain_type);
+/* mmchain with a row function: out[m] = t(X) %*% f(X %*% v, w, y), X read once.  f is a postfix program of
+ * SYSML_FUSED_TOKENs (as for sysml_b200_fused_cellwise) over three inputs per row -- 0: (X %*% v)[i], 1: w[i], 2: y[i]
+ * (w / y may be NULL when the program does not read them) -- and up to 4 constants; it leaves one value, or two, in which
+ * case the second is written to side_out[i].  Stands in for  ba+* (X %*% v), the cellwise instructions of f, r' and ba+*
+ * (t(X) %*% .)  where the reference's MapMultChain has only the three fixed forms XtXv / XtwXv / XtXvy
+ * (MapMultChain.java:31-32; LibMatrixMult.matrixMultChain, LibMatrixMult.java:243-268) -- e.g. the outer step of GLM.dml
+ * for Poisson / log link: f = y - exp(eta) with exp(eta), the next inner loop's weights, as the second value
+ * (scripts/algorithms/GLM.dml:702-706, 1011-1030).  The program is interpreted once per row (a few dozen instructions
+ * next to the row's kilobytes).  At most 24 tokens, stack depth 8, cols <= 8192 (SYSML_E_UNSUPPORTED above). */
+int sysml_b200_mmchain_rowfn_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w, const double* y,
+                                   const int32_t* program, int n_tokens, const double* consts, int n_consts, int n_results,
+                                   double* side_out, double* out, int64_t n, int64_t m);
 /* One whole conjugate-gradient iteration of LinearRegCG / GLM (scripts/algorithms/LinearRegCG.dml:176-195; inner CG of
  * GLM.dml:1011-1030) on this rank's row shard, in two launches:
  *   q = t(X) %*% (w * (X %*% p))  [chain_type as for mmchain; summed over the ranks of comm unless comm is NULL]

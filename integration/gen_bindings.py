@@ -45,6 +45,8 @@ HOST_ARRAYS = {
     ("sysml_b200_csr_csr_op", "c_nnz"): "long_out",
     ("sysml_b200_csr_to_psell", "n_slots"): "long_out",
     ("sysml_b200_csr_to_psell", "n_groups"): "long_out",
+    ("sysml_b200_mmchain_rowfn_dense", "program"): "int_in",
+    ("sysml_b200_mmchain_rowfn_dense", "consts"): "double_in",
     ("sysml_b200_fused_multi_agg", "inputs"): "long_in",
     ("sysml_b200_fused_multi_agg", "input_kinds"): "int_in",
     ("sysml_b200_fused_multi_agg", "consts"): "double_in",

@@ -93,8 +93,10 @@ def linreg_cg(g, X, y, reg=1e-6, tol=1e-6, maxi=0, comm=None, fused_tail=True, l
     return out, i
 
 
-def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1e-10, comm=None):
+def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1e-10, comm=None, fused_outer=True):
     """Poisson regression with log link by Newton / IRLS; every inner CG step is mmchain XtwXv.
+    fused_outer: the outer step's  eta = X %*% beta; mu = exp(eta); grad = t(X) %*% (y - mu)  as ONE pass over X
+    (mmchain with a row function) instead of two products and two cellwise passes.
     Returns (beta ndarray, list of inner iteration counts)."""
     n, m = X.rows, X.cols
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
@@ -103,10 +105,15 @@ def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1
     g.call("sysml_b200_fill", _p(beta), m, 0.0)
     inner_counts = []
     for _ in range(outer_iters):
-        g.call("sysml_b200_matmult_dense", _p(X), _p(beta), _p(eta), n, m, m, 1, 0, 0)        # eta = X %*% beta
-        g.call("sysml_b200_unary", _p(eta), _p(mu), n, L.UNARY_OPS["exp"])                    # mu = exp(eta) (= weights w)
-        g.call("sysml_b200_binary_mm", _p(y), _p(mu), _p(resid), n, 1, 0, L.BINARY_OPS["-"])  # y - mu
-        g.call("sysml_b200_matmult_dense", _p(X), _p(resid), _p(grad), n, m, n, 1, 1, 0)      # t(X) %*% (y - mu)
+        if fused_outer and m <= 8192:
+            E = L.Expr
+            mu_e = E.input(0).unary("exp")
+            L.mmchainRowFn(g, "mmchain", X, beta, [E.input(1) - mu_e, mu_e], w=y, out=grad, side=mu)  # grad = t(X) %*% (y - exp(X beta)); mu
+        else:
+            g.call("sysml_b200_matmult_dense", _p(X), _p(beta), _p(eta), n, m, m, 1, 0, 0)        # eta = X %*% beta
+            g.call("sysml_b200_unary", _p(eta), _p(mu), n, L.UNARY_OPS["exp"])                    # mu = exp(eta) (= weights w)
+            g.call("sysml_b200_binary_mm", _p(y), _p(mu), _p(resid), n, 1, 0, L.BINARY_OPS["-"])  # y - mu
+            g.call("sysml_b200_matmult_dense", _p(X), _p(resid), _p(grad), n, m, n, 1, 1, 0)      # t(X) %*% (y - mu)
         _allreduce(comm, grad, m)
         if reg:
             g.call("sysml_b200_axpy", _p(grad), _p(beta), -float(reg), _p(grad), m, 1, 0)

@@ -22,6 +22,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "cellwise_rt.cuh"
 
 struct sysml_b200_comm;
 int sysml_launch_finish_exchange(sysml_b200_ctx* ctx, sysml_b200_comm* comm, const double* partial, int P, int m, double* out, int rop,
@@ -29,7 +30,7 @@ int sysml_launch_finish_exchange(sysml_b200_ctx* ctx, sysml_b200_comm* comm, con
 
 namespace {
 
-enum { MODE_CHAIN = 0, MODE_MV = 1, MODE_VM = 2 };
+enum { MODE_CHAIN = 0, MODE_MV = 1, MODE_VM = 2, MODE_FN = 3 };  // FN: a chain whose row function is a postfix program
 
 struct StreamArgs {
   const double* X;
@@ -48,6 +49,10 @@ struct StreamArgs {
   int pdl;                // launch this kernel and its finishing kernel as programmatic dependents of their predecessors
   double *cg_r, *cg_beta, *cg_nr2;  // non-null -> the finishing kernel also applies the CG m-vector tail (v is p, out is q)
   double cg_lambda;
+  // MODE_FN: t[i] = fn(eta[i], w[i], y2[i]); a second result goes to side[i]
+  const double* y2;
+  double* side;
+  sysml_rt::RowProgram fn;
 };
 
 // NTC consumer threads (+32 producer), TC threads cooperate on one row, CPT columns per thread,
@@ -141,7 +146,7 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
     const i64 r0 = tile * R + (i64)g * RG;
 
     double wv[RG];
-    const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv);
+    const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv) || (MODE == MODE_FN && a.w != nullptr);
     if (need_w && !a.w_smem) {
 #pragma unroll
       for (int rr = 0; rr < RG; rr++) wv[rr] = (r0 + rr < n) ? __ldg(a.w + r0 + rr) : 0.0;
@@ -228,6 +233,19 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
       } else if (a.ct == SYSML_CHAIN_XtXvy) {
 #pragma unroll
         for (int rr = 0; rr < RG; rr++) t[rr] -= wv[rr];
+      }
+    } else if (MODE == MODE_FN) {
+      // the row function, once per row (every thread of the row's group evaluates it: no broadcast needed); thread 0 of
+      // the group writes the second result
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) {
+        double in[3], res[2];
+        in[0] = t[rr];
+        in[1] = wv[rr];
+        in[2] = (a.y2 && r0 + rr < n) ? __ldg(a.y2 + r0 + rr) : 0.0;
+        sysml_rt::row_eval(a.fn, in, res);
+        t[rr] = (r0 + rr < n) ? res[0] : 0.0;  // rows past the end are zero-filled in the tile: they must add nothing
+        if (tt == 0 && a.side && r0 + rr < n) a.side[r0 + rr] = res[1];
       }
     } else {
 #pragma unroll
@@ -317,7 +335,7 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   a.total_tiles = (a.n + R - 1) / R;
   const size_t stage_bytes = (size_t)R * a.m * 8;
   a.use_tma = ((reinterpret_cast<uintptr_t>(a.X) & 15) == 0) && (stage_bytes % 16 == 0) && (stage_bytes < (1u << 20));
-  const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv);
+  const bool need_w = MODE == MODE_VM || (MODE == MODE_CHAIN && a.ct != SYSML_CHAIN_XtXv) || (MODE == MODE_FN && a.w != nullptr);
   // narrow rows only: there a tile is consumed in a few hundred cycles and a global load of w sits on its critical
   // path (10M x 100 XtwXv: 1.73 -> 1.18 ms); with 8 KB rows the consumers' own loads are hidden and the extra
   // 32-byte copy per tile costs more than it saves (10M x 1000: 11.2 -> 11.8 ms)
@@ -563,6 +581,43 @@ extern "C" int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b20
   a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = chain_type; a.comm = comm;
   a.pdl = 1;
   return launch_rowstream<MODE_CHAIN>(ctx, a);
+}
+
+// out = t(X) %*% f(X %*% v, w, y) with the row function f given as a postfix program, X read ONCE; a second value left by
+// the program is written to side_out (one per row).  The chain types of mmchain_dense are the programs "in0", "in0 * in1",
+// "in0 - in1"; this is the same kernel with the row function interpreted once per row (cellwise_rt.cuh).
+extern "C" int sysml_b200_mmchain_rowfn_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w, const double* y,
+                                              const int32_t* program, int n_tokens, const double* consts, int n_consts, int n_results,
+                                              double* side_out, double* out, int64_t n, int64_t m) {
+  SYSML_ENTER(ctx);
+  if (n < 0 || m < 0) return sysml_set_error(ctx, SYSML_E_DIM, "mmchain_rowfn: negative dimension (%lld x %lld)", (long long)n, (long long)m);
+  if (!program || (n_consts > 0 && !consts)) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: null program / constants");
+  if (const char* why = sysml_rt::validate(program, n_tokens, 3, n_consts, n_results)) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: %s", why);
+  for (int t = 0; t < n_tokens; t++) {
+    const int kind = (program[t] >> 24) & 0xff, arg = program[t] & 0xffffff;
+    if (kind == SYSML_FUSED_IN && n > 0 && ((arg == 1 && !w) || (arg == 2 && !y)))
+      return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: the program reads input %d, which is null", arg);
+  }
+  if (n_results == 2 && n > 0 && !side_out) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: two results but side_out is null");
+  if (m > 0 && !out) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: out is null");
+  if (m == 0) return SYSML_OK;
+  if (n == 0) {
+    SYSML_CUDA(ctx, cudaMemsetAsync(out, 0, (size_t)m * sizeof(double), ctx->stream));
+    return SYSML_OK;
+  }
+  if (!X || !v) return sysml_set_error(ctx, SYSML_E_INVALID, "mmchain_rowfn: X or v is null");
+  if (m > 8192)
+    return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "mmchain_rowfn: more than 8192 columns: a row no longer fits on chip between the two products; run matmult, the cellwise chain and matmult");
+  StreamArgs a{};
+  a.X = X; a.v = v; a.w = w; a.out = out; a.n = n; a.m = (int)m; a.ct = 0; a.comm = nullptr;
+  a.pdl = 0;
+  a.y2 = y;
+  a.side = n_results == 2 ? side_out : nullptr;
+  a.fn.n_tokens = n_tokens;
+  a.fn.n_results = n_results;
+  for (int t = 0; t < n_tokens; t++) a.fn.tok[t] = program[t];
+  for (int c = 0; c < n_consts; c++) a.fn.k[c] = consts[c];
+  return launch_rowstream<MODE_FN>(ctx, a);
 }
 
 // One conjugate-gradient iteration of LinearRegCG / GLM on this rank's row shard in TWO launches:

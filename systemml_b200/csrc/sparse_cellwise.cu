@@ -25,34 +25,14 @@
 #include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
-#include "cellwise_ops.cuh"
+#include "cellwise_rt.cuh"
 
 namespace {
 
 enum { M_SCALAR_R = 0, M_SCALAR_L = 1, M_UNARY = 2, M_DENSE = 3, M_COL = 4, M_ROW = 5 };
 
-#define SYSML_FOR_ALL_BINOPS(X) \
-  X(0) X(1) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12) X(13) X(14) X(15) X(16) X(17) X(18)
-#define SYSML_FOR_ALL_UNOPS(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6) X(7) X(8) X(9) X(10) X(11) X(12)
-
-__device__ __noinline__ double binop_rt(int op, double x, double y) {
-  switch (op) {
-#define X(o) \
-  case o: return sysml_ops::binop<o>(x, y);
-    SYSML_FOR_ALL_BINOPS(X)
-#undef X
-  }
-  return 0.0;
-}
-__device__ __noinline__ double unop_rt(int op, double x) {
-  switch (op) {
-#define X(o) \
-  case o: return sysml_ops::unop<o>(x);
-    SYSML_FOR_ALL_UNOPS(X)
-#undef X
-  }
-  return 0.0;
-}
+using sysml_rt::binop_rt;
+using sysml_rt::unop_rt;
 
 struct CellArgs {
   const int* rp;

@@ -331,6 +331,35 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     return out
 
 
+def mmchainRowFn(gCtx, instName, X, v, exprs, w=None, y=None, consts=(), out=None, side=None):
+    """out = t(X) %*% f(X %*% v, w, y) in ONE pass over a dense X, f an expression over Expr.input(0) = (X %*% v)[i],
+    input(1) = w[i], input(2) = y[i]; a second expression, if given, is written per row to `side` (n x 1).
+    Generalises MapMultChain's XtXv / XtwXv / XtXvy (MapMultChain.java:31-32) to any row function -- e.g. GLM's outer
+    step. Returns (out, side)."""
+    n, m = X.rows, X.cols
+    if X.isSparse():
+        raise native.NativeError(native.E_UNSUPPORTED, "mmchainRowFn: dense X only")
+    if v.rows * v.cols != m:
+        _dim_error("mmchainRowFn: v has %d cells, X has %d columns" % (v.rows * v.cols, m))
+    for o in (w, y):
+        if o is not None and o.rows * o.cols != n:
+            _dim_error("mmchainRowFn: the row vectors must have %d cells" % n)
+    exprs = list(exprs) if isinstance(exprs, (list, tuple)) else [exprs]
+    tokens = []
+    for e in exprs:
+        tokens += e.tokens if isinstance(e, Expr) else list(e)
+    if out is None:
+        out = GPUObject.allocate_dense(gCtx, m, 1)
+    if len(exprs) == 2 and side is None:
+        side = GPUObject.allocate_dense(gCtx, n, 1)
+    cs = (C.c_double * max(len(consts), 1))(*[float(c) for c in consts])
+    pg = (C.c_int32 * len(tokens))(*tokens)
+    gCtx.call("sysml_b200_mmchain_rowfn_dense", _p(X.ptr), _p(v.ptr), _p(w.ptr) if w is not None else None,
+              _p(y.ptr) if y is not None else None, pg, len(tokens), cs, len(consts), len(exprs),
+              _p(side.ptr) if side is not None else None, _p(out.ptr), n, m)
+    return out, side
+
+
 def fusedMultiAggregate(gCtx, instName, inputs, exprs, consts=(), rows=None, cols=None, out=None):
     """sum(expr_j(inputs)) for every expression in ONE pass over the operands -- the code generator's multi-aggregate
     template (runtime/codegen/SpoofMultiAggregate.java). Returns the sums as a list of floats (one read-back).

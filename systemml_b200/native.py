@@ -68,6 +68,7 @@ SIGNATURES = {
     "sysml_b200_csr_unary_op": (ci, [vp, vp, vp, vp, i64, i64, ci, vp, vp, vp, pi64]),
     "sysml_b200_csr_dense_op": (ci, [vp, vp, vp, vp, i64, i64, vp, ci, ci, ci, vp, vp, vp, pi64]),
     "sysml_b200_csr_csr_op": (ci, [vp, vp, vp, vp, vp, vp, vp, i64, i64, ci, vp, vp, vp, pi64]),
+    "sysml_b200_mmchain_rowfn_dense": (ci, [vp, vp, vp, vp, vp, vp, ci, vp, ci, ci, vp, vp, i64, i64]),
     "sysml_b200_fused_cellwise": (ci, [vp, vp, vp, ci, vp, ci, vp, ci, i64, i64, ci, vp]),
     "sysml_b200_fused_multi_agg": (ci, [vp, vp, vp, ci, vp, ci, vp, ci, i64, i64, ci, vp]),
     "sysml_b200_transpose": (ci, [vp, vp, vp, i64, i64]),

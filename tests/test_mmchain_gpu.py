@@ -196,3 +196,58 @@ def test_full_size_properties_10M_x_1000(gctx):
     assert_equal_matrices(exp, sub.to_host(), what="first 100k rows")
     X.free()
     w.free()
+
+
+@pytest.mark.parametrize("n,m", [(3471, 567), (1000, 1), (257, 4097), (20_000, 1000), (999, 8192), (5, 100), (4099, 64)])
+def test_mmchain_with_a_row_function(gctx, n, m):
+    """sysml_b200_mmchain_rowfn_dense: out = t(X) %*% f(X %*% v, w, y) in one pass, f a postfix program.
+    (1) With f = the three fixed chain types the result is bit for bit mmchain_dense's (same kernel, same order).
+    (2) GLM's outer step for Poisson / log (GLM.dml:702-706): f = y - exp(eta) with mu = exp(eta) as the per-row second
+    result, against the unfused evaluation through the oracle: X %*% v (matrixMultDenseDense), exp, minus (LibMatrixBincell),
+    t(X) %*% . (VM form) -- 1e-9 per cell; mu itself to 1e-13 (CUDA's exp vs the host's).
+    (3) Inputs the program does not read may be NULL; a malformed program or a missing input is refused."""
+    from systemml_b200 import LibMatrixB200 as L, native
+    E = L.Expr
+    X = O.java_test_matrix(n, m, -1, 1, 0.9, 7)
+    v = O.java_test_matrix(m, 1, -0.5, 0.5, 1.0, 3) / max(1.0, np.sqrt(m) / 4)
+    w = O.java_test_matrix(n, 1, 0, 1, 1.0, 10)
+    y = np.floor(O.java_test_matrix(n, 1, 0, 6, 1.0, 11))
+    dX, dv, dw, dy = gctx.dense(X), gctx.dense(v), gctx.dense(w), gctx.dense(y)
+    for ct, prog in (("XtXv", E.input(0)), ("XtwXv", E.input(0) * E.input(1)), ("XtXvy", E.input(0) - E.input(1))):
+        ref = L.mmchain(gctx, "mmchain", dX, dv, dw if ct != "XtXv" else None, ct).to_host()
+        got, _ = L.mmchainRowFn(gctx, "mmchain", dX, dv, prog, w=dw if ct != "XtXv" else None)
+        assert np.array_equal(ref, got.to_host()), ct
+    mu_e = E.input(0).unary("exp")
+    grad, mu = L.mmchainRowFn(gctx, "mmchain", dX, dv, [E.input(2) - mu_e, mu_e], y=dy)
+    eta = O.matmult_dense(X, v, 4)[0]
+    mu_ref = np.exp(eta)
+    np.testing.assert_allclose(mu.to_host(), mu_ref, rtol=1e-13, atol=0)
+    resid = y - mu_ref
+    exp = (X.astype(np.longdouble).T @ resid.astype(np.longdouble)).astype(np.float64)
+    assert_parity(exp.reshape(-1), grad.to_host().reshape(-1), (np.abs(X).T @ np.abs(resid)).reshape(-1), n, what="mmchain rowfn %dx%d" % (n, m))
+    # a constant in the program, both row vectors, one result
+    got, side = L.mmchainRowFn(gctx, "mmchain", dX, dv, (E.input(0) * E.const(0) + E.input(1)) * E.input(2), w=dw, y=dy, consts=(0.25,))
+    assert side is None
+    t = (eta * 0.25 + w) * y
+    exp = (X.astype(np.longdouble).T @ t.astype(np.longdouble)).astype(np.float64)
+    assert_parity(exp.reshape(-1), got.to_host().reshape(-1), (np.abs(X).T @ np.abs(t)).reshape(-1), n, what="mmchain rowfn const %dx%d" % (n, m))
+    with pytest.raises(native.NativeError, match="null"):
+        L.mmchainRowFn(gctx, "mmchain", dX, dv, E.input(0) * E.input(1))          # reads w, which is not given
+    with pytest.raises(native.NativeError):
+        L.mmchainRowFn(gctx, "mmchain", dX, dv, [E.input(0)] * 3)                  # three results
+    with pytest.raises(native.NativeError):
+        L.mmchainRowFn(gctx, "mmchain", dX, gctx.dense(np.zeros((m + 1, 1))), E.input(0))
+
+
+def test_mmchain_row_function_limits(gctx):
+    from systemml_b200 import LibMatrixB200 as L, native
+    E = L.Expr
+    dX, dv = gctx.dense(np.ones((4, 8200))), gctx.dense(np.ones((8200, 1)))
+    with pytest.raises(native.NativeError, match="8192"):
+        L.mmchainRowFn(gctx, "mmchain", dX, dv, E.input(0))
+    # log of a zero-filled padding row must not leak: n = 5 rows in tiles of 4 or more
+    X = O.java_test_matrix(5, 40, 0.5, 1, 1.0, 2)
+    v = np.ones((40, 1))
+    got, _ = L.mmchainRowFn(gctx, "mmchain", gctx.dense(X), gctx.dense(v), E.input(0).unary("log"))
+    exp = X.T @ np.log(X @ v)
+    np.testing.assert_allclose(got.to_host(), exp, rtol=1e-12)
