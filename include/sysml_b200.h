@@ -524,7 +524,7 @@ int sysml_b200_mmchain_dense_allreduce(sysml_b200_ctx* ctx, sysml_b200_comm* com
  * (MapMultChain.java:31-32; LibMatrixMult.matrixMultChain, LibMatrixMult.java:243-268) -- e.g. the outer step of GLM.dml
  * for Poisson / log link: f = y - exp(eta) with exp(eta), the next inner loop's weights, as the second value
  * (scripts/algorithms/GLM.dml:702-706, 1011-1030).  The program is interpreted once per row (a few dozen instructions
- * next to the row's kilobytes).  At most 24 tokens, stack depth 8, cols <= 8192 (SYSML_E_UNSUPPORTED above). */
+ * next to the row's kilobytes).  At most 24 tokens, stack depth 6, cols <= 8192 (SYSML_E_UNSUPPORTED above). */
 int sysml_b200_mmchain_rowfn_dense(sysml_b200_ctx* ctx, const double* X, const double* v, const double* w, const double* y,
                                    const int32_t* program, int n_tokens, const double* consts, int n_consts, int n_results,
                                    double* side_out, double* out, int64_t n, int64_t m);

@@ -33,7 +33,7 @@ static __device__ __noinline__ double unop_rt(int op, double x) {
   return 0.0;
 }
 
-// a validated postfix program (host side: sysml_rt_validate below), at most 24 tokens, stack depth at most 8
+// a validated postfix program (host side: validate below), at most 24 tokens, stack depth at most 6
 struct RowProgram {
   int n_tokens;
   int n_results;  // values left on the stack: 1 or 2
@@ -41,32 +41,49 @@ struct RowProgram {
   double k[4];
 };
 
-// in[0..2]: the row's inputs; res[0..n_results-1]: the values the program leaves (result 0 deepest)
-static __device__ __noinline__ void row_eval(const RowProgram& f, const double* in, double* res) {
-  double st[8];
-  int sp = 0;
+// in0..in2: the row's inputs; r0 (and r1 when the program leaves two values; result 0 is the deeper one).
+// One thread runs this per row on the critical path of its tile, so it is written for latency: the stack is six
+// registers that shift (no local memory), the operators are inlined switches, the tokens come from the kernel's
+// constant bank.
+static __device__ __forceinline__ void row_eval(const RowProgram& f, double in0, double in1, double in2, double& r0, double& r1) {
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, s4 = 0.0, s5 = 0.0;  // s0 = top of stack
   for (int t = 0; t < f.n_tokens; t++) {
-    const int kind = (f.tok[t] >> 24) & 0xff, arg = f.tok[t] & 0xffffff;
-    switch (kind) {
-      case SYSML_FUSED_IN: st[sp++] = in[arg]; break;
-      case SYSML_FUSED_CONST: st[sp++] = f.k[arg]; break;
-      case SYSML_FUSED_BINARY:
-        st[sp - 2] = binop_rt(arg, st[sp - 2], st[sp - 1]);
-        sp--;
-        break;
-      case SYSML_FUSED_UNARY: st[sp - 1] = unop_rt(arg, st[sp - 1]); break;
-      case SYSML_FUSED_PICK:
-        st[sp] = st[sp - 1 - arg];
-        sp++;
-        break;
-      case SYSML_FUSED_NIP:
-        st[sp - 2] = st[sp - 1];
-        sp--;
-        break;
+    const int tk = f.tok[t];
+    const int kind = (tk >> 24) & 0xff, arg = tk & 0xffffff;
+    if (kind == SYSML_FUSED_BINARY) {
+      double v;
+      switch (arg) {
+#define X(o) \
+  case o: v = sysml_ops::binop<o>(s1, s0); break;
+        SYSML_RT_ALL_BINOPS(X)
+#undef X
+        default: v = 0.0;
+      }
+      s0 = v; s1 = s2; s2 = s3; s3 = s4; s4 = s5;
+    } else if (kind == SYSML_FUSED_UNARY) {
+      switch (arg) {
+#define X(o) \
+  case o: s0 = sysml_ops::unop<o>(s0); break;
+        SYSML_RT_ALL_UNOPS(X)
+#undef X
+      }
+    } else if (kind == SYSML_FUSED_NIP) {
+      s1 = s2; s2 = s3; s3 = s4; s4 = s5;
+    } else {
+      double v;
+      if (kind == SYSML_FUSED_IN) v = arg == 0 ? in0 : (arg == 1 ? in1 : in2);
+      else if (kind == SYSML_FUSED_CONST) v = f.k[arg];
+      else v = arg == 0 ? s0 : (arg == 1 ? s1 : (arg == 2 ? s2 : (arg == 3 ? s3 : (arg == 4 ? s4 : s5))));  // PICK
+      s5 = s4; s4 = s3; s3 = s2; s2 = s1; s1 = s0; s0 = v;
     }
   }
-  res[0] = st[0];
-  if (f.n_results > 1) res[1] = st[1];
+  if (f.n_results > 1) {
+    r0 = s1;
+    r1 = s0;
+  } else {
+    r0 = s0;
+    r1 = 0.0;
+  }
 }
 
 // host: checks a program against the interpreter's limits; returns nullptr or what is wrong with it
@@ -105,7 +122,7 @@ static inline const char* validate(const int32_t* prog, int n_tokens, int n_inpu
         break;
       default: return "unknown token kind";
     }
-    if (sp > 8) return "stack deeper than 8";
+    if (sp > 6) return "stack deeper than 6";
   }
   if (sp != n_results) return "program must leave exactly one value per result on the stack";
   return nullptr;

@@ -69,7 +69,9 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
   uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw);
   uint64_t* empty = full + STAGES;
   double* red = reinterpret_cast<double*>(smem_raw + 128);          // [2][G][NWG][RG]
-  double* tiles = reinterpret_cast<double*>(smem_raw + 128 + 2 * G * NWG * RG * 8 + 0);
+  constexpr int FNB = (MODE == MODE_FN) ? 2 * G * RG * 8 : 0;       // MODE_FN: [2][G][RG] results of the row function
+  double* fnbuf = red + 2 * G * NWG * RG;
+  double* tiles = reinterpret_cast<double*>(smem_raw + 128 + 2 * G * NWG * RG * 8 + FNB);
   // tiles must be 16B aligned: 128 + multiple of 16 (2*G*NWG*RG*8 is a multiple of 16)
   const int tid = threadIdx.x;
   const int m = a.m;
@@ -235,18 +237,25 @@ __global__ void __launch_bounds__(NTC + 32) rowstream_kernel(const StreamArgs a)
         for (int rr = 0; rr < RG; rr++) t[rr] -= wv[rr];
       }
     } else if (MODE == MODE_FN) {
-      // the row function, once per row (every thread of the row's group evaluates it: no broadcast needed); thread 0 of
-      // the group writes the second result
+      // the row function, ONCE per row: thread rr of the group evaluates row rr (it sits on the tile's critical path), the group picks the
+      // results up from shared memory after a barrier of its own
+      double* fb = fnbuf + ((size_t)(it & 1) * G + g) * RG;
+      if (tt < RG) {  // threads 0 .. RG-1 of the group: one row each, side by side (one pass through the interpreter)
+        double e_in = t[0], w_in = wv[0];
 #pragma unroll
-      for (int rr = 0; rr < RG; rr++) {
-        double in[3], res[2];
-        in[0] = t[rr];
-        in[1] = wv[rr];
-        in[2] = (a.y2 && r0 + rr < n) ? __ldg(a.y2 + r0 + rr) : 0.0;
-        sysml_rt::row_eval(a.fn, in, res);
-        t[rr] = (r0 + rr < n) ? res[0] : 0.0;  // rows past the end are zero-filled in the tile: they must add nothing
-        if (tt == 0 && a.side && r0 + rr < n) a.side[r0 + rr] = res[1];
+        for (int rr = 1; rr < RG; rr++) {
+          e_in = (tt == rr) ? t[rr] : e_in;
+          w_in = (tt == rr) ? wv[rr] : w_in;
+        }
+        const bool live = r0 + tt < n;
+        double res0, res1;
+        sysml_rt::row_eval(a.fn, e_in, w_in, (a.y2 && live) ? __ldg(a.y2 + r0 + tt) : 0.0, res0, res1);
+        fb[tt] = live ? res0 : 0.0;  // rows past the end are zero-filled in the tile: they must add nothing
+        if (a.side && live) a.side[r0 + tt] = res1;
       }
+      named_bar_sync(1 + g, TC);
+#pragma unroll
+      for (int rr = 0; rr < RG; rr++) t[rr] = fb[rr];
     } else {
 #pragma unroll
       for (int rr = 0; rr < RG; rr++) t[rr] = wv[rr];
@@ -329,7 +338,7 @@ int launch_cfg(sysml_b200_ctx* ctx, StreamArgs a, int ctas_per_sm) {
   constexpr int R = G * RG;
   constexpr int NWG = TC / 32;
   auto kern = rowstream_kernel<MODE, NTC, TC, CPT, RG, STAGES, XSMEM>;
-  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8;
+  const size_t smem = 128 + 2 * G * NWG * RG * 8 + (MODE == MODE_FN ? 2 * G * RG * 8 : 0) + (size_t)STAGES * R * a.m * 8 + (size_t)STAGES * R * 8;
   if (smem > (size_t)ctx->max_smem_optin) return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "rowstream: smem %zu too large", smem);
   SYSML_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   a.total_tiles = (a.n + R - 1) / R;
