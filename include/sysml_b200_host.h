@@ -87,6 +87,12 @@ int sysml_b200_ec_set_eviction_policy(sysml_b200_ec* ec, const char* policy);
 /* MatrixBlock.evalSparseFormatInMemory(rows, cols, nnz) (MatrixBlock.java:1001-1015): 1 when a block with that many
  * non-zeros is kept in sparse format, 0 when dense.  Pure host arithmetic, no context needed. */
 int sysml_b200_eval_sparse_format_in_memory(int64_t rows, int64_t cols, int64_t nnz);
+/* The rule by which a cellwise instruction keeps a CSR operand CSR (pure host logic, no device needed): kind 0 = matrix op
+ * scalar (ScalarOperator.java:53-59, 84-89; RightScalarOperator.java:42-49; LeftScalarOperator.java:41-46 -- except that
+ * Power with a negative constant, which the reference lists although 0^c is infinite, takes the dense form here),
+ * kind 1 = matrix op matrix (BinaryOperator.java:60-66), kind 2 = unary builtin (UnaryOperator.java:38-47).
+ * opcode as in the instruction string ("*", "/", "^2", "max", "sqrt", ...).  Returns 1 / 0, or -1 for a bad kind. */
+int sysml_b200_cellwise_sparse_safe(const char* opcode, int kind, double constant, int scalar_left);
 /* MatrixBlock.examSparsity on the host copy of a variable (fetched from the device first when that copy is the
  * valid one), as LibMatrixMult applies it to every matmult result (LibMatrixMult.java:113,149,168,225): the block
  * is rewritten as CSR when evalSparseFormatInMemory says so.  *is_sparse receives the resulting format; the exact

@@ -1369,6 +1369,17 @@ int sysml_b200_ec_set_eviction_policy(sysml_b200_ec* ec, const char* policy) {
   })
 }
 
+int sysml_b200_cellwise_sparse_safe(const char* opcode, int kind, double constant, int scalar_left) {
+  if (!opcode) return -1;
+  const std::string o = opcode;
+  switch (kind) {
+    case 0: return scalarSparseSafe(o, constant, scalar_left != 0) ? 1 : 0;
+    case 1: return binarySparseSafe(o) ? 1 : 0;
+    case 2: return unarySparseSafe(o) ? 1 : 0;
+  }
+  return -1;
+}
+
 int sysml_b200_eval_sparse_format_in_memory(int64_t rows, int64_t cols, int64_t nnz) {
   return evalSparseFormatInMemory(rows, cols, nnz) ? 1 : 0;
 }

@@ -112,6 +112,7 @@ SIGNATURES = {
     "sysml_b200_ec_stats": (ci, [vp, pi64]),
     "sysml_b200_ec_set_eviction_policy": (ci, [vp, C.c_char_p]),
     "sysml_b200_eval_sparse_format_in_memory": (ci, [i64, i64, i64]),
+    "sysml_b200_cellwise_sparse_safe": (ci, [C.c_char_p, ci, dbl, ci]),
     "sysml_b200_ec_exam_sparsity": (ci, [vp, C.c_char_p, pint]),
     "sysml_b200_ec_is_sparse_on_device": (ci, [vp, C.c_char_p, pint]),
 }

@@ -58,3 +58,47 @@ def test_eval_sparse_format_in_memory_known_answers():
     assert ev(100, 4, 40) is False               # sp 0.1: 84 + 800 + 40*124 = 5844 > 3244
     assert ev(10, 1000, 100) is True             # sp 0.01: cnnz 10, rlen 10: 84 + 80 + 10*196 = 2124 < 80044
     assert ev(0, 10, 0) is False
+
+
+# ---- which cellwise instructions keep a CSR operand CSR: hand-derived from the constructors of ScalarOperator
+# (J/runtime/matrix/operators/ScalarOperator.java:53-59, isSparseSafeStatic :84-89), RightScalarOperator (:42-49),
+# LeftScalarOperator (:41-46), BinaryOperator (:60-66), UnaryOperator (:38-47) -- not produced by running anything ----
+SCALAR_RULES = [
+    # opcode, constant, scalar on the left?, sparse-safe?
+    ("*", 3.0, False, True), ("*", 0.0, True, True), ("*2", 2.0, False, True), ("^2", 2.0, False, True), ("&&", 1.0, False, True),
+    ("-nz", 5.0, False, True),
+    ("!=", 0.0, False, True), ("!=", 1.0, False, False), ("==", 2.0, False, True), ("==", 0.0, False, False),
+    ("-", 0.0, False, True), ("-", 1.0, False, False), ("+", 0.0, False, False),          # Plus is not in the list, even with 0
+    ("max", 0.0, False, True), ("max", -1.0, True, True), ("max", 0.5, False, False),
+    ("min", 0.0, False, True), ("min", 2.0, True, True), ("min", -0.5, False, False),
+    (">", 0.0, False, True), (">", 1.0, False, True), (">", -1.0, False, False),              # X > c is 0 at 0 iff c >= 0
+    (">=", 1.0, False, True), (">=", 0.0, False, False),
+    ("<", 0.0, False, True), ("<", -1.0, False, True), ("<", 1.0, False, False),
+    ("<=", -1.0, False, True), ("<=", 0.0, False, False),
+    ("/", 2.0, False, True), ("/", 0.0, False, False), ("/", 2.0, True, False),               # c / X is infinite at 0
+    ("^", 2.0, False, True), ("^", 0.0, False, False),
+    ("^", -1.0, False, False),    # the reference says true (RightScalarOperator.java:47, "Power && cst != 0"); 0^-1 is Inf: dense here
+    (">", 0.0, True, True), (">", -1.0, True, True), (">", 1.0, True, False),                 # c > X at X = 0
+    (">=", -1.0, True, True), (">=", 0.0, True, False),
+    ("<", 0.0, True, True), ("<", 1.0, True, True), ("<", -1.0, True, False),
+    ("<=", 1.0, True, True), ("<=", 0.0, True, False),
+    ("%%", 3.0, False, False), ("%/%", 3.0, False, False), ("1-*", 0.0, False, False), ("||", 0.0, False, False),
+]
+
+
+@pytest.mark.parametrize("opcode,c,left,exp", SCALAR_RULES)
+def test_scalar_sparse_safety_rule(opcode, c, left, exp):
+    from systemml_b200 import native
+    assert native.load().sysml_b200_cellwise_sparse_safe(opcode.encode(), 0, float(c), int(left)) == int(exp)
+
+
+def test_binary_and_unary_sparse_safety_rules():
+    from systemml_b200 import native
+    lib = native.load()
+    safe2 = {"+", "-", "*", "&&", "||"}          # BinaryOperator: Plus, Multiply, Minus, And, Or (+*/-* take the axpy path)
+    for o in ("+", "-", "*", "/", "^", "<", "<=", ">", ">=", "==", "!=", "min", "max", "&&", "||", "1-*", "-nz", "%%", "%/%"):
+        assert lib.sysml_b200_cellwise_sparse_safe(o.encode(), 1, 0.0, 0) == int(o in safe2), o
+    safe1 = {"sin", "tan", "tanh", "round", "abs", "sqrt", "sign"}   # UnaryOperator: SIN TAN (SINH) TANH ROUND ABS SQRT (SPROP LOG_NZ) SIGN
+    for o in ("exp", "log", "abs", "sqrt", "round", "floor", "ceil", "sin", "cos", "tan", "tanh", "sign", "sigmoid"):
+        assert lib.sysml_b200_cellwise_sparse_safe(o.encode(), 2, 0.0, 0) == int(o in safe1), o
+    assert lib.sysml_b200_cellwise_sparse_safe(b"*", 7, 0.0, 0) == -1
