@@ -139,6 +139,19 @@ __global__ void __launch_bounds__(CW_WARPS * 32) csr_cell_kernel(CellArgs a, int
   }
 }
 
+// Numeric pass when the symbolic pass found that nothing is dropped (the usual case: X * 0.5, abs(X), X * row vector without
+// zeros): the result has the operand's structure, so the cells are independent of their rows -- one flat, fully coalesced
+// pass that copies the column indices and writes the values.  (Modes that need the row of a cell keep the row walk.)
+template <int MODE, int OPT>
+__global__ void __launch_bounds__(256) csr_cell_flat_kernel(CellArgs a, i64 nnz, int* __restrict__ cci, double* __restrict__ cva) {
+  const i64 stride = (i64)gridDim.x * blockDim.x;
+  for (i64 k = (i64)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+    const int c = a.ci[k];
+    cci[k] = c;
+    cva[k] = cell_value<MODE, OPT>(a, ldg_stream(a.va + k), 0, c);
+  }
+}
+
 // two CSR operands: sorted merge per row.  Multiply: inner join (mergeForSparseBinary :1282-1296); every other
 // operator: outer join with op(a,0) / op(0,b) at the cells only one side stores (:1298-1321)
 template <bool FILL>
@@ -303,7 +316,36 @@ int run_cell(sysml_b200_ctx* ctx, const char* who, int mode, const CellArgs& a, 
     }
     return SYSML_OK;
   }
-  if (fill) return launch_cell_mode(ctx, mode, a, true, nullptr, c_rowptr, c_colind, c_val);
+  if (fill) {
+    if (mode == M_SCALAR_R || mode == M_SCALAR_L || mode == M_UNARY || mode == M_ROW) {
+      // same number of cells in the result as in the operand <=> every row kept all of its cells
+      int na = 0, nc = 0;
+      int rc = fetch(ctx, &na, a.rp + a.rows, sizeof(int));
+      if (rc) return rc;
+      rc = fetch(ctx, &nc, c_rowptr + a.rows, sizeof(int));
+      if (rc) return rc;
+      if (na == nc) {
+        if (na == 0) return SYSML_OK;
+        const unsigned g = grid_for(ctx, na, 256 * 4);
+        const bool mult = mode != M_UNARY && a.op == SYSML_OP_MULTIPLY;
+#define FLAT(M)                                                                                                              \
+  case M:                                                                                                                    \
+    if (mult) csr_cell_flat_kernel<M, SYSML_OP_MULTIPLY><<<g, 256, 0, ctx->stream>>>(a, (i64)na, c_colind, c_val);          \
+    else csr_cell_flat_kernel<M, -1><<<g, 256, 0, ctx->stream>>>(a, (i64)na, c_colind, c_val);                              \
+    break;
+        switch (mode) {
+          FLAT(M_SCALAR_R)
+          FLAT(M_SCALAR_L)
+          FLAT(M_UNARY)
+          FLAT(M_ROW)
+        }
+#undef FLAT
+        SYSML_LAUNCH_CHECK(ctx, "csr_cell_flat_kernel");
+        return SYSML_OK;
+      }
+    }
+    return launch_cell_mode(ctx, mode, a, true, nullptr, c_rowptr, c_colind, c_val);
+  }
   Scratch s;
   int rc = get_scratch(ctx, a.rows, &s);
   if (rc) return rc;
