@@ -413,8 +413,9 @@ int sysml_b200_csr_dense_op(sysml_b200_ctx* ctx, const int32_t* rowptr, const in
   if (rows > 0 && cols > 0 && !B) return sysml_set_error(ctx, SYSML_E_INVALID, "csr_dense_op: null dense operand");
   // a full dense operand: the reference's sparse result comes from safeBinaryMMSparseDenseSkip (stored cells only), which it
   // takes for Multiply and for Divide by an operand without zeros; And gives the same cells under safeBinaryMMGeneric
-  if (bcast == SYSML_BCAST_NONE && op != SYSML_OP_MULTIPLY && op != SYSML_OP_DIVIDE && op != SYSML_OP_AND)
-    return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "csr_dense_op: operator %d has no sparse form against a dense matrix: use the dense form", op);
+  if (bcast == SYSML_BCAST_NONE && op != SYSML_OP_MULTIPLY && op != SYSML_OP_AND && !(op == SYSML_OP_DIVIDE && !dense_left))
+    return sysml_set_error(ctx, SYSML_E_UNSUPPORTED, "csr_dense_op: operator %d has no sparse form against a dense matrix%s: use the dense form", op,
+                           dense_left ? " on its left" : "");
   CellArgs a{rowptr, colind, val, rows, cols, op, dense_left ? 1 : 0, 0.0, B};
   return run_cell(ctx, "csr_dense_op", bcast == SYSML_BCAST_NONE ? M_DENSE : (bcast == SYSML_BCAST_COL ? M_COL : M_ROW), a, c_rowptr, c_colind,
                   c_val, c_nnz);

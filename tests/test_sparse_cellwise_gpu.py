@@ -106,6 +106,8 @@ def test_csr_op_dense_operand(gctx, rows, cols, sp):
     # dense on the left (commutes for Multiply; the reference's skip path takes either side, LibMatrixBincell.java:766-770)
     got = L.sparseDenseOp(gctx, "*", dA, gctx.dense(holes), OPS["*"], dense_left=True)
     assert np.array_equal(_dense_of(got.to_host(), A.shape), holes * A + 0.0)
+    with pytest.raises(native.NativeError, match="sparse"):       # dense / CSR divides by the cells that are not stored
+        L.sparseDenseOp(gctx, "/", dA, gctx.dense(full), OPS["/"], dense_left=True)
     # not sparse-safe for this operand: the reference would fill the cells the rows do not store
     bad = [("+", col), ("-", row), ("||", row), ("max", np.abs(col)), ("+", full), ("%%", full)]
     if np.any(col == 0):
