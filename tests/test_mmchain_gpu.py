@@ -198,7 +198,8 @@ def test_full_size_properties_10M_x_1000(gctx):
     w.free()
 
 
-@pytest.mark.parametrize("n,m", [(3471, 567), (1000, 1), (257, 4097), (20_000, 1000), (999, 8192), (5, 100), (4099, 64)])
+@pytest.mark.parametrize("n,m", [(3471, 567), (1000, 1), (257, 4097), (20_000, 1000), (999, 8192), (5, 100), (4099, 64), (501, 2000), (303, 3000),
+                                 (2001, 200), (130, 5601)])
 def test_mmchain_with_a_row_function(gctx, n, m):
     """sysml_b200_mmchain_rowfn_dense: out = t(X) %*% f(X %*% v, w, y) in one pass, f a postfix program.
     (1) With f = the three fixed chain types the result is bit for bit mmchain_dense's (same kernel, same order).
