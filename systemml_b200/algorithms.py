@@ -260,7 +260,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
     return res, it, obj
 
 
-def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
+def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log, comm=None):
     """The same iterations with the whole step in one pass over X (sysml_b200_kmeans_step, csrc/kmeans.cu): distances on the
     FP64 tensor cores, row minimum with the script's tie rule, centroid sums, counts and sum(minD) -- D, minD and P never
     exist in memory.  The k x m algebra around it (rowSums(C^2), the division by the counts) stays as instructions."""
@@ -269,6 +269,7 @@ def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
     Cc, Cn, c2, den, s1 = alloc(k, m), alloc(k, m), alloc(k, 1), alloc(k, 1), alloc(1, 1)
     g.call("sysml_b200_d2d", _p(Cc), _p(C0), 8 * k * m)
     g.call("sysml_b200_agg_unary_dense", _p(X), n, m, L.AGG_SUMSQ, L.DIR_ALL, _p(s1))
+    _allreduce(comm, s1, 1)           # X row-sharded over the ranks of comm: every n-sum is a local sum + one exchange
     sumXsq = _scalar(g, s1)
     wcss, it, term = float("inf"), 0, 0
     while term == 0:
@@ -279,6 +280,9 @@ def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
             for o in (Cc, Cn, c2, den, s1):
                 o.free()
             raise
+        _allreduce(comm, Cn, k * m)   # t(P) %*% X: k x m doubles (40 KB at C5)
+        _allreduce(comm, den, k)      # colSums(P)
+        _allreduce(comm, s1, 1)       # sum(minD)
         wcss_old, wcss = wcss, sumXsq + _scalar(g, s1)
         g.call("sysml_b200_binary_mm", _p(Cn), _p(den), _p(Cn), k, m, L.BCAST_COL, L.BINARY_OPS["/"])  # / t(P_denom)
         it += 1
@@ -298,18 +302,22 @@ def _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log):
     return out, it, wcss, term
 
 
-def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None):
+def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None, comm=None):
     """One run of the Lloyd iterations of scripts/algorithms/Kmeans.dml:130-176 from given initial centroids
     (BASELINE config C5: X 10M x 100, k = 50).  X: GPUObject n x m dense, C0: GPUObject k x m.
     Per iteration: D = -2*(X %*% t(C)) + t(rowSums(C^2)); minD = rowMins(D); P = (D <= minD) / rowSums(D <= minD);
     C_new = (t(P) %*% X) / t(colSums(P)).  Returns (C ndarray, iterations, wcss, termination code 1/2/3).
     fused: True = the one-pass step kernel when the shape fits it, else the fused cellwise chains; "chains" = the chains;
-    False = one launch per operator (the reference's plan); "step" = the one-pass kernel or an error."""
+    False = one launch per operator (the reference's plan); "step" = the one-pass kernel or an error.
+    comm: X is this rank's row shard; the k x m sums, the k counts and sum(minD) are exchanged once per iteration
+    (t(P) %*% X "yes -- one exchange"); every rank returns the same centroids. One-pass plan only."""
     n, m, k = X.rows, X.cols, C0.rows
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
+    if comm is not None:
+        fused = "step"
     if fused == "step":
-        return _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log)
+        return _kmeans_lloyd_one_pass(g, X, C0, max_iter, eps, log, comm)
     if fused is True:
         from . import native
         try:

@@ -86,6 +86,14 @@ def _worker(rank, world, port, n, m, out_dir):
     g.call("sysml_b200_unary", C.c_void_p(ya.ptr), C.c_void_p(ya.ptr), a1 - a0, 0)      # y = exp(X b): noiseless Poisson means
     gb, inner = glm_poisson_log(g, Xa, ya, reg=0.0, outer_iters=4, inner_iters=20, inner_tol=1e-8, comm=comm)
     res["glm_beta"], res["glm_inner"] = gb, np.array(inner)
+    # Kmeans, row-sharded: the one-pass Lloyd step per rank + one exchange of the k x m sums, the counts and sum(minD)
+    from systemml_b200.algorithms import kmeans_lloyd
+    nk, mk, kk = 40_000, 20, 6
+    k0, k1 = row_shard(nk, world, rank)
+    Xk = g.rand(k1 - k0, mk, seed=50, offset=k0 * mk, lo=-10.0, hi=10.0)
+    C0 = g.rand(kk, mk, seed=51, lo=-10.0, hi=10.0)
+    Ck, itk, wk, tk = kmeans_lloyd(g, Xk, C0, max_iter=8, eps=1e-9, comm=comm2)
+    res["kmeans_C"], res["kmeans_meta"] = Ck, np.array([itk, wk, tk])
     big = g.rand(200_000, 1, seed=30 + rank)                            # longer than the mailbox: goes in pieces
     comm2.allreduce(big.ptr, 200_000, "sum")
     res["big"] = big.to_host().reshape(-1)
@@ -147,5 +155,11 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
     yg = np.exp(Xa @ O.rand_uniform(ma, seed=43, lo=-0.05, hi=0.05))
     egb = cpu_glm_poisson_log(Xa, yg, 0.0, 4, 20, 1e-8, O.num_threads())
     assert assert_close(egb, r[0]["glm_beta"], 1e-9)
+    from oracle.algorithms_cpu import cpu_kmeans_lloyd
+    Xk = O.rand_uniform(40_000 * 20, seed=50, lo=-10.0, hi=10.0).reshape(40_000, 20)
+    Ck0 = O.rand_uniform(6 * 20, seed=51, lo=-10.0, hi=10.0).reshape(6, 20)
+    eC, eit, ew, et = cpu_kmeans_lloyd(Xk, Ck0, 8, 1e-9)
+    assert int(r[0]["kmeans_meta"][0]) == eit and int(r[0]["kmeans_meta"][2]) == et
+    assert assert_close(eC, r[0]["kmeans_C"], 1e-9) and abs(r[0]["kmeans_meta"][1] - ew) <= 1e-9 * abs(ew)
     exp_cs = O.agg_unary_dense(X, O.SUM, O.COL, 4)
     assert np.max(np.abs(r[0]["cs"] - exp_cs)) < 1e-9 * np.max(np.abs(exp_cs)) + 1e-9
