@@ -146,13 +146,15 @@ def glm_poisson_log(g, X, y, reg=0.0, outer_iters=8, inner_iters=20, inner_tol=1
     return out, inner_counts
 
 
-def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column_copy=False):
+def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column_copy=False, comm=None):
     """scripts/algorithms/l2-svm.dml:103-154 (intercept = 0, labels already -1/+1): non-linear CG on the squared-hinge
     primal with an exact Newton line search.  X: GPUObject n x m, dense or CSR (BASELINE config C3 is CSR 50M x 10k);
     Y: GPUObject n x 1.  Per outer iteration the O(nnz) work is X %*% s and t(X) %*% (out * Y); everything else is
     chains over n-vectors, each evaluated in one pass by fusedCellwise (fused=True) or operator by operator
     (fused=False, the reference's plan).  column_copy=True runs t(X) %*% y as a gather over the column-ordered copy of a
-    CSR X (csrc/psell.cu; deterministic), False as the scatter kernel.  Returns (w ndarray, iterations, final objective)."""
+    CSR X (csrc/psell.cu; deterministic), False as the scatter kernel.  comm: X and Y are this rank's row shard:
+    X %*% s needs no exchange, t(X) %*% (out*Y) and every sum over an n-vector are a local result + one exchange, the
+    m-vectors are replicated; every rank returns the same w (fused plan only).  Returns (w ndarray, iterations, final objective)."""
     n, m = X.rows, X.cols
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
@@ -180,13 +182,22 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
 
     fs, fs4 = alloc(1, 1), alloc(4, 1)
 
+    if comm is not None and not fused:
+        raise ValueError("l2svm: the row-sharded plan runs the fused chains")
+
     def fsum(inputs, expr, consts=()):
+        if comm is not None and inputs[0].rows == n:      # a sum over row-sharded n-vectors: local sum, then one exchange
+            return fsums(inputs, [expr], consts)[0]
         return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs)
 
     def fsums(inputs, exprs, consts=()):
         # several sums over the same operands in one pass (the code generator's multi-aggregate template); with fused=False
         # one pass per sum, as separate instructions would run
         if fused:
+            if comm is not None and inputs[0].rows == n:
+                L.fusedMultiAggregate(g, "spoof", inputs, exprs, consts, out=fs4, read_back=False)
+                _allreduce(comm, fs4, len(exprs))
+                return [float(v) for v in g.d2h(fs4.ptr, (len(exprs),))]
             return L.fusedMultiAggregate(g, "spoof", inputs, exprs, consts, out=fs4)
         return [fsum(inputs, e, consts) for e in exprs]
 
@@ -199,6 +210,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
     g.call("sysml_b200_fill", _p(w), m, 0.0)
     g.call("sysml_b200_fill", _p(Xw), n, 0.0)
     xt_times(Y, g_old)
+    _allreduce(comm, g_old, m)
     g.call("sysml_b200_d2d", _p(s), _p(g_old), 8 * m)
     # inputs of the n-vector chains: 0 = Y, 1 = Xw, 2 = Xd; constants: 0 = 1.0, 1 = 0.0, 2 = step_sz
     out_e = E.const(0) - E.input(0) * (E.input(1) + E.const(2) * E.input(2))          # 1 - Y * (Xw + step_sz*Xd)
@@ -244,6 +256,7 @@ def l2svm(g, X, Y, reg=1.0, tol=0.001, maxiter=100, fused=True, log=None, column
             g.call("sysml_b200_binary_mm", _p(t1), _p(Y), _p(oy), n, 1, 0, L.BINARY_OPS["*"])
         obj = 0.5 * osum + reg / 2.0 * dot(w, w)
         xt_times(oy, g_new)
+        _allreduce(comm, g_new, m)
         g.call("sysml_b200_axpy", _p(g_new), _p(w), -float(reg), _p(g_new), m, 1, 0)     # g_new = t(X)(out*Y) - reg*w
         tmp, gn2, go2 = fsums([s, g_old, g_new], [E.input(0) * E.input(1), E.input(2) * E.input(2), E.input(1) * E.input(1)])
         be = gn2 / go2

@@ -360,7 +360,7 @@ def mmchainRowFn(gCtx, instName, X, v, exprs, w=None, y=None, consts=(), out=Non
     return out, side
 
 
-def fusedMultiAggregate(gCtx, instName, inputs, exprs, consts=(), rows=None, cols=None, out=None):
+def fusedMultiAggregate(gCtx, instName, inputs, exprs, consts=(), rows=None, cols=None, out=None, read_back=True):
     """sum(expr_j(inputs)) for every expression in ONE pass over the operands -- the code generator's multi-aggregate
     template (runtime/codegen/SpoofMultiAggregate.java). Returns the sums as a list of floats (one read-back).
     `out` may name a device buffer of at least len(exprs) doubles to reuse."""
@@ -392,6 +392,8 @@ def fusedMultiAggregate(gCtx, instName, inputs, exprs, consts=(), rows=None, col
     pg = (C.c_int32 * len(tokens))(*tokens)
     try:
         gCtx.call("sysml_b200_fused_multi_agg", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, k, _p(out.ptr))
+        if not read_back:       # the caller combines the sums on the device first (a sharded operand)
+            return None
         return [float(v) for v in gCtx.d2h(out.ptr, (k,))]
     finally:
         if not given:

@@ -94,6 +94,18 @@ def _worker(rank, world, port, n, m, out_dir):
     C0 = g.rand(kk, mk, seed=51, lo=-10.0, hi=10.0)
     Ck, itk, wk, tk = kmeans_lloyd(g, Xk, C0, max_iter=8, eps=1e-9, comm=comm2)
     res["kmeans_C"], res["kmeans_meta"] = Ck, np.array([itk, wk, tk])
+    # L2SVM on a row-sharded CSR matrix: X %*% s local, t(X) %*% (out*Y) and the n-vector sums exchanged
+    from systemml_b200.algorithms import l2svm
+    ns, ms = 30_000, 300
+    s0, s1 = row_shard(ns, world, rank)
+    Xs_csr = g.rand_csr(s1 - s0, ms, 12, 60, row_offset=s0)
+    vs = g.rand(ms, 1, seed=61)
+    sc = g.empty(s1 - s0, 1)
+    g.call("sysml_b200_matmult_csr_dense", C.c_void_p(Xs_csr.csr.rowPtr), C.c_void_p(Xs_csr.csr.colInd), C.c_void_p(Xs_csr.csr.val),
+           C.c_void_p(vs.ptr), C.c_void_p(sc.ptr), s1 - s0, ms, ms, 1, 0)
+    Ys = g.dense(np.where(sc.to_host() > 0, 1.0, -1.0))
+    wsv, its_s, obj_s = l2svm(g, Xs_csr, Ys, reg=1.0, tol=0.001, maxiter=8, comm=comm2)
+    res["l2svm_w"], res["l2svm_meta"] = wsv, np.array([its_s, obj_s])
     big = g.rand(200_000, 1, seed=30 + rank)                            # longer than the mailbox: goes in pieces
     comm2.allreduce(big.ptr, 200_000, "sum")
     res["big"] = big.to_host().reshape(-1)
@@ -130,7 +142,7 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
         assert rel < 1e-9
     Xs = O.rand_uniform(n * 160, seed=21).reshape(n, 160)
     Pm = O.rand_uniform(n * 24, seed=22).reshape(n, 24)
-    for key in ("tsmm", "tpx", "uacmax", "uacmin", "sum", "big", "cs", "linreg_beta", "glm_beta", "glm_inner"):
+    for key in ("tsmm", "tpx", "uacmax", "uacmin", "sum", "big", "cs", "linreg_beta", "glm_beta", "glm_inner", "kmeans_C", "kmeans_meta", "l2svm_w", "l2svm_meta"):
         for k in range(1, world):
             assert np.array_equal(r[0][key], r[k][key]), "%s differs on rank %d" % (key, k)
     exp_t, _ = O.tsmm_dense(Xs, True, O.num_threads())
@@ -155,6 +167,15 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
     yg = np.exp(Xa @ O.rand_uniform(ma, seed=43, lo=-0.05, hi=0.05))
     egb = cpu_glm_poisson_log(Xa, yg, 0.0, 4, 20, 1e-8, O.num_threads())
     assert assert_close(egb, r[0]["glm_beta"], 1e-9)
+    from oracle.algorithms_cpu import cpu_l2svm
+    rp, ci, va = O.rand_csr(30_000, 300, 12, 60)
+    Xd = np.zeros((30_000, 300))
+    for i in range(30_000):
+        Xd[i, ci[rp[i]:rp[i + 1]]] = va[rp[i]:rp[i + 1]]
+    Yd = np.where(Xd @ O.rand_uniform(300, seed=61) > 0, 1.0, -1.0)
+    ew, eits, eobj = cpu_l2svm(Xd, Yd, 1.0, 0.001, 8)
+    assert int(r[0]["l2svm_meta"][0]) == eits and abs(r[0]["l2svm_meta"][1] - eobj) <= 1e-9 * abs(eobj)
+    assert assert_close(ew, r[0]["l2svm_w"], 1e-9)
     from oracle.algorithms_cpu import cpu_kmeans_lloyd
     Xk = O.rand_uniform(40_000 * 20, seed=50, lo=-10.0, hi=10.0).reshape(40_000, 20)
     Ck0 = O.rand_uniform(6 * 20, seed=51, lo=-10.0, hi=10.0).reshape(6, 20)
