@@ -393,15 +393,18 @@ def kmeans_lloyd(g, X, C0, max_iter=20, eps=1e-6, fused=True, log=None, comm=Non
     return out, it, wcss, term
 
 
-def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0, log=None):
+def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0, log=None, comm=None, n_total=None):
     """scripts/algorithms/MultiLogReg.dml:150-340 with icpt = 0 (BASELINE config C4: X 1M x 5000, K = 20):
     trust-region Newton with a conjugate-gradient inner solver.  X: GPUObject N x D; Y: GPUObject N x K, the one-hot
     labels of the K non-baseline classes; y_last: GPUObject N x 1, the indicator of the baseline class (the script's
     Y[, K+1]).  The script carries N x (K+1) matrices whose last column of LT is identically zero; here that column
     is implicit: rowMaxs(LT) = max(rowMaxs(X B), 0), rowSums(exp_LT) = rowSums(exp(X B - mx)) + exp(-mx), which are
     the same operations on the same values.  The O(N D K) work per inner iteration is X %*% V and t(X) %*% (N x K).
+    comm: X, Y, y_last are this rank's row shard of an n_total-row problem: X %*% V and the row-wise chains need no
+    exchange; t(X) %*% (N x K) and every sum over N rows are a local result + one exchange; the D x K matrices are replicated.
     Returns (B ndarray D x K, outer iterations, objective)."""
     N, Dm, K = X.rows, X.cols, Y.cols
+    Ntot = int(n_total) if n_total is not None else N
     E = L.Expr
     alloc = lambda r_, c_: GPUObject.allocate_dense(g, r_, c_)
     eta0, eta1, eta2, sigma1, sigma2, sigma3, psi = 1e-4, 0.25, 0.75, 0.25, 0.5, 4.0, 0.1
@@ -409,6 +412,10 @@ def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0,
     fs = alloc(1, 1)
 
     def fsum(inputs, expr, consts=()):
+        if comm is not None and inputs[0].rows == N and N != Dm:   # a sum over the row-sharded operands: local sum + one exchange
+            L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs, read_back=False)
+            _allreduce(comm, fs, 1)
+            return _scalar(g, fs)
         return L.fusedCellwise(g, "spoof", inputs, expr, consts, "sum", out=fs)
 
     def dotm(a, b):
@@ -416,6 +423,7 @@ def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0,
 
     def xt_times(M_, out):     # out (D x K) = t(X) %*% M_ (N x K)
         g.call("sysml_b200_matmult_dense", _p(X), _p(M_), _p(out), N, Dm, N, K, 1, 0)
+        _allreduce(comm, out, Dm * K)
 
     def x_times(V_, out):      # out (N x K) = X %*% V_ (D x K)
         g.call("sysml_b200_matmult_dense", _p(X), _p(V_), _p(out), N, Dm, Dm, K, 0, 0)
@@ -425,7 +433,14 @@ def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0,
 
     rsx = alloc(N, 1)
     g.call("sysml_b200_agg_unary_dense", _p(X), N, Dm, L.AGG_SUMSQ, L.DIR_ROW, _p(rsx))
-    mxs = L.unaryAggregate(g, "uamax", rsx, "uamax")
+    if comm is not None:
+        mxd = alloc(1, 1)
+        g.call("sysml_b200_agg_unary_dense", _p(rsx), N, 1, L.AGG_MAX, L.DIR_ALL, _p(mxd))
+        comm.allreduce(mxd.ptr, 1, "max")
+        mxs = _scalar(g, mxd)
+        mxd.free()
+    else:
+        mxs = L.unaryAggregate(g, "uamax", rsx, "uamax")
     rsx.free()
     delta = 0.5 * np.sqrt(Dm) / np.sqrt(mxs)
     lam = float(reg)
@@ -434,7 +449,7 @@ def multilogreg(g, X, Y, y_last, reg=0.0, tol=1e-6, maxiter=100, maxinneriter=0,
     mx, rs, rs2b = alloc(N, 1), alloc(N, 1), alloc(N, 1)
     g.call("sysml_b200_fill", _p(B), Dm * K, 0.0)
     g.call("sysml_b200_fill", _p(P), N * K, 1.0 / (K + 1))
-    obj = N * np.log(K + 1)
+    obj = Ntot * np.log(K + 1)
 
     def gradient(Pm, Bm):
         g.call("sysml_b200_binary_mm", _p(Pm), _p(Y), _p(T1), N, K, 0, L.BINARY_OPS["-"])    # P - Y

@@ -289,7 +289,7 @@ class Expr:
         return out
 
 
-def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None, out=None):
+def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, cols=None, out=None, read_back=True):
     """One-pass evaluation of a cellwise chain over `inputs` (GPUObjects: rows x cols matrices, rows x 1 column
     vectors or 1 x cols row vectors), optionally reduced by sum / rowSums / colSums -- the GPU twin of the code
     generator's cellwise template (runtime/codegen/SpoofCellwise.java).  Returns a GPUObject, or a float for
@@ -323,7 +323,7 @@ def fusedCellwise(gCtx, instName, inputs, expr, consts=(), agg=None, rows=None, 
     cs = (C.c_double * max(len(consts), 1))(*[float(c) for c in consts])
     pg = (C.c_int32 * len(tokens))(*tokens)
     gCtx.call("sysml_b200_fused_cellwise", ptrs, kd, n, cs, len(consts), pg, len(tokens), rows, cols, a, _p(out.ptr))
-    if a in (1, 4, 7):
+    if a in (1, 4, 7) and read_back:
         v = float(gCtx.d2h(out.ptr, (1,))[0])
         if not given:
             out.free()

@@ -26,6 +26,15 @@ def _free_port():
     return p
 
 
+def _multilogreg_problem():
+    rng = np.random.default_rng(3)
+    N, D, K = 24_000, 40, 4
+    X = rng.uniform(-1, 1, (N, D))
+    labels = np.argmax(X @ rng.normal(size=(D, K + 1)) + 0.5 * rng.gumbel(size=(N, K + 1)), axis=1)
+    Yfull = np.eye(K + 1)[labels]
+    return X, np.ascontiguousarray(Yfull[:, :K]), np.ascontiguousarray(Yfull[:, K:])
+
+
 def _worker(rank, world, port, n, m, out_dir):
     import ctypes as C
     import torch.distributed as dist
@@ -106,6 +115,13 @@ def _worker(rank, world, port, n, m, out_dir):
     Ys = g.dense(np.where(sc.to_host() > 0, 1.0, -1.0))
     wsv, its_s, obj_s = l2svm(g, Xs_csr, Ys, reg=1.0, tol=0.001, maxiter=8, comm=comm2)
     res["l2svm_w"], res["l2svm_meta"] = wsv, np.array([its_s, obj_s])
+    # MultiLogReg, row-sharded: X %*% V and the row-wise chains local, t(X) %*% (N x K) and the N-row sums exchanged
+    from systemml_b200.algorithms import multilogreg
+    Xm, Ym, ylm = _multilogreg_problem()
+    m0, m1 = row_shard(Xm.shape[0], world, rank)
+    Bm, itm, objm = multilogreg(g, g.dense(Xm[m0:m1]), g.dense(Ym[m0:m1]), g.dense(ylm[m0:m1]), reg=1.0, tol=1e-6, maxiter=6, comm=comm2,
+                                n_total=Xm.shape[0])
+    res["mlr_B"], res["mlr_meta"] = Bm, np.array([itm, objm])
     big = g.rand(200_000, 1, seed=30 + rank)                            # longer than the mailbox: goes in pieces
     comm2.allreduce(big.ptr, 200_000, "sum")
     res["big"] = big.to_host().reshape(-1)
@@ -142,7 +158,7 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
         assert rel < 1e-9
     Xs = O.rand_uniform(n * 160, seed=21).reshape(n, 160)
     Pm = O.rand_uniform(n * 24, seed=22).reshape(n, 24)
-    for key in ("tsmm", "tpx", "uacmax", "uacmin", "sum", "big", "cs", "linreg_beta", "glm_beta", "glm_inner", "kmeans_C", "kmeans_meta", "l2svm_w", "l2svm_meta"):
+    for key in ("tsmm", "tpx", "uacmax", "uacmin", "sum", "big", "cs", "linreg_beta", "glm_beta", "glm_inner", "kmeans_C", "kmeans_meta", "l2svm_w", "l2svm_meta", "mlr_B", "mlr_meta"):
         for k in range(1, world):
             assert np.array_equal(r[0][key], r[k][key]), "%s differs on rank %d" % (key, k)
     exp_t, _ = O.tsmm_dense(Xs, True, O.num_threads())
@@ -167,6 +183,11 @@ def test_fused_allreduce_mmchain_multi_gpu(tmp_path, world):
     yg = np.exp(Xa @ O.rand_uniform(ma, seed=43, lo=-0.05, hi=0.05))
     egb = cpu_glm_poisson_log(Xa, yg, 0.0, 4, 20, 1e-8, O.num_threads())
     assert assert_close(egb, r[0]["glm_beta"], 1e-9)
+    from oracle.algorithms_cpu import cpu_multilogreg
+    Xm, Ym, ylm = _multilogreg_problem()
+    eB, eitm, eobjm = cpu_multilogreg(Xm, Ym, ylm, 1.0, 1e-6, 6, 0)
+    assert int(r[0]["mlr_meta"][0]) == eitm and abs(r[0]["mlr_meta"][1] - eobjm) <= 1e-9 * abs(eobjm)
+    assert assert_close(eB, r[0]["mlr_B"], 1e-9)
     from oracle.algorithms_cpu import cpu_l2svm
     rp, ci, va = O.rand_csr(30_000, 300, 12, 60)
     Xd = np.zeros((30_000, 300))
