@@ -22,8 +22,19 @@ print("Per-launch times are cold-cache and serialised: compare SHARES with bench
 print("| kernel | launches | total | mean | share |\n|---|---:|---:|---:|---:|")
 for k, v in sorted(tot.items(), key=lambda kv: -kv[1]):
     print("| `%s` | %d | %d | %d | %.4f |" % (k[:110], cnt[k], v, v / cnt[k], v / allt))
-stream = sum(v for k, v in tot.items() if k.startswith("void rowstream_kernel<0"))
-fin = sum(v for k, v in tot.items() if "finish_exchange_kernel" in k and ", 1>" in k)
-if stream and fin:
+# one CG step = one full-size streaming launch + one finishing launch: compare per-launch means (the list also holds the
+# short streaming launches of the cold / binaryblock legs, which are left out: only launches above half the longest count)
+r = csv.reader(rows)
+next(r)
+sl, fl = [], []
+for row in r:
+    name, v = row[ki], float(row[vi].replace(",", ""))
+    if "rowstream_kernel<0" in name:
+        sl.append(v)
+    elif "finish_exchange_kernel" in name and ", 1>" in name:
+        fl.append(v)
+if sl and fl:
+    big = [v for v in sl if v > 0.5 * max(sl)]
+    ms, mf = sum(big) / len(big), sum(fl) / len(fl)
     print("\nA CG step is two launches: `rowstream_kernel<0,...>` (mmchain XtwXv) and `finish_exchange_kernel<..., CG>` (fold of the per-CTA partials + the m-vector tail).")
-    print("The streaming kernel's share of those two under ncu: %.4f." % (stream / (stream + fin)))
+    print("Per-launch means under ncu: %d full-size streaming launches %.0f ns, %d finishing launches %.0f ns: the streaming kernel's share of a step is %.4f." % (len(big), ms, len(fl), mf, ms / (ms + mf)))
